@@ -1,0 +1,615 @@
+// C ABI of libfvsrn_b200.so (see include/fvsrn_b200.h). Host logic mirrors the reference's module code:
+// SceneNetwork builders / .volnet I/O (renderer/volume_interpolation_network.cpp), constant packing + launch
+// (image_evaluator_simple.cpp:198-361, volume_interpolation.cpp:26-127). No CPU fallback: compute entry points
+// need a CUDA device.
+#include "../../include/fvsrn_b200.h"
+#include "launch.cuh"
+#include "network.hpp"
+#include <cmath>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+using namespace fvsrn;
+
+namespace {
+thread_local std::string g_last_error;
+
+int fail(const std::string& msg) { g_last_error = msg; return 1; }
+
+#define FV_TRY try {
+#define FV_CATCH } catch (const std::exception& e) { return fail(e.what()); } catch (...) { return fail("unknown error"); }
+#define CUDA_OK(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) \
+    throw std::runtime_error(std::string(#expr) + " failed: " + cudaGetErrorString(_e)); } while (0)
+
+struct DeviceGrid { __half* data = nullptr; int C = 0, Z = 0, Y = 0, X = 0; };
+} // namespace
+
+struct fvsrn_network {
+    Network net;
+    // GPU resources (valid when prepared)
+    bool prepared = false;
+    int device = -1, sm_count = 0;
+    uint4* d_blob = nullptr; int blob_bytes = 0;
+    int off_w0 = 0, off_wh = 0, off_wlast = 0, off_bias = 0, off_fourier = 0;
+    int H16 = 0, GC16 = 0, dir = 0, num_hidden = 0, activation = 0; float act_param = 1.f;
+    std::vector<DeviceGrid> d_time, d_ens;
+    unsigned int* d_tile_counter = nullptr;   // ring of work-queue counters (one per launch in flight)
+    int tile_counter_slots = 0, tile_counter_next = 0;
+    float* d_scratch = nullptr; size_t scratch_bytes = 0;  // staging for the *_host entry points
+    unsigned long long launches = 0;
+};
+
+namespace {
+
+void release_gpu(fvsrn_network* h) {
+    if (h->device >= 0) cudaSetDevice(h->device);
+    if (h->d_blob) cudaFree(h->d_blob);
+    for (auto& g : h->d_time) if (g.data) cudaFree(g.data);
+    for (auto& g : h->d_ens) if (g.data) cudaFree(g.data);
+    if (h->d_tile_counter) cudaFree(h->d_tile_counter);
+    if (h->d_scratch) cudaFree(h->d_scratch);
+    h->d_blob = nullptr; h->d_time.clear(); h->d_ens.clear(); h->d_tile_counter = nullptr;
+    h->d_scratch = nullptr; h->scratch_bytes = 0; h->prepared = false;
+}
+
+// fp16 channel-last [Z][Y][X][C] copy of a latent grid (decodes byte encodings on the way)
+std::vector<uint16_t> grid_channel_last(const LatentGrid& g) {
+    std::vector<uint16_t> out(size_t(g.C) * g.Z * g.Y * g.X);
+    for (int z = 0; z < g.Z; ++z) for (int y = 0; y < g.Y; ++y) for (int x = 0; x < g.X; ++x) {
+        uint16_t* o = out.data() + ((size_t(z) * g.Y + y) * g.X + x) * g.C;
+        for (int c = 0; c < g.C; ++c) o[c] = f32_to_f16(g.decoded(c, z, y, x));
+    }
+    return out;
+}
+
+// Fragment-ordered constant blob (see srn_core.cuh): W0 | hidden W | last W | biases | Fourier matrix
+void build_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
+    const Network& n = h->net;
+    std::string why;
+    if (!n.valid(&why)) throw std::runtime_error("scene network is not valid: " + why);
+    if (n.num_fourier <= 0) throw std::runtime_error("unsupported on the B200 path: networks without Fourier features");
+    if (n.output_mode > OUT_RGBO_DIRECT) throw std::runtime_error(std::string("unsupported on the B200 path: output mode ") + kOutputModeNames[n.output_mode]);
+    const int H = n.input_channels_out();
+    const int GC = n.latent_channels();
+    if (!(H == 32 || H == 48 || H == 64 || H == 96 || H == 128))
+        throw std::runtime_error("unsupported hidden width " + std::to_string(H) + " (supported: 32, 48, 64, 96, 128)");
+    if (!(GC == 0 || GC == 16 || GC == 32)) throw std::runtime_error("unsupported latent channel count " + std::to_string(GC));
+    const int L = int(n.layers.size());
+    if (L < 2) throw std::runtime_error("need at least one hidden layer and the output layer");
+    const Layer& l0 = n.layers[0];
+    if (l0.cout != H) throw std::runtime_error("hidden width must equal 4(+4)+2*numFourier (reference :142-152)");
+    for (int i = 1; i + 1 < L; ++i)
+        if (n.layers[i].cin != H || n.layers[i].cout != H) throw std::runtime_error("all hidden layers must have the same width");
+    const Layer& last = n.layers[L - 1];
+    if (last.cin != H || last.cout > 8) throw std::runtime_error("bad output layer");
+    const int act = l0.activation;
+    for (int i = 0; i + 1 < L; ++i) {
+        if (n.layers[i].activation != act) throw std::runtime_error("all hidden layers must share one activation");
+        if (n.layers[i].activation_param != l0.activation_param) throw std::runtime_error("Extra parameter of the activation must be the same over all layers");
+    }
+    if (act == ACT_SIGMOID) throw std::runtime_error("Sigmoid is not a valid hidden activation");
+    h->H16 = H / 16; h->GC16 = GC / 16; h->dir = n.has_direction ? 1 : 0;
+    h->num_hidden = L - 2; h->activation = act; h->act_param = l0.activation_param;
+
+    auto frag_layer = [&](const Layer& l, int K, int N, int Npad, std::vector<uint8_t>& dst) {
+        // B fragment of mma.m16n8k16 (col-major B[k][n] = W[n][k]): lane (g = lane/4, t = lane%4) holds
+        // b0 = W[n0+g][k0+2t..2t+1], b1 = W[n0+g][k0+2t+8..2t+9]
+        const int KT = K / 16, NT = Npad / 8;
+        auto W = [&](int nn, int kk) -> uint16_t { return (nn < N) ? l.w(nn, kk) : uint16_t(0); };
+        for (int kt = 0; kt < KT; ++kt)
+            for (int ntp = 0; ntp < (NT + 1) / 2; ++ntp)
+                for (int lane = 0; lane < 32; ++lane)
+                    for (int j = 0; j < (NT >= 2 ? 2 : 1); ++j) {
+                        const int nt = 2 * ntp + j, g = lane / 4, t = lane % 4;
+                        const int nn = nt * 8 + g, k0 = kt * 16 + 2 * t;
+                        const uint16_t v[4] = {W(nn, k0), W(nn, k0 + 1), W(nn, k0 + 8), W(nn, k0 + 9)};
+                        const uint8_t* p = reinterpret_cast<const uint8_t*>(v);
+                        dst.insert(dst.end(), p, p + 8);
+                    }
+    };
+    blob.clear();
+    h->off_w0 = 0;
+    frag_layer(l0, H + GC, H, H, blob);
+    h->off_wh = int(blob.size());
+    for (int i = 1; i + 1 < L; ++i) frag_layer(n.layers[i], H, H, H, blob);
+    h->off_wlast = int(blob.size());
+    frag_layer(last, H, last.cout, 8, blob);
+    h->off_bias = int(blob.size());
+    for (int i = 0; i + 1 < L; ++i) {
+        const uint8_t* p = reinterpret_cast<const uint8_t*>(n.layers[i].bias.data());
+        blob.insert(blob.end(), p, p + 2 * H);
+    }
+    for (int i = 0; i < 8; ++i) {
+        const uint16_t v = i < last.cout ? last.bias[i] : uint16_t(0);
+        blob.push_back(uint8_t(v & 0xff)); blob.push_back(uint8_t(v >> 8));
+    }
+    while (blob.size() % 16) blob.push_back(0);
+    h->off_fourier = int(blob.size());
+    {
+        const uint8_t* p = reinterpret_cast<const uint8_t*>(n.fourier.data());
+        blob.insert(blob.end(), p, p + 2 * n.fourier.size());
+    }
+    while (blob.size() % 16) blob.push_back(0);
+    h->blob_bytes = int(blob.size());
+}
+
+launch_fn pick_launcher(int H16) {
+    switch (H16) {
+        case 2: return launch_h2; case 3: return launch_h3; case 4: return launch_h4;
+        case 6: return launch_h6; case 8: return launch_h8;
+    }
+    return nullptr;
+}
+
+// device-side view of the network for a given absolute time / ensemble (reference fillConstantMemory :1290-1352)
+NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, bool unit_box) {
+    const Network& n = h->net;
+    NetParams P{};
+    P.blob = h->d_blob; P.blob_bytes = h->blob_bytes;
+    P.off_w0 = h->off_w0; P.off_wh = h->off_wh; P.off_wlast = h->off_wlast; P.off_bias = h->off_bias; P.off_fourier = h->off_fourier;
+    P.num_hidden = h->num_hidden; P.activation = h->activation; P.act_param = h->act_param;
+    P.output_mode = n.output_mode; P.has_time = n.has_time ? 1 : 0; P.dir_in_fourier = n.direction_in_fourier ? 1 : 0;
+    P.time_value = 0.f;
+    int g = 0;
+    if (n.has_latent_grid) {
+        if (!h->d_time.empty()) {
+            const float t = n.interpolate_time(time_abs);
+            const int lo = std::min(int(t), n.time_num - 1), hi = std::min(lo + 1, n.time_num - 1);
+            const float frac = (lo == hi) ? 0.f : t - std::floor(t);
+            P.time_value = t;
+            const DeviceGrid& A = h->d_time[lo]; const DeviceGrid& B = h->d_time[hi];
+            P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
+            for (int i = 0; i < A.C / 16; ++i, ++g) P.groups[g] = GridGroup{A.data + 16 * i, B.data + 16 * i, frac, A.C * 2 / 16};
+        }
+        if (!h->d_ens.empty()) {
+            const DeviceGrid& A = h->d_ens[n.interpolate_ensemble(ensemble)];
+            P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
+            for (int i = 0; i < A.C / 16; ++i, ++g) P.groups[g] = GridGroup{A.data + 16 * i, A.data + 16 * i, 0.f, A.C * 2 / 16};
+        }
+    }
+    for (int i = 0; i < 3; ++i) { P.box_min[i] = unit_box ? 0.f : n.box_min[i]; P.box_size[i] = unit_box ? 1.f : n.box_size[i]; }
+    return P;
+}
+
+void require_prepared(fvsrn_network* h) {
+    if (!h) throw std::runtime_error("null network handle");
+    if (!h->prepared) throw std::runtime_error("network is not prepared: call fvsrn_network_prepare first");
+    CUDA_OK(cudaSetDevice(h->device));
+}
+
+unsigned int* next_tile_counter(fvsrn_network* h, cudaStream_t s) {
+    unsigned int* c = h->d_tile_counter + h->tile_counter_next;
+    h->tile_counter_next = (h->tile_counter_next + 1) % h->tile_counter_slots;
+    CUDA_OK(cudaMemsetAsync(c, 0, sizeof(unsigned int), s));
+    return c;
+}
+
+} // namespace
+
+// =========================================================================================== C ABI
+extern "C" {
+
+int fvsrn_abi_version(void) { return FVSRN_ABI_VERSION; }
+const char* fvsrn_last_error(void) { return g_last_error.c_str(); }
+
+int fvsrn_network_create(fvsrn_network** out) {
+    FV_TRY
+    if (!out) return fail("out is null");
+    *out = new fvsrn_network();
+    return 0;
+    FV_CATCH
+}
+
+void fvsrn_network_free(fvsrn_network* net) {
+    if (!net) return;
+    release_gpu(net);
+    delete net;
+}
+
+int fvsrn_network_load_volnet(const void* bytes, size_t n, fvsrn_network** out) {
+    FV_TRY
+    if (!bytes || !out) return fail("null argument");
+    fvsrn_network* h = new fvsrn_network();
+    try { h->net = Network::load(static_cast<const uint8_t*>(bytes), n); }
+    catch (...) { delete h; throw; }
+    *out = h;
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_save_volnet(const fvsrn_network* net, void* buf, size_t cap, size_t* written) {
+    FV_TRY
+    if (!net || !written) return fail("null argument");
+    const std::vector<uint8_t> b = net->net.save();
+    *written = b.size();
+    if (!buf) return 0;
+    if (cap < b.size()) return fail("buffer too small");
+    std::memcpy(buf, b.data(), b.size());
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_set_input(fvsrn_network* net, int has_time, int has_direction) {
+    FV_TRY
+    if (!net) return fail("null network handle");
+    net->net.has_time = has_time != 0; net->net.has_direction = has_direction != 0;
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_set_fourier(fvsrn_network* net, const float* B, int nf, int cin, int premultiplied) {
+    FV_TRY
+    if (!net || !B) return fail("null argument");
+    Network& n = net->net;
+    if (cin == 3) n.direction_in_fourier = false;
+    else if (cin == 6) {
+        if (!n.has_direction) return fail("hasDirection==false, but the fourier matrix has input channels for the direction");
+        n.direction_in_fourier = true;
+    } else return fail("Unrecognized number of input channels. Actual: " + std::to_string(cin) + ", expected: 3 or 6");
+    n.num_fourier = nf;
+    n.fourier.assign(size_t(nf) * cin, 0);
+    for (int o = 0; o < nf; ++o) for (int i = 0; i < cin; ++i) // reference :150-154 (double 2*pi times float, then to half)
+        n.fourier[o + size_t(nf) * i] = f32_to_f16(float((premultiplied ? 1.0 : 2.0 * M_PI) * double(B[size_t(o) * cin + i])));
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_disable_fourier(fvsrn_network* net) {
+    if (!net) return fail("null network handle");
+    net->net.num_fourier = 0; net->net.direction_in_fourier = false; net->net.fourier.clear();
+    return 0;
+}
+
+int fvsrn_network_set_output_mode(fvsrn_network* net, const char* mode) {
+    FV_TRY
+    if (!net || !mode) return fail("null argument");
+    net->net.output_mode = output_mode_from_string(mode);
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_add_layer(fvsrn_network* net, const float* W, const float* b, int cout, int cin,
+                            const char* activation, float activation_param) {
+    FV_TRY
+    if (!net || !W || !b || !activation) return fail("null argument");
+    if (cout <= 0 || cin <= 0) return fail("bad layer size");
+    Layer l; l.cin = cin; l.cout = cout;
+    l.activation = activation_from_string(activation); l.activation_param = activation_param;
+    l.weights.resize(size_t(cin) * cout); l.bias.resize(cout);
+    for (size_t i = 0; i < l.weights.size(); ++i) l.weights[i] = f32_to_f16(W[i]);
+    for (int i = 0; i < cout; ++i) l.bias[i] = f32_to_f16(b[i]);
+    net->net.add_layer(l);
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_set_latent_grid_layout(fvsrn_network* net, int time_min, int time_num, int time_step,
+                                         int ensemble_min, int ensemble_num) {
+    FV_TRY
+    if (!net) return fail("null network handle");
+    if (time_num < 0 || ensemble_num < 0 || time_step <= 0) return fail("bad latent grid layout");
+    Network& n = net->net;
+    n.has_latent_grid = true;
+    n.time_min = time_min; n.time_num = time_num; n.time_step = time_step;
+    n.ensemble_min = ensemble_min; n.ensemble_num = ensemble_num;
+    n.time_grids.assign(time_num, LatentGrid()); n.ensemble_grids.assign(ensemble_num, LatentGrid());
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_set_time_grid(fvsrn_network* net, int index, const float* grid, int C, int Z, int Y, int X,
+                                int encoding, double* encoding_error) {
+    FV_TRY
+    if (!net || !grid) return fail("null argument");
+    if (index < 0 || index >= int(net->net.time_grids.size())) return fail("index out of bounds!");
+    const double e = net->net.time_grids[index].from_dense(grid, C, Z, Y, X, encoding);
+    if (encoding_error) *encoding_error = e;
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_set_ensemble_grid(fvsrn_network* net, int index, const float* grid, int C, int Z, int Y, int X,
+                                    int encoding, double* encoding_error) {
+    FV_TRY
+    if (!net || !grid) return fail("null argument");
+    if (index < 0 || index >= int(net->net.ensemble_grids.size())) return fail("index out of bounds!");
+    const double e = net->net.ensemble_grids[index].from_dense(grid, C, Z, Y, X, encoding);
+    if (encoding_error) *encoding_error = e;
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_set_box(fvsrn_network* net, const float box_min[3], const float box_size[3]) {
+    if (!net || !box_min || !box_size) return fail("null argument");
+    for (int i = 0; i < 3; ++i) { net->net.box_min[i] = box_min[i]; net->net.box_size[i] = box_size[i]; }
+    return 0;
+}
+int fvsrn_network_get_box(const fvsrn_network* net, float box_min[3], float box_size[3]) {
+    if (!net || !box_min || !box_size) return fail("null argument");
+    for (int i = 0; i < 3; ++i) { box_min[i] = net->net.box_min[i]; box_size[i] = net->net.box_size[i]; }
+    return 0;
+}
+int fvsrn_network_valid(const fvsrn_network* net) {
+    if (!net) return 0;
+    std::string why;
+    const bool ok = net->net.valid(&why);
+    if (!ok) g_last_error = why;
+    return ok ? 1 : 0;
+}
+int fvsrn_network_num_parameters(const fvsrn_network* net) { return net ? net->net.num_parameters() : 0; }
+int fvsrn_network_compute_max_warps(const fvsrn_network* net, int only_shared, int adjoint) {
+    return net ? net->net.compute_max_warps(only_shared != 0, adjoint != 0) : -1;
+}
+int fvsrn_network_set_time_and_ensemble(fvsrn_network* net, float time, int ensemble) {
+    if (!net) return fail("null network handle");
+    net->net.set_time_and_ensemble(time, ensemble);
+    return 0;
+}
+
+int fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info) {
+    if (!net || !info) return fail("null argument");
+    const Network& n = net->net;
+    std::memset(info, 0, sizeof(*info));
+    info->has_time = n.has_time; info->has_direction = n.has_direction; info->num_fourier = n.num_fourier;
+    info->direction_in_fourier = n.direction_in_fourier; info->output_mode = n.output_mode;
+    info->num_layers = int(n.layers.size());
+    info->hidden_channels = n.layers.empty() ? 0 : n.layers[0].cout;
+    info->latent_channels = n.latent_channels();
+    const LatentGrid* g = !n.time_grids.empty() ? &n.time_grids[0] : (!n.ensemble_grids.empty() ? &n.ensemble_grids[0] : nullptr);
+    if (g) { info->grid_x = g->X; info->grid_y = g->Y; info->grid_z = g->Z; info->grid_encoding = g->encoding; }
+    info->time_min = n.time_min; info->time_num = n.time_num; info->time_step = n.time_step;
+    info->ensemble_min = n.ensemble_min; info->ensemble_num = n.ensemble_num;
+    info->activation = n.layers.empty() ? ACT_NONE : n.layers[0].activation;
+    info->activation_param = n.layers.empty() ? 1.f : n.layers[0].activation_param;
+    info->channels_out = kOutputModeChannelsOut[n.output_mode];
+    return 0;
+}
+
+int fvsrn_network_prepare(fvsrn_network* net, int device, void* stream) {
+    FV_TRY
+    if (!net) return fail("null network handle");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+        return fail("no CUDA device available: the fV-SRN B200 path has no CPU fallback");
+    if (device < 0 || device >= count) return fail("invalid device index");
+    release_gpu(net);
+    std::vector<uint8_t> blob;
+    build_blob(net, blob);
+    CUDA_OK(cudaSetDevice(device));
+    net->device = device;
+    cudaDeviceProp prop;
+    CUDA_OK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail("the fV-SRN B200 kernels are built for sm_100a only; found sm_" + std::to_string(prop.major * 10 + prop.minor));
+    net->sm_count = prop.multiProcessorCount;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CUDA_OK(cudaMalloc(&net->d_blob, blob.size()));
+    CUDA_OK(cudaMemcpyAsync(net->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice, s));
+    auto upload = [&](const LatentGrid& g) {
+        DeviceGrid d; d.C = g.C; d.Z = g.Z; d.Y = g.Y; d.X = g.X;
+        const std::vector<uint16_t> cl = grid_channel_last(g);
+        CUDA_OK(cudaMalloc(&d.data, cl.size() * 2));
+        CUDA_OK(cudaMemcpyAsync(d.data, cl.data(), cl.size() * 2, cudaMemcpyHostToDevice, s));
+        CUDA_OK(cudaStreamSynchronize(s)); // cl is a temporary
+        return d;
+    };
+    if (net->net.has_latent_grid) {
+        for (const auto& g : net->net.time_grids) net->d_time.push_back(upload(g));
+        for (const auto& g : net->net.ensemble_grids) net->d_ens.push_back(upload(g));
+        const DeviceGrid* r = !net->d_time.empty() ? &net->d_time[0] : &net->d_ens[0];
+        for (const auto& g : net->d_time) if (g.X != r->X || g.Y != r->Y || g.Z != r->Z) return fail("all latent grids must share one resolution");
+        for (const auto& g : net->d_ens) if (g.X != r->X || g.Y != r->Y || g.Z != r->Z) return fail("all latent grids must share one resolution");
+    }
+    net->tile_counter_slots = 256;
+    CUDA_OK(cudaMalloc(&net->d_tile_counter, sizeof(unsigned int) * net->tile_counter_slots));
+    CUDA_OK(cudaMemsetAsync(net->d_tile_counter, 0, sizeof(unsigned int) * net->tile_counter_slots, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    net->prepared = true;
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_network_clear_gpu_resources(fvsrn_network* net) {
+    if (!net) return fail("null network handle");
+    release_gpu(net);
+    return 0;
+}
+
+} // extern "C"
+
+// =========================================================================================== compute entry points
+namespace {
+
+__global__ void extract_color_kernel(const float* __restrict__ img, float* __restrict__ out, long long hw, long long total) {
+    // (B,8,H,W) -> (B,4,H,W): reference SelectOutputChannelKernel, ChannelColor branch (iimage_evaluator_cuda.cu:21-80)
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long b = i / (4 * hw), r = i - b * 4 * hw;
+        out[i] = img[b * 8 * hw + r];
+    }
+}
+
+void ensure_scratch(fvsrn_network* h, size_t bytes) {
+    if (h->scratch_bytes >= bytes) return;
+    if (h->d_scratch) CUDA_OK(cudaFree(h->d_scratch));
+    h->d_scratch = nullptr; h->scratch_bytes = 0;
+    CUDA_OK(cudaMalloc(&h->d_scratch, bytes));
+    h->scratch_bytes = bytes;
+}
+
+void do_evaluate(fvsrn_network* h, const float* pos, const float* dir, float* out, int64_t n, cudaStream_t s) {
+    require_prepared(h);
+    if (n < 0) throw std::runtime_error("negative sample count");
+    if (n == 0) return;
+    if (!pos || !out) throw std::runtime_error("null device pointer");
+    if (h->net.has_direction && !dir) throw std::runtime_error("the network uses directions, but no directions were passed");
+    // reference volume_interpolation.cpp:45-48: positions are in the unit cube
+    const NetParams P = make_net_params(h, h->net.current_time, h->net.current_ensemble, true);
+    EvalParams E{pos, dir, out, (long long)n, kOutputModeChannelsOut[h->net.output_mode]};
+    LaunchCfg cfg; cfg.sm_count = h->sm_count;
+    cfg.max_blocks = ((n + 31) / 32 + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    launch_fn fn = pick_launcher(h->H16);
+    if (!fn) throw std::runtime_error("no kernel for this hidden width");
+    CUDA_OK(fn(KIND_EVAL, h->GC16, h->dir, P, &E, &cfg, s));
+    h->launches++;
+}
+
+void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStream_t s) {
+    require_prepared(h);
+    if (!p || !out) throw std::runtime_error("null argument");
+    if (p->width <= 0 || p->height <= 0 || p->batch <= 0) throw std::runtime_error("image size and batch must be positive");
+    if (!p->camera_matrix_dev) throw std::runtime_error("camera matrix is null");
+    if (!(p->stepsize > 0.f)) throw std::runtime_error("stepsize must be positive");
+    const bool is_rgbo = h->net.output_mode >= OUT_RGBO;
+    if (!is_rgbo) {
+        if (!p->tf_dev) throw std::runtime_error("texture tensor is not defined");
+        if (p->tf_kind < 0 || p->tf_kind > 2) throw std::runtime_error("unknown transfer function kind");
+        if (p->tf_kind != FVSRN_TF_IDENTITY && p->tf_resolution < 2) throw std::runtime_error("transfer function needs at least 2 entries");
+        const int floats = p->tf_kind == 0 ? p->tf_resolution * 5 : (p->tf_kind == 1 ? p->tf_resolution * 4 : 2);
+        if (floats > kTfSmemFloats) throw std::runtime_error("transfer function too large for the fused kernel (max 204 control points / 256 texels)");
+        if (p->tf_batch != 1 && p->tf_batch != p->batch) throw std::runtime_error("transfer function batch must be 1 or equal to the camera batch");
+    }
+    if (h->net.has_direction && false) {}
+    int spp = p->samples_per_pixel <= 0 ? 1 : p->samples_per_pixel;
+    int side = int(std::lround(std::sqrt(double(spp))));
+    if (side * side != spp) throw std::runtime_error("samples_per_pixel must be a square number (1, 4, 9, ...)");
+    DvrParams D{};
+    D.W = p->width; D.H = p->height;
+    D.x0 = p->tile_x0; D.y0 = p->tile_y0;
+    D.tw = p->tile_w > 0 ? p->tile_w : p->width - p->tile_x0;
+    D.th = p->tile_h > 0 ? p->tile_h : p->height - p->tile_y0;
+    if (D.x0 < 0 || D.y0 < 0 || D.tw <= 0 || D.th <= 0 || D.x0 + D.tw > D.W || D.y0 + D.th > D.H) throw std::runtime_error("tile rectangle outside the image");
+    D.cam = p->camera_matrix_dev;
+    D.tan_half_fovy = std::tan(p->fov_y_radians * 0.5f);
+    D.aspect = float(double(p->width) / double(p->height)); // camera->setAspectRatio, image_evaluator_simple.cpp:204
+    D.stepsize = p->stepsize; D.alpha_early_out = p->alpha_early_out;
+    D.dmin = p->density_min; D.inv_range = 1.0f / (p->density_max - p->density_min);
+    D.early_out = p->early_out; D.blend_mode = p->blend_mode;
+    D.tf_kind = is_rgbo ? 2 : p->tf_kind; D.tf_R = p->tf_resolution; D.tf_batch = is_rgbo ? 1 : p->tf_batch;
+    D.tf = is_rgbo ? reinterpret_cast<const float*>(h->d_blob) : p->tf_dev; // rgbo networks skip the TF; any readable pointer
+    D.spp = spp; D.spp_side = side;
+    D.out = out; D.sb = p->out_stride_b; D.sc = p->out_stride_c; D.sy = p->out_stride_y; D.sx = p->out_stride_x;
+    D.step_count = p->step_count_dev; D.counters = p->counters_dev;
+    D.tiles_x = (D.tw + kTileW - 1) / kTileW; D.tiles_y = (D.th + kTileH - 1) / kTileH;
+    launch_fn fn = pick_launcher(h->H16);
+    if (!fn) throw std::runtime_error("no kernel for this hidden width");
+    auto launch = [&](int b0, int nb, float time_abs) {
+        const NetParams P = make_net_params(h, time_abs, h->net.current_ensemble, false);
+        DvrParams d = D; d.b0 = b0; d.nb = nb;
+        d.num_tiles = d.tiles_x * d.tiles_y * nb;
+        d.tile_counter = next_tile_counter(h, s);
+        LaunchCfg cfg; cfg.sm_count = h->sm_count;
+        cfg.max_blocks = (d.num_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
+        CUDA_OK(fn(KIND_DVR, h->GC16, h->dir, P, &d, &cfg, s));
+        h->launches++;
+    };
+    if (p->view_times_host) { // one launch per view: every view selects its own keyframe pair (time sweeps)
+        for (int b = 0; b < p->batch; ++b) {
+            const float t = std::min(std::max(p->view_times_host[b], float(h->net.time_min)), float(h->net.time_max_inclusive()));
+            launch(b, 1, t);
+        }
+    } else launch(0, p->batch, h->net.current_time);
+}
+
+} // namespace
+
+extern "C" {
+
+int fvsrn_evaluate(fvsrn_network* net, const float* positions_dev, const float* directions_dev, float* out_dev,
+                   int64_t n, void* stream) {
+    FV_TRY
+    do_evaluate(net, positions_dev, directions_dev, out_dev, n, static_cast<cudaStream_t>(stream));
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_evaluate_host(fvsrn_network* net, const float* positions_host, const float* directions_host, float* out_host,
+                        int64_t n, void* stream) {
+    FV_TRY
+    require_prepared(net);
+    if (n <= 0) return n == 0 ? 0 : fail("negative sample count");
+    if (!positions_host || !out_host) return fail("null host pointer");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int cout = kOutputModeChannelsOut[net->net.output_mode];
+    const size_t pos_b = size_t(n) * 12, dir_b = directions_host ? pos_b : 0, out_b = size_t(n) * 4 * cout;
+    ensure_scratch(net, pos_b + dir_b + out_b + 64);
+    char* base = reinterpret_cast<char*>(net->d_scratch);
+    float* d_pos = reinterpret_cast<float*>(base);
+    float* d_dir = directions_host ? reinterpret_cast<float*>(base + pos_b) : nullptr;
+    float* d_out = reinterpret_cast<float*>(base + ((pos_b + dir_b + 15) / 16) * 16);
+    CUDA_OK(cudaMemcpyAsync(d_pos, positions_host, pos_b, cudaMemcpyHostToDevice, s));
+    if (d_dir) CUDA_OK(cudaMemcpyAsync(d_dir, directions_host, dir_b, cudaMemcpyHostToDevice, s));
+    do_evaluate(net, d_pos, d_dir, d_out, n, s);
+    CUDA_OK(cudaMemcpyAsync(out_host, d_out, out_b, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_render_dvr(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_dev, void* stream) {
+    FV_TRY
+    do_render(net, p, out_dev, static_cast<cudaStream_t>(stream));
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_host, void* stream) {
+    FV_TRY
+    require_prepared(net);
+    if (!p || !out_host) return fail("null argument");
+    if (p->out_stride_x != 1 || p->out_stride_y != p->width || p->out_stride_c != (int64_t)p->width * p->height ||
+        p->out_stride_b != 8ll * p->width * p->height)
+        return fail("fvsrn_render_dvr_host needs a contiguous (B,8,H,W) output");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bool is_rgbo = net->net.output_mode >= OUT_RGBO;
+    const size_t cam_b = size_t(p->batch) * 36;
+    const int tf_floats = is_rgbo ? 0 : (p->tf_kind == 0 ? p->tf_resolution * 5 : (p->tf_kind == 1 ? p->tf_resolution * 4 : 2)) * p->tf_batch;
+    const size_t tf_off = ((cam_b + 15) / 16) * 16, img_off = ((tf_off + size_t(tf_floats) * 4 + 255) / 256) * 256;
+    const size_t img_b = size_t(p->batch) * 8 * p->width * p->height * 4;
+    ensure_scratch(net, img_off + img_b);
+    char* base = reinterpret_cast<char*>(net->d_scratch);
+    CUDA_OK(cudaMemcpyAsync(base, p->camera_matrix_dev, cam_b, cudaMemcpyHostToDevice, s));
+    if (tf_floats) CUDA_OK(cudaMemcpyAsync(base + tf_off, p->tf_dev, size_t(tf_floats) * 4, cudaMemcpyHostToDevice, s));
+    fvsrn_dvr_params q = *p;
+    q.camera_matrix_dev = reinterpret_cast<const float*>(base);
+    q.tf_dev = reinterpret_cast<const float*>(base + tf_off);
+    float* d_img = reinterpret_cast<float*>(base + img_off);
+    if (q.tile_w > 0 || q.tile_h > 0 || q.tile_x0 > 0 || q.tile_y0 > 0) CUDA_OK(cudaMemsetAsync(d_img, 0, img_b, s));
+    do_render(net, &q, d_img, s);
+    CUDA_OK(cudaMemcpyAsync(out_host, d_img, img_b, cudaMemcpyDeviceToHost, s));
+    CUDA_OK(cudaStreamSynchronize(s));
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_extract_color(const float* img_dev, float* out_dev, int batch, int height, int width, void* stream) {
+    FV_TRY
+    if (!img_dev || !out_dev) return fail("null device pointer");
+    const long long hw = (long long)height * width, total = hw * 4 * batch;
+    if (total <= 0) return 0;
+    const int threads = 256;
+    const int blocks = int(std::min<long long>((total + threads - 1) / threads, 148 * 16));
+    extract_color_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(img_dev, out_dev, hw, total);
+    CUDA_OK(cudaGetLastError());
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
+    FV_TRY
+    require_prepared(net);
+    if (!info) return fail("null argument");
+    const NetParams P = make_net_params(net, net->net.current_time, net->net.current_ensemble, false);
+    LaunchCfg cfg; cfg.sm_count = net->sm_count; cfg.query_only = 1;
+    launch_fn fn = pick_launcher(net->H16);
+    if (!fn) return fail("no kernel for this hidden width");
+    CUDA_OK(fn(kernel == 0 ? KIND_DVR : KIND_EVAL, net->GC16, net->dir, P, nullptr, &cfg, nullptr));
+    info->device = net->device; info->sm_count = net->sm_count;
+    info->block_threads = kWarpsPerBlock * 32; info->blocks_per_sm = cfg.blocks_per_sm; info->grid_blocks = cfg.grid;
+    info->smem_bytes_per_block = cfg.smem; info->regs_per_thread = cfg.regs;
+    info->rays_per_warp_tile_x = kTileW; info->rays_per_warp_tile_y = kTileH;
+    info->kernel_launches = net->launches;
+    return 0;
+    FV_CATCH
+}
+
+} // extern "C"

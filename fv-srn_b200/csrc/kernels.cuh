@@ -1,0 +1,254 @@
+// The two kernels of the hot path:
+//   dvr_kernel   <- ImageEvaluatorSimpleKernel + RayEvaluationSteppingDvr::eval + TF + Blending
+//                   (reference renderer_image_evaluator_simple.cuh:36-127, renderer_ray_evaluation_stepping_dvr.cuh:49-157)
+//   eval_kernel  <- EvaluateNoBatches (reference renderer_volume_kernels1.cuh:15-71)
+// Persistent CTAs; every warp owns an 8x4 pixel tile (32 rays) and marches it in lock-step, one SRN sample per
+// lane per step = one 32-row MMA tile per step. Warps never synchronise with each other after the weights have
+// been pinned in shared memory, so latency is hidden by warp-level parallelism.
+#pragma once
+#include "srn_core.cuh"
+#include <cfloat>
+
+namespace fvsrn {
+
+constexpr int kWarpsPerBlock = 4;
+constexpr int kTileW = 8, kTileH = 4;
+constexpr int kTfSmemFloats = 1024; // 256 x float4 texture TF or up to 204 piecewise control points
+
+struct DvrParams {
+    int W, H;                 // full image
+    int x0, y0, tw, th;       // rendered sub-rectangle
+    int b0, nb;               // first batch index and number of batches of this launch
+    const float* cam;         // (B,3,3)
+    float tan_half_fovy, aspect;
+    float stepsize, alpha_early_out, dmin, inv_range;
+    int early_out, blend_mode;
+    int tf_kind, tf_R, tf_batch;
+    const float* tf;
+    int spp, spp_side;
+    float* out;
+    long long sb, sc, sy, sx;
+    int* step_count;                    // optional (B,H,W)
+    unsigned long long* counters;       // optional [valid, executed]
+    unsigned int* tile_counter;         // work queue
+    int tiles_x, tiles_y, num_tiles;
+};
+
+struct EvalParams {
+    const float* pos;   // (N,3)
+    const float* dir;   // (N,3) or null
+    float* out;         // (N,cout)
+    long long n;
+    int cout;
+};
+
+// copy the constant blob to shared memory (reference: VolumeInterpolationTensorcores ctor :401-564)
+__device__ __forceinline__ void load_blob(const NetParams& P, uint4* sblob) {
+    const int n16 = P.blob_bytes / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) sblob[i] = __ldg(P.blob + i);
+}
+
+__device__ __forceinline__ float4 tf_piecewise(const float* tf, int R, float d) { // reference renderer_tf_piecewise.cuh:27-52
+    int i;
+    for (i = 0; i < R - 2; ++i)
+        if (tf[(i + 1) * 5 + 4] > d) break;
+    const float* v0 = tf + i * 5;
+    const float* v1 = v0 + 5;
+    const float p0 = v0[4], p1 = v1[4];
+    d = fminf(fmaxf(d, p0), p1);
+    const float f = __fdividef(d - p0, p1 - p0);
+    return make_float4(v0[0] + f * (v1[0] - v0[0]), v0[1] + f * (v1[1] - v0[1]), v0[2] + f * (v1[2] - v0[2]),
+                       v0[3] + f * (v1[3] - v0[3]));
+}
+__device__ __forceinline__ float4 tf_texture(const float* tf, int R, float d) { // reference renderer_tf_texture.cuh:46-56
+    const float x = d * float(R) - 0.5f;
+    const float fl = floorf(x);
+    const int di = int(fl);
+    const float df = x - fl;
+    const float* v0 = tf + 4 * min(max(di, 0), R - 1);
+    const float* v1 = tf + 4 * min(max(di + 1, 0), R - 1);
+    return make_float4(v0[0] + df * (v1[0] - v0[0]), v0[1] + df * (v1[1] - v0[1]), v0[2] + df * (v1[2] - v0[2]),
+                       v0[3] + df * (v1[3] - v0[3]));
+}
+
+template <int H16, int GC16, bool DIR>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
+    using Net = Srn<H16, GC16, DIR>;
+    extern __shared__ uint4 smem[];
+    uint4* sblob = smem;
+    const int blob16 = (P.blob_bytes + 15) / 16;
+    float* stf = reinterpret_cast<float*>(smem + blob16);
+    uint4* stage_all = smem + blob16 + kTfSmemFloats / 4;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint4* stage = stage_all + warp * (Net::STAGE_BYTES / 16);
+
+    load_blob(P, sblob);
+    const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : (D.tf_kind == 1 ? D.tf_R * 4 : 2);
+    if (D.tf_batch == 1)
+        for (int i = threadIdx.x; i < tf_floats; i += blockDim.x) stf[i] = __ldg(D.tf + i);
+    __syncthreads();
+
+    const uint32_t sblob_addr = smem_u32(sblob);
+    const ActConst ac = make_act_const(P.activation, P.act_param);
+    const float3 bmin = make_float3(P.box_min[0], P.box_min[1], P.box_min[2]);
+    const float3 bsize = make_float3(P.box_size[0], P.box_size[1], P.box_size[2]);
+    const float3 binv = make_float3(1.f / bsize.x, 1.f / bsize.y, 1.f / bsize.z);
+    const bool is_rgbo = P.output_mode >= D_OUT_RGBO;
+
+    unsigned long long n_valid = 0, n_exec = 0;
+    for (;;) {
+        int tile = 0;
+        if (lane == 0) tile = int(atomicAdd(D.tile_counter, 1u));
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= D.num_tiles) break;
+        const int tiles_per_img = D.tiles_x * D.tiles_y;
+        const int bl = tile / tiles_per_img;            // local batch
+        const int trem = tile - bl * tiles_per_img;
+        const int ty = trem / D.tiles_x, tx = trem - ty * D.tiles_x;
+        const int b = D.b0 + bl;
+        const int x = D.x0 + tx * kTileW + (lane & (kTileW - 1));
+        const int y = D.y0 + ty * kTileH + (lane / kTileW);
+        const bool in_img = (x < D.x0 + D.tw) && (y < D.y0 + D.th);
+        const float* tfp = (D.tf_batch == 1) ? stf : (D.tf + (size_t)b * tf_floats);
+
+        // camera frame, reference renderer_camera.cuh:34-52
+        const float* cm = D.cam + (size_t)b * 9;
+        const float3 eye = make_float3(__ldg(cm + 0), __ldg(cm + 1), __ldg(cm + 2));
+        const float3 right = make_float3(__ldg(cm + 3), __ldg(cm + 4), __ldg(cm + 5));
+        const float3 up = make_float3(__ldg(cm + 6), __ldg(cm + 7), __ldg(cm + 8));
+        const float3 front = make_float3(up.y * right.z - up.z * right.y, up.z * right.x - up.x * right.z,
+                                         up.x * right.y - up.y * right.x); // cross(up, right)
+        const float tan_y = D.tan_half_fovy, tan_x = tan_y * D.aspect;
+
+        float4 pix_color = make_float4(0.f, 0.f, 0.f, 0.f);
+        float pix_depth = 0.f;
+        int last_steps = 0;
+        for (int s = 0; s < D.spp; ++s) {   // warp-uniform trip count
+            float nx = float(x), ny = float(y);
+            if (D.spp > 1) {                // deterministic stratified sub-pixel offsets
+                nx += (float(s % D.spp_side) + 0.5f) / float(D.spp_side) - 0.5f;
+                ny += (float(s / D.spp_side) + 0.5f) / float(D.spp_side) - 0.5f;
+            }
+            const float ndc_x = 2.f * (nx + 0.5f) / float(D.W) - 1.f;   // reference renderer_image_evaluator_simple.cuh:84-86
+            const float ndc_y = 2.f * (ny + 0.5f) / float(D.H) - 1.f;
+            float3 dir = make_float3(front.x + ndc_x * tan_x * right.x + ndc_y * tan_y * up.x,
+                                     front.y + ndc_x * tan_x * right.y + ndc_y * tan_y * up.y,
+                                     front.z + ndc_x * tan_x * right.z + ndc_y * tan_y * up.z);
+            const float inv_len = rsqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
+            dir.x *= inv_len; dir.y *= inv_len; dir.z *= inv_len;
+            // AABB, reference renderer_utils.cuh:91-105
+            const float ix = 1.0f / dir.x, iy = 1.0f / dir.y, iz = 1.0f / dir.z;
+            const float t1 = (bmin.x - eye.x) * ix, t2 = (bmin.x + bsize.x - eye.x) * ix;
+            const float t3 = (bmin.y - eye.y) * iy, t4 = (bmin.y + bsize.y - eye.y) * iy;
+            const float t5 = (bmin.z - eye.z) * iz, t6 = (bmin.z + bsize.z - eye.z) * iz;
+            float tmin = fmaxf(fmaxf(fminf(t1, t2), fminf(t3, t4)), fminf(t5, t6));
+            float tmax = fminf(fminf(fmaxf(t1, t2), fmaxf(t3, t4)), fmaxf(t5, t6));
+            tmin = fmaxf(tmin, 0.f);
+            tmax = fminf(tmax, FLT_MAX);
+            if (!in_img) tmax = -1.f;       // lanes outside the image never become valid
+
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            float acc_depth = 0.f;
+            int steps = 0;
+            // lock-step march, reference renderer_ray_evaluation_stepping_dvr.cuh:84-154
+            for (int i = 0;; ++i) {
+                const float t = tmin + float(i) * D.stepsize;
+                bool valid = (t <= tmax);
+                if (D.early_out) valid = valid && (acc.w < D.alpha_early_out);
+                if (!__any_sync(0xffffffffu, valid)) break;
+                n_exec += 32;
+                float px = 0.f, py = 0.f, pz = 0.f;
+                if (valid) {
+                    px = ((eye.x + dir.x * t) - bmin.x) * binv.x;
+                    py = ((eye.y + dir.y * t) - bmin.y) * binv.y;
+                    pz = ((eye.z + dir.z * t) - bmin.z) * binv.z;
+                }
+                float o[4];
+                Net::forward(P, sblob_addr, stage, ac, px, py, pz, dir.x, dir.y, dir.z, o);
+                if (!valid) continue;
+                ++steps;
+                float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (!is_rgbo) {
+                    const float value = (P.output_mode == D_OUT_DENSITY) ? sigmoidf_(o[0]) : o[0];
+                    if (value >= D.dmin) {
+                        const float d2 = fminf(fmaxf((value - D.dmin) * D.inv_range, 0.f), 1.f);
+                        if (D.tf_kind == 0) c = tf_piecewise(tfp, D.tf_R, d2);
+                        else if (D.tf_kind == 1) c = tf_texture(tfp, D.tf_R, d2);
+                        else c = make_float4(d2 * tfp[1], d2 * tfp[1], d2 * tfp[1], d2 * tfp[0]);
+                        c.w *= D.stepsize;
+                    }
+                } else {    // colour network, SKIP_TRANSFER_FUNCTION path (:103-109) + output parametrisation (:1054-1072)
+                    if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
+                    else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
+                    c.w *= D.stepsize;
+                }
+                if (c.w > 0.f) {    // blending, reference renderer_blending.cuh:36-51 (normal is zero for density networks)
+                    const float a = (D.blend_mode == 1) ? 1.f - __expf(-c.w) : fminf(1.f, c.w);
+                    const float k = (1.f - acc.w) * a;
+                    acc.x += k * c.x; acc.y += k * c.y; acc.z += k * c.z;
+                    acc_depth += k * t;
+                    acc.w += k;
+                }
+            }
+            n_valid += steps;
+            last_steps = steps;
+            pix_color.x += acc.x; pix_color.y += acc.y; pix_color.z += acc.z; pix_color.w += acc.w;
+            pix_depth += acc_depth * acc.w;     // reference renderer_image_evaluator_simple.cuh:101-103
+        }
+        if (in_img) {   // reference :106-124
+            const float inv_s = 1.f / float(D.spp);
+            float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
+            const float depth = pix_depth / pix_color.w;    // NaN for empty pixels, as in the reference
+            o[0 * D.sc] = pix_color.x * inv_s; o[1 * D.sc] = pix_color.y * inv_s; o[2 * D.sc] = pix_color.z * inv_s;
+            o[3 * D.sc] = pix_color.w * inv_s;
+            o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
+            o[7 * D.sc] = depth;
+            if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
+        }
+    }
+    if (D.counters) {
+        for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);
+        if (lane == 0) { atomicAdd(D.counters + 0, n_valid); atomicAdd(D.counters + 1, n_exec); }
+    }
+}
+
+template <int H16, int GC16, bool DIR>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+eval_kernel(const __grid_constant__ NetParams P, const __grid_constant__ EvalParams E) {
+    using Net = Srn<H16, GC16, DIR>;
+    extern __shared__ uint4 smem[];
+    uint4* sblob = smem;
+    const int blob16 = (P.blob_bytes + 15) / 16;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint4* stage = smem + blob16 + warp * (Net::STAGE_BYTES / 16);
+    load_blob(P, sblob);
+    __syncthreads();
+    const uint32_t sblob_addr = smem_u32(sblob);
+    const ActConst ac = make_act_const(P.activation, P.act_param);
+    const long long warps_total = (long long)gridDim.x * kWarpsPerBlock;
+    const long long n32 = (E.n + 31) / 32;
+    for (long long w = (long long)blockIdx.x * kWarpsPerBlock + warp; w < n32; w += warps_total) {
+        const long long i = w * 32 + lane;
+        const bool valid = i < E.n;
+        float px = 0.f, py = 0.f, pz = 0.f, dx = 0.f, dy = 0.f, dz = 0.f;
+        if (valid) {
+            px = __ldg(E.pos + 3 * i); py = __ldg(E.pos + 3 * i + 1); pz = __ldg(E.pos + 3 * i + 2);
+            if (DIR && E.dir) { dx = __ldg(E.dir + 3 * i); dy = __ldg(E.dir + 3 * i + 1); dz = __ldg(E.dir + 3 * i + 2); }
+        }
+        float o[4];
+        Net::forward(P, sblob_addr, stage, ac, px, py, pz, dx, dy, dz, o);
+        if (!valid) continue;
+        // output parametrisation, reference :1054-1072, 1149-1158 (value, not valueNoClamping)
+        if (P.output_mode == D_OUT_DENSITY) E.out[i] = sigmoidf_(o[0]);
+        else if (P.output_mode == D_OUT_DENSITY_DIRECT) E.out[i] = o[0];
+        else {
+            float4 c;
+            if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
+            else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
+            reinterpret_cast<float4*>(E.out)[i] = c;
+        }
+    }
+}
+
+} // namespace fvsrn

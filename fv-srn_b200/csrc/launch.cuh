@@ -1,0 +1,75 @@
+// Launch plumbing shared by api.cu and the per-width instantiation units (inst_hN.cu).
+// Replaces the run-time NVRTC assembly of reference renderer/kernel_loader.cpp:197-273 by ahead-of-time
+// sm_100a instantiations selected from the network's shape (hidden width, latent channels, direction input).
+#pragma once
+#include "kernels.cuh"
+#include <cuda_runtime.h>
+
+namespace fvsrn {
+
+struct LaunchCfg {
+    int sm_count = 0;
+    int blocks_per_sm = 0;   // filled by the launcher (occupancy query)
+    int grid = 0;            // filled by the launcher
+    int smem = 0;
+    int regs = 0;
+    int query_only = 0;      // 1: only fill the fields above, do not launch
+    long long max_blocks = 0; // upper bound on useful blocks (0 = none)
+};
+
+enum { KIND_DVR = 0, KIND_EVAL = 1 };
+
+// kp points to a DvrParams (KIND_DVR) or EvalParams (KIND_EVAL)
+typedef cudaError_t (*launch_fn)(int kind, int gc16, int dir, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s);
+cudaError_t launch_h2(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
+cudaError_t launch_h3(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
+cudaError_t launch_h4(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
+cudaError_t launch_h6(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
+cudaError_t launch_h8(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
+
+template <int H16, int GC16, bool DIR>
+cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s) {
+    using Net = Srn<H16, GC16, DIR>;
+    const int blob = ((P.blob_bytes + 15) / 16) * 16;
+    const int smem = blob + (kind == KIND_DVR ? kTfSmemFloats * 4 : 0) + kWarpsPerBlock * Net::STAGE_BYTES;
+    const void* fn = (kind == KIND_DVR) ? (const void*)dvr_kernel<H16, GC16, DIR> : (const void*)eval_kernel<H16, GC16, DIR>;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    int bps = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, kWarpsPerBlock * 32, smem);
+    if (e != cudaSuccess) return e;
+    if (bps < 1) return cudaErrorLaunchOutOfResources;
+    cudaFuncAttributes fa;
+    e = cudaFuncGetAttributes(&fa, fn);
+    if (e != cudaSuccess) return e;
+    long long grid = (long long)bps * cfg->sm_count;
+    if (cfg->max_blocks > 0 && grid > cfg->max_blocks) grid = cfg->max_blocks;
+    if (grid < 1) grid = 1;
+    cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = fa.numRegs;
+    if (cfg->query_only) return cudaSuccess;
+    if (kind == KIND_DVR)
+        dvr_kernel<H16, GC16, DIR><<<int(grid), kWarpsPerBlock * 32, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
+    else
+        eval_kernel<H16, GC16, DIR><<<int(grid), kWarpsPerBlock * 32, smem, s>>>(P, *static_cast<const EvalParams*>(kp));
+    return cudaGetLastError();
+}
+
+template <int H16>
+cudaError_t launch_width(int kind, int gc16, int dir, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s) {
+    if (!dir) {
+        switch (gc16) {
+            case 0: return launch_one<H16, 0, false>(kind, P, kp, cfg, s);
+            case 1: return launch_one<H16, 1, false>(kind, P, kp, cfg, s);
+            case 2: return launch_one<H16, 2, false>(kind, P, kp, cfg, s);
+        }
+    } else {
+        switch (gc16) {
+            case 0: return launch_one<H16, 0, true>(kind, P, kp, cfg, s);
+            case 1: return launch_one<H16, 1, true>(kind, P, kp, cfg, s);
+            case 2: return launch_one<H16, 2, true>(kind, P, kp, cfg, s);
+        }
+    }
+    return cudaErrorInvalidValue;
+}
+
+} // namespace fvsrn

@@ -1,0 +1,197 @@
+/*
+ * fvsrn_b200.h — C ABI of the B200-native fV-SRN hot path (libfvsrn_b200.so).
+ *
+ * One hot path, behind the reference's own module API:
+ *   the fused scene-representation-network (SRN) evaluation inside the DVR ray-marcher.
+ *
+ * Every entry point replaces (or is what a maintainer would bind from) one reference
+ * interface; the file:line cited beside each is the reference code it stands in for
+ * (paths relative to the fV-SRN tree).  No torch / pybind types cross this boundary:
+ * plain pointers, sizes, an opaque handle and a CUDA stream passed as void*.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; the message is in
+ *     fvsrn_last_error() (thread-local).  The reference throws std::runtime_error
+ *     (renderer/pytorch_utils.h:5-13, kernel_loader.cpp:19-31); a C++/pybind shim maps
+ *     non-zero -> throw, the Python host mirror maps it to RuntimeError.
+ *   - device pointers are suffixed _dev, host pointers _host.
+ *   - `stream` is a cudaStream_t (the caller's current stream, as
+ *     renderer/iimage_evaluator.cpp:167-170 does); NULL = default stream.
+ *   - there is NO CPU fallback: compute entry points fail when no CUDA device is present.
+ */
+#ifndef FVSRN_B200_H
+#define FVSRN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FVSRN_ABI_VERSION 1
+
+typedef struct fvsrn_network fvsrn_network; /* opaque: renderer::SceneNetwork + its GPU resources */
+
+/* Layer::Activation, renderer/volume_interpolation_network.h (names: volume_interpolation_network.cpp:223-230) */
+enum fvsrn_activation {
+    FVSRN_ACT_RELU = 0, FVSRN_ACT_SINE = 1, FVSRN_ACT_SNAKE = 2, FVSRN_ACT_SNAKEALT = 3,
+    FVSRN_ACT_SIGMOID = 4, FVSRN_ACT_NONE = 5
+};
+/* OutputParametrization::OutputMode, volume_interpolation_network.cpp:165-175 */
+enum fvsrn_output_mode {
+    FVSRN_OUT_DENSITY = 0, FVSRN_OUT_DENSITY_DIRECT = 1, FVSRN_OUT_RGBO = 2, FVSRN_OUT_RGBO_DIRECT = 3
+    /* 4..8 (densitygrad*, densitycurvature*) are parsed/saved but not evaluated: SURVEY §8 row f4 */
+};
+/* LatentGrid::Encoding, volume_interpolation_network.cpp:564-614 */
+enum fvsrn_grid_encoding { FVSRN_GRID_FLOAT = 0, FVSRN_GRID_BYTE_LINEAR = 1, FVSRN_GRID_BYTE_GAUSSIAN = 2 };
+/* BLENDING_MODE, renderer/renderer_blending.cuh:7-8 */
+enum fvsrn_blend_mode { FVSRN_BLEND_ALPHA = 0, FVSRN_BLEND_BEER_LAMBERT = 1 };
+/* transfer function kinds on the hot path */
+enum fvsrn_tf_kind {
+    FVSRN_TF_PIECEWISE = 0, /* renderer/renderer_tf_piecewise.cuh:27-62, tensor (B,R,5) = r,g,b,absorption,pos */
+    FVSRN_TF_TEXTURE = 1,   /* renderer/renderer_tf_texture.cuh:41-60 (tensor variant), (B,R,4) rgba */
+    FVSRN_TF_IDENTITY = 2   /* renderer/renderer_tf_identity.cuh: rgb = density*scale_c, absorption = density*scale_a */
+};
+
+/* ------------------------------------------------------------------------------------------
+ * Network lifetime and .volnet I/O
+ *   replaces renderer::SceneNetwork::{load,save}   volume_interpolation_network.cpp:1059-1104
+ * ------------------------------------------------------------------------------------------ */
+int  fvsrn_abi_version(void);
+const char* fvsrn_last_error(void);
+
+int  fvsrn_network_create(fvsrn_network** out);                                   /* SceneNetwork()  :797-804 */
+void fvsrn_network_free(fvsrn_network* net);
+int  fvsrn_network_load_volnet(const void* bytes, size_t n, fvsrn_network** out); /* SceneNetwork::load :1059-1086 */
+/* two-call pattern: buf==NULL -> *written = required size */
+int  fvsrn_network_save_volnet(const fvsrn_network* net, void* buf, size_t cap, size_t* written); /* ::save :1088-1104 */
+
+/* Builders mirroring the pyrenderer surface (volume_interpolation_network.cpp:1828-1972) */
+int  fvsrn_network_set_input(fvsrn_network* net, int has_time, int has_direction);
+/* B is (nf, cin) row-major fp32, cin = 3 or 6; premultiplied=0 multiplies by 2*pi.
+ * InputParametrization::setFourierMatrixFromTensor :129-156 */
+int  fvsrn_network_set_fourier(fvsrn_network* net, const float* B_host, int nf, int cin, int premultiplied);
+int  fvsrn_network_disable_fourier(fvsrn_network* net);
+int  fvsrn_network_set_output_mode(fvsrn_network* net, const char* mode);          /* OutputModeFromString :177-184 */
+/* W is (cout, cin) row-major fp32 (torch nn.Linear.weight), b is (cout).
+ * SceneNetwork::addLayerFromTorch :896-921 (+ addLayer re-layout :806-894) */
+int  fvsrn_network_add_layer(fvsrn_network* net, const float* W_host, const float* b_host,
+                             int cout, int cin, const char* activation, float activation_param);
+/* LatentGridTimeAndEnsemble(time_min,time_num,time_step,ensemble_min,ensemble_num) :756-796 */
+int  fvsrn_network_set_latent_grid_layout(fvsrn_network* net, int time_min, int time_num, int time_step,
+                                          int ensemble_min, int ensemble_num);
+/* grid is (C,Z,Y,X) fp32 row-major (torch (1,C,Z,Y,X)); LatentGrid(t, encoding) :290-334.
+ * returns the encoding error (mean abs) through *encoding_error if non-NULL. */
+int  fvsrn_network_set_time_grid(fvsrn_network* net, int index, const float* grid_host,
+                                 int C, int Z, int Y, int X, int encoding, double* encoding_error);
+int  fvsrn_network_set_ensemble_grid(fvsrn_network* net, int index, const float* grid_host,
+                                     int C, int Z, int Y, int X, int encoding, double* encoding_error);
+int  fvsrn_network_set_box(fvsrn_network* net, const float box_min[3], const float box_size[3]);
+int  fvsrn_network_get_box(const fvsrn_network* net, float box_min[3], float box_size[3]);
+int  fvsrn_network_valid(const fvsrn_network* net);                                /* SceneNetwork::valid :940-985; 1 = valid */
+int  fvsrn_network_num_parameters(const fvsrn_network* net);                       /* :1043-1055 */
+int  fvsrn_network_compute_max_warps(const fvsrn_network* net, int only_shared, int adjoint); /* :987-1041 */
+int  fvsrn_network_set_time_and_ensemble(fvsrn_network* net, float time, int ensemble);       /* :923-938 */
+
+/* Introspection (what a binding needs to expose .input/.output/.latent_grid read-only) */
+typedef struct fvsrn_network_info {
+    int has_time, has_direction, num_fourier, direction_in_fourier;
+    int output_mode;          /* fvsrn_output_mode (or 4..8) */
+    int num_layers;           /* linear layers incl. the last */
+    int hidden_channels;      /* H */
+    int latent_channels;      /* total latent-grid channels (0 if none) */
+    int grid_x, grid_y, grid_z;
+    int time_min, time_num, time_step, ensemble_min, ensemble_num;
+    int grid_encoding;
+    int activation;           /* of the hidden layers */
+    float activation_param;
+    int channels_out;         /* 1 (density*) or 4 (rgbo*) */
+} fvsrn_network_info;
+int  fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info);
+
+/* Upload weights (fragment-ordered fp16) and the fp16 channel-last latent grids to `device`.
+ * replaces SceneNetwork::fillConstantMemory :1236-1417, LatentGrid::copyGridToGPU :524-535 and the
+ * per-network NVRTC specialisation in renderer/kernel_loader.cpp:197-273 (kernels are AOT sm_100a). */
+int  fvsrn_network_prepare(fvsrn_network* net, int device, void* stream);
+int  fvsrn_network_clear_gpu_resources(fvsrn_network* net);                        /* :1106-1113 */
+
+/* ------------------------------------------------------------------------------------------
+ * World-space batch query
+ *   replaces IVolumeInterpolation::evaluate + EvaluateNoBatches
+ *   renderer/volume_interpolation.cpp:26-127, renderer/renderer_volume_kernels1.cuh:15-71
+ *   positions (N,3) fp32 in [0,1]^3 (the reference forces the box to the unit cube, :45-48),
+ *   directions (N,3) or NULL, out (N,channels_out) fp32.
+ * ------------------------------------------------------------------------------------------ */
+int  fvsrn_evaluate(fvsrn_network* net, const float* positions_dev, const float* directions_dev,
+                    float* out_dev, int64_t n, void* stream);
+/* same call with HOST buffers (copies inside; pinned memory makes them asynchronous) */
+int  fvsrn_evaluate_host(fvsrn_network* net, const float* positions_host, const float* directions_host,
+                         float* out_host, int64_t n, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * DVR frame
+ *   replaces ImageEvaluatorSimple::render -> ImageEvaluatorSimpleKernel
+ *   renderer/image_evaluator_simple.cpp:198-361, renderer/renderer_image_evaluator_simple.cuh:36-127,
+ *   renderer/renderer_ray_evaluation_stepping_dvr.cuh:49-157, renderer/renderer_camera.cuh:31-52,
+ *   renderer/renderer_tf_piecewise.cuh:27-62, renderer/renderer_tf_texture.cuh:41-60,
+ *   renderer/renderer_blending.cuh:36-51
+ * ------------------------------------------------------------------------------------------ */
+typedef struct fvsrn_dvr_params {
+    int width, height, batch;       /* full image size and camera batch B */
+    /* sub-rectangle actually rendered (screen-tile sharding); ndc is still relative to width x height.
+     * tile_w/tile_h == 0 means the full image. */
+    int tile_x0, tile_y0, tile_w, tile_h;
+    /* camera: (B,3,3) fp32 rows = eye, right, up (camera.cpp:495-549) */
+    const float* camera_matrix_dev;
+    float fov_y_radians;
+    /* RayEvaluationSteppingDvrParameters, renderer_ray_evaluation_stepping_dvr.cuh:22-29 */
+    float stepsize;
+    float alpha_early_out;          /* 1 - 1e-5 in the reference (ray_evaluation_stepping.cpp:603-623) */
+    float density_min, density_max;
+    int   early_out;                /* RAY_EVALUATION_STEPPING__ENABLE_EARLY_OUT */
+    int   blend_mode;               /* fvsrn_blend_mode */
+    /* transfer function */
+    int   tf_kind;                  /* fvsrn_tf_kind */
+    const float* tf_dev;            /* piecewise: (tf_batch,R,5); texture: (tf_batch,R,4); identity: 2 floats */
+    int   tf_resolution;            /* R */
+    int   tf_batch;                 /* 1 (broadcast) or B */
+    /* samples per pixel: 1 = reference DVR (ray_evaluation.h:61); n>1 = deterministic stratified
+     * sqrt(n) x sqrt(n) sub-pixel offsets (no reference analogue) */
+    int   samples_per_pixel;
+    /* per-view latent time (view-sharded time sweeps): NULL = use set_time_and_ensemble for all views,
+     * else host array of `batch` absolute times */
+    const float* view_times_host;
+    /* output strides in ELEMENTS of the (B,8,H,W) fp32 tensor (any layout, renderer/pytorch_utils.h:39-43) */
+    int64_t out_stride_b, out_stride_c, out_stride_y, out_stride_x;
+    /* optional debug/statistics outputs (may be NULL) */
+    int32_t* step_count_dev;        /* (B,H,W) int32 contiguous: valid steps of each ray (last sample of the pixel) */
+    unsigned long long* counters_dev; /* [0] += valid samples, [1] += executed (lock-step) samples */
+} fvsrn_dvr_params;
+
+int  fvsrn_render_dvr(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_dev, void* stream);
+/* HOST-buffer variant: camera matrix, TF and output image live on the host; the call stages them
+ * (H2D camera+TF, D2H image) on `stream` and synchronises before returning. `p->camera_matrix_dev`
+ * and `p->tf_dev` are interpreted as HOST pointers, `out_host` is (B,8,H,W) with the given strides. */
+int  fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_host, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * (B,8,H,W) -> (B,4,H,W) colour extraction; replaces IImageEvaluator::extractColor /
+ * SelectOutputChannelKernel, renderer/iimage_evaluator_cuda.cu:21-80 (ChannelColor only). SURVEY f1.
+ * ------------------------------------------------------------------------------------------ */
+int  fvsrn_extract_color(const float* img_dev, float* out_dev, int batch, int height, int width, void* stream);
+
+/* Launch diagnostics (stand-in for compute_max_warps / KernelLoader occupancy query) */
+typedef struct fvsrn_query_info {
+    int device, sm_count;
+    int block_threads, blocks_per_sm, grid_blocks;
+    int smem_bytes_per_block, regs_per_thread;
+    int rays_per_warp_tile_x, rays_per_warp_tile_y;
+    unsigned long long kernel_launches; /* number of fvsrn kernels launched by this handle so far */
+} fvsrn_query_info;
+int  fvsrn_query(fvsrn_network* net, int kernel /*0 = dvr, 1 = evaluate*/, fvsrn_query_info* info);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FVSRN_B200_H */
