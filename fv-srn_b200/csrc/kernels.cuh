@@ -93,7 +93,7 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
     const ActConst ac = make_act_const(P.activation, P.act_param);
     const float3 bmin = make_float3(P.box_min[0], P.box_min[1], P.box_min[2]);
     const float3 bsize = make_float3(P.box_size[0], P.box_size[1], P.box_size[2]);
-    const float3 binv = make_float3(1.f / bsize.x, 1.f / bsize.y, 1.f / bsize.z);
+    const float3 binv = make_float3(__fdiv_rn(1.f, bsize.x), __fdiv_rn(1.f, bsize.y), __fdiv_rn(1.f, bsize.z));
     const bool is_rgbo = P.output_mode >= D_OUT_RGBO;
 
     unsigned long long n_valid = 0, n_exec = 0;
@@ -117,9 +117,11 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
         const float3 eye = make_float3(__ldg(cm + 0), __ldg(cm + 1), __ldg(cm + 2));
         const float3 right = make_float3(__ldg(cm + 3), __ldg(cm + 4), __ldg(cm + 5));
         const float3 up = make_float3(__ldg(cm + 6), __ldg(cm + 7), __ldg(cm + 8));
-        const float3 front = make_float3(up.y * right.z - up.z * right.y, up.z * right.x - up.x * right.z,
-                                         up.x * right.y - up.y * right.x); // cross(up, right)
-        const float tan_y = D.tan_half_fovy, tan_x = tan_y * D.aspect;
+        // explicit rounding order (no compiler FMA contraction) so that the CPU oracle reproduces ray setup bit for bit
+        const float3 front = make_float3(__fmaf_rn(up.y, right.z, -__fmul_rn(up.z, right.y)),
+                                         __fmaf_rn(up.z, right.x, -__fmul_rn(up.x, right.z)),
+                                         __fmaf_rn(up.x, right.y, -__fmul_rn(up.y, right.x))); // cross(up, right)
+        const float tan_y = D.tan_half_fovy, tan_x = __fmul_rn(tan_y, D.aspect);
 
         float4 pix_color = make_float4(0.f, 0.f, 0.f, 0.f);
         float pix_depth = 0.f;
@@ -127,21 +129,23 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
         for (int s = 0; s < D.spp; ++s) {   // warp-uniform trip count
             float nx = float(x), ny = float(y);
             if (D.spp > 1) {                // deterministic stratified sub-pixel offsets
-                nx += (float(s % D.spp_side) + 0.5f) / float(D.spp_side) - 0.5f;
-                ny += (float(s / D.spp_side) + 0.5f) / float(D.spp_side) - 0.5f;
+                nx = __fadd_rn(nx, __fsub_rn(__fdiv_rn(float(s % D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
+                ny = __fadd_rn(ny, __fsub_rn(__fdiv_rn(float(s / D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
             }
-            const float ndc_x = 2.f * (nx + 0.5f) / float(D.W) - 1.f;   // reference renderer_image_evaluator_simple.cuh:84-86
-            const float ndc_y = 2.f * (ny + 0.5f) / float(D.H) - 1.f;
-            float3 dir = make_float3(front.x + ndc_x * tan_x * right.x + ndc_y * tan_y * up.x,
-                                     front.y + ndc_x * tan_x * right.y + ndc_y * tan_y * up.y,
-                                     front.z + ndc_x * tan_x * right.z + ndc_y * tan_y * up.z);
-            const float inv_len = rsqrtf(dir.x * dir.x + dir.y * dir.y + dir.z * dir.z);
-            dir.x *= inv_len; dir.y *= inv_len; dir.z *= inv_len;
+            const float ndc_x = __fsub_rn(__fdiv_rn(2.f * (nx + 0.5f), float(D.W)), 1.f);   // reference renderer_image_evaluator_simple.cuh:84-86
+            const float ndc_y = __fsub_rn(__fdiv_rn(2.f * (ny + 0.5f), float(D.H)), 1.f);
+            const float sx = __fmul_rn(ndc_x, tan_x), sy = __fmul_rn(ndc_y, tan_y);
+            float3 dir = make_float3(__fmaf_rn(sy, up.x, __fmaf_rn(sx, right.x, front.x)),
+                                     __fmaf_rn(sy, up.y, __fmaf_rn(sx, right.y, front.y)),
+                                     __fmaf_rn(sy, up.z, __fmaf_rn(sx, right.z, front.z)));
+            const float len2 = __fmaf_rn(dir.z, dir.z, __fmaf_rn(dir.y, dir.y, __fmul_rn(dir.x, dir.x)));
+            const float inv_len = __fdiv_rn(1.0f, __fsqrt_rn(len2));
+            dir.x = __fmul_rn(dir.x, inv_len); dir.y = __fmul_rn(dir.y, inv_len); dir.z = __fmul_rn(dir.z, inv_len);
             // AABB, reference renderer_utils.cuh:91-105
-            const float ix = 1.0f / dir.x, iy = 1.0f / dir.y, iz = 1.0f / dir.z;
-            const float t1 = (bmin.x - eye.x) * ix, t2 = (bmin.x + bsize.x - eye.x) * ix;
-            const float t3 = (bmin.y - eye.y) * iy, t4 = (bmin.y + bsize.y - eye.y) * iy;
-            const float t5 = (bmin.z - eye.z) * iz, t6 = (bmin.z + bsize.z - eye.z) * iz;
+            const float ix = __fdiv_rn(1.0f, dir.x), iy = __fdiv_rn(1.0f, dir.y), iz = __fdiv_rn(1.0f, dir.z);
+            const float t1 = __fmul_rn(__fsub_rn(bmin.x, eye.x), ix), t2 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.x, bsize.x), eye.x), ix);
+            const float t3 = __fmul_rn(__fsub_rn(bmin.y, eye.y), iy), t4 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.y, bsize.y), eye.y), iy);
+            const float t5 = __fmul_rn(__fsub_rn(bmin.z, eye.z), iz), t6 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.z, bsize.z), eye.z), iz);
             float tmin = fmaxf(fmaxf(fminf(t1, t2), fminf(t3, t4)), fminf(t5, t6));
             float tmax = fminf(fminf(fmaxf(t1, t2), fmaxf(t3, t4)), fmaxf(t5, t6));
             tmin = fmaxf(tmin, 0.f);
@@ -153,16 +157,16 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
             int steps = 0;
             // lock-step march, reference renderer_ray_evaluation_stepping_dvr.cuh:84-154
             for (int i = 0;; ++i) {
-                const float t = tmin + float(i) * D.stepsize;
+                const float t = __fmaf_rn(float(i), D.stepsize, tmin);
                 bool valid = (t <= tmax);
                 if (D.early_out) valid = valid && (acc.w < D.alpha_early_out);
                 if (!__any_sync(0xffffffffu, valid)) break;
                 n_exec += 32;
                 float px = 0.f, py = 0.f, pz = 0.f;
                 if (valid) {
-                    px = ((eye.x + dir.x * t) - bmin.x) * binv.x;
-                    py = ((eye.y + dir.y * t) - bmin.y) * binv.y;
-                    pz = ((eye.z + dir.z * t) - bmin.z) * binv.z;
+                    px = __fmul_rn(__fsub_rn(__fmaf_rn(dir.x, t, eye.x), bmin.x), binv.x);
+                    py = __fmul_rn(__fsub_rn(__fmaf_rn(dir.y, t, eye.y), bmin.y), binv.y);
+                    pz = __fmul_rn(__fsub_rn(__fmaf_rn(dir.z, t, eye.z), bmin.z), binv.z);
                 }
                 float o[4];
                 Net::forward(P, sblob_addr, stage, ac, px, py, pz, dir.x, dir.y, dir.z, o);

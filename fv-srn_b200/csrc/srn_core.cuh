@@ -230,7 +230,7 @@ struct Srn {
         if (GC16 > 0) {
             // trilinear latent fetch. Sampling position p*N - 0.5 with border clamp == tex3D(normalised, clamp, linear)
             // == grid_sample(align_corners=False, padding_mode='border') (reference :573-605, volume_interpolation_network.cpp:470-504)
-            const float ux = px * float(P.gx) - 0.5f, uy = py * float(P.gy) - 0.5f, uz = pz * float(P.gz) - 0.5f;
+            const float ux = __fmaf_rn(px, float(P.gx), -0.5f), uy = __fmaf_rn(py, float(P.gy), -0.5f), uz = __fmaf_rn(pz, float(P.gz), -0.5f);
             const float flx = floorf(ux), fly = floorf(uy), flz = floorf(uz);
             const float fx = ux - flx, fy = uy - fly, fz = uz - flz;
             const int ix = int(flx), iy = int(fly), iz = int(flz);
@@ -257,7 +257,7 @@ struct Srn {
                         const uint4* ptr = base + (size_t)((zi * P.gy + yi) * P.gx + xi) * G.voxel_stride;
                         v[c][0] = __ldg(ptr);
                         v[c][1] = __ldg(ptr + 1);
-                        w2[c] = __float2half2_rn(((wz[c >> 2] * wy[(c >> 1) & 1]) * wx[c & 1]) * ws);
+                        w2[c] = __float2half2_rn(__fmul_rn(__fmul_rn(__fmul_rn(wz[c >> 2], wy[(c >> 1) & 1]), wx[c & 1]), ws));
                     }
 #pragma unroll
                     for (int c = 0; c < 8; ++c) {

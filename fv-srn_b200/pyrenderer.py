@@ -1,0 +1,582 @@
+"""
+Host-side mirror of the reference's ``pyrenderer`` module for the SRN/DVR hot path.
+
+Same class names, attribute names, argument meaning and error behaviour (RuntimeError) as the pybind11 module
+built from bindings/bindings.cpp + the ``registerPybindModule`` functions of
+renderer/volume_interpolation_network.cpp:1817-2007, renderer/ray_evaluation_stepping.cpp:781-801,
+renderer/image_evaluator_simple.cpp:427-475, renderer/iimage_evaluator.cpp:325-358,
+renderer/transfer_function_piecewise.cpp:110-111, renderer/transfer_function_texture.cpp:246-264 and
+renderer/camera.cpp:200-222,385-396 — so that callers written against the reference
+(applications/volnet/inference.py:461-625) run unchanged. All compute goes through the C ABI of
+libfvsrn_b200.so; torch tensors exist only at this boundary (device memory + current stream).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check
+
+
+# ------------------------------------------------------------------------------------------------ small value types
+class _Vec3:
+    __slots__ = ("x", "y", "z")
+
+    def __init__(self, x=0.0, y=0.0, z=0.0):
+        self.x, self.y, self.z = float(x), float(y), float(z)
+
+    def __iter__(self): return iter((self.x, self.y, self.z))
+    def __repr__(self): return f"{type(self).__name__}({self.x}, {self.y}, {self.z})"
+
+
+class float3(_Vec3): pass
+class double3(_Vec3): pass
+
+
+class _Vec4:
+    __slots__ = ("x", "y", "z", "w")
+
+    def __init__(self, x=0.0, y=0.0, z=0.0, w=0.0):
+        self.x, self.y, self.z, self.w = float(x), float(y), float(z), float(w)
+
+    def __iter__(self): return iter((self.x, self.y, self.z, self.w))
+
+
+class float4(_Vec4): pass
+class double4(_Vec4): pass
+
+
+class Parameter:
+    """renderer/parameter.h:19-107: ``.value`` is a scalar/vector or a batched torch tensor."""
+
+    def __init__(self, value=None):
+        self.value = value
+        self.grad = None
+        self.forwardIndex = None
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def sync():
+    torch.cuda.synchronize()
+
+
+def cleanup():
+    pass
+
+
+class GPUTimer:
+    """cudaEvent pair, bindings/bindings.cpp:101-131."""
+
+    def __init__(self):
+        self._a = torch.cuda.Event(enable_timing=True); self._b = torch.cuda.Event(enable_timing=True)
+
+    def start(self): self._a.record()
+    def stop(self): self._b.record()
+
+    def elapsed_milliseconds(self):
+        self._b.synchronize()
+        return self._a.elapsed_time(self._b)
+
+
+# ------------------------------------------------------------------------------------------------ SceneNetwork
+class _Enum:
+    def __init__(self, name, index): self.name, self.index = name, index
+    def __repr__(self): return self.name
+    def __eq__(self, o): return isinstance(o, _Enum) and o.index == self.index and type(o) is type(self)
+    def __hash__(self): return hash((type(self).__name__, self.index))
+
+
+class SceneNetwork:
+    """renderer::SceneNetwork (volume_interpolation_network.cpp:797-1113, pybind :1828-1972)."""
+
+    class Layer:
+        class Activation(_Enum): pass
+        _names = ["ReLU", "Sine", "Snake", "SnakeAlt", "Sigmoid", "None"]
+
+        @staticmethod
+        def ActivationFromString(s):
+            if s not in SceneNetwork.Layer._names:
+                raise RuntimeError("No output mode found matching string " + s)
+            return SceneNetwork.Layer.Activation(s, SceneNetwork.Layer._names.index(s))
+
+    class OutputParametrization:
+        class OutputMode(_Enum): pass
+        _names = ["density", "density:direct", "rgbo", "rgbo:direct", "densitygrad", "densitygrad:direct",
+                  "densitygrad:cubic", "densitycurvature", "densitycurvature:direct"]
+
+        @staticmethod
+        def OutputModeFromString(s):
+            names = SceneNetwork.OutputParametrization._names
+            if s not in names:
+                raise RuntimeError("No output mode found matching string " + s)
+            return SceneNetwork.OutputParametrization.OutputMode(s, names.index(s))
+
+        def __init__(self, owner): self._o = owner
+
+        @property
+        def output_mode(self):
+            return SceneNetwork.OutputParametrization.OutputMode(
+                SceneNetwork.OutputParametrization._names[self._o._info().output_mode], self._o._info().output_mode)
+
+        @output_mode.setter
+        def output_mode(self, m):
+            name = m.name if isinstance(m, _Enum) else str(m)
+            check(_lib.lib().fvsrn_network_set_output_mode(self._o._h, name.encode()))
+
+    class LatentGrid:
+        class Encoding(_Enum): pass
+    LatentGrid.Float = LatentGrid.Encoding("Float", 0)
+    LatentGrid.ByteLinear = LatentGrid.Encoding("ByteLinear", 1)
+    LatentGrid.ByteGaussian = LatentGrid.Encoding("ByteGaussian", 2)
+
+    class LatentGridTimeAndEnsemble:
+        """(time_min, time_num, time_step, ensemble_min, ensemble_num), :756-796."""
+
+        def __init__(self, time_min=0, time_num=0, time_step=1, ensemble_min=0, ensemble_num=0):
+            self.time_min, self.time_num, self.time_step = int(time_min), int(time_num), int(time_step)
+            self.ensemble_min, self.ensemble_num = int(ensemble_min), int(ensemble_num)
+            self._time = [None] * self.time_num
+            self._ens = [None] * self.ensemble_num
+
+        @staticmethod
+        def _dense(t):
+            if t.dim() != 5 or t.shape[0] != 1:
+                raise RuntimeError("Expected a tensor of shape (1,C,Z,Y,X)")
+            return np.ascontiguousarray(t.detach().to("cpu", torch.float32).numpy()[0])
+
+        def set_time_grid_from_torch(self, index, t, encoding):
+            if not (0 <= index < self.time_num):
+                raise RuntimeError("index out of bounds!")
+            self._time[index] = (self._dense(t), encoding.index)
+            return 0.0
+
+        def set_ensemble_grid_from_torch(self, index, t, encoding):
+            if not (0 <= index < self.ensemble_num):
+                raise RuntimeError("index out of bounds!")
+            self._ens[index] = (self._dense(t), encoding.index)
+            return 0.0
+
+        def is_valid(self):
+            gs = self._time + self._ens
+            return bool(gs) and all(g is not None and g[0].shape[0] % 16 == 0 for g in gs)
+
+    class _Input:
+        """InputParametrization proxy (:68-156)."""
+
+        def __init__(self, owner):
+            self._o = owner; self._has_time = False; self._has_direction = False
+
+        def _push(self): check(_lib.lib().fvsrn_network_set_input(self._o._h, int(self._has_time), int(self._has_direction)))
+
+        @property
+        def has_time(self): return bool(self._o._info().has_time)
+
+        @has_time.setter
+        def has_time(self, v): self._has_time = bool(v); self._push()
+
+        @property
+        def has_direction(self): return bool(self._o._info().has_direction)
+
+        @has_direction.setter
+        def has_direction(self, v): self._has_direction = bool(v); self._push()
+
+        @property
+        def num_fourier_features(self): return self._o._info().num_fourier
+
+        def set_fourier_matrix_from_tensor(self, t, premultiplied):
+            if t.dim() != 2:
+                raise RuntimeError("Expected a 2D tensor")
+            a = np.ascontiguousarray(t.detach().to("cpu", torch.float32).numpy())
+            check(_lib.lib().fvsrn_network_set_fourier(self._o._h, a.ctypes.data, a.shape[0], a.shape[1], int(bool(premultiplied))))
+
+        def disable_fourier_features(self):
+            check(_lib.lib().fvsrn_network_disable_fourier(self._o._h))
+
+    def __init__(self, _handle=None):
+        L = _lib.lib()
+        if _handle is None:
+            h = C.c_void_p()
+            check(L.fvsrn_network_create(C.byref(h)))
+            _handle = h
+        self._h = _handle
+        self.input = SceneNetwork._Input(self)
+        if _handle is not None:
+            i = self._info(); self.input._has_time, self.input._has_direction = bool(i.has_time), bool(i.has_direction)
+        self.output = SceneNetwork.OutputParametrization(self)
+        self._latent_grid = None
+        self._prepared_device = None
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.lib().fvsrn_network_free(self._h); self._h = None
+        except Exception:
+            pass
+
+    def _info(self):
+        info = _lib.NetworkInfo()
+        check(_lib.lib().fvsrn_network_get_info(self._h, C.byref(info)))
+        return info
+
+    # -- latent grid
+    @property
+    def latent_grid(self): return self._latent_grid
+
+    @latent_grid.setter
+    def latent_grid(self, g):
+        L = _lib.lib()
+        check(L.fvsrn_network_set_latent_grid_layout(self._h, g.time_min, g.time_num, g.time_step, g.ensemble_min, g.ensemble_num))
+        for idx, item in enumerate(g._time):
+            if item is None:
+                raise RuntimeError("One latent grid was null")
+            a, enc = item
+            check(L.fvsrn_network_set_time_grid(self._h, idx, a.ctypes.data, *a.shape, enc, None))
+        for idx, item in enumerate(g._ens):
+            if item is None:
+                raise RuntimeError("One latent grid was null")
+            a, enc = item
+            check(L.fvsrn_network_set_ensemble_grid(self._h, idx, a.ctypes.data, *a.shape, enc, None))
+        self._latent_grid = g
+        self._prepared_device = None
+
+    # -- layers
+    def add_layer(self, weights, bias, activation, activation_parameter=1.0):
+        if weights.dim() != 2 or bias.dim() != 1 or weights.shape[0] != bias.shape[0]:
+            raise RuntimeError("Expected weights (cout,cin) and bias (cout)")
+        w = np.ascontiguousarray(weights.detach().to("cpu", torch.float32).numpy())
+        b = np.ascontiguousarray(bias.detach().to("cpu", torch.float32).numpy())
+        name = activation.name if isinstance(activation, _Enum) else str(activation)
+        check(_lib.lib().fvsrn_network_add_layer(self._h, w.ctypes.data, b.ctypes.data, w.shape[0], w.shape[1],
+                                                 name.encode(), float(activation_parameter)))
+        self._prepared_device = None
+
+    # -- box
+    def _get_box(self):
+        mn, sz = (C.c_float * 3)(), (C.c_float * 3)()
+        check(_lib.lib().fvsrn_network_get_box(self._h, C.byref(mn), C.byref(sz)))
+        return float3(*mn), float3(*sz)
+
+    def _set_box(self, mn, sz):
+        check(_lib.lib().fvsrn_network_set_box(self._h, C.byref((C.c_float * 3)(*mn)), C.byref((C.c_float * 3)(*sz))))
+
+    @property
+    def box_min(self): return self._get_box()[0]
+
+    @box_min.setter
+    def box_min(self, v): self._set_box(tuple(v), tuple(self._get_box()[1]))
+
+    @property
+    def box_size(self): return self._get_box()[1]
+
+    @box_size.setter
+    def box_size(self, v): self._set_box(tuple(self._get_box()[0]), tuple(v))
+
+    def valid(self): return _lib.lib().fvsrn_network_valid(self._h) == 1
+    def num_parameters(self): return _lib.lib().fvsrn_network_num_parameters(self._h)
+    def compute_max_warps(self, only_shared, adjoint=False):
+        return _lib.lib().fvsrn_network_compute_max_warps(self._h, int(bool(only_shared)), int(bool(adjoint)))
+
+    def clear_gpu_resources(self):
+        check(_lib.lib().fvsrn_network_clear_gpu_resources(self._h)); self._prepared_device = None
+
+    def set_time_and_ensemble(self, time, ensemble):
+        check(_lib.lib().fvsrn_network_set_time_and_ensemble(self._h, float(time), int(ensemble)))
+
+    def to_bytes(self) -> bytes:
+        n = C.c_size_t()
+        check(_lib.lib().fvsrn_network_save_volnet(self._h, None, 0, C.byref(n)))
+        buf = C.create_string_buffer(n.value)
+        check(_lib.lib().fvsrn_network_save_volnet(self._h, buf, n.value, C.byref(n)))
+        return buf.raw[:n.value]
+
+    def save(self, path):
+        data = self.to_bytes()
+        with open(path, "wb") as f:
+            f.write(data)
+
+    @staticmethod
+    def from_bytes(data: bytes):
+        h = C.c_void_p()
+        check(_lib.lib().fvsrn_network_load_volnet(data, len(data), C.byref(h)))
+        return SceneNetwork(h)
+
+    @staticmethod
+    def load(path):
+        with open(path, "rb") as f:
+            return SceneNetwork.from_bytes(f.read())
+
+    # -- GPU residency (replaces fillConstantMemory / copyGridToGPU)
+    def _ensure_prepared(self):
+        dev = torch.cuda.current_device() if torch.cuda.is_available() else 0
+        if self._prepared_device != dev:
+            check(_lib.lib().fvsrn_network_prepare(self._h, dev, _stream_ptr() if torch.cuda.is_available() else None))
+            self._prepared_device = dev
+
+
+# ------------------------------------------------------------------------------------------------ volume module
+class VolumeInterpolationNetwork:
+    """renderer::VolumeInterpolationNetwork (:1419-1726, pybind :1974-2005) + IVolumeInterpolation::evaluate."""
+
+    def __init__(self):
+        self._networks = []
+        self._current = None
+        self.only_shared_memory = False   # kept for API compatibility; the B200 kernel always pins weights in smem
+        self.gradient_mode = "OFF_OR_DIRECT"
+
+    def set_network(self, net: SceneNetwork):
+        if net is None or not net.valid():
+            raise RuntimeError("scene network is not valid")
+        self._networks = [net]; self._current = net
+
+    def add_network(self, net: SceneNetwork):
+        if net is None or not net.valid():
+            raise RuntimeError("scene network is not valid")
+        self._networks.append(net)
+        if self._current is None:
+            self._current = net
+
+    def select_network(self, index): self._current = self._networks[index]
+    def load_network(self, path): self.set_network(SceneNetwork.load(path))
+    def current_network(self): return self._current
+    def box_min(self): return self._require().box_min
+    def box_size(self): return self._require().box_size
+
+    def _require(self) -> SceneNetwork:
+        if self._current is None:
+            raise RuntimeError("No network specified")
+        return self._current
+
+    def evaluate(self, positions: torch.Tensor, directions: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """positions (N,3) CUDA float32 in [0,1]^3 -> (N,C) float32 (volume_interpolation.cpp:26-127)."""
+        net = self._require()
+        if not positions.is_cuda:
+            raise RuntimeError("positions must reside on the GPU")
+        if positions.dim() != 2 or positions.shape[1] != 3:
+            raise RuntimeError("positions must be of shape (N,3)")
+        if positions.dtype != torch.float32:
+            raise RuntimeError("positions must be of dtype float32")
+        positions = positions.contiguous()
+        if directions is not None:
+            directions = directions.to(torch.float32).contiguous()
+        net._ensure_prepared()
+        cout = net._info().channels_out
+        out = torch.empty((positions.shape[0], cout), dtype=torch.float32, device=positions.device)
+        check(_lib.lib().fvsrn_evaluate(net._h, positions.data_ptr(), directions.data_ptr() if directions is not None else None,
+                                        out.data_ptr(), positions.shape[0], _stream_ptr()))
+        return out
+
+
+# ------------------------------------------------------------------------------------------------ TF modules
+class ITransferFunction:
+    kind = -1
+
+    def _tensor(self) -> torch.Tensor: raise NotImplementedError
+
+    def evaluate(self, density, min_density, max_density):
+        """CPU-free convenience used by callers for previews: evaluates with stepsize 1 on the GPU via torch ops."""
+        raise RuntimeError("ITransferFunction.evaluate tensor op is not part of the B200 hot path (SURVEY §8 f2)")
+
+
+class TransferFunctionPiecewiseLinear(ITransferFunction):
+    """tensor (B,R,5) = r,g,b,absorption,position (transfer_function_piecewise.cpp:145-164, 264-278)."""
+    kind = 0
+
+    def __init__(self):
+        self.tensor = Parameter(None)
+
+    def _tensor(self):
+        t = self.tensor.value
+        if t is None:
+            raise RuntimeError("texture tensor is not defined")
+        if not t.is_cuda:
+            raise RuntimeError("texture tensor must reside on the GPU")
+        if t.dim() != 3 or t.shape[2] != 5:
+            raise RuntimeError("texture tensor must be of shape (B,R,5)")
+        return t.to(torch.float32).contiguous()
+
+
+class TransferFunctionTexture(ITransferFunction):
+    """tensor (B,R,4) rgba, sampled like a clamped, linearly filtered 1-D texture (renderer_tf_texture.cuh:46-56)."""
+    kind = 1
+
+    def __init__(self):
+        self.tensor = Parameter(None)
+        self.preintegration_mode = 0
+
+    def switch_to_tensor(self): pass
+
+    def _tensor(self):
+        if self.preintegration_mode != 0:
+            raise RuntimeError("pre-integrated texture TFs are not part of the B200 hot path")
+        t = self.tensor.value
+        if t is None:
+            raise RuntimeError("texture tensor is not defined")
+        if not t.is_cuda or t.dim() != 3 or t.shape[2] != 4:
+            raise RuntimeError("texture tensor must be a CUDA tensor of shape (B,R,4)")
+        return t.to(torch.float32).contiguous()
+
+
+class TransferFunctionIdentity(ITransferFunction):
+    """rgb = density*scale_emission, absorption = density*scale_absorption (renderer_tf_identity.cuh)."""
+    kind = 2
+
+    def __init__(self, scale_absorption=10.0, scale_emission=1.0):
+        self.absorption_scaling = float(scale_absorption)
+        self.emission_scaling = float(scale_emission)
+
+    def _tensor(self):
+        return torch.tensor([[[self.absorption_scaling, self.emission_scaling]]], dtype=torch.float32, device="cuda")
+
+
+class Blending:
+    class BlendMode(_Enum): pass
+    Alpha = BlendMode("Alpha", 0)
+    BeerLambert = BlendMode("BeerLambert", 1)
+
+    def __init__(self):
+        self.blendMode = Blending.BeerLambert   # reference default, blending.h:54
+
+
+class BRDFLambert:
+    """Only the pass-through configuration is on the hot path (renderer_brdf_lambert.cuh:61-102)."""
+
+    def __init__(self):
+        self.enable_phong = False
+        self.enable_magnitude_scaling = False
+
+
+class RayEvaluationSteppingDvr:
+    """renderer::RayEvaluationSteppingDvr (ray_evaluation_stepping.cpp:535-623, pybind :781-801)."""
+
+    def __init__(self):
+        self.stepsize = 0.005            # ray_evaluation_stepping.h:14
+        self.min_density = 0.0
+        self.max_density = 1.0
+        self.early_out = True
+        self.alpha_early_out = 1.0 - 1e-5
+        self.blending = Blending()
+        self.tf: Optional[ITransferFunction] = TransferFunctionPiecewiseLinear()
+        self.brdf = BRDFLambert()
+        self.volume = None
+
+    def convert_to_texture_tf(self):
+        raise RuntimeError("convert_to_texture_tf is not part of the B200 hot path")
+
+
+# ------------------------------------------------------------------------------------------------ camera
+class Orientation(_Enum): pass
+
+
+class CameraOnASphere:
+    """renderer::CameraOnASphere: pitch/yaw/distance -> (B,3,3) reference frame (camera.cpp:480-581)."""
+    Xp, Xm, Yp, Ym, Zp, Zm = (Orientation(n, i) for i, n in enumerate(["Xp", "Xm", "Yp", "Ym", "Zp", "Zm"]))
+
+    def __init__(self):
+        self.orientation = CameraOnASphere.Ym
+        self.center = Parameter(double3(0, 0, 0))
+        self.pitchYawDistance = Parameter(double3(0, 0, 1))
+        self.fovY_radians = math.radians(45.0)
+        self._matrix: Optional[torch.Tensor] = None
+
+    @property
+    def fov_y_radians(self): return self.fovY_radians
+
+    @staticmethod
+    def reference_frame(pitch, yaw, distance, center=(0, 0, 0), orientation_index=3) -> np.ndarray:
+        """eulerToCartesian + computeParameters + updateCameraMatrix (camera.cpp:485-509, 553-581)."""
+        from .scenes import camera_reference_frame
+        return camera_reference_frame(pitch, yaw, distance, center, orientation_index)
+
+    def set_parameters(self, t: torch.Tensor):
+        if t.dim() != 3 or t.shape[1:] != (3, 3):
+            raise RuntimeError("camera parameters must be of shape (B,3,3)")
+        self._matrix = t.to(device="cuda", dtype=torch.float32).contiguous()
+
+    def get_parameters(self) -> torch.Tensor:
+        if self._matrix is not None:
+            return self._matrix
+        pyd, c = self.pitchYawDistance.value, self.center.value
+        m = CameraOnASphere.reference_frame(pyd.x, pyd.y, pyd.z, tuple(c), self.orientation.index)
+        return torch.from_numpy(m).to("cuda")
+
+
+# ------------------------------------------------------------------------------------------------ image evaluator
+class ImageEvaluatorSimple:
+    """renderer::ImageEvaluatorSimple::render (image_evaluator_simple.cpp:198-361) -> torch (B,8,H,W) float32."""
+
+    def __init__(self):
+        self.camera = CameraOnASphere()
+        self.ray_evaluator = RayEvaluationSteppingDvr()
+        self.volume: Optional[VolumeInterpolationNetwork] = None
+        self.samples_per_pixel = 1
+        self.selected_channel = "ChannelColor"
+        # B200 additions (all optional): screen-tile sharding, per-view times, statistics
+        self.tile = None                     # (x0, y0, w, h)
+        self.view_times = None               # list of absolute times, one per camera batch entry
+        self.collect_statistics = False
+        self.last_step_counts: Optional[torch.Tensor] = None
+        self.last_counters: Optional[torch.Tensor] = None
+
+    def _volume(self):
+        v = self.volume if self.volume is not None else self.ray_evaluator.volume
+        if v is None:
+            raise RuntimeError("No volume specified")
+        return v
+
+    def _params(self, width, height, cam, tf, out_strides):
+        re = self.ray_evaluator
+        p = _lib.DvrParams()
+        p.width, p.height, p.batch = width, height, cam.shape[0]
+        if self.tile is not None:
+            p.tile_x0, p.tile_y0, p.tile_w, p.tile_h = self.tile
+        p.camera_matrix_dev = cam.data_ptr()
+        p.fov_y_radians = self.camera.fovY_radians
+        p.stepsize, p.alpha_early_out = re.stepsize, re.alpha_early_out
+        p.density_min, p.density_max = re.min_density, re.max_density
+        p.early_out, p.blend_mode = int(bool(re.early_out)), re.blending.blendMode.index
+        if tf is not None:
+            p.tf_kind, p.tf_dev = re.tf.kind, tf.data_ptr()
+            p.tf_resolution, p.tf_batch = (tf.shape[1] if re.tf.kind != 2 else 0), tf.shape[0]
+        p.samples_per_pixel = self.samples_per_pixel
+        p.out_stride_b, p.out_stride_c, p.out_stride_y, p.out_stride_x = out_strides
+        return p
+
+    def render(self, width: int, height: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        vol = self._volume()
+        net = vol._require()
+        net._ensure_prepared()
+        cam = self.camera.get_parameters()
+        is_rgbo = net._info().channels_out == 4
+        tf = None if is_rgbo else self.ray_evaluator.tf._tensor()
+        B = cam.shape[0]
+        if out is None or tuple(out.shape) != (B, 8, height, width) or out.dtype != torch.float32 or not out.is_cuda:
+            out = torch.empty((B, 8, height, width), dtype=torch.float32, device="cuda") if self.tile is None \
+                else torch.zeros((B, 8, height, width), dtype=torch.float32, device="cuda")
+        p = self._params(width, height, cam, tf, out.stride())
+        keep = []
+        if self.view_times is not None:
+            vt = (C.c_float * B)(*[float(t) for t in self.view_times]); keep.append(vt)
+            p.view_times_host = C.cast(vt, C.c_void_p)
+        if self.collect_statistics:
+            self.last_step_counts = torch.zeros((B, height, width), dtype=torch.int32, device="cuda")
+            self.last_counters = torch.zeros(2, dtype=torch.int64, device="cuda")
+            p.step_count_dev = self.last_step_counts.data_ptr(); p.counters_dev = self.last_counters.data_ptr()
+        check(_lib.lib().fvsrn_render_dvr(net._h, C.byref(p), out.data_ptr(), _stream_ptr()))
+        return out
+
+    def extract_color(self, img: torch.Tensor) -> torch.Tensor:
+        """(B,8,H,W) -> (B,4,H,W), iimage_evaluator.cpp:26-135 (ChannelColor)."""
+        if img.dim() != 4 or img.shape[1] != 8:
+            raise RuntimeError("expected a (B,8,H,W) tensor")
+        img = img.contiguous()
+        out = torch.empty((img.shape[0], 4, img.shape[2], img.shape[3]), dtype=torch.float32, device=img.device)
+        check(_lib.lib().fvsrn_extract_color(img.data_ptr(), out.data_ptr(), img.shape[0], img.shape[2], img.shape[3], _stream_ptr()))
+        return out

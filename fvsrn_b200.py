@@ -1,0 +1,10 @@
+"""Loader shim: makes the package directory ``fv-srn_b200/`` importable as ``fvsrn_b200``."""
+import importlib.util as _u
+import os as _os
+import sys as _sys
+
+_dir = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "fv-srn_b200")
+_spec = _u.spec_from_file_location("fvsrn_b200", _os.path.join(_dir, "__init__.py"), submodule_search_locations=[_dir])
+_mod = _u.module_from_spec(_spec)
+_sys.modules["fvsrn_b200"] = _mod
+_spec.loader.exec_module(_mod)
