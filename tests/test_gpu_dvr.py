@@ -1,0 +1,169 @@
+"""GPU parity tests of the fused DVR frame (ImageEvaluatorSimple.render) — see test_gpu_parity.py for the tolerances."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import Golden, golden_names, psnr
+from test_gpu_parity import env, _volume, _evaluator, RGBA_TOL  # noqa: F401
+
+pytestmark = pytest.mark.gpu
+
+DVR_CASES = [n for n in golden_names() if Golden(n).has_dvr]
+
+
+def _check_steps(got_steps, want_steps, max_frac=0.02):
+    """Step counts must equal the oracle's; a ray may differ only when its termination test (alpha vs 1-1e-5, or the
+    density-min skip) is decided inside fp16 noise. Such rays are rare; they are counted and bounded."""
+    diff = got_steps != want_steps
+    assert diff.mean() <= max_frac, f"{diff.mean():.4f} of rays differ in step count"
+    return float(diff.mean())
+
+
+@pytest.mark.parametrize("name", DVR_CASES)
+def test_dvr_matches_oracle_and_reference(env, name, plume_tf):
+    g = Golden(name)
+    vol = _volume(env, g.volnet_bytes)
+    vol.current_network().set_time_and_ensemble(g.time, 0)
+    ie = _evaluator(env, vol, g.camera, plume_tf, g.dvr_step)
+    W = g.dvr_size
+    img = ie.render(W, W)
+    assert tuple(img.shape) == (1, 8, W, W) and img.dtype == env.torch.float32
+    img = img.cpu().numpy()
+    ref, steps, nvalid = env.oracle.render_dvr(g.net, width=W, height=W, camera=g.camera, fov_y=env.scenes.DEFAULT_FOV_Y,
+                                               stepsize=g.dvr_step, tf=plume_tf, time=g.time)
+    assert np.abs(img[:, :4] - ref[:, :4]).max() <= RGBA_TOL
+    assert psnr(img[0, :4], g.dvr) >= 50.0                              # vs the reference's PyTorch marcher
+    assert not img[:, 4:7].any()                                        # normals are zero for density networks
+    empty = ref[0, 3] == 0
+    assert np.isnan(img[0, 7][empty]).all()                             # depth 0/0, as the reference
+    np.testing.assert_allclose(img[0, 7][~empty], ref[0, 7][~empty], rtol=0, atol=5e-3)
+    _check_steps(ie.last_step_counts.cpu().numpy(), steps)
+    counters = ie.last_counters.cpu().numpy()
+    assert abs(int(counters[0]) - nvalid) <= 0.001 * nvalid and counters[1] >= counters[0]
+    color = ie.extract_color(env.torch.from_numpy(img).cuda()).cpu().numpy()
+    assert np.array_equal(np.nan_to_num(color), np.nan_to_num(img[:, :4]))
+
+
+def test_dvr_no_early_out_counts_are_exact(env, plume_tf):
+    """Without early termination the step count depends only on fp32 ray setup -> bit-exact vs the oracle."""
+    g = Golden("c3_relu_gauss")
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, g.camera, plume_tf, 1 / 100, early_out=False)
+    ie.render(40, 24)
+    _, steps, _ = env.oracle.render_dvr(g.net, width=40, height=24, camera=g.camera, fov_y=env.scenes.DEFAULT_FOV_Y,
+                                        stepsize=1 / 100, tf=plume_tf, early_out=False)
+    assert np.array_equal(ie.last_step_counts.cpu().numpy(), steps)
+
+
+def test_dvr_texture_tf_alpha_blend_density_range(env, plume_tf):
+    g = Golden("sine_48")
+    tex = env.scenes.texture_tf_from_piecewise(plume_tf, 256)
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, g.camera, tex, 1 / 80, tf_kind=1, min_density=0.2, max_density=0.9)
+    ie.ray_evaluator.blending.blendMode = env.pr.Blending.Alpha
+    img = ie.render(32, 32).cpu().numpy()
+    ref, steps, _ = env.oracle.render_dvr(g.net, width=32, height=32, camera=g.camera, fov_y=env.scenes.DEFAULT_FOV_Y, stepsize=1 / 80,
+                                          tf=tex, tf_kind=1, density_min=0.2, density_max=0.9, blend_mode=0)
+    assert np.abs(img[:, :4] - ref[:, :4]).max() <= RGBA_TOL
+    _check_steps(ie.last_step_counts.cpu().numpy(), steps)
+
+
+def test_dvr_rgbo_network_skips_tf(env):
+    g = Golden("rgbo_32")
+    cam = env.scenes.camera_reference_frame(**env.scenes.DEFAULT_CAMERA)
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, cam, None, 1 / 64, tf_kind=-1)
+    img = ie.render(32, 32).cpu().numpy()
+    ref, _, _ = env.oracle.render_dvr(g.net, width=32, height=32, camera=cam, fov_y=env.scenes.DEFAULT_FOV_Y, stepsize=1 / 64, tf=None)
+    assert np.abs(img[:, :4] - ref[:, :4]).max() <= RGBA_TOL
+
+
+def test_dvr_tiles_and_views_compose(env, plume_tf):
+    """Screen-tile sharding (C4) and view batches (C5): tiles rendered separately equal the full frame bit for bit."""
+    g = Golden("c1_relu_nerf")
+    cams = env.scenes.camera_sweep(3)
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, cams, plume_tf, 1 / 64)
+    W, H = 64, 40
+    full = ie.render(W, H).cpu().numpy()
+    assert full.shape == (3, 8, H, W)
+    acc = np.zeros_like(full)
+    for (x0, y0, w, h) in [(0, 0, 24, 40), (24, 0, 40, 16), (24, 16, 40, 24)]:
+        ie.tile = (x0, y0, w, h)
+        part = ie.render(W, H).cpu().numpy()
+        acc[:, :, y0:y0 + h, x0:x0 + w] = part[:, :, y0:y0 + h, x0:x0 + w]
+    assert np.array_equal(np.nan_to_num(acc), np.nan_to_num(full))
+    ie.tile = None
+    for b in range(3):
+        ie.camera.set_parameters(env.torch.from_numpy(cams[b:b + 1]))
+        one = ie.render(W, H).cpu().numpy()
+        assert np.array_equal(np.nan_to_num(one[0]), np.nan_to_num(full[b]))
+
+
+def test_dvr_per_view_times(env, plume_tf):
+    g = Golden("c5_time")
+    cams = env.scenes.camera_sweep(4)
+    times = [0.0, 0.5, 1.25, 2.0]
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, cams, plume_tf, 1 / 64)
+    ie.view_times = times
+    img = ie.render(32, 32).cpu().numpy()
+    for b, t in enumerate(times):
+        ref, _, _ = env.oracle.render_dvr(g.net, width=32, height=32, camera=cams[b:b + 1], fov_y=env.scenes.DEFAULT_FOV_Y,
+                                          stepsize=1 / 64, tf=plume_tf, time=t)
+        assert np.abs(img[b, :4] - ref[0, :4]).max() <= RGBA_TOL, (b, t)
+
+
+def test_dvr_supersampling_matches_oracle(env, plume_tf):
+    g = Golden("c3_relu_gauss")
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, g.camera, plume_tf, 1 / 64)
+    ie.samples_per_pixel = 4
+    img = ie.render(24, 24).cpu().numpy()
+    ref, _, _ = env.oracle.render_dvr(g.net, width=24, height=24, camera=g.camera, fov_y=env.scenes.DEFAULT_FOV_Y, stepsize=1 / 64,
+                                      tf=plume_tf, spp=4)
+    assert np.abs(img[:, :4] - ref[:, :4]).max() <= RGBA_TOL
+    ie.samples_per_pixel = 3
+    with pytest.raises(RuntimeError, match="square"):
+        ie.render(24, 24)
+
+
+def test_dvr_host_entry_point_and_strides(env, plume_tf):
+    g = Golden("c1_relu_nerf")
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, g.camera, plume_tf, 1 / 64)
+    W = H = 48
+    dev = ie.render(W, H).cpu().numpy()
+    net = vol.current_network()
+    cam = np.ascontiguousarray(g.camera, np.float32); tf = np.ascontiguousarray(plume_tf, np.float32)
+    p = ie._params(W, H, env.torch.from_numpy(cam), env.torch.from_numpy(tf), (8 * W * H, W * H, W, 1))
+    p.camera_matrix_dev = cam.ctypes.data; p.tf_dev = tf.ctypes.data
+    out = np.empty((1, 8, H, W), np.float32)
+    env.lib.check(env.lib.lib().fvsrn_render_dvr_host(net._h, C.byref(p), out.ctypes.data, None))
+    assert np.array_equal(np.nan_to_num(out), np.nan_to_num(dev))
+    # channel-last output tensor: any stride layout is accepted (renderer/pytorch_utils.h:39-43)
+    buf = env.torch.empty((1, H, W, 8), device="cuda").permute(0, 3, 1, 2)
+    got = ie.render(W, H, out=buf)
+    assert got.data_ptr() == buf.data_ptr()
+    assert np.array_equal(np.nan_to_num(got.cpu().numpy()), np.nan_to_num(dev))
+
+
+def test_full_size_properties(env, plume_tf):
+    """BASELINE C3 size (1024^2, step 1/512): properties that need no oracle run — determinism, tile composition,
+    alpha in [0,1], empty pixels exactly where the ray misses the box, useful <= executed samples."""
+    net = env.scenes.make_network(hidden=32, num_layers=4, grid_res=32, activation="ReLU", seed=42, last_gain=6.0)
+    cam = env.scenes.camera_reference_frame(**env.scenes.DEFAULT_CAMERA)
+    vol = _volume(env, net)
+    ie = _evaluator(env, vol, cam, plume_tf, 1 / 512)
+    a = ie.render(1024, 1024).cpu().numpy()
+    c1 = ie.last_counters.cpu().numpy().copy()
+    b = ie.render(1024, 1024).cpu().numpy()
+    assert np.array_equal(np.nan_to_num(a), np.nan_to_num(b))
+    assert a[:, 3].min() >= 0 and a[:, 3].max() <= 1.0 and np.isfinite(a[:, :4]).all()
+    steps = ie.last_step_counts.cpu().numpy()
+    assert ((steps == 0) == (a[:, 3] == 0)).mean() > 0.999 and steps.max() <= 887
+    assert 0 < c1[0] <= c1[1] and c1[0] == steps.sum()
+    ie.tile = (512, 256, 256, 512)
+    t = ie.render(1024, 1024).cpu().numpy()
+    assert np.array_equal(np.nan_to_num(t[:, :, 256:768, 512:768]), np.nan_to_num(a[:, :, 256:768, 512:768]))

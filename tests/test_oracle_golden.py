@@ -1,0 +1,63 @@
+"""
+Pins the CPU oracle (oracle/fvsrn_oracle.c) against the fixtures generated from the REFERENCE's own PyTorch code
+(applications/volnet/network.py and raytracing.py, see tests/golden/make_golden.py). CPU only.
+Mirrors unittests/testSRN.cpp:327-432: 256 uniform positions, |kernel-semantics - torch| < 1e-2.
+"""
+import numpy as np
+import pytest
+
+from conftest import Golden, golden_names, psnr
+
+import oracle
+from fvsrn_b200 import scenes, volnet
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_oracle_points_match_reference_network(name):
+    g = Golden(name)
+    o16 = oracle.evaluate(g.net, g.positions, time=g.time)
+    o32 = oracle.evaluate(g.net, g.positions, time=g.time, fp32=True)
+    assert np.isfinite(o16).all() and np.isfinite(o32).all()           # testSRN.cpp:399-403 (no NaN)
+    # 'world' = unclamped output of the reference module (network.py:204-235) = IVolumeInterpolation::evaluate
+    assert np.abs(o16 - g.world).max() < 1e-2                            # the reference's own tolerance, testSRN.cpp:408-411
+    assert np.abs(o32 - g.world).max() < 6e-3                            # fp32 math on fp16-rounded weights / grid
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names() if Golden(n).has_dvr])
+def test_oracle_dvr_matches_reference_raymarcher(name, plume_tf):
+    g = Golden(name)
+    for fp32 in (True, False):
+        img, steps, nvalid = oracle.render_dvr(g.net, width=g.dvr_size, height=g.dvr_size, camera=g.camera,
+                                               fov_y=scenes.DEFAULT_FOV_Y, stepsize=g.dvr_step, tf=plume_tf, time=g.time, fp32=fp32)
+        assert psnr(img[0, :4], g.dvr) >= 50.0, "north_star: PSNR >= 50 dB against the reference's PyTorch render"
+        assert int(steps.sum()) == nvalid
+        assert np.isnan(img[0, 7][img[0, 3] == 0]).all()                 # depth = 0/0 for empty pixels, as the reference
+
+
+def test_oracle_is_deterministic_and_tile_consistent(plume_tf):
+    g = Golden("c1_relu_nerf")
+    kw = dict(width=32, height=32, camera=g.camera, fov_y=scenes.DEFAULT_FOV_Y, stepsize=1 / 64, tf=plume_tf)
+    full, steps, _ = oracle.render_dvr(g.net, **kw)
+    again, steps2, _ = oracle.render_dvr(g.net, **kw)
+    assert np.array_equal(np.nan_to_num(full), np.nan_to_num(again)) and np.array_equal(steps, steps2)
+    part, psteps, _ = oracle.render_dvr(g.net, tile=(8, 16, 16, 8), **kw)
+    assert np.array_equal(np.nan_to_num(part[:, :, 16:24, 8:24]), np.nan_to_num(full[:, :, 16:24, 8:24]))
+    assert np.array_equal(psteps[:, 16:24, 8:24], steps[:, 16:24, 8:24])
+    assert not part[:, :4, :16].any()
+
+
+def test_oracle_early_out_only_removes_steps(plume_tf):
+    g = Golden("c3_snakealt_nerf")
+    kw = dict(width=24, height=24, camera=g.camera, fov_y=scenes.DEFAULT_FOV_Y, stepsize=1 / 96, tf=plume_tf)
+    a, sa, _ = oracle.render_dvr(g.net, early_out=True, alpha_early_out=0.9, **kw)
+    b, sb, _ = oracle.render_dvr(g.net, early_out=False, **kw)
+    assert (sa <= sb).all() and (sa < sb).any()
+    assert a[0, 3].max() < 1.0 and (a[0, 3][sa[0] < sb[0]] >= 0.9).all()
+
+
+def test_volnet_python_roundtrip():
+    """testSRN.cpp:413-430: save -> load preserves every field."""
+    for name in golden_names():
+        g = Golden(name)
+        again = volnet.dumps(volnet.loads(g.volnet_bytes))
+        assert again == g.volnet_bytes
