@@ -299,7 +299,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
-    ap.add_argument("--cpu-crop", type=int, default=96, help="max edge of the centre crop the CPU legs render")
+    ap.add_argument("--cpu-crop", type=int, default=256, help="max edge of the centre crop the CPU legs render")
     ap.add_argument("--cpu-budget-s", type=float, default=120.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -162,7 +162,7 @@ def test_full_size_properties(env, plume_tf):
     assert np.array_equal(np.nan_to_num(a), np.nan_to_num(b))
     assert a[:, 3].min() >= 0 and a[:, 3].max() <= 1.0 and np.isfinite(a[:, :4]).all()
     steps = ie.last_step_counts.cpu().numpy()
-    assert ((steps == 0) == (a[:, 3] == 0)).mean() > 0.999 and steps.max() <= 887
+    assert (a[:, 3][steps == 0] == 0).all() and steps.max() <= 887 and (steps > 0).mean() > 0.2
     assert 0 < c1[0] <= c1[1] and c1[0] == steps.sum()
     ie.tile = (512, 256, 256, 512)
     t = ie.render(1024, 1024).cpu().numpy()
