@@ -71,6 +71,94 @@ __device__ __forceinline__ float4 tf_texture(const float* tf, int R, float d) { 
                        v0[3] + df * (v1[3] - v0[3]));
 }
 
+struct Ray { float3 eye, dir; float tmin, tmax; };
+struct CamFrame { float3 eye, right, up, front; float tan_x, tan_y; };
+
+// camera frame, reference renderer_camera.cuh:34-52
+__device__ __forceinline__ CamFrame load_camera(const DvrParams& D, int b) {
+    CamFrame c;
+    const float* cm = D.cam + (size_t)b * 9;
+    c.eye = make_float3(__ldg(cm + 0), __ldg(cm + 1), __ldg(cm + 2));
+    c.right = make_float3(__ldg(cm + 3), __ldg(cm + 4), __ldg(cm + 5));
+    c.up = make_float3(__ldg(cm + 6), __ldg(cm + 7), __ldg(cm + 8));
+    // explicit rounding order (no compiler FMA contraction) so that the CPU oracle reproduces ray setup bit for bit
+    c.front = make_float3(__fmaf_rn(c.up.y, c.right.z, -__fmul_rn(c.up.z, c.right.y)),
+                          __fmaf_rn(c.up.z, c.right.x, -__fmul_rn(c.up.x, c.right.z)),
+                          __fmaf_rn(c.up.x, c.right.y, -__fmul_rn(c.up.y, c.right.x))); // cross(up, right)
+    c.tan_y = D.tan_half_fovy; c.tan_x = __fmul_rn(c.tan_y, D.aspect);
+    return c;
+}
+
+// ray through pixel (x,y), sub-sample s (reference renderer_image_evaluator_simple.cuh:84-86, renderer_camera.cuh:41-51)
+// and its box interval (renderer_utils.cuh:91-105, renderer_ray_evaluation_stepping_dvr.cuh:66-71)
+__device__ __forceinline__ Ray make_ray(const DvrParams& D, const CamFrame& c, int x, int y, int s, float3 bmin, float3 bsize) {
+    float nx = float(x), ny = float(y);
+    if (D.spp > 1) {                // deterministic stratified sub-pixel offsets
+        nx = __fadd_rn(nx, __fsub_rn(__fdiv_rn(float(s % D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
+        ny = __fadd_rn(ny, __fsub_rn(__fdiv_rn(float(s / D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
+    }
+    const float ndc_x = __fsub_rn(__fdiv_rn(2.f * (nx + 0.5f), float(D.W)), 1.f);
+    const float ndc_y = __fsub_rn(__fdiv_rn(2.f * (ny + 0.5f), float(D.H)), 1.f);
+    const float sx = __fmul_rn(ndc_x, c.tan_x), sy = __fmul_rn(ndc_y, c.tan_y);
+    float3 dir = make_float3(__fmaf_rn(sy, c.up.x, __fmaf_rn(sx, c.right.x, c.front.x)),
+                             __fmaf_rn(sy, c.up.y, __fmaf_rn(sx, c.right.y, c.front.y)),
+                             __fmaf_rn(sy, c.up.z, __fmaf_rn(sx, c.right.z, c.front.z)));
+    const float len2 = __fmaf_rn(dir.z, dir.z, __fmaf_rn(dir.y, dir.y, __fmul_rn(dir.x, dir.x)));
+    const float inv_len = __fdiv_rn(1.0f, __fsqrt_rn(len2));
+    dir.x = __fmul_rn(dir.x, inv_len); dir.y = __fmul_rn(dir.y, inv_len); dir.z = __fmul_rn(dir.z, inv_len);
+    const float3 eye = c.eye;
+    const float ix = __fdiv_rn(1.0f, dir.x), iy = __fdiv_rn(1.0f, dir.y), iz = __fdiv_rn(1.0f, dir.z);
+    const float t1 = __fmul_rn(__fsub_rn(bmin.x, eye.x), ix), t2 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.x, bsize.x), eye.x), ix);
+    const float t3 = __fmul_rn(__fsub_rn(bmin.y, eye.y), iy), t4 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.y, bsize.y), eye.y), iy);
+    const float t5 = __fmul_rn(__fsub_rn(bmin.z, eye.z), iz), t6 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.z, bsize.z), eye.z), iz);
+    Ray r; r.eye = eye; r.dir = dir;
+    r.tmin = fmaxf(fmaxf(fmaxf(fminf(t1, t2), fminf(t3, t4)), fminf(t5, t6)), 0.f);
+    r.tmax = fminf(fminf(fminf(fmaxf(t1, t2), fmaxf(t3, t4)), fmaxf(t5, t6)), FLT_MAX);
+    return r;
+}
+
+// network output -> colour + absorption of one sample (TF or colour network), reference
+// renderer_ray_evaluation_stepping_dvr.cuh:100-140, renderer_volume_tensorcores.cuh:1054-1072, 1149-1158
+__device__ __forceinline__ float4 shade_sample(const NetParams& P, const DvrParams& D, const float* tfp, const float (&o)[4]) {
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (P.output_mode < D_OUT_RGBO) {
+        const float value = (P.output_mode == D_OUT_DENSITY) ? sigmoidf_(o[0]) : o[0];
+        if (value >= D.dmin) {
+            const float d2 = fminf(fmaxf((value - D.dmin) * D.inv_range, 0.f), 1.f);
+            if (D.tf_kind == 0) c = tf_piecewise(tfp, D.tf_R, d2);
+            else if (D.tf_kind == 1) c = tf_texture(tfp, D.tf_R, d2);
+            else c = make_float4(d2 * tfp[1], d2 * tfp[1], d2 * tfp[1], d2 * tfp[0]);
+            c.w *= D.stepsize;
+        }
+    } else {    // colour network, SKIP_TRANSFER_FUNCTION path
+        if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
+        else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
+        c.w *= D.stepsize;
+    }
+    return c;
+}
+// front-to-back compositing, reference renderer_blending.cuh:36-51 (normal is zero for density networks)
+__device__ __forceinline__ void blend_sample(const DvrParams& D, float4 c, float t, float4& acc, float& acc_depth) {
+    if (c.w > 0.f) {
+        const float a = (D.blend_mode == 1) ? 1.f - __expf(-c.w) : fminf(1.f, c.w);
+        const float k = (1.f - acc.w) * a;
+        acc.x += k * c.x; acc.y += k * c.y; acc.z += k * c.z;
+        acc_depth += k * t;
+        acc.w += k;
+    }
+}
+// pixel write, reference renderer_image_evaluator_simple.cuh:101-124
+__device__ __forceinline__ void write_pixel(const DvrParams& D, int b, int x, int y, float4 pix_color, float pix_depth, int last_steps) {
+    const float inv_s = 1.f / float(D.spp);
+    float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
+    const float depth = pix_depth / pix_color.w;    // NaN for empty pixels, as in the reference
+    o[0 * D.sc] = pix_color.x * inv_s; o[1 * D.sc] = pix_color.y * inv_s; o[2 * D.sc] = pix_color.z * inv_s;
+    o[3 * D.sc] = pix_color.w * inv_s;
+    o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
+    o[7 * D.sc] = depth;
+    if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
+}
+
 template <int H16, int GC16, bool DIR>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
@@ -94,8 +182,6 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
     const float3 bmin = make_float3(P.box_min[0], P.box_min[1], P.box_min[2]);
     const float3 bsize = make_float3(P.box_size[0], P.box_size[1], P.box_size[2]);
     const float3 binv = make_float3(__fdiv_rn(1.f, bsize.x), __fdiv_rn(1.f, bsize.y), __fdiv_rn(1.f, bsize.z));
-    const bool is_rgbo = P.output_mode >= D_OUT_RGBO;
-
     unsigned long long n_valid = 0, n_exec = 0;
     for (;;) {
         int tile = 0;
@@ -112,45 +198,16 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
         const bool in_img = (x < D.x0 + D.tw) && (y < D.y0 + D.th);
         const float* tfp = (D.tf_batch == 1) ? stf : (D.tf + (size_t)b * tf_floats);
 
-        // camera frame, reference renderer_camera.cuh:34-52
-        const float* cm = D.cam + (size_t)b * 9;
-        const float3 eye = make_float3(__ldg(cm + 0), __ldg(cm + 1), __ldg(cm + 2));
-        const float3 right = make_float3(__ldg(cm + 3), __ldg(cm + 4), __ldg(cm + 5));
-        const float3 up = make_float3(__ldg(cm + 6), __ldg(cm + 7), __ldg(cm + 8));
-        // explicit rounding order (no compiler FMA contraction) so that the CPU oracle reproduces ray setup bit for bit
-        const float3 front = make_float3(__fmaf_rn(up.y, right.z, -__fmul_rn(up.z, right.y)),
-                                         __fmaf_rn(up.z, right.x, -__fmul_rn(up.x, right.z)),
-                                         __fmaf_rn(up.x, right.y, -__fmul_rn(up.y, right.x))); // cross(up, right)
-        const float tan_y = D.tan_half_fovy, tan_x = __fmul_rn(tan_y, D.aspect);
+        const CamFrame cf = load_camera(D, b);
 
         float4 pix_color = make_float4(0.f, 0.f, 0.f, 0.f);
         float pix_depth = 0.f;
         int last_steps = 0;
         for (int s = 0; s < D.spp; ++s) {   // warp-uniform trip count
-            float nx = float(x), ny = float(y);
-            if (D.spp > 1) {                // deterministic stratified sub-pixel offsets
-                nx = __fadd_rn(nx, __fsub_rn(__fdiv_rn(float(s % D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
-                ny = __fadd_rn(ny, __fsub_rn(__fdiv_rn(float(s / D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
-            }
-            const float ndc_x = __fsub_rn(__fdiv_rn(2.f * (nx + 0.5f), float(D.W)), 1.f);   // reference renderer_image_evaluator_simple.cuh:84-86
-            const float ndc_y = __fsub_rn(__fdiv_rn(2.f * (ny + 0.5f), float(D.H)), 1.f);
-            const float sx = __fmul_rn(ndc_x, tan_x), sy = __fmul_rn(ndc_y, tan_y);
-            float3 dir = make_float3(__fmaf_rn(sy, up.x, __fmaf_rn(sx, right.x, front.x)),
-                                     __fmaf_rn(sy, up.y, __fmaf_rn(sx, right.y, front.y)),
-                                     __fmaf_rn(sy, up.z, __fmaf_rn(sx, right.z, front.z)));
-            const float len2 = __fmaf_rn(dir.z, dir.z, __fmaf_rn(dir.y, dir.y, __fmul_rn(dir.x, dir.x)));
-            const float inv_len = __fdiv_rn(1.0f, __fsqrt_rn(len2));
-            dir.x = __fmul_rn(dir.x, inv_len); dir.y = __fmul_rn(dir.y, inv_len); dir.z = __fmul_rn(dir.z, inv_len);
-            // AABB, reference renderer_utils.cuh:91-105
-            const float ix = __fdiv_rn(1.0f, dir.x), iy = __fdiv_rn(1.0f, dir.y), iz = __fdiv_rn(1.0f, dir.z);
-            const float t1 = __fmul_rn(__fsub_rn(bmin.x, eye.x), ix), t2 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.x, bsize.x), eye.x), ix);
-            const float t3 = __fmul_rn(__fsub_rn(bmin.y, eye.y), iy), t4 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.y, bsize.y), eye.y), iy);
-            const float t5 = __fmul_rn(__fsub_rn(bmin.z, eye.z), iz), t6 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.z, bsize.z), eye.z), iz);
-            float tmin = fmaxf(fmaxf(fminf(t1, t2), fminf(t3, t4)), fminf(t5, t6));
-            float tmax = fminf(fminf(fmaxf(t1, t2), fmaxf(t3, t4)), fmaxf(t5, t6));
-            tmin = fmaxf(tmin, 0.f);
-            tmax = fminf(tmax, FLT_MAX);
-            if (!in_img) tmax = -1.f;       // lanes outside the image never become valid
+            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize);
+            const float3 eye = r.eye, dir = r.dir;
+            const float tmin = r.tmin;
+            const float tmax = in_img ? r.tmax : -1.f;  // lanes outside the image never become valid
 
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             float acc_depth = 0.f;
@@ -172,44 +229,14 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
                 Net::forward(P, sblob_addr, stage, ac, px, py, pz, dir.x, dir.y, dir.z, o);
                 if (!valid) continue;
                 ++steps;
-                float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (!is_rgbo) {
-                    const float value = (P.output_mode == D_OUT_DENSITY) ? sigmoidf_(o[0]) : o[0];
-                    if (value >= D.dmin) {
-                        const float d2 = fminf(fmaxf((value - D.dmin) * D.inv_range, 0.f), 1.f);
-                        if (D.tf_kind == 0) c = tf_piecewise(tfp, D.tf_R, d2);
-                        else if (D.tf_kind == 1) c = tf_texture(tfp, D.tf_R, d2);
-                        else c = make_float4(d2 * tfp[1], d2 * tfp[1], d2 * tfp[1], d2 * tfp[0]);
-                        c.w *= D.stepsize;
-                    }
-                } else {    // colour network, SKIP_TRANSFER_FUNCTION path (:103-109) + output parametrisation (:1054-1072)
-                    if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
-                    else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
-                    c.w *= D.stepsize;
-                }
-                if (c.w > 0.f) {    // blending, reference renderer_blending.cuh:36-51 (normal is zero for density networks)
-                    const float a = (D.blend_mode == 1) ? 1.f - __expf(-c.w) : fminf(1.f, c.w);
-                    const float k = (1.f - acc.w) * a;
-                    acc.x += k * c.x; acc.y += k * c.y; acc.z += k * c.z;
-                    acc_depth += k * t;
-                    acc.w += k;
-                }
+                blend_sample(D, shade_sample(P, D, tfp, o), t, acc, acc_depth);
             }
             n_valid += steps;
             last_steps = steps;
             pix_color.x += acc.x; pix_color.y += acc.y; pix_color.z += acc.z; pix_color.w += acc.w;
             pix_depth += acc_depth * acc.w;     // reference renderer_image_evaluator_simple.cuh:101-103
         }
-        if (in_img) {   // reference :106-124
-            const float inv_s = 1.f / float(D.spp);
-            float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
-            const float depth = pix_depth / pix_color.w;    // NaN for empty pixels, as in the reference
-            o[0 * D.sc] = pix_color.x * inv_s; o[1 * D.sc] = pix_color.y * inv_s; o[2 * D.sc] = pix_color.z * inv_s;
-            o[3 * D.sc] = pix_color.w * inv_s;
-            o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
-            o[7 * D.sc] = depth;
-            if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
-        }
+        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps);
     }
     if (D.counters) {
         for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);

@@ -2,7 +2,7 @@
 // Replaces the run-time NVRTC assembly of reference renderer/kernel_loader.cpp:197-273 by ahead-of-time
 // sm_100a instantiations selected from the network's shape (hidden width, latent channels, direction input).
 #pragma once
-#include "kernels.cuh"
+#include "kernels_tc.cuh"
 #include <cuda_runtime.h>
 
 namespace fvsrn {
@@ -13,11 +13,12 @@ struct LaunchCfg {
     int grid = 0;            // filled by the launcher
     int smem = 0;
     int regs = 0;
+    int threads = 0;
     int query_only = 0;      // 1: only fill the fields above, do not launch
     long long max_blocks = 0; // upper bound on useful blocks (0 = none)
 };
 
-enum { KIND_DVR = 0, KIND_EVAL = 1 };
+enum { KIND_DVR = 0, KIND_EVAL = 1, KIND_DVR_TC = 2, KIND_EVAL_TC = 3 };  // _TC: tcgen05/TMEM kernels (kernels_tc.cuh)
 
 // kp points to a DvrParams (KIND_DVR) or EvalParams (KIND_EVAL)
 typedef cudaError_t (*launch_fn)(int kind, int gc16, int dir, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s);
@@ -30,27 +31,34 @@ cudaError_t launch_h8(int, int, int, const NetParams&, const void*, LaunchCfg*, 
 template <int H16, int GC16, bool DIR>
 cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s) {
     using Net = Srn<H16, GC16, DIR>;
+    const bool is_tc = kind >= KIND_DVR_TC, is_dvr = (kind == KIND_DVR || kind == KIND_DVR_TC);
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
-    const int smem = blob + (kind == KIND_DVR ? kTfSmemFloats * 4 : 0) + kWarpsPerBlock * Net::STAGE_BYTES;
-    const void* fn = (kind == KIND_DVR) ? (const void*)dvr_kernel<H16, GC16, DIR> : (const void*)eval_kernel<H16, GC16, DIR>;
+    const int threads = is_tc ? kTcThreads : kWarpsPerBlock * 32;
+    const int smem = blob + (is_dvr ? kTfSmemFloats * 4 : 0) + (is_tc ? int(sizeof(TcShared)) : kWarpsPerBlock * Net::STAGE_BYTES);
+    const void* fn = kind == KIND_DVR ? (const void*)dvr_kernel<H16, GC16, DIR>
+                   : kind == KIND_EVAL ? (const void*)eval_kernel<H16, GC16, DIR>
+                   : kind == KIND_DVR_TC ? (const void*)dvr_tc_kernel<H16, GC16, DIR> : (const void*)eval_tc_kernel<H16, GC16, DIR>;
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     int bps = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, kWarpsPerBlock * 32, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, threads, smem);
     if (e != cudaSuccess) return e;
     if (bps < 1) return cudaErrorLaunchOutOfResources;
+    if (is_tc) bps = min(bps, 512 / SrnTc<H16, GC16, DIR>::TMEM_COLS);   // TMEM: 512 columns per SM
     cudaFuncAttributes fa;
     e = cudaFuncGetAttributes(&fa, fn);
     if (e != cudaSuccess) return e;
     long long grid = (long long)bps * cfg->sm_count;
     if (cfg->max_blocks > 0 && grid > cfg->max_blocks) grid = cfg->max_blocks;
     if (grid < 1) grid = 1;
-    cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = fa.numRegs;
+    cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = fa.numRegs; cfg->threads = threads;
     if (cfg->query_only) return cudaSuccess;
-    if (kind == KIND_DVR)
-        dvr_kernel<H16, GC16, DIR><<<int(grid), kWarpsPerBlock * 32, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
-    else
-        eval_kernel<H16, GC16, DIR><<<int(grid), kWarpsPerBlock * 32, smem, s>>>(P, *static_cast<const EvalParams*>(kp));
+    switch (kind) {
+        case KIND_DVR: dvr_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp)); break;
+        case KIND_EVAL: eval_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp)); break;
+        case KIND_DVR_TC: dvr_tc_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp)); break;
+        default: eval_tc_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp)); break;
+    }
     return cudaGetLastError();
 }
 

@@ -184,19 +184,14 @@ struct Srn {
         }
     }
 
-    // Evaluate the network for the sample owned by this lane. All 32 lanes must call (warp-synchronous).
-    // (px,py,pz) is the position in the unit cube, (dx,dy,dz) the ray direction (DIR only).
-    // out[0..3]: raw last-layer outputs (before the output parametrisation).
-    static __device__ __forceinline__ void forward(const NetParams& P, uint32_t sblob, uint4* stage, const ActConst& ac,
-                                                   float px, float py, float pz, float dx, float dy, float dz,
-                                                   float (&out)[4]) {
-        const int lane = threadIdx.x & 31;
-        __syncwarp();
-        // ---------------- layer-0 inputs in registers: [px,py,pz,time|0,(dx,dy,dz,0),cos x NF,sin x NF,latent x GC]
-        uint32_t row[K0 / 2];
+    // Layer-0 inputs of the sample owned by this thread, packed fp16x2:
+    // [px,py,pz,time|0,(dx,dy,dz,0),cos x NF,sin x NF,latent x GC]   (reference :768-808, 839-910)
+    // ch3_one: put 1.0 into channel 3 when the network has no time input (the tcgen05 path folds the bias there).
+    static __device__ __forceinline__ void build_row(const NetParams& P, uint32_t sblob, float px, float py, float pz,
+                                                     float dx, float dy, float dz, bool ch3_one, uint32_t (&row)[K0 / 2]) {
         const __half hx = __float2half_rn(px), hy = __float2half_rn(py), hz = __float2half_rn(pz);
         row[0] = h2u(__halves2half2(hx, hy));
-        row[1] = h2u(__halves2half2(hz, P.has_time ? __float2half_rn(P.time_value) : __float2half_rn(0.f)));
+        row[1] = h2u(__halves2half2(hz, P.has_time ? __float2half_rn(P.time_value) : __float2half_rn(ch3_one ? 1.f : 0.f)));
         __half2 d2x, d2y, d2z;
         if (DIR) {
             const __half hdx = __float2half_rn(dx), hdy = __float2half_rn(dy), hdz = __float2half_rn(dz);
@@ -271,6 +266,18 @@ struct Srn {
                 for (int j = 0; j < 8; ++j) row[H / 2 + g * 8 + j] = h2u(acc[j]);
             }
         }
+    }
+
+    // Evaluate the network for the sample owned by this lane. All 32 lanes must call (warp-synchronous).
+    // (px,py,pz) is the position in the unit cube, (dx,dy,dz) the ray direction (DIR only).
+    // out[0..3]: raw last-layer outputs (before the output parametrisation).
+    static __device__ __forceinline__ void forward(const NetParams& P, uint32_t sblob, uint4* stage, const ActConst& ac,
+                                                   float px, float py, float pz, float dx, float dy, float dz,
+                                                   float (&out)[4]) {
+        const int lane = threadIdx.x & 31;
+        __syncwarp();
+        uint32_t row[K0 / 2];
+        build_row(P, sblob, px, py, pz, dx, dy, dz, false, row);
         // ---------------- stage the 32 x K0 tile (row = lane) and pick it up as A fragments
 #pragma unroll
         for (int j = 0; j < ROW_CHUNKS; ++j)
