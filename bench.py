@@ -170,6 +170,7 @@ def run_b200(args):
     net, tf_np, scenes = make_scene(args.workload)
     S = w["size"]
     sn = pr.SceneNetwork.from_bytes(volnet.dumps(net))
+    sn.kernel_mode = args.kernel_mode
     vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
     ie = pr.ImageEvaluatorSimple(); ie.volume = vol
     cams = scenes.camera_sweep(world)                       # view-sharded multi-view batch: one view per rank per step
@@ -267,7 +268,7 @@ def run_b200(args):
                     "h2d_bytes_per_step": int(host_cam.numel() * 4 + host_tf.numel() * 4), "d2h_bytes_per_step": int(host_img.numel() * 4)},
             "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
-                         "traffic": None, "kernel": "dvr_kernel", "flop_per_sample": w["flop"], "peak_source": pk["source"] + ", burst bf16",
+                         "traffic": None, "kernel": "dvr_tc_kernel (tcgen05.mma + TMEM)" if args.kernel_mode == "tcgen05" else "dvr_kernel (mma.sync)", "flop_per_sample": w["flop"], "peak_source": pk["source"] + ", burst bf16",
                          "executed_frac": (cnt[1] * w["flop"]) / (kernel_ms * 1e-3) / 1e12 / pk["tflops"], "kernel_ms": kernel_ms / args.steps},
             "clocks": clocks, "wall_s_timed_region": t_wall,
         }
@@ -302,6 +303,8 @@ def main():
     ap.add_argument("--cpu-crop", type=int, default=256, help="max edge of the centre crop the CPU legs render")
     ap.add_argument("--cpu-budget-s", type=float, default=120.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel-mode", default="tcgen05", choices=["tcgen05", "mma_sync"],
+                    help="tcgen05: tcgen05.mma/TMEM kernel (default); mma_sync: reference-precision fp16-accumulate kernel")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

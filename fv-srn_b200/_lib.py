@@ -14,7 +14,7 @@ SYMBOLS = [
     "fvsrn_network_set_output_mode", "fvsrn_network_add_layer", "fvsrn_network_set_latent_grid_layout",
     "fvsrn_network_set_time_grid", "fvsrn_network_set_ensemble_grid", "fvsrn_network_set_box", "fvsrn_network_get_box",
     "fvsrn_network_valid", "fvsrn_network_num_parameters", "fvsrn_network_compute_max_warps",
-    "fvsrn_network_set_time_and_ensemble", "fvsrn_network_get_info", "fvsrn_network_prepare",
+    "fvsrn_network_set_time_and_ensemble", "fvsrn_network_get_info", "fvsrn_network_set_kernel_mode", "fvsrn_network_get_kernel_mode", "fvsrn_network_prepare",
     "fvsrn_network_clear_gpu_resources", "fvsrn_evaluate", "fvsrn_evaluate_host", "fvsrn_render_dvr",
     "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_query",
 ]
@@ -83,6 +83,8 @@ def lib():
         "fvsrn_network_compute_max_warps": [vp, i, i],
         "fvsrn_network_set_time_and_ensemble": [vp, f, i],
         "fvsrn_network_get_info": [vp, C.POINTER(NetworkInfo)],
+        "fvsrn_network_set_kernel_mode": [vp, i],
+        "fvsrn_network_get_kernel_mode": [vp],
         "fvsrn_network_prepare": [vp, i, vp],
         "fvsrn_network_clear_gpu_resources": [vp],
         "fvsrn_evaluate": [vp, vp, vp, vp, i64, vp],

@@ -7,6 +7,7 @@
 #include "network.hpp"
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -32,6 +33,10 @@ struct fvsrn_network {
     int device = -1, sm_count = 0;
     uint4* d_blob = nullptr; int blob_bytes = 0;
     int off_w0 = 0, off_wh = 0, off_wlast = 0, off_bias = 0, off_fourier = 0;
+    // tcgen05 path: K-major UMMA weight tiles (+ bias chunks) and the Fourier matrix
+    uint4* d_tc_blob = nullptr; int tc_blob_bytes = 0;
+    int tc_off_w0 = 0, tc_off_wh = 0, tc_off_wlast = 0, tc_off_fourier = 0;
+    int kernel_mode = FVSRN_KERNEL_TCGEN05;
     int H16 = 0, GC16 = 0, dir = 0, num_hidden = 0, activation = 0; float act_param = 1.f;
     std::vector<DeviceGrid> d_time, d_ens;
     unsigned int* d_tile_counter = nullptr;   // ring of work-queue counters (one per launch in flight)
@@ -45,6 +50,8 @@ namespace {
 void release_gpu(fvsrn_network* h) {
     if (h->device >= 0) cudaSetDevice(h->device);
     if (h->d_blob) cudaFree(h->d_blob);
+    if (h->d_tc_blob) cudaFree(h->d_tc_blob);
+    h->d_tc_blob = nullptr;
     for (auto& g : h->d_time) if (g.data) cudaFree(g.data);
     for (auto& g : h->d_ens) if (g.data) cudaFree(g.data);
     if (h->d_tile_counter) cudaFree(h->d_tile_counter);
@@ -134,6 +141,41 @@ void build_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
     h->blob_bytes = int(blob.size());
 }
 
+// Blob of the tcgen05 path (see srn_tc.cuh / kernels_tc.cuh): per layer the B operand W[n][k] as K-major, no-swizzle
+// UMMA tiles. A K=16 instruction step reads two K chunks of 8; a chunk holds N/8 core matrices (8 rows n x 16 B of k)
+// back to back, so LBO (K direction) = (N/8)*128 B and SBO (N direction) = 128 B. After the data steps every layer
+// carries one more step whose k=0 column is the bias (multiplied by the constant "ones" A chunk). Layer 0 of a network
+// without time input has its bias in input column 3 instead (the row builder writes 1.0 there).
+void build_tc_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
+    const Network& n = h->net;
+    const int H = 16 * h->H16, GC = 16 * h->GC16, L = int(n.layers.size());
+    auto put_layer = [&](const Layer& l, int K, int N, int Npad, bool bias_in_col3) {
+        const size_t base = blob.size();
+        blob.resize(base + size_t(K + 16) * Npad * 2, 0);
+        uint16_t* dst = reinterpret_cast<uint16_t*>(blob.data() + base);
+        auto at = [&](int nn, int kk) -> uint16_t& { return dst[size_t(kk / 8) * (Npad / 8) * 64 + size_t(nn / 8) * 64 + (nn % 8) * 8 + (kk % 8)]; };
+        for (int nn = 0; nn < N; ++nn) {
+            for (int kk = 0; kk < K; ++kk) at(nn, kk) = l.w(nn, kk);
+            if (bias_in_col3) at(nn, 3) = l.bias[nn];
+            else at(nn, K) = l.bias[nn];
+        }
+    };
+    blob.clear();
+    h->tc_off_w0 = 0;
+    put_layer(n.layers[0], H + GC, H, H, !n.has_time);
+    h->tc_off_wh = int(blob.size());
+    for (int i = 1; i + 1 < L; ++i) put_layer(n.layers[i], H, H, H, false);
+    h->tc_off_wlast = int(blob.size());
+    put_layer(n.layers[L - 1], H, n.layers[L - 1].cout, 16, false);
+    h->tc_off_fourier = int(blob.size());
+    {
+        const uint8_t* p = reinterpret_cast<const uint8_t*>(n.fourier.data());
+        blob.insert(blob.end(), p, p + 2 * n.fourier.size());
+    }
+    while (blob.size() % 16) blob.push_back(0);
+    h->tc_blob_bytes = int(blob.size());
+}
+
 launch_fn pick_launcher(int H16) {
     switch (H16) {
         case 2: return launch_h2; case 3: return launch_h3; case 4: return launch_h4;
@@ -146,8 +188,13 @@ launch_fn pick_launcher(int H16) {
 NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, bool unit_box) {
     const Network& n = h->net;
     NetParams P{};
-    P.blob = h->d_blob; P.blob_bytes = h->blob_bytes;
-    P.off_w0 = h->off_w0; P.off_wh = h->off_wh; P.off_wlast = h->off_wlast; P.off_bias = h->off_bias; P.off_fourier = h->off_fourier;
+    if (h->kernel_mode == FVSRN_KERNEL_TCGEN05) {
+        P.blob = h->d_tc_blob; P.blob_bytes = h->tc_blob_bytes;
+        P.off_w0 = h->tc_off_w0; P.off_wh = h->tc_off_wh; P.off_wlast = h->tc_off_wlast; P.off_bias = 0; P.off_fourier = h->tc_off_fourier;
+    } else {
+        P.blob = h->d_blob; P.blob_bytes = h->blob_bytes;
+        P.off_w0 = h->off_w0; P.off_wh = h->off_wh; P.off_wlast = h->off_wlast; P.off_bias = h->off_bias; P.off_fourier = h->off_fourier;
+    }
     P.num_hidden = h->num_hidden; P.activation = h->activation; P.act_param = h->act_param;
     P.output_mode = n.output_mode; P.has_time = n.has_time ? 1 : 0; P.dir_in_fourier = n.direction_in_fourier ? 1 : 0;
     P.time_value = 0.f;
@@ -169,6 +216,8 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
         }
     }
     for (int i = 0; i < 3; ++i) { P.box_min[i] = unit_box ? 0.f : n.box_min[i]; P.box_size[i] = unit_box ? 1.f : n.box_size[i]; }
+    static const int dbg = [] { const char* e = std::getenv("FVSRN_TC_DEBUG"); return e ? std::atoi(e) : 0; }();
+    P.dbg_flags = dbg;
     return P;
 }
 
@@ -347,6 +396,14 @@ int fvsrn_network_set_time_and_ensemble(fvsrn_network* net, float time, int ense
     return 0;
 }
 
+int fvsrn_network_set_kernel_mode(fvsrn_network* net, int mode) {
+    if (!net) return fail("null network handle");
+    if (mode != FVSRN_KERNEL_MMA_SYNC && mode != FVSRN_KERNEL_TCGEN05) return fail("unknown kernel mode");
+    net->kernel_mode = mode;
+    return 0;
+}
+int fvsrn_network_get_kernel_mode(const fvsrn_network* net) { return net ? net->kernel_mode : -1; }
+
 int fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info) {
     if (!net || !info) return fail("null argument");
     const Network& n = net->net;
@@ -385,6 +442,11 @@ int fvsrn_network_prepare(fvsrn_network* net, int device, void* stream) {
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     CUDA_OK(cudaMalloc(&net->d_blob, blob.size()));
     CUDA_OK(cudaMemcpyAsync(net->d_blob, blob.data(), blob.size(), cudaMemcpyHostToDevice, s));
+    std::vector<uint8_t> tc_blob;
+    build_tc_blob(net, tc_blob);
+    CUDA_OK(cudaMalloc(&net->d_tc_blob, tc_blob.size()));
+    CUDA_OK(cudaMemcpyAsync(net->d_tc_blob, tc_blob.data(), tc_blob.size(), cudaMemcpyHostToDevice, s));
+    CUDA_OK(cudaStreamSynchronize(s)); // blobs are locals
     auto upload = [&](const LatentGrid& g) {
         DeviceGrid d; d.C = g.C; d.Z = g.Z; d.Y = g.Y; d.X = g.X;
         const std::vector<uint16_t> cl = grid_channel_last(g);
@@ -445,11 +507,12 @@ void do_evaluate(fvsrn_network* h, const float* pos, const float* dir, float* ou
     // reference volume_interpolation.cpp:45-48: positions are in the unit cube
     const NetParams P = make_net_params(h, h->net.current_time, h->net.current_ensemble, true);
     EvalParams E{pos, dir, out, (long long)n, kOutputModeChannelsOut[h->net.output_mode]};
+    const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05;
     LaunchCfg cfg; cfg.sm_count = h->sm_count;
-    cfg.max_blocks = ((n + 31) / 32 + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    cfg.max_blocks = tc ? (n + kTcThreads - 1) / kTcThreads : ((n + 31) / 32 + kWarpsPerBlock - 1) / kWarpsPerBlock;
     launch_fn fn = pick_launcher(h->H16);
     if (!fn) throw std::runtime_error("no kernel for this hidden width");
-    CUDA_OK(fn(KIND_EVAL, h->GC16, h->dir, P, &E, &cfg, s));
+    CUDA_OK(fn(tc ? KIND_EVAL_TC : KIND_EVAL, h->GC16, h->dir, P, &E, &cfg, s));
     h->launches++;
 }
 
@@ -489,7 +552,9 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     D.spp = spp; D.spp_side = side;
     D.out = out; D.sb = p->out_stride_b; D.sc = p->out_stride_c; D.sy = p->out_stride_y; D.sx = p->out_stride_x;
     D.step_count = p->step_count_dev; D.counters = p->counters_dev;
-    D.tiles_x = (D.tw + kTileW - 1) / kTileW; D.tiles_y = (D.th + kTileH - 1) / kTileH;
+    const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05;
+    const int tile_w = tc ? kTcTileW : kTileW, tile_h = tc ? kTcTileH : kTileH;
+    D.tiles_x = (D.tw + tile_w - 1) / tile_w; D.tiles_y = (D.th + tile_h - 1) / tile_h;
     launch_fn fn = pick_launcher(h->H16);
     if (!fn) throw std::runtime_error("no kernel for this hidden width");
     auto launch = [&](int b0, int nb, float time_abs) {
@@ -498,8 +563,8 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         d.num_tiles = d.tiles_x * d.tiles_y * nb;
         d.tile_counter = next_tile_counter(h, s);
         LaunchCfg cfg; cfg.sm_count = h->sm_count;
-        cfg.max_blocks = (d.num_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
-        CUDA_OK(fn(KIND_DVR, h->GC16, h->dir, P, &d, &cfg, s));
+        cfg.max_blocks = tc ? d.num_tiles : (d.num_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
+        CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, s));
         h->launches++;
     };
     if (p->view_times_host) { // one launch per view: every view selects its own keyframe pair (time sweeps)
@@ -602,11 +667,12 @@ int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     LaunchCfg cfg; cfg.sm_count = net->sm_count; cfg.query_only = 1;
     launch_fn fn = pick_launcher(net->H16);
     if (!fn) return fail("no kernel for this hidden width");
-    CUDA_OK(fn(kernel == 0 ? KIND_DVR : KIND_EVAL, net->GC16, net->dir, P, nullptr, &cfg, nullptr));
+    const bool tc = net->kernel_mode == FVSRN_KERNEL_TCGEN05;
+    CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, nullptr, &cfg, nullptr));
     info->device = net->device; info->sm_count = net->sm_count;
-    info->block_threads = kWarpsPerBlock * 32; info->blocks_per_sm = cfg.blocks_per_sm; info->grid_blocks = cfg.grid;
+    info->block_threads = cfg.threads; info->blocks_per_sm = cfg.blocks_per_sm; info->grid_blocks = cfg.grid;
     info->smem_bytes_per_block = cfg.smem; info->regs_per_thread = cfg.regs;
-    info->rays_per_warp_tile_x = kTileW; info->rays_per_warp_tile_y = kTileH;
+    info->rays_per_warp_tile_x = tc ? kTcTileW : kTileW; info->rays_per_warp_tile_y = tc ? kTcTileH : kTileH;
     info->kernel_launches = net->launches;
     return 0;
     FV_CATCH

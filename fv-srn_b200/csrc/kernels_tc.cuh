@@ -32,17 +32,19 @@ struct SrnTc {
         uint32_t sblob;       // shared address of the blob
         uint32_t bar;         // shared address of the MMA-completion mbarrier
         uint32_t phase;
+        uint32_t swap;
         tc::ActF af;
     };
 
     // one thread: issue the K steps of a layer. A chunks at A_COL + 8*kt, then (optionally) the ones chunk.
     static __device__ __forceinline__ void issue_layer(const Ctx& c, uint32_t w_addr, int n, int kt_data, bool bias_chunk) {
         const uint32_t idesc = tc::make_idesc(128, n);
-        const uint32_t lbo = uint32_t(n / 8) * 128u, step = 2u * lbo;
+        const uint32_t kstride = uint32_t(n / 8) * 128u, step = 2u * kstride;
+        const uint32_t lbo = c.swap ? 128u : kstride, sbo = c.swap ? kstride : 128u;
         for (int kt = 0; kt < kt_data; ++kt)
-            tc::mma_ts(c.tmem_base + D_COL, c.tmem_base + A_COL + 8 * kt, tc::make_b_desc(w_addr + kt * step, lbo, 128u), idesc, kt > 0);
+            tc::mma_ts(c.tmem_base + D_COL, c.tmem_base + A_COL + 8 * kt, tc::make_b_desc(w_addr + kt * step, lbo, sbo), idesc, kt > 0);
         if (bias_chunk)
-            tc::mma_ts(c.tmem_base + D_COL, c.tmem_base + ONES_COL, tc::make_b_desc(w_addr + kt_data * step, lbo, 128u), idesc, 1u);
+            tc::mma_ts(c.tmem_base + D_COL, c.tmem_base + ONES_COL, tc::make_b_desc(w_addr + kt_data * step, lbo, sbo), idesc, 1u);
         tc::mma_commit(c.bar);
     }
 
@@ -133,6 +135,7 @@ __device__ __forceinline__ typename Net::Ctx tc_prologue(const NetParams& P, TcS
     c.sblob = smem_u32(sblob);
     c.bar = smem_u32(&sh->bar);
     c.phase = 0;
+    c.swap = uint32_t(P.dbg_flags & 1);
     c.af = tc::make_actf(P.activation, P.act_param);
     Net::init_tmem(c);
     return c;

@@ -46,6 +46,7 @@ struct NetParams {
     GridGroup groups[4];
     float box_min[3];
     float box_size[3];
+    int dbg_flags;       // bring-up switches (env FVSRN_TC_DEBUG): bit0 = swap LBO/SBO of the UMMA weight descriptors
 };
 
 // ------------------------------------------------------------------ small PTX wrappers

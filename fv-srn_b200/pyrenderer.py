@@ -23,6 +23,12 @@ from . import _lib
 from ._lib import check
 
 
+# Kernel family used by networks created from now on (B200 addition, see fvsrn_network_set_kernel_mode):
+# "tcgen05" (default; tcgen05.mma + TMEM, fp32 accumulate) or "mma_sync" (reference-precision fp16-accumulate mode).
+KERNEL_MODES = {"mma_sync": 0, "tcgen05": 1}
+DEFAULT_KERNEL_MODE = __import__("os").environ.get("FVSRN_KERNEL_MODE", "tcgen05")
+
+
 # ------------------------------------------------------------------------------------------------ small value types
 class _Vec3:
     __slots__ = ("x", "y", "z")
@@ -213,6 +219,7 @@ class SceneNetwork:
         self.output = SceneNetwork.OutputParametrization(self)
         self._latent_grid = None
         self._prepared_device = None
+        self.kernel_mode = DEFAULT_KERNEL_MODE
 
     def __del__(self):
         try:
@@ -316,6 +323,9 @@ class SceneNetwork:
     # -- GPU residency (replaces fillConstantMemory / copyGridToGPU)
     def _ensure_prepared(self):
         dev = torch.cuda.current_device() if torch.cuda.is_available() else 0
+        if self.kernel_mode not in KERNEL_MODES:
+            raise RuntimeError(f"unknown kernel mode {self.kernel_mode!r} (expected one of {sorted(KERNEL_MODES)})")
+        check(_lib.lib().fvsrn_network_set_kernel_mode(self._h, KERNEL_MODES[self.kernel_mode]))
         if self._prepared_device != dev:
             check(_lib.lib().fvsrn_network_prepare(self._h, dev, _stream_ptr() if torch.cuda.is_available() else None))
             self._prepared_device = dev

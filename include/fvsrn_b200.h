@@ -110,6 +110,14 @@ typedef struct fvsrn_network_info {
 } fvsrn_network_info;
 int  fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info);
 
+/* Which sm_100a kernel family evaluates the SRN (no reference analogue; the reference picks wmma by NVRTC defines):
+ *   FVSRN_KERNEL_TCGEN05  (default) tcgen05.mma with TMEM accumulators (fp32 accumulate), 128 rays per CTA in lock-step
+ *   FVSRN_KERNEL_MMA_SYNC reference-precision mode: mma.sync m16n8k16 with fp16 accumulation in the reference's
+ *                         K order (renderer_volume_tensorcores.cuh:856-910), 32 rays per warp - used for step-count parity */
+enum { FVSRN_KERNEL_MMA_SYNC = 0, FVSRN_KERNEL_TCGEN05 = 1 };
+int  fvsrn_network_set_kernel_mode(fvsrn_network* net, int mode);
+int  fvsrn_network_get_kernel_mode(const fvsrn_network* net);
+
 /* Upload weights (fragment-ordered fp16) and the fp16 channel-last latent grids to `device`.
  * replaces SceneNetwork::fillConstantMemory :1236-1417, LatentGrid::copyGridToGPU :524-535 and the
  * per-network NVRTC specialisation in renderer/kernel_loader.cpp:197-273 (kernels are AOT sm_100a). */

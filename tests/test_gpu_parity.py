@@ -21,15 +21,17 @@ POINT_TOL = 1e-2      # reference's own point-wise tolerance
 ORACLE_POINT_TOL = 4e-3  # CUDA vs kernel-semantics oracle: only HMMA-internal rounding and SFU sin/cos differ
 
 
-@pytest.fixture(scope="module")
-def env():
+@pytest.fixture(scope="module", params=["tcgen05", "mma_sync"])
+def env(request):
+    """Every GPU parity test runs once per kernel family (tcgen05/TMEM default, mma.sync reference-precision mode)."""
     import torch
     assert torch.cuda.is_available(), "GPU tests need a CUDA device"
     import fvsrn_b200  # noqa: F401
     from fvsrn_b200 import pyrenderer as pr, scenes, volnet, _lib
     import oracle
     _lib.lib()
-    return type("Env", (), dict(torch=torch, pr=pr, scenes=scenes, volnet=volnet, oracle=oracle, lib=_lib))
+    pr.DEFAULT_KERNEL_MODE = request.param
+    return type("Env", (), dict(torch=torch, pr=pr, scenes=scenes, volnet=volnet, oracle=oracle, lib=_lib, mode=request.param))
 
 
 def _volume(env, net_or_bytes):
