@@ -23,7 +23,11 @@ int fail(const std::string& msg) { g_last_error = msg; return 1; }
 #define CUDA_OK(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) \
     throw std::runtime_error(std::string(#expr) + " failed: " + cudaGetErrorString(_e)); } while (0)
 
-struct DeviceGrid { __half* data = nullptr; int C = 0, Z = 0, Y = 0, X = 0; };
+struct DeviceGrid {
+    __half* data = nullptr; int C = 0, Z = 0, Y = 0, X = 0;   // channel-last fp16 (mma.sync path)
+    std::vector<cudaArray_t> arrays;                          // C/4 fp16 RGBA 3-D arrays + texture objects (tcgen05 path)
+    std::vector<cudaTextureObject_t> tex;
+};
 } // namespace
 
 struct fvsrn_network {
@@ -52,8 +56,12 @@ void release_gpu(fvsrn_network* h) {
     if (h->d_blob) cudaFree(h->d_blob);
     if (h->d_tc_blob) cudaFree(h->d_tc_blob);
     h->d_tc_blob = nullptr;
-    for (auto& g : h->d_time) if (g.data) cudaFree(g.data);
-    for (auto& g : h->d_ens) if (g.data) cudaFree(g.data);
+    for (auto* v : {&h->d_time, &h->d_ens})
+        for (auto& g : *v) {
+            if (g.data) cudaFree(g.data);
+            for (auto t : g.tex) cudaDestroyTextureObject(t);
+            for (auto a : g.arrays) cudaFreeArray(a);
+        }
     if (h->d_tile_counter) cudaFree(h->d_tile_counter);
     if (h->d_scratch) cudaFree(h->d_scratch);
     h->d_blob = nullptr; h->d_time.clear(); h->d_ens.clear(); h->d_tile_counter = nullptr;
@@ -207,15 +215,23 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
             P.time_value = t;
             const DeviceGrid& A = h->d_time[lo]; const DeviceGrid& B = h->d_time[hi];
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
-            for (int i = 0; i < A.C / 16; ++i, ++g) P.groups[g] = GridGroup{A.data + 16 * i, B.data + 16 * i, frac, A.C * 2 / 16};
+            for (int i = 0; i < A.C / 16; ++i, ++g) {
+                P.groups[g] = GridGroup{A.data + 16 * i, B.data + 16 * i, frac, A.C * 2 / 16};
+                for (int q = 0; q < 4; ++q) { P.tex_a[4 * g + q] = A.tex[4 * i + q]; P.tex_b[4 * g + q] = B.tex[4 * i + q]; }
+            }
         }
         if (!h->d_ens.empty()) {
             const DeviceGrid& A = h->d_ens[n.interpolate_ensemble(ensemble)];
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
-            for (int i = 0; i < A.C / 16; ++i, ++g) P.groups[g] = GridGroup{A.data + 16 * i, A.data + 16 * i, 0.f, A.C * 2 / 16};
+            for (int i = 0; i < A.C / 16; ++i, ++g) {
+                P.groups[g] = GridGroup{A.data + 16 * i, A.data + 16 * i, 0.f, A.C * 2 / 16};
+                for (int q = 0; q < 4; ++q) P.tex_a[4 * g + q] = P.tex_b[4 * g + q] = A.tex[4 * i + q];
+            }
         }
     }
     for (int i = 0; i < 3; ++i) { P.box_min[i] = unit_box ? 0.f : n.box_min[i]; P.box_size[i] = unit_box ? 1.f : n.box_size[i]; }
+    if (n.fourier.size() > 2 * sizeof(P.fourier2) / sizeof(P.fourier2[0])) throw std::runtime_error("Fourier matrix too large");
+    std::memcpy(P.fourier2, n.fourier.data(), n.fourier.size() * 2);
     static const int dbg = [] { const char* e = std::getenv("FVSRN_TC_DEBUG"); return e ? std::atoi(e) : 0; }();
     P.dbg_flags = dbg;
     return P;
@@ -453,6 +469,28 @@ int fvsrn_network_prepare(fvsrn_network* net, int device, void* stream) {
         CUDA_OK(cudaMalloc(&d.data, cl.size() * 2));
         CUDA_OK(cudaMemcpyAsync(d.data, cl.data(), cl.size() * 2, cudaMemcpyHostToDevice, s));
         CUDA_OK(cudaStreamSynchronize(s)); // cl is a temporary
+        // the same voxels as C/4 half4 textures: clamp addressing, linear filter, normalised coordinates
+        // (reference LatentGrid::GPUArray, volume_interpolation_network.cpp:470-504, with fp16 instead of fp32 texels)
+        std::vector<uint16_t> sub(size_t(g.Z) * g.Y * g.X * 4);
+        for (int q = 0; q < g.C / 4; ++q) {
+            for (size_t v = 0; v < size_t(g.Z) * g.Y * g.X; ++v)
+                for (int c = 0; c < 4; ++c) sub[v * 4 + c] = cl[v * g.C + q * 4 + c];
+            cudaChannelFormatDesc fd = cudaCreateChannelDescHalf4();
+            cudaArray_t arr = nullptr;
+            CUDA_OK(cudaMalloc3DArray(&arr, &fd, make_cudaExtent(g.X, g.Y, g.Z)));
+            d.arrays.push_back(arr);
+            cudaMemcpy3DParms cp = {};
+            cp.srcPtr = make_cudaPitchedPtr(sub.data(), size_t(g.X) * 8, g.X, g.Y);
+            cp.dstArray = arr; cp.extent = make_cudaExtent(g.X, g.Y, g.Z); cp.kind = cudaMemcpyHostToDevice;
+            CUDA_OK(cudaMemcpy3D(&cp));
+            cudaResourceDesc rd = {}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+            cudaTextureDesc td = {};
+            td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+            td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 1;
+            cudaTextureObject_t t = 0;
+            CUDA_OK(cudaCreateTextureObject(&t, &rd, &td, nullptr));
+            d.tex.push_back(t);
+        }
         return d;
     };
     if (net->net.has_latent_grid) {
@@ -509,7 +547,7 @@ void do_evaluate(fvsrn_network* h, const float* pos, const float* dir, float* ou
     EvalParams E{pos, dir, out, (long long)n, kOutputModeChannelsOut[h->net.output_mode]};
     const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05;
     LaunchCfg cfg; cfg.sm_count = h->sm_count;
-    cfg.max_blocks = tc ? (n + kTcThreads - 1) / kTcThreads : ((n + 31) / 32 + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    cfg.max_blocks = tc ? (n + 2 * kTcComputeThreads - 1) / (2 * kTcComputeThreads) : ((n + 31) / 32 + kWarpsPerBlock - 1) / kWarpsPerBlock;
     launch_fn fn = pick_launcher(h->H16);
     if (!fn) throw std::runtime_error("no kernel for this hidden width");
     CUDA_OK(fn(tc ? KIND_EVAL_TC : KIND_EVAL, h->GC16, h->dir, P, &E, &cfg, s));

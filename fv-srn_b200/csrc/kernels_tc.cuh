@@ -1,25 +1,39 @@
 // tcgen05 / TMEM versions of the two kernels of the hot path (fast mode, see srn_tc.cuh):
 //   dvr_tc_kernel   <- ImageEvaluatorSimpleKernel + RayEvaluationSteppingDvr::eval + TF + Blending
 //   eval_tc_kernel  <- EvaluateNoBatches
-// One CTA = 128 threads = 128 rays (a 16x8 pixel tile, each warp an 8x4 sub-tile) marched in lock-step: one SRN sample
-// per thread per step = one M=128 UMMA tile per step. Persistent CTAs pull tiles from an atomic queue; several CTAs
-// are resident per SM so that one CTA's MMA / TMEM latency is covered by the others' feature and fetch work.
+// One CTA = 4 compute warps (128 threads = 128 rays, a 16x8 pixel tile, each warp an 8x4 sub-tile) + 1 MMA warp.
+// The rays are marched in lock-step: one SRN sample per compute thread per step = one M=128 UMMA tile per step, two
+// steps ("slots") in flight. Compute warps never wait for each other: they publish their operand rows with an
+// mbarrier arrive and move on to the other slot; the elected thread of the MMA warp waits for the four warps of a
+// slot, issues that layer's tcgen05.mma chain and commits to the slot's completion mbarrier. Persistent CTAs pull
+// tiles from an atomic queue; several CTAs are resident per SM.
 #pragma once
 #include "kernels.cuh"
 #include "srn_tc.cuh"
 
 namespace fvsrn {
 
-constexpr int kTcThreads = 128;
+constexpr int kTcComputeThreads = 128;
+constexpr int kTcThreads = 160;            // + the MMA warp
 constexpr int kTcTileW = 16, kTcTileH = 8;
 
-template <int H16, int GC16, bool DIR>
+struct TcShared {           // fixed part of the dynamic shared memory, placed first (48 bytes)
+    unsigned long long ready[2];   // slot operands written: one arrival per compute warp
+    unsigned long long done[2];    // slot MMA chain complete (tcgen05.commit)
+    uint32_t tmem_addr;
+    int tile;
+    int pad[2];
+};
+
+template <int H16, int GC16, bool DIR, bool RELU>
 struct SrnTc {
     using Core = Srn<H16, GC16, DIR>;
     static constexpr int H = Core::H, K0 = Core::K0, KT0 = K0 / 16, KTH = H / 16;
     static constexpr int NLAST = 16;                       // last layer padded to N = 16 (M=128 needs N % 16 == 0)
-    // TMEM columns (32-bit): D | ones chunk | A
-    static constexpr int D_COL = 0, ONES_COL = H, A_COL = H + 8, USED_COLS = H + 8 + K0 / 2;
+    // TMEM columns (32-bit): ones chunk | slot 0: D, A | slot 1: D, A
+    static constexpr int ONES_COL = 0, SLOT_COLS = H + K0 / 2, USED_COLS = 8 + 2 * SLOT_COLS;
+    static __host__ __device__ constexpr int d_col(int slot) { return 8 + slot * SLOT_COLS; }
+    static __host__ __device__ constexpr int a_col(int slot) { return 8 + slot * SLOT_COLS + H; }
     static constexpr int TMEM_COLS = USED_COLS <= 32 ? 32 : USED_COLS <= 64 ? 64 : USED_COLS <= 128 ? 128 : USED_COLS <= 256 ? 256 : 512;
     // weight tiles in the blob (K-major core matrices, chunk-major): bytes
     static __host__ __device__ constexpr int w0_bytes() { return (K0 + 16) * H * 2; }
@@ -30,100 +44,182 @@ struct SrnTc {
         uint32_t tmem_lane;   // TMEM base address of this thread's lane quadrant (lane field = 32 * (warp % 4))
         uint32_t tmem_base;   // allocation base (lane 0)
         uint32_t sblob;       // shared address of the blob
-        uint32_t bar;         // shared address of the MMA-completion mbarrier
-        uint32_t phase;
-        uint32_t swap;
+        uint32_t ready, done; // shared addresses of the mbarrier pairs (slot s at +8 s)
+        uint32_t phase;       // parity of the next phase to wait for; both slots advance together
         tc::ActF af;
     };
 
-    // one thread: issue the K steps of a layer. A chunks at A_COL + 8*kt, then (optionally) the ones chunk.
-    static __device__ __forceinline__ void issue_layer(const Ctx& c, uint32_t w_addr, int n, int kt_data, bool bias_chunk) {
-        const uint32_t idesc = tc::make_idesc(128, n);
-        const uint32_t kstride = uint32_t(n / 8) * 128u, step = 2u * kstride;
-        const uint32_t lbo = c.swap ? 128u : kstride, sbo = c.swap ? kstride : 128u;
-        for (int kt = 0; kt < kt_data; ++kt)
-            tc::mma_ts(c.tmem_base + D_COL, c.tmem_base + A_COL + 8 * kt, tc::make_b_desc(w_addr + kt * step, lbo, sbo), idesc, kt > 0);
-        if (bias_chunk)
-            tc::mma_ts(c.tmem_base + D_COL, c.tmem_base + ONES_COL, tc::make_b_desc(w_addr + kt_data * step, lbo, sbo), idesc, 1u);
-        tc::mma_commit(c.bar);
+    // Layer-0 inputs of the sample owned by this thread (same channel order and fp16 rounding points as
+    // Srn::build_row), built for issue-slot economy: Fourier matrix from the constant bank, latent vector through the
+    // texture units (4 x tex3D<half4> per 16 channels, hardware trilinear filter = the reference's own fetch,
+    // renderer_volume_tensorcores.cuh:573-605), channel 3 = 1 when the network has no time input (bias column).
+    static __device__ __forceinline__ void build_row(const NetParams& P, float px, float py, float pz,
+                                                     float dx, float dy, float dz, uint32_t (&row)[K0 / 2]) {
+        constexpr int FOFF = Core::FOFF, NF = Core::NF;
+        const __half hx = __float2half_rn(px), hy = __float2half_rn(py), hz = __float2half_rn(pz);
+        row[0] = h2u(__halves2half2(hx, hy));
+        row[1] = h2u(__halves2half2(hz, __float2half_rn(P.has_time ? P.time_value : 1.f)));
+        __half2 d2x, d2y, d2z;
+        if (DIR) {
+            const __half hdx = __float2half_rn(dx), hdy = __float2half_rn(dy), hdz = __float2half_rn(dz);
+            row[2] = h2u(__halves2half2(hdx, hdy));
+            row[3] = h2u(__halves2half2(hdz, __float2half_rn(0.f)));
+            d2x = __half2half2(hdx); d2y = __half2half2(hdy); d2z = __half2half2(hdz);
+        }
+        const __half2 x2 = __half2half2(hx), y2 = __half2half2(hy), z2 = __half2half2(hz);
+#pragma unroll
+        for (int i = 0; i < NF; i += 2) {   // reference :795-807: phase accumulated in fp16 (hmul, hfma, hfma), then cos / sin
+            __half2 c = __hmul2(x2, u2h(P.fourier2[(i + 0 * NF) / 2]));
+            c = __hfma2(y2, u2h(P.fourier2[(i + 1 * NF) / 2]), c);
+            c = __hfma2(z2, u2h(P.fourier2[(i + 2 * NF) / 2]), c);
+            if (DIR) {
+                if (P.dir_in_fourier) {
+                    c = __hfma2(d2x, u2h(P.fourier2[(i + 3 * NF) / 2]), c);
+                    c = __hfma2(d2y, u2h(P.fourier2[(i + 4 * NF) / 2]), c);
+                    c = __hfma2(d2z, u2h(P.fourier2[(i + 5 * NF) / 2]), c);
+                }
+            }
+            const float2 cf = __half22float2(c);
+            float s0, c0, s1, c1;
+            __sincosf(cf.x, &s0, &c0);
+            __sincosf(cf.y, &s1, &c1);
+            row[FOFF / 2 + i / 2] = tc::pack_h2(c0, c1);
+            row[FOFF / 2 + NF / 2 + i / 2] = tc::pack_h2(s0, s1);
+        }
+#pragma unroll
+        for (int g = 0; g < GC16; ++g) {
+            const float frac = P.groups[g].frac;    // CTA-uniform
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float4 v = tex3D<float4>(P.tex_a[4 * g + q], px, py, pz);
+                if (frac > 0.f) {   // temporal lerp of the two keyframes after the fetch, in fp32 (reference :590-604)
+                    const float4 w = tex3D<float4>(P.tex_b[4 * g + q], px, py, pz);
+                    v.x = fmaf(frac, w.x - v.x, v.x); v.y = fmaf(frac, w.y - v.y, v.y);
+                    v.z = fmaf(frac, w.z - v.z, v.z); v.w = fmaf(frac, w.w - v.w, v.w);
+                }
+                row[H / 2 + g * 8 + 2 * q] = tc::pack_h2(v.x, v.y);
+                row[H / 2 + g * 8 + 2 * q + 1] = tc::pack_h2(v.z, v.w);
+            }
+        }
     }
 
-    // per-CTA set-up after TMEM allocation: the constant ones chunk
+    // MMA thread: issue the K steps of one layer of one slot and commit to the slot's completion barrier.
+    // The smem descriptor of K step kt differs from step 0 only in the address field of its low word.
+    static __device__ __forceinline__ void issue_layer(const Ctx& c, int slot, uint32_t w_addr, int n, int kt_data, bool bias_chunk) {
+        const uint32_t idesc = tc::make_idesc(128, n);
+        const uint32_t kstride = uint32_t(n / 8) * 128u;                    // LBO: distance between the two K chunks of a step
+        uint32_t lo = ((w_addr >> 4) & 0x3FFFu) | (((kstride >> 4) & 0x3FFFu) << 16);
+        const uint32_t hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, descriptor version 1
+        const uint32_t step = (2u * kstride) >> 4;
+        const uint32_t d = c.tmem_base + d_col(slot);
+        uint32_t a = c.tmem_base + a_col(slot);
+        for (int kt = 0; kt < kt_data; ++kt, lo += step, a += 8) tc::mma_ts2(d, a, lo, hi, idesc, kt > 0);
+        if (bias_chunk) tc::mma_ts2(d, c.tmem_base + ONES_COL, lo, hi, idesc, 1u);
+        tc::mma_commit(c.done + 8 * slot);
+    }
+
+    // per-CTA set-up after TMEM allocation: the constant ones chunk (compute threads)
     static __device__ __forceinline__ void init_tmem(const Ctx& c) {
         uint32_t ones[8] = {0x00003C00u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};   // (half 1.0, half 0), zeros
         tc::tmem_st8(c.tmem_lane + ONES_COL, ones, 0);
         tc::wait_st();
     }
 
-    // Evaluate the network for the 128 samples of the CTA (row = this thread's layer-0 inputs, build_row(..., ch3_one=true)).
-    // Every thread of the CTA must call. Returns false (out undefined) when no thread of the CTA is `active`.
-    static __device__ __forceinline__ bool mlp(const NetParams& P, Ctx& c, const uint32_t (&row)[K0 / 2], bool active, float (&out)[4]) {
-#pragma unroll
-        for (int kt = 0; kt < KT0; ++kt) tc::tmem_st8(c.tmem_lane + A_COL + 8 * kt, row, 8 * kt);
+    // compute warp: this warp's operand rows of `slot` are in TMEM -> one arrival on the slot's ready barrier
+    static __device__ __forceinline__ void publish(const Ctx& c, int slot) {
         tc::wait_st();
         tc::fence_before_sync();
-        if (!__syncthreads_or(active ? 1 : 0)) return false;
-        if (threadIdx.x == 0) {
-            tc::fence_after_sync();
-            issue_layer(c, c.sblob + P.off_w0, H, KT0, P.has_time != 0);
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) tc::mbar_arrive(c.ready + 8 * slot);
+    }
+
+    // this thread's layer-0 row of one slot -> TMEM A operand
+    static __device__ __forceinline__ void store_row(const Ctx& c, int slot, const uint32_t (&row)[K0 / 2]) {
+#pragma unroll
+        for (int kt = 0; kt < KT0; ++kt) tc::tmem_st8(c.tmem_lane + a_col(slot) + 8 * kt, row, 8 * kt);
+        publish(c, slot);
+    }
+
+    // epilogue of one slot: accumulator row -> activation -> fp16 A operand of the next layer
+    static __device__ __forceinline__ void epilogue(const Ctx& c, int slot, int act) {
+#pragma unroll
+        for (int c0 = 0; c0 < H; c0 += 32) {
+            uint32_t v[32];
+            if (H - c0 >= 32) tc::tmem_ld32(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld16(c.tmem_lane + d_col(slot) + c0, v);
+            tc::wait_ld();
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                pk[j] = (H - c0 >= 32 || j < 8) ? (RELU ? tc::pack_relu(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]))
+                                                        : tc::act_pack(act, c.af, v[2 * j], v[2 * j + 1])) : 0u;
+            if (H - c0 >= 32) tc::tmem_st16(c.tmem_lane + a_col(slot) + c0 / 2, pk, 0); else tc::tmem_st8(c.tmem_lane + a_col(slot) + c0 / 2, pk, 0);
         }
+    }
+
+    // Compute warps: run the layer chain for the 2 x 128 samples whose layer-0 rows were stored with store_row().
+    // A warp that is not `warp_active` (all its rays finished) keeps the barrier protocol going but skips the arithmetic.
+    static __device__ __forceinline__ void mlp_compute(const NetParams& P, Ctx& c, bool warp_active, float (&out0)[4], float (&out1)[4]) {
         const int act = P.activation;
 #pragma unroll 1
         for (int l = 0; l <= P.num_hidden; ++l) {
-            tc::mbar_wait(c.bar, c.phase); c.phase ^= 1u;
-            tc::fence_after_sync();
-            // epilogue: accumulator row -> activation -> fp16 A operand of the next layer
 #pragma unroll
-            for (int c0 = 0; c0 < H; c0 += 32) {
-                uint32_t v[32];
-                if (H - c0 >= 32) tc::tmem_ld32(c.tmem_lane + D_COL + c0, v); else tc::tmem_ld16(c.tmem_lane + D_COL + c0, v);
-                tc::wait_ld();
-                uint32_t pk[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) pk[j] = (H - c0 >= 32 || j < 8) ? tc::act_pack(act, c.af, v[2 * j], v[2 * j + 1]) : 0u;
-                if (H - c0 >= 32) tc::tmem_st16(c.tmem_lane + A_COL + c0 / 2, pk, 0); else tc::tmem_st8(c.tmem_lane + A_COL + c0 / 2, pk, 0);
-            }
-            tc::wait_st();
-            tc::fence_before_sync();
-            __syncthreads();
-            if (threadIdx.x == 0) {
+            for (int slot = 0; slot < 2; ++slot) {
+                tc::mbar_wait(c.done + 8 * slot, c.phase);
                 tc::fence_after_sync();
-                if (l < P.num_hidden) issue_layer(c, c.sblob + P.off_wh + l * wh_bytes(), H, KTH, true);
-                else issue_layer(c, c.sblob + P.off_wlast, NLAST, KTH, true);
+                if (warp_active) epilogue(c, slot, act);
+                publish(c, slot);
+            }
+            c.phase ^= 1u;
+        }
+#pragma unroll
+        for (int slot = 0; slot < 2; ++slot) {
+            float (&out)[4] = slot == 0 ? out0 : out1;
+            tc::mbar_wait(c.done + 8 * slot, c.phase);
+            tc::fence_after_sync();
+            if (P.output_mode >= D_OUT_RGBO) {
+                uint32_t o[4];
+                tc::tmem_ld4(c.tmem_lane + d_col(slot), o);
+                tc::wait_ld();
+                out[0] = __uint_as_float(o[0]); out[1] = __uint_as_float(o[1]); out[2] = __uint_as_float(o[2]); out[3] = __uint_as_float(o[3]);
+            } else {
+                uint32_t o;
+                tc::tmem_ld1(c.tmem_lane + d_col(slot), o);
+                tc::wait_ld();
+                out[0] = __uint_as_float(o); out[1] = out[2] = out[3] = 0.f;
             }
         }
-        tc::mbar_wait(c.bar, c.phase); c.phase ^= 1u;
-        tc::fence_after_sync();
-        if (P.output_mode >= D_OUT_RGBO) {
-            uint32_t o[4];
-            tc::tmem_ld4(c.tmem_lane + D_COL, o);
-            tc::wait_ld();
-            out[0] = __uint_as_float(o[0]); out[1] = __uint_as_float(o[1]); out[2] = __uint_as_float(o[2]); out[3] = __uint_as_float(o[3]);
-        } else {
-            uint32_t o;
-            tc::tmem_ld1(c.tmem_lane + D_COL, o);
-            tc::wait_ld();
-            out[0] = __uint_as_float(o); out[1] = out[2] = out[3] = 0.f;
-        }
-        // the next call's tcgen05.st / mma may only start after every thread has read its outputs
+        c.phase ^= 1u;
+        // the next trip's tcgen05.st / mma may only start after this thread has read its outputs
         tc::fence_before_sync();
-        return true;
+    }
+
+    // MMA thread: the matching issue schedule of one trip. `c.phase` here is the parity of the ready barriers.
+    static __device__ __forceinline__ void mlp_issue(const NetParams& P, Ctx& c) {
+#pragma unroll 1
+        for (int l = -1; l <= P.num_hidden; ++l) {
+#pragma unroll
+            for (int slot = 0; slot < 2; ++slot) {
+                tc::mbar_wait(c.ready + 8 * slot, c.phase);
+                tc::fence_after_sync();
+                if (l < 0) issue_layer(c, slot, c.sblob + P.off_w0, H, KT0, P.has_time != 0);
+                else if (l < P.num_hidden) issue_layer(c, slot, c.sblob + P.off_wh + l * wh_bytes(), H, KTH, true);
+                else issue_layer(c, slot, c.sblob + P.off_wlast, NLAST, KTH, true);
+            }
+            c.phase ^= 1u;
+        }
     }
 };
 
-struct TcShared {           // fixed part of the dynamic shared memory, placed first
-    unsigned long long bar;
-    uint32_t tmem_addr;
-    int tile;
-};
-
-// common prologue: blob -> smem, mbarrier, TMEM allocation
+// common prologue: blob -> smem, mbarriers, TMEM allocation (by the MMA warp)
 template <class Net>
 __device__ __forceinline__ typename Net::Ctx tc_prologue(const NetParams& P, TcShared* sh, uint4* sblob) {
     load_blob(P, sblob);
     const int warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) tc::mbar_init(smem_u32(&sh->bar), 1);
-    if (warp == 0) tc::tmem_alloc(smem_u32(&sh->tmem_addr), Net::TMEM_COLS);
+    if (threadIdx.x == 0) {
+        tc::mbar_init(smem_u32(&sh->ready[0]), 4); tc::mbar_init(smem_u32(&sh->ready[1]), 4);
+        tc::mbar_init(smem_u32(&sh->done[0]), 1); tc::mbar_init(smem_u32(&sh->done[1]), 1);
+    }
+    if (warp == 4) tc::tmem_alloc(smem_u32(&sh->tmem_addr), Net::TMEM_COLS);
     // make the generic-proxy writes of the weights visible to the tensor-core (async) proxy
     asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
     tc::fence_before_sync();
@@ -133,31 +229,32 @@ __device__ __forceinline__ typename Net::Ctx tc_prologue(const NetParams& P, TcS
     c.tmem_base = sh->tmem_addr;
     c.tmem_lane = c.tmem_base + (uint32_t((warp & 3) * 32) << 16);
     c.sblob = smem_u32(sblob);
-    c.bar = smem_u32(&sh->bar);
+    c.ready = smem_u32(&sh->ready[0]);
+    c.done = smem_u32(&sh->done[0]);
     c.phase = 0;
-    c.swap = uint32_t(P.dbg_flags & 1);
     c.af = tc::make_actf(P.activation, P.act_param);
-    Net::init_tmem(c);
+    if (warp < 4) Net::init_tmem(c);
     return c;
 }
 template <class Net>
 __device__ __forceinline__ void tc_epilogue(const typename Net::Ctx& c) {
     tc::fence_before_sync();
     __syncthreads();
-    if ((threadIdx.x >> 5) == 0) tc::tmem_dealloc(c.tmem_base, Net::TMEM_COLS);
+    if ((threadIdx.x >> 5) == 4) tc::tmem_dealloc(c.tmem_base, Net::TMEM_COLS);
 }
 
-template <int H16, int GC16, bool DIR>
-__global__ void __launch_bounds__(kTcThreads)
+template <int H16, int GC16, bool DIR, bool RELU>
+__global__ void __launch_bounds__(kTcThreads, H16 <= 2 ? 4 : 1)
 dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
-    using Net = SrnTc<H16, GC16, DIR>;
+    using Net = SrnTc<H16, GC16, DIR, RELU>;
     using Core = typename Net::Core;
     extern __shared__ uint4 smem[];
     TcShared* sh = reinterpret_cast<TcShared*>(smem);
-    uint4* sblob = smem + 1;
+    uint4* sblob = smem + 3;
     const int blob16 = (P.blob_bytes + 15) / 16;
     float* stf = reinterpret_cast<float*>(sblob + blob16);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool is_mma_warp = warp == 4;
 
     typename Net::Ctx ctx = tc_prologue<Net>(P, sh, sblob);
     const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : (D.tf_kind == 1 ? D.tf_R * 4 : 2);
@@ -169,7 +266,7 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
     const float3 bsize = make_float3(P.box_size[0], P.box_size[1], P.box_size[2]);
     const float3 binv = make_float3(__fdiv_rn(1.f, bsize.x), __fdiv_rn(1.f, bsize.y), __fdiv_rn(1.f, bsize.z));
     // pixel of this thread inside the CTA tile: warps 2x2, lanes 8x4
-    const int lx = (warp & 1) * 8 + (lane & 7), ly = (warp >> 1) * 4 + (lane >> 3);
+    const int lx = (warp & 1) * 8 + (lane & 7), ly = ((warp >> 1) & 1) * 4 + (lane >> 3);
 
     unsigned long long n_valid = 0, n_exec = 0;
     for (;;) {
@@ -183,6 +280,18 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
         const int trem = tile - bl * tiles_per_img;
         const int ty = trem / D.tiles_x, tx = trem - ty * D.tiles_x;
         const int b = D.b0 + bl;
+
+        if (is_mma_warp) {
+            // ---------------------------------------------------------------- MMA warp: one elected thread issues
+            for (int s = 0; s < D.spp; ++s)
+                for (;;) {
+                    if (!__syncthreads_or(0)) break;
+                    if (lane == 0) Net::mlp_issue(P, ctx);
+                    __syncwarp();
+                }
+            continue;
+        }
+        // -------------------------------------------------------------------- compute warps
         const int x = D.x0 + tx * kTcTileW + lx;
         const int y = D.y0 + ty * kTcTileH + ly;
         const bool in_img = (x < D.x0 + D.tw) && (y < D.y0 + D.th);
@@ -198,25 +307,53 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             float acc_depth = 0.f;
             int steps = 0;
-            // lock-step march of the 128 rays, reference renderer_ray_evaluation_stepping_dvr.cuh:84-154
-            for (int i = 0;; ++i) {
-                const float t = __fmaf_rn(float(i), D.stepsize, r.tmin);
-                bool valid = (t <= tmax);
-                if (D.early_out) valid = valid && (acc.w < D.alpha_early_out);
-                float px = 0.f, py = 0.f, pz = 0.f;
-                if (valid) {
-                    px = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.x, t, r.eye.x), bmin.x), binv.x);
-                    py = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.y, t, r.eye.y), bmin.y), binv.y);
-                    pz = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.z, t, r.eye.z), bmin.z), binv.z);
+            // lock-step march of the 128 rays, reference renderer_ray_evaluation_stepping_dvr.cuh:84-154. Two consecutive
+            // steps are evaluated per trip (slot 0 = step i, slot 1 = step i+1, the second speculatively: whether it is
+            // needed is only known after step i has been composited); samples are blended in order, so the result is
+            // the sequential one.
+            for (int i = 0;; i += 2) {
+                const float t0 = __fmaf_rn(float(i), D.stepsize, r.tmin);
+                const float t1 = __fmaf_rn(float(i + 1), D.stepsize, r.tmin);
+                const bool alive = !D.early_out || (acc.w < D.alpha_early_out);
+                const bool valid0 = (t0 <= tmax) && alive;
+                const bool in1 = (t1 <= tmax) && alive;
+                if (!__syncthreads_or(valid0 ? 1 : 0)) break;
+                // a warp whose 32 rays are all finished keeps the barrier protocol going but skips the arithmetic
+                const bool warp_active = __any_sync(0xffffffffu, valid0);
+                if (warp_active) {
+                    float px = 0.f, py = 0.f, pz = 0.f;
+                    if (valid0) {
+                        px = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.x, t0, r.eye.x), bmin.x), binv.x);
+                        py = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.y, t0, r.eye.y), bmin.y), binv.y);
+                        pz = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.z, t0, r.eye.z), bmin.z), binv.z);
+                    }
+                    uint32_t row[Core::K0 / 2];
+                    Net::build_row(P, px, py, pz, r.dir.x, r.dir.y, r.dir.z, row);
+                    Net::store_row(ctx, 0, row);
+                } else Net::publish(ctx, 0);
+                if (warp_active) {
+                    float px = 0.f, py = 0.f, pz = 0.f;
+                    if (in1) {
+                        px = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.x, t1, r.eye.x), bmin.x), binv.x);
+                        py = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.y, t1, r.eye.y), bmin.y), binv.y);
+                        pz = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.z, t1, r.eye.z), bmin.z), binv.z);
+                    }
+                    uint32_t row[Core::K0 / 2];
+                    Net::build_row(P, px, py, pz, r.dir.x, r.dir.y, r.dir.z, row);
+                    Net::store_row(ctx, 1, row);
+                } else Net::publish(ctx, 1);
+                float o0[4], o1[4];
+                Net::mlp_compute(P, ctx, warp_active, o0, o1);
+                if (lane == 0) n_exec += 64;
+                if (valid0) {
+                    ++steps;
+                    blend_sample(D, shade_sample(P, D, tfp, o0), t0, acc, acc_depth);
                 }
-                uint32_t row[Core::K0 / 2];
-                Core::build_row(P, ctx.sblob, px, py, pz, r.dir.x, r.dir.y, r.dir.z, true, row);
-                float o[4];
-                if (!Net::mlp(P, ctx, row, valid, o)) break;
-                if (lane == 0) n_exec += 32;
-                if (!valid) continue;
-                ++steps;
-                blend_sample(D, shade_sample(P, D, tfp, o), t, acc, acc_depth);
+                const bool valid1 = in1 && (!D.early_out || (acc.w < D.alpha_early_out));
+                if (valid1) {
+                    ++steps;
+                    blend_sample(D, shade_sample(P, D, tfp, o1), t1, acc, acc_depth);
+                }
             }
             n_valid += steps;
             last_steps = steps;
@@ -225,43 +362,60 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
         }
         if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps);
     }
-    if (D.counters) {
+    if (D.counters && !is_mma_warp) {
         for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);
         if (lane == 0) { atomicAdd(D.counters + 0, n_valid); atomicAdd(D.counters + 1, n_exec); }
     }
     tc_epilogue<Net>(ctx);
 }
 
-template <int H16, int GC16, bool DIR>
+template <int H16, int GC16, bool DIR, bool RELU>
 __global__ void __launch_bounds__(kTcThreads)
 eval_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ EvalParams E) {
-    using Net = SrnTc<H16, GC16, DIR>;
+    using Net = SrnTc<H16, GC16, DIR, RELU>;
     using Core = typename Net::Core;
     extern __shared__ uint4 smem[];
     TcShared* sh = reinterpret_cast<TcShared*>(smem);
-    uint4* sblob = smem + 1;
+    uint4* sblob = smem + 3;
     typename Net::Ctx ctx = tc_prologue<Net>(P, sh, sblob);
-    const long long n128 = (E.n + 127) / 128;
-    for (long long w = blockIdx.x; w < n128; w += gridDim.x) {
-        const long long i = w * 128 + threadIdx.x;
-        const bool valid = i < E.n;
-        float px = 0.f, py = 0.f, pz = 0.f, dx = 0.f, dy = 0.f, dz = 0.f;
-        if (valid) {
-            px = __ldg(E.pos + 3 * i); py = __ldg(E.pos + 3 * i + 1); pz = __ldg(E.pos + 3 * i + 2);
-            if (DIR && E.dir) { dx = __ldg(E.dir + 3 * i); dy = __ldg(E.dir + 3 * i + 1); dz = __ldg(E.dir + 3 * i + 2); }
-        }
-        uint32_t row[Core::K0 / 2];
-        Core::build_row(P, ctx.sblob, px, py, pz, dx, dy, dz, true, row);
-        float o[4];
-        Net::mlp(P, ctx, row, true, o);
-        if (!valid) continue;
-        if (P.output_mode == D_OUT_DENSITY) E.out[i] = sigmoidf_(o[0]);
-        else if (P.output_mode == D_OUT_DENSITY_DIRECT) E.out[i] = o[0];
-        else {
-            float4 c;
-            if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
-            else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
-            reinterpret_cast<float4*>(E.out)[i] = c;
+    const long long n256 = (E.n + 255) / 256;
+    if ((threadIdx.x >> 5) == 4) {
+        if ((threadIdx.x & 31) == 0)
+            for (long long w = blockIdx.x; w < n256; w += gridDim.x) Net::mlp_issue(P, ctx);
+        __syncwarp();
+    } else {
+        for (long long w = blockIdx.x; w < n256; w += gridDim.x) {
+            long long idx[2]; bool valid[2];
+#pragma unroll
+            for (int slot = 0; slot < 2; ++slot) {
+                const long long i = w * 256 + slot * 128 + threadIdx.x;
+                idx[slot] = i; valid[slot] = i < E.n;
+                float px = 0.f, py = 0.f, pz = 0.f, dx = 0.f, dy = 0.f, dz = 0.f;
+                if (valid[slot]) {
+                    px = __ldg(E.pos + 3 * i); py = __ldg(E.pos + 3 * i + 1); pz = __ldg(E.pos + 3 * i + 2);
+                    if (DIR && E.dir) { dx = __ldg(E.dir + 3 * i); dy = __ldg(E.dir + 3 * i + 1); dz = __ldg(E.dir + 3 * i + 2); }
+                }
+                uint32_t row[Core::K0 / 2];
+                Net::build_row(P, px, py, pz, dx, dy, dz, row);
+                Net::store_row(ctx, slot, row);
+            }
+            float o0[4], o1[4];
+            Net::mlp_compute(P, ctx, true, o0, o1);
+#pragma unroll
+            for (int slot = 0; slot < 2; ++slot) {
+                if (!valid[slot]) continue;
+                const float (&o)[4] = slot == 0 ? o0 : o1;
+                const long long i = idx[slot];
+                // output parametrisation, reference :1054-1072, 1149-1158 (value, not valueNoClamping)
+                if (P.output_mode == D_OUT_DENSITY) E.out[i] = sigmoidf_(o[0]);
+                else if (P.output_mode == D_OUT_DENSITY_DIRECT) E.out[i] = o[0];
+                else {
+                    float4 c;
+                    if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
+                    else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
+                    reinterpret_cast<float4*>(E.out)[i] = c;
+                }
+            }
         }
     }
     tc_epilogue<Net>(ctx);

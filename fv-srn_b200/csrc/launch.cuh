@@ -35,19 +35,29 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
     const int threads = is_tc ? kTcThreads : kWarpsPerBlock * 32;
     const int smem = blob + (is_dvr ? kTfSmemFloats * 4 : 0) + (is_tc ? int(sizeof(TcShared)) : kWarpsPerBlock * Net::STAGE_BYTES);
+    const bool relu = P.activation == D_ACT_RELU;   // the common case gets its own instantiation of the tcgen05 kernels
     const void* fn = kind == KIND_DVR ? (const void*)dvr_kernel<H16, GC16, DIR>
                    : kind == KIND_EVAL ? (const void*)eval_kernel<H16, GC16, DIR>
-                   : kind == KIND_DVR_TC ? (const void*)dvr_tc_kernel<H16, GC16, DIR> : (const void*)eval_tc_kernel<H16, GC16, DIR>;
+                   : kind == KIND_DVR_TC ? (relu ? (const void*)dvr_tc_kernel<H16, GC16, DIR, true> : (const void*)dvr_tc_kernel<H16, GC16, DIR, false>)
+                                         : (relu ? (const void*)eval_tc_kernel<H16, GC16, DIR, true> : (const void*)eval_tc_kernel<H16, GC16, DIR, false>);
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     int bps = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, threads, smem);
     if (e != cudaSuccess) return e;
     if (bps < 1) return cudaErrorLaunchOutOfResources;
-    if (is_tc) bps = min(bps, 512 / SrnTc<H16, GC16, DIR>::TMEM_COLS);   // TMEM: 512 columns per SM
     cudaFuncAttributes fa;
     e = cudaFuncGetAttributes(&fa, fn);
     if (e != cudaSuccess) return e;
+    if (is_tc) {
+        // The occupancy API reports 1 CTA/SM for kernels that allocate TMEM; co-residency is in fact bounded by
+        // registers, shared memory (+1 KiB reserved per CTA) and the 512 TMEM columns of an SM (measured:
+        // profiles/microbench). Surplus CTAs of the persistent grid would only queue, never deadlock.
+        const int by_regs = 65536 / (((fa.numRegs + 7) / 8 * 8) * threads);
+        const int by_smem = int((228 * 1024) / (size_t(smem) + 1024));
+        const int by_tmem = 512 / SrnTc<H16, GC16, DIR, true>::TMEM_COLS;
+        bps = max(1, min(min(by_regs, by_smem), min(by_tmem, 16)));
+    }
     long long grid = (long long)bps * cfg->sm_count;
     if (cfg->max_blocks > 0 && grid > cfg->max_blocks) grid = cfg->max_blocks;
     if (grid < 1) grid = 1;
@@ -56,8 +66,14 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     switch (kind) {
         case KIND_DVR: dvr_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp)); break;
         case KIND_EVAL: eval_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp)); break;
-        case KIND_DVR_TC: dvr_tc_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp)); break;
-        default: eval_tc_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp)); break;
+        case KIND_DVR_TC:
+            if (relu) dvr_tc_kernel<H16, GC16, DIR, true><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
+            else dvr_tc_kernel<H16, GC16, DIR, false><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
+            break;
+        default:
+            if (relu) eval_tc_kernel<H16, GC16, DIR, true><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp));
+            else eval_tc_kernel<H16, GC16, DIR, false><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp));
+            break;
     }
     return cudaGetLastError();
 }

@@ -46,6 +46,11 @@ struct NetParams {
     GridGroup groups[4];
     float box_min[3];
     float box_size[3];
+    // tcgen05 path: latent grids as hardware-filtered fp16 RGBA 3-D textures (4 channels each; the reference's own
+    // addressing: normalised coordinates, clamp, linear - volume_interpolation_network.cpp:470-504) and the Fourier
+    // matrix as fp16x2 pairs in the kernel-parameter constant bank (index (k*NF + i)/2)
+    unsigned long long tex_a[8], tex_b[8];
+    uint32_t fourier2[192];
     int dbg_flags;       // bring-up switches (env FVSRN_TC_DEBUG): bit0 = swap LBO/SBO of the UMMA weight descriptors
 };
 

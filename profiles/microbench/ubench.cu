@@ -120,6 +120,50 @@ __global__ void __launch_bounds__(128) fetch_ldg_kernel(const uint4* __restrict_
     out[i] = r;
 }
 
+// hybrid: channels 0-7 through the texture units, channels 8-15 through LDG.128 (are TMU filter rate and LSU return
+// bandwidth independent limits?)
+__global__ void __launch_bounds__(128) fetch_hybrid_kernel(Tex4 T, const uint4* __restrict__ grid, int N, int steps, float* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    __half2 tot[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) tot[j] = __float2half2_rn(0.f);
+    for (int s = 0; s < steps; ++s) {
+        float x, y, z; ray_pos(i, s, x, y, z);
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+            const float4 v = tex3D<float4>(T.t[g], x, y, z);
+            tot[2 * g] = __hadd2(tot[2 * g], __floats2half2_rn(v.x, v.y));
+            tot[2 * g + 1] = __hadd2(tot[2 * g + 1], __floats2half2_rn(v.z, v.w));
+        }
+        const float ux = x * N - 0.5f, uy = y * N - 0.5f, uz = z * N - 0.5f;
+        const float flx = floorf(ux), fly = floorf(uy), flz = floorf(uz);
+        const float fx = ux - flx, fy = uy - fly, fz = uz - flz;
+        const int ix = int(flx), iy = int(fly), iz = int(flz);
+        const int xs[2] = {min(max(ix, 0), N - 1), min(max(ix + 1, 0), N - 1)};
+        const int ys[2] = {min(max(iy, 0), N - 1), min(max(iy + 1, 0), N - 1)};
+        const int zs[2] = {min(max(iz, 0), N - 1), min(max(iz + 1, 0), N - 1)};
+        const float wx[2] = {1.f - fx, fx}, wy[2] = {1.f - fy, fy}, wz[2] = {1.f - fz, fz};
+        __half2 acc[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[j] = __float2half2_rn(0.f);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const uint4* p = grid + (size_t)((zs[c >> 2] * N + ys[(c >> 1) & 1]) * N + xs[c & 1]) * 2;
+            const uint4 b = __ldg(p + 1);
+            const __half2 w = __float2half2_rn(wz[c >> 2] * wy[(c >> 1) & 1] * wx[c & 1]);
+            const uint32_t u[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[j] = __hfma2(w, *reinterpret_cast<const __half2*>(&u[j]), acc[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) tot[4 + j] = __hadd2(tot[4 + j], acc[j]);
+    }
+    float r = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r += __low2float(tot[j]) + __high2float(tot[j]);
+    out[i] = r;
+}
+
 // ---------------------------------------------------------------- 3. MUFU sin/cos throughput
 __global__ void __launch_bounds__(128) mufu_kernel(int iters, float* out) {
     float a = threadIdx.x * 0.001f, s = 0.f;
@@ -129,6 +173,15 @@ __global__ void __launch_bounds__(128) mufu_kernel(int iters, float* out) {
         a += 0.01f;
     }
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// 4. weight quantisation of the texture filter: a 2x2x2 half4 texture whose value is the x index -> result = alpha_q(a)
+__global__ void texq_kernel(cudaTextureObject_t t, int n, float* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float a = float(i) / float(n);            // wanted fractional weight
+    const float x = (0.5f + a) / 2.f;               // normalised coordinate: xB = x*2 - 0.5 = a
+    out[i] = tex3D<float4>(t, x, 0.25f, 0.25f).x;
 }
 
 int main() {
@@ -189,8 +242,40 @@ int main() {
     CK(cudaEventElapsedTime(&ms, e0, e1)); CK(cudaMemcpy(o2.data(), d_out, rays * 4, cudaMemcpyDeviceToHost));
     printf("fetch LDG.128 x16 + HFMA2: %.3f ms, %.3e samples/s, %.2f clk/sample/SM at max clock\n", ms, double(rays) * steps / (ms * 1e-3),
            ms * 1e-3 * clk_khz * 1e3 * sms / (double(rays) * steps));
+    for (int rep = 0; rep < 2; ++rep) {
+        CK(cudaEventRecord(e0)); fetch_hybrid_kernel<<<rays / 128, 128>>>(T, d_grid, N, steps, d_out); CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1)); CK(cudaGetLastError());
+    }
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    printf("fetch hybrid (2 tex3D + 8 LDG.128): %.3f ms, %.3e samples/s, %.2f clk/sample/SM at max clock\n", ms, double(rays) * steps / (ms * 1e-3),
+           ms * 1e-3 * clk_khz * 1e3 * sms / (double(rays) * steps));
     double md = 0; for (int i = 0; i < rays; ++i) md = fmax(md, fabs(double(o1[i]) - o2[i]) / steps);
     printf("tex vs ldg: max |diff| per step (sum over 16 channels) %.3e\n", md);
+    {   // 4
+        cudaChannelFormatDesc fd = cudaCreateChannelDescHalf4();
+        cudaArray_t arr; CK(cudaMalloc3DArray(&arr, &fd, make_cudaExtent(2, 2, 2)));
+        std::vector<__half> sub(8 * 4);
+        for (int v = 0; v < 8; ++v) for (int c = 0; c < 4; ++c) sub[v * 4 + c] = __float2half(float(v & 1));
+        cudaMemcpy3DParms cp = {};
+        cp.srcPtr = make_cudaPitchedPtr(sub.data(), 2 * 8, 2, 2); cp.dstArray = arr; cp.extent = make_cudaExtent(2, 2, 2); cp.kind = cudaMemcpyHostToDevice;
+        CK(cudaMemcpy3D(&cp));
+        cudaResourceDesc rd = {}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+        cudaTextureDesc td = {}; td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 1;
+        cudaTextureObject_t t; CK(cudaCreateTextureObject(&t, &rd, &td, nullptr));
+        const int n = 4096; float* d_q; CK(cudaMalloc(&d_q, n * 4));
+        texq_kernel<<<n / 128, 128>>>(t, n, d_q); CK(cudaDeviceSynchronize());
+        std::vector<float> q(n); CK(cudaMemcpy(q.data(), d_q, n * 4, cudaMemcpyDeviceToHost));
+        // model candidates: round-to-nearest / truncation of a*256
+        int bad_rn = 0, bad_tr = 0; double maxdev = 0;
+        for (int i = 0; i < n; ++i) {
+            const float a = float(i) / n;
+            if (q[i] != floorf(a * 256.f + 0.5f) / 256.f) ++bad_rn;
+            if (q[i] != floorf(a * 256.f) / 256.f) ++bad_tr;
+            maxdev = fmax(maxdev, fabs(q[i] - a));
+        }
+        printf("texq: %d samples, mismatches vs round-to-nearest(a*256)/256: %d, vs trunc: %d, max |alpha_q - a| = %.5f\n", n, bad_rn, bad_tr, maxdev);
+        printf("texq first values:"); for (int i = 0; i < 40; ++i) printf(" %.5f", q[i]); printf("\n");
+    }
     // 3
     for (int rep = 0; rep < 2; ++rep) {
         CK(cudaEventRecord(e0)); mufu_kernel<<<sms * 16, 128>>>(4096, d_out); CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1)); CK(cudaGetLastError());
