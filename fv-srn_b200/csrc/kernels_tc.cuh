@@ -88,17 +88,22 @@ struct SrnTc {
         }
 #pragma unroll
         for (int g = 0; g < GC16; ++g) {
-            const float frac = P.groups[g].frac;    // CTA-uniform
+            const float frac = P.groups[g].frac;    // grid-uniform
+            float4 v[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) v[q] = tex3D<float4>(P.tex_a[4 * g + q], px, py, pz);
+            if (frac > 0.f) {   // temporal lerp of the two keyframes after the fetch, in fp32 (reference :590-604)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 w = tex3D<float4>(P.tex_b[4 * g + q], px, py, pz);
+                    v[q].x = fmaf(frac, w.x - v[q].x, v[q].x); v[q].y = fmaf(frac, w.y - v[q].y, v[q].y);
+                    v[q].z = fmaf(frac, w.z - v[q].z, v[q].z); v[q].w = fmaf(frac, w.w - v[q].w, v[q].w);
+                }
+            }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                float4 v = tex3D<float4>(P.tex_a[4 * g + q], px, py, pz);
-                if (frac > 0.f) {   // temporal lerp of the two keyframes after the fetch, in fp32 (reference :590-604)
-                    const float4 w = tex3D<float4>(P.tex_b[4 * g + q], px, py, pz);
-                    v.x = fmaf(frac, w.x - v.x, v.x); v.y = fmaf(frac, w.y - v.y, v.y);
-                    v.z = fmaf(frac, w.z - v.z, v.z); v.w = fmaf(frac, w.w - v.w, v.w);
-                }
-                row[H / 2 + g * 8 + 2 * q] = tc::pack_h2(v.x, v.y);
-                row[H / 2 + g * 8 + 2 * q + 1] = tc::pack_h2(v.z, v.w);
+                row[H / 2 + g * 8 + 2 * q] = tc::pack_h2(v[q].x, v[q].y);
+                row[H / 2 + g * 8 + 2 * q + 1] = tc::pack_h2(v[q].z, v[q].w);
             }
         }
     }

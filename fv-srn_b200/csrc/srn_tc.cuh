@@ -54,10 +54,10 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 #else
     asm volatile("{\n\t.reg .pred p;\n\t"
                  "WAIT_%=:\n\t"
-                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+                 "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"   // suspends up to the hint: no busy polling
                  "@p bra DONE_%=;\n\t"
                  "bra WAIT_%=;\n\t"
-                 "DONE_%=:\n\t}\n" :: "r"(bar), "r"(parity) : "memory");
+                 "DONE_%=:\n\t}\n" :: "r"(bar), "r"(parity), "r"(0x989680u) : "memory");
 #endif
 }
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
