@@ -36,7 +36,7 @@ class _Net(C.Structure):
         ("wlast", C.c_void_p), ("blast", C.c_void_p),
         ("ngroups", C.c_int32), ("gx", C.c_int32), ("gy", C.c_int32), ("gz", C.c_int32),
         ("ga", C.c_void_p * 4), ("gb", C.c_void_p * 4), ("frac", C.c_float * 4), ("gstride", C.c_int32 * 4),
-        ("box_min", C.c_float * 3), ("box_size", C.c_float * 3)]
+        ("box_min", C.c_float * 3), ("box_size", C.c_float * 3), ("tex_filter", C.c_int32), ("acc32", C.c_int32)]
 
 
 class _Dvr(C.Structure):
@@ -61,10 +61,12 @@ def lib():
 class OracleNetwork:
     """Flattens a ``volnet.SceneNetwork`` (parsed .volnet) into the oracle's C struct."""
 
-    def __init__(self, net, time: float = 0.0, ensemble: int = 0, unit_box: bool = False):
+    def __init__(self, net, time: float = 0.0, ensemble: int = 0, unit_box: bool = False, tex_filter: bool = False, acc32: bool = False):
         self.net = net
         self._keep = []
         n = _Net()
+        n.acc32 = int(acc32)             # fp32 accumulation / activation per layer (tcgen05 kernels) instead of fp16 (wmma path)
+        n.tex_filter = int(tex_filter)   # latent fetch with texture-unit weight quantisation (reference / tcgen05 kernel)
         H = net.input_channels_out()
         gc = net.latent_channels()
         assert net.num_fourier > 0, "oracle: networks without Fourier features are not on the hot path"
@@ -118,9 +120,10 @@ class OracleNetwork:
     def cout(self): return int(self.c.cout)
 
 
-def evaluate(net, positions, directions=None, time=0.0, ensemble=0, fp32=False):
-    """IVolumeInterpolation::evaluate restated on the CPU. positions (N,3) in [0,1]^3 -> (N,cout) float32."""
-    on = OracleNetwork(net, time, ensemble, unit_box=True)
+def evaluate(net, positions, directions=None, time=0.0, ensemble=0, fp32=False, tex_filter=False, acc32=False):
+    """IVolumeInterpolation::evaluate restated on the CPU. positions (N,3) in [0,1]^3 -> (N,cout) float32.
+    tex_filter: fetch the latent grid with the texture unit's 8-bit fractional weights (reference + tcgen05 kernel)."""
+    on = OracleNetwork(net, time, ensemble, unit_box=True, tex_filter=tex_filter, acc32=acc32)
     pos = np.ascontiguousarray(positions, dtype=np.float32)
     d = None if directions is None else np.ascontiguousarray(directions, dtype=np.float32)
     out = np.empty((pos.shape[0], on.cout), np.float32)
@@ -129,8 +132,8 @@ def evaluate(net, positions, directions=None, time=0.0, ensemble=0, fp32=False):
     return out
 
 
-def features(net, positions, time=0.0, ensemble=0):
-    on = OracleNetwork(net, time, ensemble, unit_box=True)
+def features(net, positions, time=0.0, ensemble=0, tex_filter=False, acc32=False):
+    on = OracleNetwork(net, time, ensemble, unit_box=True, tex_filter=tex_filter, acc32=acc32)
     pos = np.ascontiguousarray(positions, dtype=np.float32)
     K0 = on.c.H + on.c.grid_c
     rows = np.empty((pos.shape[0], K0), np.float16)
@@ -140,9 +143,9 @@ def features(net, positions, time=0.0, ensemble=0):
 
 def render_dvr(net, *, width, height, camera, fov_y, stepsize, tf, tf_kind=0, alpha_early_out=1 - 1e-5,
                density_min=0.0, density_max=1.0, early_out=True, blend_mode=1, spp=1, time=0.0, ensemble=0,
-               tile=None, fp32=False):
+               tile=None, fp32=False, tex_filter=False, acc32=False):
     """ImageEvaluatorSimple::render restated on the CPU -> (img (B,8,H,W) f32, steps (B,H,W) i32, valid_samples)."""
-    on = OracleNetwork(net, time, ensemble, unit_box=False)
+    on = OracleNetwork(net, time, ensemble, unit_box=False, tex_filter=tex_filter, acc32=acc32)
     cam = np.ascontiguousarray(camera, dtype=np.float32).reshape(-1, 3, 3)
     B = cam.shape[0]
     d = _Dvr()

@@ -31,6 +31,13 @@ def env(request):
     import oracle
     _lib.lib()
     pr.DEFAULT_KERNEL_MODE = request.param
+    # the tcgen05 kernels fetch the latent grid through the texture units like the reference does (8-bit fractional
+    # filter weights) and accumulate in fp32 (TMEM); the mma.sync kernels blend the 8 corners with exact fp32-computed
+    # weights and accumulate in fp16 like the reference's wmma path. The oracle restates either arithmetic.
+    import functools, types
+    tex = request.param == "tcgen05"
+    oracle = types.SimpleNamespace(evaluate=functools.partial(oracle.evaluate, tex_filter=tex, acc32=tex),
+                                   render_dvr=functools.partial(oracle.render_dvr, tex_filter=tex, acc32=tex))
     return type("Env", (), dict(torch=torch, pr=pr, scenes=scenes, volnet=volnet, oracle=oracle, lib=_lib, mode=request.param))
 
 

@@ -21,6 +21,10 @@ def test_oracle_points_match_reference_network(name):
     # 'world' = unclamped output of the reference module (network.py:204-235) = IVolumeInterpolation::evaluate
     assert np.abs(o16 - g.world).max() < 1e-2                            # the reference's own tolerance, testSRN.cpp:408-411
     assert np.abs(o32 - g.world).max() < 6e-3                            # fp32 math on fp16-rounded weights / grid
+    # the arithmetic of the tcgen05 kernels (texture-unit latent fetch with 8-bit fractional weights, which is also how
+    # the reference kernel fetches; fp32 accumulation) is pinned to the same fixtures at the same tolerance
+    otc = oracle.evaluate(g.net, g.positions, time=g.time, tex_filter=True, acc32=True)
+    assert np.isfinite(otc).all() and np.abs(otc - g.world).max() < 1e-2
 
 
 @pytest.mark.parametrize("name", [n for n in golden_names() if Golden(n).has_dvr])
@@ -32,6 +36,9 @@ def test_oracle_dvr_matches_reference_raymarcher(name, plume_tf):
         assert psnr(img[0, :4], g.dvr) >= 50.0, "north_star: PSNR >= 50 dB against the reference's PyTorch render"
         assert int(steps.sum()) == nvalid
         assert np.isnan(img[0, 7][img[0, 3] == 0]).all()                 # depth = 0/0 for empty pixels, as the reference
+    img, _, _ = oracle.render_dvr(g.net, width=g.dvr_size, height=g.dvr_size, camera=g.camera, fov_y=scenes.DEFAULT_FOV_Y,
+                                  stepsize=g.dvr_step, tf=plume_tf, time=g.time, tex_filter=True, acc32=True)
+    assert psnr(img[0, :4], g.dvr) >= 50.0                               # tcgen05-kernel arithmetic vs the reference render
 
 
 def test_oracle_is_deterministic_and_tile_consistent(plume_tf):
