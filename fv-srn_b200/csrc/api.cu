@@ -232,6 +232,12 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
     for (int i = 0; i < 3; ++i) { P.box_min[i] = unit_box ? 0.f : n.box_min[i]; P.box_size[i] = unit_box ? 1.f : n.box_size[i]; }
     if (n.fourier.size() > 2 * sizeof(P.fourier2) / sizeof(P.fourier2[0])) throw std::runtime_error("Fourier matrix too large");
     std::memcpy(P.fourier2, n.fourier.data(), n.fourier.size() * 2);
+    {   // last layer of density networks (cout == 1) for the in-register dot product of the tcgen05 kernels
+        const Layer& last = n.layers.back();
+        uint16_t* w = reinterpret_cast<uint16_t*>(P.wlast2);
+        for (int k = 0; k < last.cin && k < 128; ++k) w[k] = last.w(0, k);
+        P.blast = f16_to_f32(last.bias[0]);
+    }
     static const int dbg = [] { const char* e = std::getenv("FVSRN_TC_DEBUG"); return e ? std::atoi(e) : 0; }();
     P.dbg_flags = dbg;
     return P;

@@ -161,21 +161,54 @@ struct SrnTc {
         }
     }
 
+    // Last hidden layer's epilogue of a density network (one output): the 1 x H last layer is a dot product of the
+    // activations this thread already holds (fp16x2 FMAs in two interleaved chains, summed in fp32), as the reference
+    // does it on the CUDA cores (renderer_volume_tensorcores.cuh:1138-1143) - no further tensor-core round trip.
+    static __device__ __forceinline__ float epilogue_dot(const NetParams& P, const Ctx& c, int slot, int act) {
+        __half2 a0 = __float2half2_rn(0.f), a1 = a0;
+#pragma unroll
+        for (int c0 = 0; c0 < H; c0 += 32) {
+            uint32_t v[32];
+            if (H - c0 >= 32) tc::tmem_ld32(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld16(c.tmem_lane + d_col(slot) + c0, v);
+            tc::wait_ld();
+#pragma unroll
+            for (int j = 0; j < 16; j += 2) {
+                if (H - c0 >= 32 || j < 8) {
+                    const uint32_t p0 = RELU ? tc::pack_relu(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])) : tc::act_pack(act, c.af, v[2 * j], v[2 * j + 1]);
+                    const uint32_t p1 = RELU ? tc::pack_relu(__uint_as_float(v[2 * j + 2]), __uint_as_float(v[2 * j + 3])) : tc::act_pack(act, c.af, v[2 * j + 2], v[2 * j + 3]);
+                    a0 = __hfma2(u2h(p0), u2h(P.wlast2[c0 / 2 + j]), a0);
+                    a1 = __hfma2(u2h(p1), u2h(P.wlast2[c0 / 2 + j + 1]), a1);
+                }
+            }
+        }
+        const float2 f0 = __half22float2(a0), f1 = __half22float2(a1);
+        return P.blast + ((f0.x + f0.y) + (f1.x + f1.y));
+    }
+
     // Compute warps: run the layer chain for the 2 x 128 samples whose layer-0 rows were stored with store_row().
     // A warp that is not `warp_active` (all its rays finished) keeps the barrier protocol going but skips the arithmetic.
     static __device__ __forceinline__ void mlp_compute(const NetParams& P, Ctx& c, bool warp_active, float (&out0)[4], float (&out1)[4]) {
         const int act = P.activation;
+        const bool scalar_last = P.output_mode < D_OUT_RGBO;    // density networks: last layer in registers
 #pragma unroll 1
         for (int l = 0; l <= P.num_hidden; ++l) {
+            const bool dot = scalar_last && l == P.num_hidden;
 #pragma unroll
             for (int slot = 0; slot < 2; ++slot) {
+                float (&out)[4] = slot == 0 ? out0 : out1;
                 tc::mbar_wait(c.done + 8 * slot, c.phase);
                 tc::fence_after_sync();
-                if (warp_active) epilogue(c, slot, act);
-                publish(c, slot);
+                if (dot) {
+                    out[0] = warp_active ? epilogue_dot(P, c, slot, act) : 0.f;
+                    out[1] = out[2] = out[3] = 0.f;
+                } else {
+                    if (warp_active) epilogue(c, slot, act);
+                    publish(c, slot);
+                }
             }
             c.phase ^= 1u;
         }
+        if (scalar_last) { tc::fence_before_sync(); return; }
 #pragma unroll
         for (int slot = 0; slot < 2; ++slot) {
             float (&out)[4] = slot == 0 ? out0 : out1;
@@ -200,8 +233,9 @@ struct SrnTc {
 
     // MMA thread: the matching issue schedule of one trip. `c.phase` here is the parity of the ready barriers.
     static __device__ __forceinline__ void mlp_issue(const NetParams& P, Ctx& c) {
+        const int last = (P.output_mode < D_OUT_RGBO) ? P.num_hidden - 1 : P.num_hidden;   // see epilogue_dot
 #pragma unroll 1
-        for (int l = -1; l <= P.num_hidden; ++l) {
+        for (int l = -1; l <= last; ++l) {
 #pragma unroll
             for (int slot = 0; slot < 2; ++slot) {
                 tc::mbar_wait(c.ready + 8 * slot, c.phase);
