@@ -154,7 +154,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     import fvsrn_b200  # noqa: F401
-    from fvsrn_b200 import pyrenderer as pr, volnet, _lib
+    from fvsrn_b200 import pyrenderer as pr, volnet, _lib, dist as fdist
 
     if not torch.cuda.is_available():
         raise RuntimeError("bench.py needs a CUDA device: the fV-SRN B200 path has no CPU fallback")
@@ -185,7 +185,6 @@ def run_b200(args):
     p = ie._params(S, S, cam_dev, tf_dev, out.stride())
     p.counters_dev = counters.data_ptr()
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    gather_list = [torch.empty((1, 4, S, S), dtype=torch.float32, device="cuda") for _ in range(world)] if (world > 1 and rank == 0) else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
 
     def step(ev=None):
@@ -194,7 +193,7 @@ def run_b200(args):
         if ev: ev[1].record()
         rgba = ie.extract_color(out)
         if world > 1:
-            dist.gather(rgba, gather_list, dst=0)
+            fdist.gather_views(rgba, world)      # one NCCL gather of the finished RGBA views on rank 0
         if ev: ev[2].record()
         return rgba
 

@@ -1,0 +1,129 @@
+"""
+Multi-GPU sharding of the DVR path. The reference is single-GPU; rays are independent, so a
+frame or a multi-view batch shards with no exchange during rendering: one process per GPU (torchrun), the network
+replicated, work partitioned by screen bands (one big frame, BASELINE C4) or by view (camera sweeps, C5), and ONE
+collective per frame / batch: the finished RGBA pieces are gathered on rank 0.
+
+Everything here is backend-agnostic (NCCL on the GPUs, gloo in the CPU tests): the partition functions are pure, the
+gather works on whatever device the tensors live on, and the renderer is passed in as a callable.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+Rect = Tuple[int, int, int, int]   # x0, y0, w, h  (the tile rectangle of fvsrn_dvr_params)
+
+
+def world_info() -> Tuple[int, int]:
+    """(rank, world_size); (0, 1) when torch.distributed is not initialised."""
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def partition_views(num_views: int, world: int, rank: int) -> List[int]:
+    """Views of a camera sweep owned by `rank`: contiguous blocks, sizes differing by at most one."""
+    if not (0 <= rank < world):
+        raise ValueError("rank out of range")
+    base, rem = divmod(num_views, world)
+    start = rank * base + min(rank, rem)
+    return list(range(start, start + base + (1 if rank < rem else 0)))
+
+
+def partition_bands(width: int, height: int, world: int, rank: int, band: int = 64) -> List[Rect]:
+    """Screen-tile sharding of one frame: full-width bands of `band` rows dealt round-robin, so that every rank gets
+    rows from all over the image (empty rays at the borders finish early; contiguous blocks would be unbalanced)."""
+    if band <= 0 or band % 8:
+        raise ValueError("band height must be a positive multiple of 8 (the kernel's pixel-tile height)")
+    rects = []
+    for i, y0 in enumerate(range(0, height, band)):
+        if i % world == rank:
+            rects.append((0, y0, width, min(band, height - y0)))
+    return rects
+
+
+def band_rows(rects: Sequence[Rect]) -> int:
+    return sum(r[3] for r in rects)
+
+
+def pack_bands(img: torch.Tensor, rects: Sequence[Rect], channels: int = 4) -> torch.Tensor:
+    """(B,C>=channels,H,W) -> (B,channels,rows,W): this rank's bands stacked along y (contiguous, ready to send)."""
+    if not rects:
+        return img.new_zeros((img.shape[0], channels, 0, img.shape[3]))
+    return torch.cat([img[:, :channels, y0:y0 + h, :] for (_, y0, _, h) in rects], dim=2).contiguous()
+
+
+def gather_bands(local: torch.Tensor, width: int, height: int, band: int = 64, dst: int = 0) -> Optional[torch.Tensor]:
+    """Gathers every rank's packed bands on `dst` and reassembles the (B,C,H,W) frame there (None elsewhere).
+    Ranks may own different numbers of rows, so pieces are padded to the largest and sent with one gather."""
+    rank, world = world_info()
+    B, Cc = local.shape[0], local.shape[1]
+    if world == 1:
+        rects = partition_bands(width, height, 1, 0, band)
+        out = local.new_empty((B, Cc, height, width)); _scatter_rows(out, local, rects)
+        return out
+    rows = [band_rows(partition_bands(width, height, world, r, band)) for r in range(world)]
+    pad = max(rows)
+    buf = local.new_zeros((B, Cc, pad, width))
+    buf[:, :, :local.shape[2]] = local
+    pieces = [torch.empty_like(buf) for _ in range(world)] if rank == dst else None
+    dist.gather(buf, pieces, dst=dst)
+    if rank != dst:
+        return None
+    out = local.new_empty((B, Cc, height, width))
+    for r in range(world):
+        _scatter_rows(out, pieces[r][:, :, :rows[r]], partition_bands(width, height, world, r, band))
+    return out
+
+
+def _scatter_rows(out: torch.Tensor, packed: torch.Tensor, rects: Sequence[Rect]) -> None:
+    y = 0
+    for (_, y0, _, h) in rects:
+        out[:, :, y0:y0 + h, :] = packed[:, :, y:y + h, :]
+        y += h
+
+
+def gather_views(local: torch.Tensor, num_views: int, dst: int = 0) -> Optional[torch.Tensor]:
+    """local (v_rank,C,H,W) = this rank's views (partition_views order) -> (num_views,C,H,W) on `dst`."""
+    rank, world = world_info()
+    if world == 1:
+        return local
+    counts = [len(partition_views(num_views, world, r)) for r in range(world)]
+    pad = max(counts)
+    buf = local.new_zeros((pad,) + tuple(local.shape[1:]))
+    buf[:local.shape[0]] = local
+    pieces = [torch.empty_like(buf) for _ in range(world)] if rank == dst else None
+    dist.gather(buf, pieces, dst=dst)
+    if rank != dst:
+        return None
+    return torch.cat([pieces[r][:counts[r]] for r in range(world)], dim=0)
+
+
+def render_frame_sharded(render_rect: Callable[[Rect], torch.Tensor], width: int, height: int, band: int = 64,
+                         dst: int = 0) -> Optional[torch.Tensor]:
+    """One frame across all ranks. `render_rect((x0,y0,w,h))` renders that rectangle into a (B,8,H,W) (or (B,4,H,W))
+    image on the local device (ImageEvaluatorSimple with `.tile` set); returns the gathered RGBA frame on `dst`."""
+    rank, world = world_info()
+    rects = partition_bands(width, height, world, rank, band)
+    parts = []
+    for r in rects:
+        img = render_rect(r)
+        parts.append(img[:, :4, r[1]:r[1] + r[3], :])
+    local = torch.cat(parts, dim=2).contiguous() if parts else None
+    if local is None:   # a rank without bands still takes part in the collective
+        probe = render_rect((0, 0, width, 8))
+        local = probe.new_zeros((probe.shape[0], 4, 0, width))
+    return gather_bands(local, width, height, band, dst)
+
+
+def render_views_sharded(render_view: Callable[[int], torch.Tensor], num_views: int, dst: int = 0) -> Optional[torch.Tensor]:
+    """A camera sweep across all ranks. `render_view(i)` -> (1,C,H,W) of view i on the local device."""
+    rank, world = world_info()
+    mine = partition_views(num_views, world, rank)
+    if not mine:
+        raise ValueError("more ranks than views")
+    local = torch.cat([render_view(i)[:, :4] for i in mine], dim=0).contiguous()
+    return gather_views(local, num_views, dst)

@@ -1,0 +1,99 @@
+"""
+Host-side logic of the multi-GPU path (fv-srn_b200/dist.py) on CPU: world_size-2 (and 3) gloo process groups, a
+deterministic stand-in renderer. The GPU path uses the same functions with NCCL (bench.py --gpus N).
+"""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import fvsrn_b200  # noqa: F401
+from fvsrn_b200 import dist as fdist
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _fake_frame(width, height, batch=1):
+    """Deterministic (B,8,H,W) 'render' every rank can compute: value = f(b, c, y, x)."""
+    b, c, y, x = np.meshgrid(np.arange(batch), np.arange(8), np.arange(height), np.arange(width), indexing="ij")
+    return torch.from_numpy((b * 1000 + c * 100 + y + x / 4096.0).astype(np.float32))
+
+
+def _worker(rank, world, port, width, height, band, views, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        full = _fake_frame(width, height, 2)
+
+        def render_rect(rect):                       # a renderer that only fills the requested rectangle
+            x0, y0, w, h = rect
+            img = torch.zeros_like(full)
+            img[:, :, y0:y0 + h, x0:x0 + w] = full[:, :, y0:y0 + h, x0:x0 + w]
+            return img
+
+        frame = fdist.render_frame_sharded(render_rect, width, height, band)
+        ok_frame = (frame is None) if rank != 0 else bool(torch.equal(frame, full[:, :4]))
+
+        def render_view(i):
+            return _fake_frame(16, 8)[:, :4] + float(i)
+
+        sweep = fdist.render_views_sharded(render_view, views)
+        if rank == 0:
+            want = torch.cat([render_view(i) for i in range(views)], dim=0)
+            ok_views = bool(torch.equal(sweep, want))
+        else:
+            ok_views = sweep is None
+        q.put((rank, ok_frame, ok_views))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,width,height,band,views", [(2, 64, 200, 64, 5), (3, 40, 136, 8, 7), (2, 32, 24, 64, 2)])
+def test_sharded_frame_and_sweep_gloo(world, width, height, band, views):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, width, height, band, views, q)) for r in range(world)]
+    for p in procs: p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok_f and ok_v for _, ok_f, ok_v in res), res
+
+
+def test_partitions_cover_everything_exactly_once():
+    for world in (1, 2, 3, 4, 8):
+        for n in (1, 7, 8, 64):
+            got = sum((fdist.partition_views(n, world, r) for r in range(world)), [])
+            assert got == list(range(n))
+            sizes = [len(fdist.partition_views(n, world, r)) for r in range(world)]
+            assert max(sizes) - min(sizes) <= 1
+        for (w, h, band) in ((2048, 2048, 64), (100, 90, 8), (64, 8, 64)):
+            cover = np.zeros((h, w), np.int32)
+            for r in range(world):
+                for (x0, y0, ww, hh) in fdist.partition_bands(w, h, world, r, band):
+                    assert x0 == 0 and ww == w and y0 % 8 == 0
+                    cover[y0:y0 + hh, x0:x0 + ww] += 1
+            assert (cover == 1).all()
+    with pytest.raises(ValueError):
+        fdist.partition_bands(64, 64, 2, 0, band=12)
+    with pytest.raises(ValueError):
+        fdist.partition_views(4, 2, 2)
+
+
+def test_single_process_paths_need_no_process_group():
+    full = _fake_frame(48, 40)
+    rects = fdist.partition_bands(48, 40, 1, 0, 16)
+    packed = fdist.pack_bands(full, rects)
+    assert packed.shape == (1, 4, 40, 48)
+    assert torch.equal(fdist.gather_bands(packed, 48, 40, 16), full[:, :4])
+    assert fdist.world_info() == (0, 1)
