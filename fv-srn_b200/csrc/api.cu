@@ -232,6 +232,17 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
     for (int i = 0; i < 3; ++i) { P.box_min[i] = unit_box ? 0.f : n.box_min[i]; P.box_size[i] = unit_box ? 1.f : n.box_size[i]; }
     if (n.fourier.size() > 2 * sizeof(P.fourier2) / sizeof(P.fourier2[0])) throw std::runtime_error("Fourier matrix too large");
     std::memcpy(P.fourier2, n.fourier.data(), n.fourier.size() * 2);
+    {   // NeRF-style Fourier matrix? B[i][i%3] = 2^(i/3) * B[i%3][i%3] (exactly, in fp16), all other entries zero
+        const int nf = n.num_fourier;
+        bool nerf = !n.direction_in_fourier && nf >= 3 && int(n.fourier.size()) == 3 * nf;
+        for (int i = 0; nerf && i < nf; ++i)
+            for (int a = 0; a < 3; ++a) {
+                const float v = f16_to_f32(n.fourier[i + size_t(nf) * a]);
+                const float want = (a == i % 3) ? std::ldexp(f16_to_f32(n.fourier[(i % 3) + size_t(nf) * (i % 3)]), i / 3) : 0.f;
+                if (v != want || (a == i % 3 && !(std::fabs(v) > 0.f && std::fabs(v) < 30000.f))) nerf = false;
+            }
+        P.fourier_nerf = nerf ? 1 : 0;
+    }
     {   // last layer of density networks (cout == 1) for the in-register dot product of the tcgen05 kernels
         const Layer& last = n.layers.back();
         uint16_t* w = reinterpret_cast<uint16_t*>(P.wlast2);

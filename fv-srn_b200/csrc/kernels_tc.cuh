@@ -25,9 +25,11 @@ struct TcShared {           // fixed part of the dynamic shared memory, placed f
     int pad[2];
 };
 
-template <int H16, int GC16, bool DIR, bool RELU>
+// VARIANT: bit 0 = ReLU hidden activation, bit 1 = NeRF-style Fourier matrix (feature i = axis i%3 times 2^(i/3))
+template <int H16, int GC16, bool DIR, int VARIANT>
 struct SrnTc {
     using Core = Srn<H16, GC16, DIR>;
+    static constexpr bool RELU = (VARIANT & 1) != 0, NERF = (VARIANT & 2) != 0;
     static constexpr int H = Core::H, K0 = Core::K0, KT0 = K0 / 16, KTH = H / 16;
     static constexpr int NLAST = 16;                       // last layer padded to N = 16 (M=128 needs N % 16 == 0)
     // TMEM columns (32-bit): ones chunk | slot 0: D, A | slot 1: D, A
@@ -66,26 +68,57 @@ struct SrnTc {
             row[3] = h2u(__halves2half2(hdz, __float2half_rn(0.f)));
             d2x = __half2half2(hdx); d2y = __half2half2(hdy); d2z = __half2half2(hdz);
         }
-        const __half2 x2 = __half2half2(hx), y2 = __half2half2(hy), z2 = __half2half2(hz);
+        if constexpr (NERF && !DIR) {
+            // NeRF-style matrix (network.py:55-63): feature i has the single entry B[i][i%3] = 2^(i/3) * B[i%3][i%3]. The
+            // reference's fp16 phase of octave k is then exactly 2^k times the octave-0 phase (power-of-two scaling
+            // commutes with rounding), so only the three base phases go through the SFU; higher octaves follow from the
+            // double-angle identities in fp32 (error growth 2x per octave, < 1e-5 after 4: far below the fp16 rounding
+            // of the feature). 6 MUFU instead of 2*NF per sample.
+            float cs[NF], sn[NF];
 #pragma unroll
-        for (int i = 0; i < NF; i += 2) {   // reference :795-807: phase accumulated in fp16 (hmul, hfma, hfma), then cos / sin
-            __half2 c = __hmul2(x2, u2h(P.fourier2[(i + 0 * NF) / 2]));
-            c = __hfma2(y2, u2h(P.fourier2[(i + 1 * NF) / 2]), c);
-            c = __hfma2(z2, u2h(P.fourier2[(i + 2 * NF) / 2]), c);
-            if (DIR) {
-                if (P.dir_in_fourier) {
-                    c = __hfma2(d2x, u2h(P.fourier2[(i + 3 * NF) / 2]), c);
-                    c = __hfma2(d2y, u2h(P.fourier2[(i + 4 * NF) / 2]), c);
-                    c = __hfma2(d2z, u2h(P.fourier2[(i + 5 * NF) / 2]), c);
+            for (int a = 0; a < 3; ++a) {
+                const __half h = a == 0 ? hx : (a == 1 ? hy : hz);
+                const uint32_t w = P.fourier2[(a + a * NF) / 2];                       // B[a][a] = entry (a + a*NF)
+                const __half b = ((a + a * NF) & 1) ? __high2half(u2h(w)) : __low2half(u2h(w));
+                float s, c;
+                __sincosf(__half2float(__hmul(h, b)), &s, &c);
+                cs[a] = c; sn[a] = s;
+#pragma unroll
+                for (int i = a + 3; i < NF; i += 3) {
+                    const float u = s + s;
+                    const float s2 = u * c;
+                    c = fmaf(-u, s, 1.0f);
+                    s = s2;
+                    cs[i] = c; sn[i] = s;
                 }
             }
-            const float2 cf = __half22float2(c);
-            float s0, c0, s1, c1;
-            __sincosf(cf.x, &s0, &c0);
-            __sincosf(cf.y, &s1, &c1);
-            row[FOFF / 2 + i / 2] = tc::pack_h2(c0, c1);
-            row[FOFF / 2 + NF / 2 + i / 2] = tc::pack_h2(s0, s1);
-        }
+#pragma unroll
+            for (int i = 0; i < NF; i += 2) {
+                row[FOFF / 2 + i / 2] = tc::pack_h2(cs[i], cs[i + 1]);
+                row[FOFF / 2 + NF / 2 + i / 2] = tc::pack_h2(sn[i], sn[i + 1]);
+            }
+        } else {
+        const __half2 x2 = __half2half2(hx), y2 = __half2half2(hy), z2 = __half2half2(hz);
+    #pragma unroll
+            for (int i = 0; i < NF; i += 2) {   // reference :795-807: phase accumulated in fp16 (hmul, hfma, hfma), then cos / sin
+                __half2 c = __hmul2(x2, u2h(P.fourier2[(i + 0 * NF) / 2]));
+                c = __hfma2(y2, u2h(P.fourier2[(i + 1 * NF) / 2]), c);
+                c = __hfma2(z2, u2h(P.fourier2[(i + 2 * NF) / 2]), c);
+                if (DIR) {
+                    if (P.dir_in_fourier) {
+                        c = __hfma2(d2x, u2h(P.fourier2[(i + 3 * NF) / 2]), c);
+                        c = __hfma2(d2y, u2h(P.fourier2[(i + 4 * NF) / 2]), c);
+                        c = __hfma2(d2z, u2h(P.fourier2[(i + 5 * NF) / 2]), c);
+                    }
+                }
+                const float2 cf = __half22float2(c);
+                float s0, c0, s1, c1;
+                __sincosf(cf.x, &s0, &c0);
+                __sincosf(cf.y, &s1, &c1);
+                row[FOFF / 2 + i / 2] = tc::pack_h2(c0, c1);
+                row[FOFF / 2 + NF / 2 + i / 2] = tc::pack_h2(s0, s1);
+            }
+    }
 #pragma unroll
         for (int g = 0; g < GC16; ++g) {
             const float frac = P.groups[g].frac;    // grid-uniform
@@ -282,10 +315,10 @@ __device__ __forceinline__ void tc_epilogue(const typename Net::Ctx& c) {
     if ((threadIdx.x >> 5) == 4) tc::tmem_dealloc(c.tmem_base, Net::TMEM_COLS);
 }
 
-template <int H16, int GC16, bool DIR, bool RELU>
+template <int H16, int GC16, bool DIR, int VARIANT>
 __global__ void __launch_bounds__(kTcThreads, H16 <= 2 ? 4 : 1)
 dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
-    using Net = SrnTc<H16, GC16, DIR, RELU>;
+    using Net = SrnTc<H16, GC16, DIR, VARIANT>;
     using Core = typename Net::Core;
     extern __shared__ uint4 smem[];
     TcShared* sh = reinterpret_cast<TcShared*>(smem);
@@ -408,10 +441,10 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
     tc_epilogue<Net>(ctx);
 }
 
-template <int H16, int GC16, bool DIR, bool RELU>
+template <int H16, int GC16, bool DIR, int VARIANT>
 __global__ void __launch_bounds__(kTcThreads)
 eval_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ EvalParams E) {
-    using Net = SrnTc<H16, GC16, DIR, RELU>;
+    using Net = SrnTc<H16, GC16, DIR, VARIANT>;
     using Core = typename Net::Core;
     extern __shared__ uint4 smem[];
     TcShared* sh = reinterpret_cast<TcShared*>(smem);

@@ -35,11 +35,15 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
     const int threads = is_tc ? kTcThreads : kWarpsPerBlock * 32;
     const int smem = blob + (is_dvr ? kTfSmemFloats * 4 : 0) + (is_tc ? int(sizeof(TcShared)) : kWarpsPerBlock * Net::STAGE_BYTES);
-    const bool relu = P.activation == D_ACT_RELU;   // the common case gets its own instantiation of the tcgen05 kernels
+    // tcgen05 kernels: the common cases (ReLU, NeRF-style Fourier matrix) get their own instantiations
+    const int variant = (P.activation == D_ACT_RELU ? 1 : 0) | ((P.fourier_nerf && !DIR) ? 2 : 0);
+    const void* tc_dvr[4] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1>,
+                             (const void*)dvr_tc_kernel<H16, GC16, DIR, DIR ? 0 : 2>, (const void*)dvr_tc_kernel<H16, GC16, DIR, DIR ? 1 : 3>};
+    const void* tc_eval[4] = {(const void*)eval_tc_kernel<H16, GC16, DIR, 0>, (const void*)eval_tc_kernel<H16, GC16, DIR, 1>,
+                              (const void*)eval_tc_kernel<H16, GC16, DIR, DIR ? 0 : 2>, (const void*)eval_tc_kernel<H16, GC16, DIR, DIR ? 1 : 3>};
     const void* fn = kind == KIND_DVR ? (const void*)dvr_kernel<H16, GC16, DIR>
                    : kind == KIND_EVAL ? (const void*)eval_kernel<H16, GC16, DIR>
-                   : kind == KIND_DVR_TC ? (relu ? (const void*)dvr_tc_kernel<H16, GC16, DIR, true> : (const void*)dvr_tc_kernel<H16, GC16, DIR, false>)
-                                         : (relu ? (const void*)eval_tc_kernel<H16, GC16, DIR, true> : (const void*)eval_tc_kernel<H16, GC16, DIR, false>);
+                   : kind == KIND_DVR_TC ? tc_dvr[variant] : tc_eval[variant];
     cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     int bps = 0;
@@ -55,7 +59,7 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
         // profiles/microbench). Surplus CTAs of the persistent grid would only queue, never deadlock.
         const int by_regs = 65536 / (((fa.numRegs + 7) / 8 * 8) * threads);
         const int by_smem = int((228 * 1024) / (size_t(smem) + 1024));
-        const int by_tmem = 512 / SrnTc<H16, GC16, DIR, true>::TMEM_COLS;
+        const int by_tmem = 512 / SrnTc<H16, GC16, DIR, 0>::TMEM_COLS;
         bps = max(1, min(min(by_regs, by_smem), min(by_tmem, 16)));
     }
     long long grid = (long long)bps * cfg->sm_count;
@@ -63,17 +67,13 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     if (grid < 1) grid = 1;
     cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = fa.numRegs; cfg->threads = threads;
     if (cfg->query_only) return cudaSuccess;
+    if (is_tc) {
+        void* args[2] = {const_cast<NetParams*>(&P), const_cast<void*>(kp)};
+        return cudaLaunchKernel(fn, dim3(unsigned(grid)), dim3(threads), args, size_t(smem), s);
+    }
     switch (kind) {
         case KIND_DVR: dvr_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp)); break;
-        case KIND_EVAL: eval_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp)); break;
-        case KIND_DVR_TC:
-            if (relu) dvr_tc_kernel<H16, GC16, DIR, true><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
-            else dvr_tc_kernel<H16, GC16, DIR, false><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
-            break;
-        default:
-            if (relu) eval_tc_kernel<H16, GC16, DIR, true><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp));
-            else eval_tc_kernel<H16, GC16, DIR, false><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp));
-            break;
+        default: eval_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp)); break;
     }
     return cudaGetLastError();
 }

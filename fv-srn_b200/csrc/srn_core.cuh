@@ -51,6 +51,7 @@ struct NetParams {
     // matrix as fp16x2 pairs in the kernel-parameter constant bank (index (k*NF + i)/2)
     unsigned long long tex_a[8], tex_b[8];
     uint32_t fourier2[192];
+    int fourier_nerf;     // Fourier matrix has the NeRF layout (see SrnTc::build_row)
     uint32_t wlast2[64];  // density networks: last-layer weights as fp16x2 pairs (k, k+1) and its bias, for the in-thread dot product
     float blast;
     int dbg_flags;       // bring-up switches (env FVSRN_TC_DEBUG): bit0 = swap LBO/SBO of the UMMA weight descriptors
