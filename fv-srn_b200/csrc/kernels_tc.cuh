@@ -141,7 +141,8 @@ struct SrnTc {
         }
     }
 
-    // MMA thread: issue the K steps of one layer of one slot and commit to the slot's completion barrier.
+    // MMA warp (all lanes, converged; one elected lane issues): the K steps of one layer of one slot + commit to the
+    // slot's completion barrier.
     // The smem descriptor of K step kt differs from step 0 only in the address field of its low word.
     static __device__ __forceinline__ void issue_layer(const Ctx& c, int slot, uint32_t w_addr, int n, int kt_data, bool bias_chunk) {
         const uint32_t idesc = tc::make_idesc(128, n);
@@ -151,9 +152,9 @@ struct SrnTc {
         const uint32_t step = (2u * kstride) >> 4;
         const uint32_t d = c.tmem_base + d_col(slot);
         uint32_t a = c.tmem_base + a_col(slot);
-        for (int kt = 0; kt < kt_data; ++kt, lo += step, a += 8) tc::mma_ts2(d, a, lo, hi, idesc, kt > 0);
-        if (bias_chunk) tc::mma_ts2(d, c.tmem_base + ONES_COL, lo, hi, idesc, 1u);
-        tc::mma_commit(c.done + 8 * slot);
+        for (int kt = 0; kt < kt_data; ++kt, lo += step, a += 8) tc::mma_ts2_elect(d, a, lo, hi, idesc, kt > 0);
+        if (bias_chunk) tc::mma_ts2_elect(d, c.tmem_base + ONES_COL, lo, hi, idesc, 1u);
+        tc::mma_commit_elect(c.done + 8 * slot);
     }
 
     // per-CTA set-up after TMEM allocation: the constant ones chunk (compute threads)
@@ -358,8 +359,7 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
             for (int s = 0; s < D.spp; ++s)
                 for (;;) {
                     if (!__syncthreads_or(0)) break;
-                    if (lane == 0) Net::mlp_issue(P, ctx);
-                    __syncwarp();
+                    Net::mlp_issue(P, ctx);
                 }
             continue;
         }
@@ -452,9 +452,7 @@ eval_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Eval
     typename Net::Ctx ctx = tc_prologue<Net>(P, sh, sblob);
     const long long n256 = (E.n + 255) / 256;
     if ((threadIdx.x >> 5) == 4) {
-        if ((threadIdx.x & 31) == 0)
-            for (long long w = blockIdx.x; w < n256; w += gridDim.x) Net::mlp_issue(P, ctx);
-        __syncwarp();
+        for (long long w = blockIdx.x; w < n256; w += gridDim.x) Net::mlp_issue(P, ctx);
     } else {
         for (long long w = blockIdx.x; w < n256; w += gridDim.x) {
             long long idx[2]; bool valid[2];
