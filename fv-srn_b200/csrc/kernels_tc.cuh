@@ -16,6 +16,58 @@ namespace fvsrn {
 constexpr int kTcComputeThreads = 128;
 constexpr int kTcThreads = 160;            // + the MMA warp
 constexpr int kTcTileW = 16, kTcTileH = 8;
+constexpr int kTcTfFloats = 2560;          // shared-memory TF: up to 204 piecewise intervals x 12 floats, or 256 x float4 texels
+
+// Transfer function staged in shared memory in evaluation-ready form. Piecewise (reference renderer_tf_piecewise.cuh:
+// 27-52): one record of three float4 per interval i = (p_i, p_{i+1}, 1/(p_{i+1}-p_i), -), v_i, v_{i+1}-v_i, so that a
+// sample costs the interval search plus three LDS.128 and four FFMA. Texture / identity TFs are copied verbatim.
+__device__ __forceinline__ void tc_stage_tf(const DvrParams& D, int b, float* stf) {
+    if (D.tf_kind == 0) {
+        const float* src = D.tf + (D.tf_batch == 1 ? 0 : (size_t)b * D.tf_R * 5);
+        for (int i = threadIdx.x; i < D.tf_R - 1; i += blockDim.x) {
+            const float* v0 = src + i * 5; const float* v1 = v0 + 5;
+            const float p0 = __ldg(v0 + 4), p1 = __ldg(v1 + 4);
+            float4* rec = reinterpret_cast<float4*>(stf) + 3 * i;
+            const float4 a = make_float4(__ldg(v0), __ldg(v0 + 1), __ldg(v0 + 2), __ldg(v0 + 3));
+            const float4 e = make_float4(__ldg(v1), __ldg(v1 + 1), __ldg(v1 + 2), __ldg(v1 + 3));
+            rec[0] = make_float4(p0, p1, __fdiv_rn(1.0f, p1 - p0), 0.f);
+            rec[1] = a;
+            rec[2] = make_float4(e.x - a.x, e.y - a.y, e.z - a.z, e.w - a.w);
+        }
+    } else {
+        const int n = D.tf_kind == 1 ? D.tf_R * 4 : 2;
+        const float* src = D.tf + (D.tf_batch == 1 ? 0 : (size_t)b * n);
+        for (int i = threadIdx.x; i < n; i += blockDim.x) stf[i] = __ldg(src + i);
+    }
+}
+__device__ __forceinline__ float4 tc_tf_piecewise(const float* stf, int R, float d) {
+    const float4* rec = reinterpret_cast<const float4*>(stf);
+    int i = 0;
+    for (; i < R - 2; ++i)
+        if (rec[3 * i].y > d) break;
+    const float4 h = rec[3 * i], v0 = rec[3 * i + 1], dv = rec[3 * i + 2];
+    const float f = (fminf(fmaxf(d, h.x), h.y) - h.x) * h.z;
+    return make_float4(fmaf(f, dv.x, v0.x), fmaf(f, dv.y, v0.y), fmaf(f, dv.z, v0.z), fmaf(f, dv.w, v0.w));
+}
+// network output -> colour + absorption of one sample; same contract as shade_sample (kernels.cuh), TF from shared memory
+__device__ __forceinline__ float4 tc_shade_sample(const NetParams& P, const DvrParams& D, const float* stf, const float (&o)[4]) {
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (P.output_mode < D_OUT_RGBO) {
+        const float value = (P.output_mode == D_OUT_DENSITY) ? sigmoidf_(o[0]) : o[0];
+        if (value >= D.dmin) {
+            const float d2 = fminf(fmaxf((value - D.dmin) * D.inv_range, 0.f), 1.f);
+            if (D.tf_kind == 0) c = tc_tf_piecewise(stf, D.tf_R, d2);
+            else if (D.tf_kind == 1) c = tf_texture(stf, D.tf_R, d2);
+            else c = make_float4(d2 * stf[1], d2 * stf[1], d2 * stf[1], d2 * stf[0]);
+            c.w *= D.stepsize;
+        }
+    } else {    // colour network, SKIP_TRANSFER_FUNCTION path
+        if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
+        else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
+        c.w *= D.stepsize;
+    }
+    return c;
+}
 
 struct TcShared {           // fixed part of the dynamic shared memory, placed first (48 bytes)
     unsigned long long ready[2];   // slot operands written: one arrival per compute warp
@@ -330,9 +382,7 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
     const bool is_mma_warp = warp == 4;
 
     typename Net::Ctx ctx = tc_prologue<Net>(P, sh, sblob);
-    const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : (D.tf_kind == 1 ? D.tf_R * 4 : 2);
-    if (D.tf_batch == 1)
-        for (int i = threadIdx.x; i < tf_floats; i += blockDim.x) stf[i] = __ldg(D.tf + i);
+    if (D.tf_batch == 1) tc_stage_tf(D, 0, stf);
     __syncthreads();
 
     const float3 bmin = make_float3(P.box_min[0], P.box_min[1], P.box_min[2]);
@@ -353,6 +403,10 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
         const int trem = tile - bl * tiles_per_img;
         const int ty = trem / D.tiles_x, tx = trem - ty * D.tiles_x;
         const int b = D.b0 + bl;
+        if (D.tf_batch != 1) {      // per-view transfer function: staged for the view this tile belongs to
+            tc_stage_tf(D, b, stf);
+            __syncthreads();
+        }
 
         if (is_mma_warp) {
             // ---------------------------------------------------------------- MMA warp: one elected thread issues
@@ -367,7 +421,6 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
         const int x = D.x0 + tx * kTcTileW + lx;
         const int y = D.y0 + ty * kTcTileH + ly;
         const bool in_img = (x < D.x0 + D.tw) && (y < D.y0 + D.th);
-        const float* tfp = (D.tf_batch == 1) ? stf : (D.tf + (size_t)b * tf_floats);
         const CamFrame cf = load_camera(D, b);
 
         float4 pix_color = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -417,14 +470,16 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
                 float o0[4], o1[4];
                 Net::mlp_compute(P, ctx, warp_active, o0, o1);
                 if (lane == 0) n_exec += 64;
+                // both samples are shaded first (independent work, interleaved by the compiler), then composited in order
+                const float4 c0 = tc_shade_sample(P, D, stf, o0), c1 = tc_shade_sample(P, D, stf, o1);
                 if (valid0) {
                     ++steps;
-                    blend_sample(D, shade_sample(P, D, tfp, o0), t0, acc, acc_depth);
+                    blend_sample(D, c0, t0, acc, acc_depth);
                 }
                 const bool valid1 = in1 && (!D.early_out || (acc.w < D.alpha_early_out));
                 if (valid1) {
                     ++steps;
-                    blend_sample(D, shade_sample(P, D, tfp, o1), t1, acc, acc_depth);
+                    blend_sample(D, c1, t1, acc, acc_depth);
                 }
             }
             n_valid += steps;

@@ -34,7 +34,7 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     const bool is_tc = kind >= KIND_DVR_TC, is_dvr = (kind == KIND_DVR || kind == KIND_DVR_TC);
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
     const int threads = is_tc ? kTcThreads : kWarpsPerBlock * 32;
-    const int smem = blob + (is_dvr ? kTfSmemFloats * 4 : 0) + (is_tc ? int(sizeof(TcShared)) : kWarpsPerBlock * Net::STAGE_BYTES);
+    const int smem = blob + (is_dvr ? (is_tc ? kTcTfFloats : kTfSmemFloats) * 4 : 0) + (is_tc ? int(sizeof(TcShared)) : kWarpsPerBlock * Net::STAGE_BYTES);
     // tcgen05 kernels: the common cases (ReLU, NeRF-style Fourier matrix) get their own instantiations
     const int variant = (P.activation == D_ACT_RELU ? 1 : 0) | ((P.fourier_nerf && !DIR) ? 2 : 0);
     const void* tc_dvr[4] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1>,
