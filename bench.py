@@ -250,6 +250,11 @@ def run_b200(args):
     line = None
     if rank == 0:
         pk = peaks()
+        traffic = None
+        try:    # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture (never measured here)
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{args.workload}:{args.kernel_mode}", {}).get("bytes")
+        except Exception:
+            pass
         qi = _lib.QueryInfo(); _lib.check(L.fvsrn_query(sn._h, 0, C.byref(qi)))
         value = useful / (total_ms * 1e-3)
         ach = (cnt[0] * w["flop"]) / (kernel_ms * 1e-3) / 1e12            # rank 0's kernel, useful samples only
@@ -267,7 +272,7 @@ def run_b200(args):
                     "h2d_bytes_per_step": int(host_cam.numel() * 4 + host_tf.numel() * 4), "d2h_bytes_per_step": int(host_img.numel() * 4)},
             "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
-                         "traffic": None, "kernel": "dvr_tc_kernel (tcgen05.mma + TMEM)" if args.kernel_mode == "tcgen05" else "dvr_kernel (mma.sync)", "flop_per_sample": w["flop"], "peak_source": pk["source"] + ", burst bf16",
+                         "traffic": traffic, "kernel": "dvr_tc_kernel (tcgen05.mma + TMEM)" if args.kernel_mode == "tcgen05" else "dvr_kernel (mma.sync)", "flop_per_sample": w["flop"], "peak_source": pk["source"] + ", burst bf16",
                          "executed_frac": (cnt[1] * w["flop"]) / (kernel_ms * 1e-3) / 1e12 / pk["tflops"], "kernel_ms": kernel_ms / args.steps},
             "clocks": clocks, "wall_s_timed_region": t_wall,
         }
