@@ -290,6 +290,19 @@ def run_b200(args):
         line["cpu_baseline"] = {"value": us / dt, "unit": "samples/s", "cores": cores, "kind": "port",
                                 "sample": f"centre {px}x{px} crop of the {S}^2 frame, oracle/torch_ref.py (reference PyTorch path restated), "
                                           f"{ex} executed / {us} useful samples in {dt:.1f} s"}
+    # ---- the reference's own tensor-core kernel (oracle/_ref PTX, built from /root/reference) on this GPU, same frame
+    if rank == 0 and world == 1 and not args.no_gpu_reference:
+        try:
+            import ref_kernel
+            if ref_kernel.available():
+                rk = ref_kernel.ReferenceDvrKernel(net)
+                _, ms = rk.render(S, S, cam_np, scenes.DEFAULT_FOV_Y, w["stepsize"], tf_np, timing_iters=3)
+                line["reference_gpu_kernel"] = {"ms_per_frame": ms, "value": useful / args.steps / (ms * 1e-3), "unit": "samples/s",
+                                                "what": "reference ImageEvaluatorSimpleKernel (wmma, NVRTC compute_75 PTX JIT-ed to sm_100), "
+                                                        f"block {rk.block}, {rk.blocks_per_sm} block(s)/SM, same weights/camera/TF",
+                                                "speedup_of_this_kernel": ms / (kernel_ms / args.steps)}
+        except Exception as e:   # no prebuilt PTX for this network shape
+            line["reference_gpu_kernel"] = {"unavailable": str(e)[:200]}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -307,6 +320,7 @@ def main():
     ap.add_argument("--cpu-crop", type=int, default=256, help="max edge of the centre crop the CPU legs render")
     ap.add_argument("--cpu-budget-s", type=float, default=120.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true", help="skip timing the reference's own kernel (oracle/_ref PTX)")
     ap.add_argument("--kernel-mode", default="tcgen05", choices=["tcgen05", "mma_sync"],
                     help="tcgen05: tcgen05.mma/TMEM kernel (default); mma_sync: reference-precision fp16-accumulate kernel")
     args = ap.parse_args()

@@ -1,0 +1,147 @@
+"""
+TEST INFRASTRUCTURE — builds the REFERENCE's own fused DVR kernel (and nothing of ours) into PTX.
+
+The reference assembles its hot path at run time with NVRTC (renderer/kernel_loader.cpp:197-273, 368-463): a list of
+#defines + #includes of renderer/*.cuh, compiled for compute_XX, loaded with cuModuleLoadDataEx. This script repeats that
+recipe where /root/reference exists (the build container), reading the headers from where they lie and
+writing ONLY into oracle/_ref/: one PTX per network configuration plus a JSON with the lowered symbol names. The PTX
+travels to the GPU box (oracle/_ref is git-ignored, not gpurun-ignored), where oracle/ref_kernel.py loads it through the
+driver API, packs the reference's __constant__ blocks and launches ImageEvaluatorSimpleKernel — the
+reference's tensor-core kernel on the B200, used by tests/ as a parity comparand and by bench.py as a GPU baseline.
+No reference source is copied into the repository.
+
+The host library of the reference cannot be built here; the two cudAD headers it would pull in are absent
+submodules, so two shim headers stand in for them (forward declarations only — the DVR forward path uses none of it).
+"""
+import glob
+import json
+import os
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(HERE, "_ref")
+REF = os.environ.get("FVSRN_REFERENCE", "/root/reference")
+
+SHIM_FORWARD = r"""
+#pragma once
+#define CUDAD_CALL_NOCONSTEXPR __host__ __device__ inline
+namespace std { using ::exp; }
+namespace cudAD {
+template<typename T, int N> struct fvar;
+template<int N, typename V, typename I> __host__ __device__ fvar<float2, N> make_float2in(const V&, const I&);
+template<int N, typename V, typename I> __host__ __device__ fvar<float3, N> make_float3in(const V&, const I&);
+template<int N, typename V, typename I> __host__ __device__ fvar<float4, N> make_float4in(const V&, const I&);
+template<int N, typename V, typename I> __host__ __device__ fvar<double2, N> make_double2in(const V&, const I&);
+template<int N, typename V, typename I> __host__ __device__ fvar<double3, N> make_double3in(const V&, const I&);
+template<int N, typename V, typename I> __host__ __device__ fvar<double4, N> make_double4in(const V&, const I&);
+}
+"""
+
+NAMES = ["ImageEvaluatorSimpleKernel", "&cameraReferenceFrameParameters", "&volumeInterpolationTensorcoresParameters",
+         "&rayEvaluationSteppingDvrParameters", "&transferFunctionPiecewiseParameters"]
+
+
+def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, early_out=1, blend_mode=1, first_last_shared=0):
+    """The translation unit IImageEvaluator::getKernel + ImageEvaluatorSimple::render assemble."""
+    d = [
+        ("KERNEL_DOUBLE_PRECISION", 0), ("KERNEL_SYNCHRONIZED_TRACING", 1), ("BLOCK_SIZE", block_size),
+        ("NUM_HIDDEN_LAYERS", num_hidden), ("HIDDEN_CHANNELS_DIV16", hidden16), ("HAS_FOURIER_FEATURES", 1),
+        ("NUM_FOURIER_FEATURES", nf), ("USE_DIRECTION", 0), ("ACTIVATION", activation), ("OUTPUT_MODE", output_mode),
+        ("FIRST_AND_LAST_IN_SHARED_MEMORY", first_last_shared), ("LATENT_GRID_CHANNELS_DIV16", 1), ("LATENT_GRID_ENCODING", 0),
+        ("PASS_TIME_TO_NETWORK", 0), ("GRADIENT_MODE", 0),
+        ("RAY_EVALUATION_STEPPING__VOLUME_INTERPOLATION_T", "::kernel::VolumeInterpolationTensorcores"),
+        ("RAY_EVALUATION_STEPPING__TRANSFER_FUNCTION_T", "::kernel::TransferFunctionPiecewise"),
+        ("RAY_EVALUATION_STEPPING__BLENDING_T", "::kernel::Blending"),
+        ("RAY_EVALUATION_STEPPING__BRDF_T", "::kernel::BRDFLambert"),
+        ("RAY_EVALUATION_STEPPING__ENABLE_EARLY_OUT", early_out), ("RAY_EVALUATION_STEPPING__SKIP_TRANSFER_FUNCTION", 0),
+        ("BLENDING_MODE", blend_mode), ("BRDF_LAMBERT_LIGHT_TYPE", 1),
+    ]
+    src = "".join(f"#define {k} {v}\n" for k, v in d)
+    for h in ("renderer_camera.cuh", "renderer_volume_tensorcores.cuh", "renderer_tf_piecewise.cuh", "renderer_blending.cuh",
+              "renderer_brdf_lambert.cuh", "renderer_ray_evaluation_stepping_dvr.cuh"):
+        src += f'#include "{h}"\n'
+    src += "#define IMAGE_EVALUATOR__CAMERA_T ::kernel::CameraReferenceFrame\n"
+    src += "#define IMAGE_EVALUATOR__RAY_EVALUATOR_T ::kernel::RayEvaluationSteppingDvr\n"
+    src += '#include "renderer_image_evaluator_simple.cuh"\n'
+    return src
+
+
+# TEST-ONLY patch, applied to the in-memory copy of two headers for the "*_steps" variants (never written anywhere): the
+# reference kernel does not output its per-ray step count (terminationIndex is a local, ..stepping_dvr.cuh:83-84,156), so
+# the count of valid steps is routed through the (otherwise zero) normal.x channel. Arithmetic and control flow of the
+# march are untouched. The unpatched PTX is the one used for RGBA parity and timing.
+STEP_PATCHES = {
+    "renderer_ray_evaluation_stepping_dvr.cuh": [
+        ("int terminationIndex;", "int terminationIndex; int fvsrnValidSteps = 0;"),
+        ("#if KERNEL_SYNCHRONIZED_TRACING==0\n\t\t\t\tif (!isValid) break;", "fvsrnValidSteps += isValid;\n#if KERNEL_SYNCHRONIZED_TRACING==0\n\t\t\t\tif (!isValid) break;"),
+        ("\t\t\treturn output;\n\t\t}\n\t};", "\t\t\toutput.normal = make_real3(real_t(fvsrnValidSteps), 0, 0);\n\t\t\treturn output;\n\t\t}\n\t};"),
+    ],
+    "renderer_image_evaluator_simple.cuh": [
+        ("out.normal += nout.normal * nout.color.w;", "out.normal += nout.normal;"),
+    ],
+}
+
+
+def compile_ptx(src, patch_steps=False):
+    from cuda.bindings import nvrtc
+
+    def ck(r):
+        if r[0] != nvrtc.nvrtcResult.NVRTC_SUCCESS:
+            raise RuntimeError(str(r[0]))
+        return r[1:] if len(r) > 2 else (r[1] if len(r) == 2 else None)
+
+    headers, names = [], []
+    for f in sorted(glob.glob(os.path.join(REF, "renderer", "*.cuh"))):
+        text = open(f, "rb").read()
+        if patch_steps and os.path.basename(f) in STEP_PATCHES:
+            t = text.decode().replace("\r\n", "\n")
+            for old, new in STEP_PATCHES[os.path.basename(f)]:
+                assert t.count(old) == 1, (os.path.basename(f), old, t.count(old))
+                t = t.replace(old, new)
+            text = t.encode()
+        headers.append(text); names.append(os.path.basename(f).encode())
+    # the two cudAD headers renderer_cudad_bridge.cuh includes by name (:7-8); the submodule is absent -> shims
+    headers += [SHIM_FORWARD.encode(), b"#pragma once\n"]
+    names += [b"forward.h", b"forward_vector.h"]
+    prog = ck(nvrtc.nvrtcCreateProgram(src.encode(), b"main.cu", len(headers), headers, names))
+    for n in NAMES:
+        ck(nvrtc.nvrtcAddNameExpression(prog, n.encode()))
+    cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+    opts = [b"--std=c++17", b"--use_fast_math", b"--generate-line-info", b"--gpu-architecture=compute_75",
+            b"-I" + cuda_inc.encode(), b"-D__NVCC__=1", b"-DCUDA_NO_HOST=1", b"-DUSE_DOUBLE_PRECISION=0"]
+    res = nvrtc.nvrtcCompileProgram(prog, len(opts), opts)
+    if res[0] != nvrtc.nvrtcResult.NVRTC_SUCCESS:
+        n = ck(nvrtc.nvrtcGetProgramLogSize(prog)); log = b" " * n
+        ck(nvrtc.nvrtcGetProgramLog(prog, log))
+        raise RuntimeError("NVRTC failed:\n" + log.decode(errors="replace")[-4000:])
+    n = ck(nvrtc.nvrtcGetPTXSize(prog)); ptx = b" " * n
+    ck(nvrtc.nvrtcGetPTX(prog, ptx))
+    lowered = {nm: ck(nvrtc.nvrtcGetLoweredName(prog, nm.encode())).decode() for nm in NAMES}
+    return ptx.rstrip(b"\x00 "), lowered
+
+
+CONFIGS = {
+    # name: hidden16, num_hidden (linear layers - 2), nf, activation, output_mode (1 = density:direct), block size
+    "h32x4_relu": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256),
+    "h32x4_snakealt": dict(hidden16=2, num_hidden=2, nf=14, activation="SnakeAlt", output_mode=1, block_size=256),
+}
+
+
+def main():
+    if not os.path.isdir(os.path.join(REF, "renderer")):
+        print(f"build_ref_ptx: {REF} not present - keeping the prebuilt files in {OUT}")
+        return 0
+    os.makedirs(OUT, exist_ok=True)
+    meta = {}
+    for base, cfg in CONFIGS.items():
+        for name, patch in ((base, False), (base + "_steps", True)):
+            ptx, lowered = compile_ptx(main_source(**cfg), patch_steps=patch)
+            open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
+            meta[name] = dict(cfg, lowered=lowered, ptx=name + ".ptx", step_count_patch=patch)
+            print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['ImageEvaluatorSimpleKernel']}")
+    json.dump(meta, open(os.path.join(OUT, "ref_kernels.json"), "w"), indent=1)
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

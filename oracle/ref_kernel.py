@@ -1,0 +1,208 @@
+"""
+TEST INFRASTRUCTURE — runs the REFERENCE's own fused DVR kernel on the GPU box.
+
+oracle/build_ref_ptx.py assembled the reference's ImageEvaluatorSimpleKernel (renderer/*.cuh, unmodified) into PTX in the
+build container; this module loads that PTX through the CUDA driver API (the reference does the same with
+cuModuleLoadDataEx, renderer/kernel_loader.cpp:496-556), fills the reference's __constant__ blocks the way its host code
+does (SceneNetwork::fillConstantMemory, renderer/volume_interpolation_network.cpp:1236-1417 — every member padded to
+32 bytes; camera / DVR / TF blocks per SURVEY App. B), uploads the latent grid as C/4 float4 3-D textures (clamp, linear,
+normalised — LatentGrid::copyGridToGPU, :470-504) and launches with the reference's launch shape
+(image_evaluator_simple.cpp:300-345: 1-D grid of BLOCK_SIZE threads, capped by occupancy).
+Used only by tests/ (parity comparand) and bench.py (GPU baseline). Nothing here is product code.
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_DIR = os.path.join(HERE, "_ref")
+
+
+def available():
+    return os.path.exists(os.path.join(REF_DIR, "ref_kernels.json"))
+
+
+def _ck(res):
+    from cuda.bindings import driver
+    err = res[0]
+    if err != driver.CUresult.CUDA_SUCCESS:
+        raise RuntimeError(f"CUDA driver error {err}")
+    return res[1] if len(res) == 2 else (res[1:] if len(res) > 2 else None)
+
+
+def _pad32(buf: bytearray):
+    while len(buf) % 32:
+        buf.append(0)
+
+
+class _Accessor3(C.Structure):   # kernel::Tensor3Read<float>: {T* data; int32 sizes[3]; int32 strides[3]} (renderer_tensor.cuh:123-183)
+    _fields_ = [("data", C.c_uint64), ("sizes", C.c_int32 * 3), ("strides", C.c_int32 * 3)]
+
+
+class _Accessor4(C.Structure):   # kernel::Tensor4RW<float>
+    _fields_ = [("data", C.c_uint64), ("sizes", C.c_int32 * 4), ("strides", C.c_int32 * 4)]
+
+
+class _CameraParams(C.Structure):  # kernel::CameraReferenceFrameParameters (renderer_camera.cuh:12-25)
+    _fields_ = [("fovY", C.c_float), ("aspect", C.c_float), ("matrix", _Accessor3)]
+
+
+class _Dim3(C.Structure):
+    _fields_ = [("x", C.c_uint32), ("y", C.c_uint32), ("z", C.c_uint32)]
+
+
+def _read3(t, broadcast=True):
+    a = _Accessor3()
+    a.data = t.data_ptr()
+    for i in range(3):
+        a.sizes[i] = t.shape[i]
+        a.strides[i] = 0 if (broadcast and t.shape[i] == 1) else t.stride(i)
+    return a
+
+
+class ReferenceDvrKernel:
+    """One JIT-loaded reference kernel bound to one network (density network, Fourier features, one static 16-channel
+    latent grid, no direction/time input — the paper-default shape)."""
+
+    def __init__(self, net, variant=None, patched_steps=False):
+        import torch
+        from cuda.bindings import driver
+        self.torch, self.drv = torch, driver
+        meta = json.load(open(os.path.join(REF_DIR, "ref_kernels.json")))
+        act = net.layers[0].activation
+        H = net.input_channels_out()
+        if variant is None:
+            variant = f"h{H}x{len(net.layers)}_{act.lower()}" + ("_steps" if patched_steps else "")
+        if variant not in meta:
+            raise RuntimeError(f"no prebuilt reference PTX for {variant} (have {sorted(meta)})")
+        m = meta[variant]
+        assert m["hidden16"] * 16 == H and m["num_hidden"] == len(net.layers) - 2 and m["nf"] == net.num_fourier
+        assert net.latent_channels() == 16 and not net.has_direction and not net.has_time
+        assert net.output_mode == {0: "density", 1: "density:direct"}[m["output_mode"]]
+        self.meta, self.block = m, m["block_size"]
+        torch.cuda.init(); torch.zeros(1, device="cuda")         # primary context current
+        ptx = open(os.path.join(REF_DIR, m["ptx"]), "rb").read() + b"\0"
+        self.module = _ck(driver.cuModuleLoadData(ptx))          # JIT compute_75 PTX -> sm_100 SASS
+        low = m["lowered"]
+        self.func = _ck(driver.cuModuleGetFunction(self.module, low["ImageEvaluatorSimpleKernel"].encode()))
+        self.g_cam = _ck(driver.cuModuleGetGlobal(self.module, low["&cameraReferenceFrameParameters"].encode()))
+        self.g_vol = _ck(driver.cuModuleGetGlobal(self.module, low["&volumeInterpolationTensorcoresParameters"].encode()))
+        self.g_dvr = _ck(driver.cuModuleGetGlobal(self.module, low["&rayEvaluationSteppingDvrParameters"].encode()))
+        self.g_tf = _ck(driver.cuModuleGetGlobal(self.module, low["&transferFunctionPiecewiseParameters"].encode()))
+        self._keep = []
+        self._upload_network(net)
+        sms = torch.cuda.get_device_properties(0).multi_processor_count
+        bps = _ck(driver.cuOccupancyMaxActiveBlocksPerMultiprocessor(self.func, self.block, 0))
+        self.max_grid = max(1, bps) * sms
+        self.blocks_per_sm = bps
+
+    # ---- latent grid -> C/4 float4 3-D textures
+    def _texture(self, vol4):
+        """vol4: (Z,Y,X,4) float32."""
+        d = self.drv
+        Z, Y, X, _ = vol4.shape
+        desc = d.CUDA_ARRAY3D_DESCRIPTOR()
+        desc.Width, desc.Height, desc.Depth = X, Y, Z
+        desc.Format = d.CUarray_format.CU_AD_FORMAT_FLOAT
+        desc.NumChannels = 4
+        desc.Flags = 0
+        arr = _ck(d.cuArray3DCreate(desc))
+        host = np.ascontiguousarray(vol4, np.float32)
+        cp = d.CUDA_MEMCPY3D()
+        cp.srcMemoryType = d.CUmemorytype.CU_MEMORYTYPE_HOST
+        cp.srcHost = host.ctypes.data
+        cp.srcPitch = X * 16
+        cp.srcHeight = Y
+        cp.dstMemoryType = d.CUmemorytype.CU_MEMORYTYPE_ARRAY
+        cp.dstArray = arr
+        cp.WidthInBytes = X * 16
+        cp.Height = Y
+        cp.Depth = Z
+        _ck(d.cuMemcpy3D(cp))
+        res = d.CUDA_RESOURCE_DESC()
+        res.resType = d.CUresourcetype.CU_RESOURCE_TYPE_ARRAY
+        res.res.array.hArray = arr
+        td = d.CUDA_TEXTURE_DESC()
+        td.addressMode = [d.CUaddress_mode.CU_TR_ADDRESS_MODE_CLAMP] * 3
+        td.filterMode = d.CUfilter_mode.CU_TR_FILTER_MODE_LINEAR
+        td.flags = d.CU_TRSF_NORMALIZED_COORDINATES
+        tex = _ck(d.cuTexObjectCreate(res, td, None))
+        self._keep.append((arr, host))
+        return int(tex)
+
+    def _upload_network(self, net):
+        H, nf = net.input_channels_out(), net.num_fourier
+        grid = (net.time_grids or net.ensemble_grids)[0]
+        # the same fp16-rounded texels every other implementation sees, stored as fp32 like the reference
+        vals = grid.values.astype(np.float32).astype(np.float16).astype(np.float32)     # (C,Z,Y,X)
+        texs = [self._texture(np.ascontiguousarray(np.transpose(vals[4 * i:4 * i + 4], (1, 2, 3, 0)))) for i in range(4)]
+        b = bytearray()
+
+        def add(x):
+            _pad32(b); b.extend(x)
+
+        add(np.ascontiguousarray(net.fourier.T, np.float16).tobytes())                  # cWeightsFourier [cin][nf]
+        add(np.array(texs, np.uint64).tobytes())                                        # cLatentGridA
+        add(np.array(texs, np.uint64).tobytes())                                        # cLatentGridB
+        add(np.zeros(16, np.float32).tobytes())                                         # cLatentGridInterpolation (time index 0)
+        add(np.ascontiguousarray(net.layers[0].weights, np.float16).tobytes())          # cWeightsLatentGrid [H][H+C]
+        add(np.ascontiguousarray(net.layers[0].bias, np.float16).tobytes())
+        add(np.ascontiguousarray(np.stack([l.weights for l in net.layers[1:-1]]), np.float16).tobytes())
+        add(np.ascontiguousarray(np.stack([l.bias for l in net.layers[1:-1]]), np.float16).tobytes())
+        add(np.ascontiguousarray(net.layers[-1].weights, np.float16).tobytes())         # cWeightsLast [H]
+        add(np.ascontiguousarray(net.layers[-1].bias, np.float16).tobytes())
+        add(np.array(net.box_min, np.float32).tobytes())
+        add(np.array(net.box_size, np.float32).tobytes())
+        add(np.array([net.layers[0].activation_param], np.float32).tobytes())
+        add(np.array([0.01], np.float32).tobytes())                                     # finiteDifferencesStepsize (unused)
+        add(np.array([0.01], np.float32).tobytes())                                     # latentGridDifferencesStepSize (unused)
+        _pad32(b)
+        dptr, size = self.g_vol
+        if H == 32 and nf == 14:
+            assert len(b) == 7840, len(b)                                               # sizeof for C3
+        assert len(b) == int(size), (len(b), int(size))
+        _ck(self.drv.cuMemcpyHtoD(dptr, bytes(b), len(b)))
+
+    def render(self, width, height, camera, fov_y, stepsize, tf, alpha_early_out=1 - 1e-5, density_min=0.0, density_max=1.0,
+               out=None, timing_iters=0):
+        """-> (B,8,H,W) float32 CUDA tensor; with timing_iters > 0 also the mean kernel time in ms (CUDA events)."""
+        torch, d = self.torch, self.drv
+        cam = torch.as_tensor(np.ascontiguousarray(camera, np.float32)).reshape(-1, 3, 3).cuda()
+        tft = torch.as_tensor(np.ascontiguousarray(tf, np.float32)).cuda()
+        tft = tft.reshape(-1, tft.shape[-2], tft.shape[-1])
+        B = cam.shape[0]
+        if (width * height * B) % 32:
+            raise RuntimeError("the reference requires W*H*B to be a multiple of 32 (image_evaluator_simple.cpp:254-264)")
+        cp = _CameraParams(); cp.fovY = fov_y; cp.aspect = float(width) / float(height); cp.matrix = _read3(cam)
+        _ck(d.cuMemcpyHtoD(self.g_cam[0], bytes(cp), C.sizeof(cp)))
+        _ck(d.cuMemcpyHtoD(self.g_dvr[0], np.array([stepsize, alpha_early_out, density_min, density_max], np.float32).tobytes(), 16))
+        ta = _read3(tft)
+        _ck(d.cuMemcpyHtoD(self.g_tf[0], bytes(ta), C.sizeof(ta)))
+        if out is None:
+            out = torch.empty((B, 8, height, width), dtype=torch.float32, device="cuda")
+        oa = _Accessor4(); oa.data = out.data_ptr()
+        for i in range(4):
+            oa.sizes[i] = out.shape[i]; oa.strides[i] = out.stride(i)
+        vs = _Dim3(width, height, B)
+        samples, time, bg = C.c_int(1), C.c_uint(0), _Accessor4()
+        args = (C.c_void_p * 5)(C.addressof(vs), C.addressof(oa), C.addressof(samples), C.addressof(time), C.addressof(bg))
+        grid = min((width * height * B + self.block - 1) // self.block, self.max_grid)
+        stream = torch.cuda.current_stream().cuda_stream
+
+        def launch():
+            _ck(d.cuLaunchKernel(self.func, grid, 1, 1, self.block, 1, 1, 0, stream, C.addressof(args), 0))
+
+        launch()
+        torch.cuda.synchronize()
+        if timing_iters <= 0:
+            return out
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ms = 0.0
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        for _ in range(timing_iters):
+            flush.zero_()
+            e0.record(); launch(); e1.record(); torch.cuda.synchronize()
+            ms += e0.elapsed_time(e1)
+        return out, ms / timing_iters
