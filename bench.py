@@ -240,6 +240,26 @@ def run_b200(args):
     e2e_s = max(1e-9, e2e_s - (time.perf_counter() - flush_t0))   # the L2 flush is hygiene, not part of the call
     clocks = sampler.stop() if sampler else None
 
+    # ---- BASELINE configs[1] (C2): world-space batch query, 2^24 random positions through the same network
+    # (IVolumeInterpolation::evaluate -> fvsrn_evaluate), device-resident positions; reported next to the DVR numbers
+    batch_query = None
+    if rank == 0 and not args.no_batch_query:
+        n_q = 1 << 24
+        gq = torch.Generator(device="cuda"); gq.manual_seed(7)
+        pos = torch.rand((n_q, 3), generator=gq, device="cuda", dtype=torch.float32)     # 192 MiB > L2
+        for _ in range(2): dens = vol.evaluate(pos)
+        torch.cuda.synchronize()
+        qe = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        reps = 5
+        qe[0].record()
+        for _ in range(reps): dens = vol.evaluate(pos)
+        qe[1].record(); torch.cuda.synchronize()
+        q_ms = qe[0].elapsed_time(qe[1]) / reps
+        batch_query = {"workload": "C2: 2^24 random positions, same network (fvsrn_evaluate)", "ms": q_ms, "value": n_q / (q_ms * 1e-3),
+                       "unit": "samples/s", "tensor_frac_of_peak": n_q * w["flop"] / (q_ms * 1e-3) / 1e12 / peaks()["tflops"],
+                       "checksum": float(dens.double().mean())}
+        del pos, dens
+
     red = torch.tensor([total_ms, kernel_ms, e2e_s], dtype=torch.float64, device="cuda")
     tot = torch.tensor([cnt[0], cnt[1]], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -274,7 +294,7 @@ def run_b200(args):
             "roofline": {"bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
                          "traffic": traffic, "kernel": "dvr_tc_kernel (tcgen05.mma + TMEM)" if args.kernel_mode == "tcgen05" else "dvr_kernel (mma.sync)", "flop_per_sample": w["flop"], "peak_source": pk["source"] + ", burst bf16",
                          "executed_frac": (cnt[1] * w["flop"]) / (kernel_ms * 1e-3) / 1e12 / pk["tflops"], "kernel_ms": kernel_ms / args.steps},
-            "clocks": clocks, "wall_s_timed_region": t_wall,
+            "clocks": clocks, "wall_s_timed_region": t_wall, "batch_query": batch_query,
         }
     # ---- CPU baseline (rank 0, N=1 only): the reference's PyTorch path on the host cores, bounded crop of the same frame
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -320,6 +340,7 @@ def main():
     ap.add_argument("--cpu-crop", type=int, default=256, help="max edge of the centre crop the CPU legs render")
     ap.add_argument("--cpu-budget-s", type=float, default=120.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-batch-query", action="store_true", help="skip the C2 world-space batch query measurement")
     ap.add_argument("--no-gpu-reference", action="store_true", help="skip timing the reference's own kernel (oracle/_ref PTX)")
     ap.add_argument("--kernel-mode", default="tcgen05", choices=["tcgen05", "mma_sync"],
                     help="tcgen05: tcgen05.mma/TMEM kernel (default); mma_sync: reference-precision fp16-accumulate kernel")
