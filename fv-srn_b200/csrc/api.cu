@@ -723,7 +723,8 @@ int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     launch_fn fn = pick_launcher(net->H16);
     if (!fn) return fail("no kernel for this hidden width");
     const bool tc = net->kernel_mode == FVSRN_KERNEL_TCGEN05;
-    CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, nullptr, &cfg, nullptr));
+    DvrParams dq{}; dq.tf_kind = 0; dq.tf_R = 8;   // a typical piecewise TF: the DVR kernels size their shared memory from it
+    CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, kernel == 0 ? &dq : nullptr, &cfg, nullptr));
     info->device = net->device; info->sm_count = net->sm_count;
     info->block_threads = cfg.threads; info->blocks_per_sm = cfg.blocks_per_sm; info->grid_blocks = cfg.grid;
     info->smem_bytes_per_block = cfg.smem; info->regs_per_thread = cfg.regs;

@@ -32,6 +32,7 @@ struct DvrParams {
     unsigned long long* counters;       // optional [valid, executed]
     unsigned int* tile_counter;         // work queue
     int tiles_x, tiles_y, num_tiles;
+    int tf_smem_floats;                 // SS-mode tcgen05 kernel: floats reserved for the staged TF (multiple of 4)
 };
 
 struct EvalParams {

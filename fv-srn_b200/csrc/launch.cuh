@@ -2,7 +2,8 @@
 // Replaces the run-time NVRTC assembly of reference renderer/kernel_loader.cpp:197-273 by ahead-of-time
 // sm_100a instantiations selected from the network's shape (hidden width, latent channels, direction input).
 #pragma once
-#include "kernels_tc.cuh"
+#include "kernels_ss.cuh"
+#include <cstdlib>
 #include <cuda_runtime.h>
 
 namespace fvsrn {
@@ -28,9 +29,59 @@ cudaError_t launch_h4(int, int, int, const NetParams&, const void*, LaunchCfg*, 
 cudaError_t launch_h6(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
 cudaError_t launch_h8(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
 
+// SS-mode tcgen05 DVR kernel (kernels_ss.cuh): hidden width 32, density networks without direction input
+template <int H16, int GC16, int NS>
+cudaError_t launch_ss_n(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, cudaStream_t s, const void* fn) {
+    using Net = SrnSs<H16, GC16, 0, NS>;
+    DvrParams D = D0;
+    const int tf_floats = D.tf_kind == 0 ? (D.tf_R - 1) * 12 : (D.tf_kind == 1 ? D.tf_R * 4 : 4);
+    D.tf_smem_floats = ((tf_floats < 16 ? 16 : tf_floats) + 3) / 4 * 4;
+    const int blob = ((P.blob_bytes + 15) / 16) * 16;
+    const int smem = int(sizeof(SsShared<NS>)) + blob + D.tf_smem_floats * 4 + Net::ONES_BYTES + NS * Net::A_BYTES;
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    cudaFuncAttributes fa;
+    e = cudaFuncGetAttributes(&fa, fn);
+    if (e != cudaSuccess) return e;
+    const int by_regs = 65536 / (((fa.numRegs + 7) / 8 * 8) * kTcThreads);
+    const int by_smem = int((227 * 1024) / (size_t(smem) + 1024));
+    const int by_tmem = 512 / Net::TMEM_COLS;
+    const int bps = max(1, min(min(by_regs, by_smem), by_tmem));
+    long long grid = (long long)bps * cfg->sm_count;
+    if (cfg->max_blocks > 0 && grid > cfg->max_blocks) grid = cfg->max_blocks;
+    if (grid < 1) grid = 1;
+    cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = fa.numRegs; cfg->threads = kTcThreads;
+    if (cfg->query_only) return cudaSuccess;
+    void* args[2] = {const_cast<NetParams*>(&P), &D};
+    return cudaLaunchKernel(fn, dim3(unsigned(grid)), dim3(kTcThreads), args, size_t(smem), s);
+}
+template <int H16, int GC16, bool DIR>
+cudaError_t launch_ss(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, cudaStream_t s, bool* handled) {
+    *handled = false;
+    if constexpr (H16 == 2 && !DIR) {
+        static const int slots = [] { const char* e = std::getenv("FVSRN_SS_SLOTS"); return e ? std::atoi(e) : 0; }();
+        if (slots == 0 || P.output_mode >= D_OUT_RGBO) return cudaSuccess;    // default: TS-mode kernel (kernels_tc.cuh)
+        const int variant = (P.activation == D_ACT_RELU ? 1 : 0) | (P.fourier_nerf ? 2 : 0);
+        *handled = true;
+        if constexpr (GC16 == 1) {      // experiment: other slot counts for the paper-default shape only
+            if (variant == 3 && slots == 2) return launch_ss_n<H16, GC16, 2>(P, D0, cfg, s, (const void*)dvr_ss_kernel<H16, GC16, 3, 2>);
+            if (variant == 3 && slots == 4) return launch_ss_n<H16, GC16, 4>(P, D0, cfg, s, (const void*)dvr_ss_kernel<H16, GC16, 3, 4>);
+        }
+        const void* fns[4] = {(const void*)dvr_ss_kernel<H16, GC16, 0, 3>, (const void*)dvr_ss_kernel<H16, GC16, 1, 3>,
+                              (const void*)dvr_ss_kernel<H16, GC16, 2, 3>, (const void*)dvr_ss_kernel<H16, GC16, 3, 3>};
+        return launch_ss_n<H16, GC16, 3>(P, D0, cfg, s, fns[variant]);
+    }
+    return cudaSuccess;
+}
+
 template <int H16, int GC16, bool DIR>
 cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s) {
     using Net = Srn<H16, GC16, DIR>;
+    if (kind == KIND_DVR_TC && kp != nullptr) {
+        bool handled = false;
+        const cudaError_t e = launch_ss<H16, GC16, DIR>(P, *static_cast<const DvrParams*>(kp), cfg, s, &handled);
+        if (e != cudaSuccess || handled) return e;
+    }
     const bool is_tc = kind >= KIND_DVR_TC, is_dvr = (kind == KIND_DVR || kind == KIND_DVR_TC);
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
     const int threads = is_tc ? kTcThreads : kWarpsPerBlock * 32;

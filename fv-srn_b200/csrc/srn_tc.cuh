@@ -85,6 +85,16 @@ __device__ __forceinline__ void mma_ts2_elect(uint32_t d_tmem, uint32_t a_tmem, 
                  "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], d, %4, p;\n\t}\n"
                  :: "r"(d_tmem), "r"(a_tmem), "r"(desc_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate) : "memory");
 }
+// SS mode: A and B both by shared-memory descriptor
+__device__ __forceinline__ void mma_ss2_elect(uint32_t d_tmem, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t"
+                 "elect.sync _|q, 0xffffffff;\n\t"
+                 "setp.ne.b32 p, %6, 0;\n\t"
+                 "mov.b64 da, {%1, %2};\n\t"
+                 "mov.b64 db, {%3, %4};\n\t"
+                 "@q tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}\n"
+                 :: "r"(d_tmem), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate) : "memory");
+}
 __device__ __forceinline__ void mma_commit_elect(uint32_t bar) {
     asm volatile("{\n\t.reg .pred q;\n\t"
                  "elect.sync _|q, 0xffffffff;\n\t"
