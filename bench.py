@@ -41,7 +41,12 @@ WORKLOADS = {
     "C1": dict(net=dict(hidden=32, num_layers=4, grid_res=16, activation="ReLU", seed=42, last_gain=6.0),
                size=256, stepsize=0.005, flop=7168, desc="fV-SRN 32x4, 16^3x16 grid; DVR 256^2, step 0.005"),
     "C4": dict(net=dict(hidden=64, num_layers=6, grid_res=64, activation="ReLU", seed=42, last_gain=4.0),
-               size=2048, stepsize=1.0 / 512, flop=43008, desc="fV-SRN 64x6, 30 Fourier, 64^3x16 grid; DVR 2048^2"),
+               size=2048, stepsize=1.0 / 512, flop=43008, spp=4, desc="fV-SRN 64x6, 30 Fourier, 64^3x16 grid; DVR 2048^2, 4 spp"),
+    "C4-1spp": dict(net=dict(hidden=64, num_layers=6, grid_res=64, activation="ReLU", seed=42, last_gain=4.0),
+                    size=2048, stepsize=1.0 / 512, flop=43008, desc="fV-SRN 64x6, 30 Fourier, 64^3x16 grid; DVR 2048^2, 1 spp"),
+    "C5": dict(net=dict(hidden=32, num_layers=4, grid_res=32, activation="ReLU", seed=42, last_gain=6.0, time_keyframes=8),
+               size=512, stepsize=1.0 / 512, flop=7168, views=8, desc="time-dependent fV-SRN 32x4 (8 keyframe grids 32^3x16, temporally "
+               "interpolated), 512^2 camera sweep with per-view time, 8 views per GPU per step"),
 }
 
 
@@ -173,17 +178,25 @@ def run_b200(args):
     sn.kernel_mode = args.kernel_mode
     vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
     ie = pr.ImageEvaluatorSimple(); ie.volume = vol
-    cams = scenes.camera_sweep(world)                       # view-sharded multi-view batch: one view per rank per step
-    cam_np = np.ascontiguousarray(cams[rank:rank + 1])
+    V = int(w.get("views", 1))                              # views per rank per step (view-sharded multi-view batch)
+    cams = scenes.camera_sweep(world * V)
+    cam_np = np.ascontiguousarray(cams[rank * V:(rank + 1) * V])
     ie.camera.set_parameters(torch.from_numpy(cam_np))
+    ie.samples_per_pixel = int(w.get("spp", 1))
+    keep_alive = []
+    T = int(w["net"].get("time_keyframes", 0))
     ie.ray_evaluator.tf.tensor.value = torch.from_numpy(tf_np).cuda()
     ie.ray_evaluator.stepsize = w["stepsize"]
     sn._ensure_prepared()
-    out = torch.empty((1, 8, S, S), dtype=torch.float32, device="cuda")
+    out = torch.empty((V, 8, S, S), dtype=torch.float32, device="cuda")
     counters = torch.zeros(2, dtype=torch.int64, device="cuda")
     cam_dev = ie.camera.get_parameters(); tf_dev = ie.ray_evaluator.tf._tensor()
     p = ie._params(S, S, cam_dev, tf_dev, out.stride())
     p.counters_dev = counters.data_ptr()
+    if T > 1:   # time sweep: view i of the whole sweep is rendered at keyframe time i (T-1) / (views-1)
+        times = [(rank * V + i) * (T - 1) / max(1, world * V - 1) for i in range(V)]
+        vt = (C.c_float * V)(*times); keep_alive.append(vt)
+        p.view_times_host = C.cast(vt, C.c_void_p)
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
 
@@ -193,7 +206,7 @@ def run_b200(args):
         if ev: ev[1].record()
         rgba = ie.extract_color(out)
         if world > 1:
-            fdist.gather_views(rgba, world)      # one NCCL gather of the finished RGBA views on rank 0
+            fdist.gather_views(rgba, world * V)  # one NCCL gather of the finished RGBA views on rank 0
         if ev: ev[2].record()
         return rgba
 
@@ -219,10 +232,11 @@ def run_b200(args):
     cnt = counters.cpu().numpy().astype(np.float64)          # [useful, executed] over the K timed steps
 
     # ---- e2e: the reference-facing call with HOST buffers (camera + TF in, (1,8,S,S) image out)
-    host_img = torch.empty((1, 8, S, S), dtype=torch.float32).pin_memory()
+    host_img = torch.empty((V, 8, S, S), dtype=torch.float32).pin_memory()
     host_cam = torch.from_numpy(cam_np.copy()).pin_memory(); host_tf = torch.from_numpy(np.ascontiguousarray(tf_np)).pin_memory()
     q = ie._params(S, S, host_cam, host_tf, (8 * S * S, S * S, S, 1))
     q.camera_matrix_dev = host_cam.data_ptr(); q.tf_dev = host_tf.data_ptr()
+    q.view_times_host = p.view_times_host
 
     def e2e_step():
         _lib.check(L.fvsrn_render_dvr_host(sn._h, C.byref(q), host_img.data_ptr(), stream))
@@ -282,15 +296,15 @@ def run_b200(args):
             "metric": "srn_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {w['desc']}", "views_per_step": world, "sharding": "one view per GPU, RGBA gathered on rank 0 (NCCL)" if world > 1 else "single GPU",
+            "config": {"workload": f"{args.workload}: {w['desc']}", "views_per_step": world * V, "samples_per_pixel": int(w.get("spp", 1)), "sharding": "one view per GPU, RGBA gathered on rank 0 (NCCL)" if world > 1 else "single GPU",
                        "l2": "256 MiB buffer written between timed steps (outside the per-step CUDA-event pairs)",
-                       "useful_samples_per_frame": useful / args.steps / world, "executed_samples_per_frame": executed / args.steps / world,
+                       "useful_samples_per_frame": useful / args.steps / world / V, "executed_samples_per_frame": executed / args.steps / world / V,
                        "kernel": {"block_threads": qi.block_threads, "blocks_per_sm": qi.blocks_per_sm, "grid": qi.grid_blocks,
                                   "smem_bytes": qi.smem_bytes_per_block, "regs": qi.regs_per_thread}},
-            "ms_per_frame": total_ms / args.steps,
-            "e2e": {"value": useful / e2e_s, "unit": "samples/s", "ms_per_frame": 1e3 * e2e_s / args.steps,
+            "ms_per_frame": total_ms / args.steps / V,
+            "e2e": {"value": useful / e2e_s, "unit": "samples/s", "ms_per_frame": 1e3 * e2e_s / args.steps / V,
                     "h2d_bytes_per_step": int(host_cam.numel() * 4 + host_tf.numel() * 4), "d2h_bytes_per_step": int(host_img.numel() * 4)},
-            "gpu_launches": 2 * args.steps,
+            "gpu_launches": (V if T > 1 else 1) * args.steps + args.steps,
             "roofline": {"bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
                          "traffic": traffic, "kernel": "dvr_tc_kernel (tcgen05.mma + TMEM)" if args.kernel_mode == "tcgen05" else "dvr_kernel (mma.sync)", "flop_per_sample": w["flop"], "peak_source": pk["source"] + ", burst bf16",
                          "executed_frac": (cnt[1] * w["flop"]) / (kernel_ms * 1e-3) / 1e12 / pk["tflops"], "kernel_ms": kernel_ms / args.steps},
@@ -302,7 +316,7 @@ def run_b200(args):
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
         tn = torch_ref.TorchNetwork(net)
-        kw = dict(width=S, height=S, camera=cam_np, fov_y=scenes.DEFAULT_FOV_Y, stepsize=w["stepsize"], tf=tf_np)
+        kw = dict(width=S, height=S, camera=cam_np[:1], fov_y=scenes.DEFAULT_FOV_Y, stepsize=w["stepsize"], tf=tf_np)   # first view, 1 spp
         torch_ref.render_dvr(tn, **dict(kw, tile=crop_for_cpu(S, 16)))
         t0 = time.perf_counter(); _, ex, _ = torch_ref.render_dvr(tn, **dict(kw, tile=crop_for_cpu(S, 16))); r = ex / (time.perf_counter() - t0)
         px = adaptive_crop(argparse.Namespace(cpu_budget_s=20.0, steps=1, cpu_crop=args.cpu_crop), w, r)
@@ -316,11 +330,11 @@ def run_b200(args):
             import ref_kernel
             if ref_kernel.available():
                 rk = ref_kernel.ReferenceDvrKernel(net)
-                _, ms = rk.render(S, S, cam_np, scenes.DEFAULT_FOV_Y, w["stepsize"], tf_np, timing_iters=3)
-                line["reference_gpu_kernel"] = {"ms_per_frame": ms, "value": useful / args.steps / (ms * 1e-3), "unit": "samples/s",
+                _, ms = rk.render(S, S, cam_np[:1], scenes.DEFAULT_FOV_Y, w["stepsize"], tf_np, timing_iters=3)
+                line["reference_gpu_kernel"] = {"ms_per_frame": ms, "value": useful / args.steps / V / (ms * 1e-3), "unit": "samples/s",
                                                 "what": "reference ImageEvaluatorSimpleKernel (wmma, NVRTC compute_75 PTX JIT-ed to sm_100), "
                                                         f"block {rk.block}, {rk.blocks_per_sm} block(s)/SM, same weights/camera/TF",
-                                                "speedup_of_this_kernel": ms / (kernel_ms / args.steps)}
+                                                "speedup_of_this_kernel": ms / (kernel_ms / args.steps / V)}
         except Exception as e:   # no prebuilt PTX for this network shape
             line["reference_gpu_kernel"] = {"unavailable": str(e)[:200]}
     if rank == 0:

@@ -105,6 +105,44 @@ def test_dvr_tiles_and_views_compose(env, plume_tf):
         assert np.array_equal(np.nan_to_num(one[0]), np.nan_to_num(full[b]))
 
 
+@pytest.mark.parametrize("W,H", [(50, 30), (37, 19), (1, 1)])
+def test_dvr_ragged_image_sizes(env, plume_tf, W, H):
+    """Image sizes that are no multiple of the screen tile (16x8 / 8x4): partial tiles must neither write outside the
+    image nor change the pixels inside it."""
+    g = Golden("c3_relu_gauss")
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, g.camera, plume_tf, 1 / 64)
+    guard = env.torch.full((1, 8, H + 2, W + 2), 7.0, dtype=env.torch.float32, device="cuda")
+    view = guard[:, :, 1:H + 1, 1:W + 1]
+    p = ie._params(W, H, ie.camera.get_parameters(), ie.ray_evaluator.tf._tensor(), view.stride())
+    sn = vol.current_network(); sn._ensure_prepared()
+    stream = C.c_void_p(env.torch.cuda.current_stream().cuda_stream)
+    env.lib.check(env.lib.lib().fvsrn_render_dvr(sn._h, C.byref(p), view.data_ptr(), stream))
+    env.torch.cuda.synchronize()
+    got = guard.cpu().numpy()
+    border = np.ones((H + 2, W + 2), bool); border[1:H + 1, 1:W + 1] = False
+    assert (got[0][:, border] == 7.0).all()                               # nothing written outside the image
+    ref, steps, _ = env.oracle.render_dvr(g.net, width=W, height=H, camera=g.camera, fov_y=env.scenes.DEFAULT_FOV_Y, stepsize=1 / 64,
+                                          tf=plume_tf)
+    assert np.abs(got[:, :4, 1:H + 1, 1:W + 1] - ref[:, :4]).max() <= RGBA_TOL
+
+
+def test_dvr_ragged_tiles_equal_the_full_frame(env, plume_tf):
+    """Rectangles that start and end off the 16x8 / 8x4 tile raster reproduce the full frame's pixels bit for bit."""
+    g = Golden("c3_relu_gauss")
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, g.camera, plume_tf, 1 / 64)
+    W, H = 53, 31
+    full = ie.render(W, H).cpu().numpy()
+    for (x0, y0, w, h) in [(3, 5, 17, 3), (0, 0, 1, 1), (52, 30, 1, 1), (7, 1, 46, 30), (16, 8, 16, 8)]:
+        ie.tile = (x0, y0, w, h)
+        part = ie.render(W, H).cpu().numpy()
+        assert np.array_equal(np.nan_to_num(part[:, :, y0:y0 + h, x0:x0 + w]), np.nan_to_num(full[:, :, y0:y0 + h, x0:x0 + w])), (x0, y0, w, h)
+        outside = np.ones((H, W), bool); outside[y0:y0 + h, x0:x0 + w] = False
+        assert not np.nan_to_num(part[0][:, outside]).any()                   # a tile render leaves the rest of the (zeroed) frame alone
+    ie.tile = None
+
+
 def test_dvr_per_view_times(env, plume_tf):
     g = Golden("c5_time")
     cams = env.scenes.camera_sweep(4)
