@@ -148,6 +148,16 @@ __device__ __forceinline__ void blend_sample(const DvrParams& D, float4 c, float
         acc.w += k;
     }
 }
+// the same compositing step without divergent branches: `on` = this sample exists (valid step of a live ray)
+__device__ __forceinline__ void blend_sample_pred(const DvrParams& D, bool on, float4 c, float t, float4& acc, float& acc_depth) {
+    float e;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(c.w * -1.4426950408889634f));
+    const float a = (D.blend_mode == 1) ? 1.f - e : fminf(1.f, c.w);
+    const float k = (on && c.w > 0.f) ? (1.f - acc.w) * a : 0.f;
+    acc.x = fmaf(k, c.x, acc.x); acc.y = fmaf(k, c.y, acc.y); acc.z = fmaf(k, c.z, acc.z);
+    acc_depth = fmaf(k, t, acc_depth);
+    acc.w += k;
+}
 // pixel write, reference renderer_image_evaluator_simple.cuh:101-124
 __device__ __forceinline__ void write_pixel(const DvrParams& D, int b, int x, int y, float4 pix_color, float pix_depth, int last_steps) {
     const float inv_s = 1.f / float(D.spp);

@@ -263,6 +263,7 @@ dvr_ss_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
                             pz = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.z, t[k], r.eye.z), bmin.z), binv.z);
                         }
                         uint32_t row[Core::K0 / 2];
+                        Tc::fetch_latent(P, px, py, pz, row);
                         Tc::build_row(P, px, py, pz, r.dir.x, r.dir.y, r.dir.z, row);
                         Net::store_row(ctx, k, row);
                     } else Net::publish(ctx, k);

@@ -16,6 +16,7 @@ namespace fvsrn {
 constexpr int kTcComputeThreads = 128;
 constexpr int kTcThreads = 160;            // + the MMA warp
 constexpr int kTcTileW = 16, kTcTileH = 8;
+constexpr int kTcTfBins = 64;              // piecewise TF search accelerator: one start interval per density bin
 constexpr int kTcTfFloats = 2560;          // shared-memory TF: up to 204 piecewise intervals x 12 floats, or 256 x float4 texels
 
 // Transfer function staged in shared memory in evaluation-ready form. Piecewise (reference renderer_tf_piecewise.cuh:
@@ -34,6 +35,17 @@ __device__ __forceinline__ void tc_stage_tf(const DvrParams& D, int b, float* st
             rec[1] = a;
             rec[2] = make_float4(e.x - a.x, e.y - a.y, e.z - a.z, e.w - a.w);
         }
+        // search accelerator: for each of 64 density bins, the interval the reference's linear search (first i with
+        // p_{i+1} > d) returns for the bin's lower edge; the search for any d of the bin starts there - same result,
+        // usually zero further steps.
+        uint8_t* bins = reinterpret_cast<uint8_t*>(stf + 12 * (D.tf_R - 1));
+        for (int bin = threadIdx.x; bin < kTcTfBins; bin += blockDim.x) {
+            const float d = float(bin) * (1.0f / kTcTfBins);
+            int i = 0;
+            for (; i < D.tf_R - 2; ++i)
+                if (__ldg(src + (i + 1) * 5 + 4) > d) break;
+            bins[bin] = uint8_t(i);
+        }
     } else {
         const int n = D.tf_kind == 1 ? D.tf_R * 4 : 2;
         const float* src = D.tf + (D.tf_batch == 1 ? 0 : (size_t)b * n);
@@ -42,10 +54,11 @@ __device__ __forceinline__ void tc_stage_tf(const DvrParams& D, int b, float* st
 }
 __device__ __forceinline__ float4 tc_tf_piecewise(const float* stf, int R, float d) {
     const float4* rec = reinterpret_cast<const float4*>(stf);
-    int i = 0;
-    for (; i < R - 2; ++i)
-        if (rec[3 * i].y > d) break;
-    const float4 h = rec[3 * i], v0 = rec[3 * i + 1], dv = rec[3 * i + 2];
+    const uint8_t* bins = reinterpret_cast<const uint8_t*>(stf + 12 * (R - 1));
+    int i = bins[min(int(d * float(kTcTfBins)), kTcTfBins - 1)];      // d in [0,1]
+    float4 h = rec[3 * i];
+    while (i < R - 2 && !(h.y > d)) h = rec[3 * ++i];
+    const float4 v0 = rec[3 * i + 1], dv = rec[3 * i + 2];
     const float f = (fminf(fmaxf(d, h.x), h.y) - h.x) * h.z;
     return make_float4(fmaf(f, dv.x, v0.x), fmaf(f, dv.y, v0.y), fmaf(f, dv.z, v0.z), fmaf(f, dv.w, v0.w));
 }
@@ -107,6 +120,39 @@ struct SrnTc {
     // Srn::build_row), built for issue-slot economy: Fourier matrix from the constant bank, latent vector through the
     // texture units (4 x tex3D<half4> per 16 channels, hardware trilinear filter = the reference's own fetch,
     // renderer_volume_tensorcores.cuh:573-605), channel 3 = 1 when the network has no time input (bias column).
+    // Latent part of the layer-0 row. Issued for both slots of a trip before any other per-sample arithmetic so that the
+    // texture latency is covered by the Fourier features of both samples.
+    static __device__ __forceinline__ void fetch_latent(const NetParams& P, float px, float py, float pz, uint32_t (&row)[K0 / 2]) {
+#pragma unroll
+        for (int g = 0; g < GC16; ++g) {
+            const float frac = P.groups[g].frac;    // grid-uniform
+#ifndef FVSRN_TEX_F16
+#define FVSRN_TEX_F16 0   // measured: the f16x2 return path is slower than fp32 return + F2FP (A/B on one B200: 6.05 vs 5.88 ms)
+#endif
+            if (frac > 0.f || !FVSRN_TEX_F16) {   // temporal lerp of the two keyframes after the fetch, in fp32 (reference :590-604)
+                float4 v[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) v[q] = tex3D<float4>(P.tex_a[4 * g + q], px, py, pz);
+                if (frac > 0.f)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 w = tex3D<float4>(P.tex_b[4 * g + q], px, py, pz);
+                    v[q].x = fmaf(frac, w.x - v[q].x, v[q].x); v[q].y = fmaf(frac, w.y - v[q].y, v[q].y);
+                    v[q].z = fmaf(frac, w.z - v[q].z, v[q].z); v[q].w = fmaf(frac, w.w - v[q].w, v[q].w);
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    row[H / 2 + g * 8 + 2 * q] = tc::pack_h2(v[q].x, v[q].y);
+                    row[H / 2 + g * 8 + 2 * q + 1] = tc::pack_h2(v[q].z, v[q].w);
+                }
+            } else {            // one keyframe: the texture unit returns the filtered texel already packed as 2 x f16x2
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    tc::tex3d_h4(P.tex_a[4 * g + q], px, py, pz, row[H / 2 + g * 8 + 2 * q], row[H / 2 + g * 8 + 2 * q + 1]);
+            }
+        }
+    }
+
     static __device__ __forceinline__ void build_row(const NetParams& P, float px, float py, float pz,
                                                      float dx, float dy, float dz, uint32_t (&row)[K0 / 2]) {
         constexpr int FOFF = Core::FOFF, NF = Core::NF;
@@ -171,26 +217,6 @@ struct SrnTc {
                 row[FOFF / 2 + NF / 2 + i / 2] = tc::pack_h2(s0, s1);
             }
     }
-#pragma unroll
-        for (int g = 0; g < GC16; ++g) {
-            const float frac = P.groups[g].frac;    // grid-uniform
-            float4 v[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) v[q] = tex3D<float4>(P.tex_a[4 * g + q], px, py, pz);
-            if (frac > 0.f) {   // temporal lerp of the two keyframes after the fetch, in fp32 (reference :590-604)
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const float4 w = tex3D<float4>(P.tex_b[4 * g + q], px, py, pz);
-                    v[q].x = fmaf(frac, w.x - v[q].x, v[q].x); v[q].y = fmaf(frac, w.y - v[q].y, v[q].y);
-                    v[q].z = fmaf(frac, w.z - v[q].z, v[q].z); v[q].w = fmaf(frac, w.w - v[q].w, v[q].w);
-                }
-            }
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                row[H / 2 + g * 8 + 2 * q] = tc::pack_h2(v[q].x, v[q].y);
-                row[H / 2 + g * 8 + 2 * q + 1] = tc::pack_h2(v[q].z, v[q].w);
-            }
-        }
     }
 
     // MMA warp (all lanes, converged; one elected lane issues): the K steps of one layer of one slot + commit to the
@@ -221,7 +247,7 @@ struct SrnTc {
         tc::wait_st();
         tc::fence_before_sync();
         __syncwarp();
-        if ((threadIdx.x & 31) == 0) tc::mbar_arrive(c.ready + 8 * slot);
+        tc::mbar_arrive_elect(c.ready + 8 * slot);
     }
 
     // this thread's layer-0 row of one slot -> TMEM A operand
@@ -276,21 +302,26 @@ struct SrnTc {
     static __device__ __forceinline__ void mlp_compute(const NetParams& P, Ctx& c, bool warp_active, float (&out0)[4], float (&out1)[4]) {
         const int act = P.activation;
         const bool scalar_last = P.output_mode < D_OUT_RGBO;    // density networks: last layer in registers
+        // hidden-to-hidden hand-overs: accumulator -> activation -> A operand of the next layer
 #pragma unroll 1
-        for (int l = 0; l <= P.num_hidden; ++l) {
-            const bool dot = scalar_last && l == P.num_hidden;
+        for (int l = scalar_last ? 1 : 0; l <= P.num_hidden; ++l) {
+#pragma unroll
+            for (int slot = 0; slot < 2; ++slot) {
+                tc::mbar_wait(c.done + 8 * slot, c.phase);
+                tc::fence_after_sync();
+                if (warp_active) epilogue(c, slot, act);
+                publish(c, slot);
+            }
+            c.phase ^= 1u;
+        }
+        if (scalar_last) {   // last hidden layer: activation + 1 x H dot product in registers
 #pragma unroll
             for (int slot = 0; slot < 2; ++slot) {
                 float (&out)[4] = slot == 0 ? out0 : out1;
                 tc::mbar_wait(c.done + 8 * slot, c.phase);
                 tc::fence_after_sync();
-                if (dot) {
-                    out[0] = warp_active ? epilogue_dot(P, c, slot, act) : 0.f;
-                    out[1] = out[2] = out[3] = 0.f;
-                } else {
-                    if (warp_active) epilogue(c, slot, act);
-                    publish(c, slot);
-                }
+                out[0] = warp_active ? epilogue_dot(P, c, slot, act) : 0.f;
+                out[1] = out[2] = out[3] = 0.f;
             }
             c.phase ^= 1u;
         }
@@ -353,9 +384,14 @@ __device__ __forceinline__ typename Net::Ctx tc_prologue(const NetParams& P, TcS
     typename Net::Ctx c;
     c.tmem_base = sh->tmem_addr;
     c.tmem_lane = c.tmem_base + (uint32_t((warp & 3) * 32) << 16);
+    asm volatile("" : "+r"(c.tmem_lane));   // opaque: kept in a register instead of being re-derived from %tid at every TMEM access
     c.sblob = smem_u32(sblob);
     c.ready = smem_u32(&sh->ready[0]);
-    c.done = smem_u32(&sh->done[0]);
+#ifndef FVSRN_OPAQUE_BAR
+#define FVSRN_OPAQUE_BAR 1
+#endif
+    if (FVSRN_OPAQUE_BAR) asm volatile("" : "+r"(c.ready));   // opaque: not re-derived (S2R SR_CgaCtaId + LEA) at every wait
+    c.done = c.ready + 16;
     c.phase = 0;
     c.af = tc::make_actf(P.activation, P.act_param);
     if (warp < 4) Net::init_tmem(c);
@@ -446,41 +482,42 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
                 // a warp whose 32 rays are all finished keeps the barrier protocol going but skips the arithmetic
                 const bool warp_active = __any_sync(0xffffffffu, valid0);
                 if (warp_active) {
-                    float px = 0.f, py = 0.f, pz = 0.f;
+                    float px = 0.f, py = 0.f, pz = 0.f, qx = 0.f, qy = 0.f, qz = 0.f;
                     if (valid0) {
                         px = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.x, t0, r.eye.x), bmin.x), binv.x);
                         py = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.y, t0, r.eye.y), bmin.y), binv.y);
                         pz = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.z, t0, r.eye.z), bmin.z), binv.z);
                     }
-                    uint32_t row[Core::K0 / 2];
-                    Net::build_row(P, px, py, pz, r.dir.x, r.dir.y, r.dir.z, row);
-                    Net::store_row(ctx, 0, row);
-                } else Net::publish(ctx, 0);
-                if (warp_active) {
-                    float px = 0.f, py = 0.f, pz = 0.f;
                     if (in1) {
-                        px = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.x, t1, r.eye.x), bmin.x), binv.x);
-                        py = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.y, t1, r.eye.y), bmin.y), binv.y);
-                        pz = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.z, t1, r.eye.z), bmin.z), binv.z);
+                        qx = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.x, t1, r.eye.x), bmin.x), binv.x);
+                        qy = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.y, t1, r.eye.y), bmin.y), binv.y);
+                        qz = __fmul_rn(__fsub_rn(__fmaf_rn(r.dir.z, t1, r.eye.z), bmin.z), binv.z);
                     }
-                    uint32_t row[Core::K0 / 2];
-                    Net::build_row(P, px, py, pz, r.dir.x, r.dir.y, r.dir.z, row);
-                    Net::store_row(ctx, 1, row);
-                } else Net::publish(ctx, 1);
+                    uint32_t row0[Core::K0 / 2], row1[Core::K0 / 2];
+#ifndef FVSRN_TEX_EARLY
+#define FVSRN_TEX_EARLY 1
+#endif
+                    Net::fetch_latent(P, px, py, pz, row0);
+                    if (FVSRN_TEX_EARLY) Net::fetch_latent(P, qx, qy, qz, row1);
+                    Net::build_row(P, px, py, pz, r.dir.x, r.dir.y, r.dir.z, row0);
+                    Net::store_row(ctx, 0, row0);
+                    if (!FVSRN_TEX_EARLY) Net::fetch_latent(P, qx, qy, qz, row1);
+                    Net::build_row(P, qx, qy, qz, r.dir.x, r.dir.y, r.dir.z, row1);
+                    Net::store_row(ctx, 1, row1);
+                } else {
+                    Net::publish(ctx, 0);
+                    Net::publish(ctx, 1);
+                }
                 float o0[4], o1[4];
                 Net::mlp_compute(P, ctx, warp_active, o0, o1);
                 if (lane == 0) n_exec += 64;
                 // both samples are shaded first (independent work, interleaved by the compiler), then composited in order
                 const float4 c0 = tc_shade_sample(P, D, stf, o0), c1 = tc_shade_sample(P, D, stf, o1);
-                if (valid0) {
-                    ++steps;
-                    blend_sample(D, c0, t0, acc, acc_depth);
-                }
+                steps += valid0 ? 1 : 0;
+                blend_sample_pred(D, valid0, c0, t0, acc, acc_depth);
                 const bool valid1 = in1 && (!D.early_out || (acc.w < D.alpha_early_out));
-                if (valid1) {
-                    ++steps;
-                    blend_sample(D, c1, t1, acc, acc_depth);
-                }
+                steps += valid1 ? 1 : 0;
+                blend_sample_pred(D, valid1, c1, t1, acc, acc_depth);
             }
             n_valid += steps;
             last_steps = steps;
@@ -521,6 +558,7 @@ eval_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Eval
                     if (DIR && E.dir) { dx = __ldg(E.dir + 3 * i); dy = __ldg(E.dir + 3 * i + 1); dz = __ldg(E.dir + 3 * i + 2); }
                 }
                 uint32_t row[Core::K0 / 2];
+                Net::fetch_latent(P, px, py, pz, row);
                 Net::build_row(P, px, py, pz, dx, dy, dz, row);
                 Net::store_row(ctx, slot, row);
             }

@@ -34,7 +34,7 @@ template <int H16, int GC16, int NS>
 cudaError_t launch_ss_n(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, cudaStream_t s, const void* fn) {
     using Net = SrnSs<H16, GC16, 0, NS>;
     DvrParams D = D0;
-    const int tf_floats = D.tf_kind == 0 ? (D.tf_R - 1) * 12 : (D.tf_kind == 1 ? D.tf_R * 4 : 4);
+    const int tf_floats = D.tf_kind == 0 ? (D.tf_R - 1) * 12 + kTcTfBins / 4 : (D.tf_kind == 1 ? D.tf_R * 4 : 4);
     D.tf_smem_floats = ((tf_floats < 16 ? 16 : tf_floats) + 3) / 4 * 4;
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
     const int smem = int(sizeof(SsShared<NS>)) + blob + D.tf_smem_floats * 4 + Net::ONES_BYTES + NS * Net::A_BYTES;

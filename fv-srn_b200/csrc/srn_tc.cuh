@@ -63,6 +63,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" :: "r"(bar) : "memory");
 }
+// converged warp: one elected lane arrives (no %tid read, no divergent branch)
+__device__ __forceinline__ void mbar_arrive_elect(uint32_t bar) {
+    asm volatile("{\n\t.reg .pred q;\n\t"
+                 "elect.sync _|q, 0xffffffff;\n\t"
+                 "@q mbarrier.arrive.shared::cta.b64 _, [%0];\n\t}\n" :: "r"(bar) : "memory");
+}
 // arrive on the mbarrier once all previously issued tcgen05.mma of this thread have completed
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" :: "r"(bar) : "memory");
@@ -152,6 +158,11 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[N]
 __device__ __forceinline__ uint32_t pack_relu(float lo, float hi) {   // (half(max(lo,0)), half(max(hi,0)))
     uint32_t r; asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;\n" : "=r"(r) : "f"(hi), "f"(lo)); return r;
 }
+// filtered fetch of a half4 3-D texture with the result left in fp16 (two f16x2 registers): no fp32 round trip
+__device__ __forceinline__ void tex3d_h4(cudaTextureObject_t t, float x, float y, float z, uint32_t& xy, uint32_t& zw) {
+    asm("tex.3d.v2.f16x2.f32 {%0, %1}, [%2, {%3, %4, %5, %5}];" : "=r"(xy), "=r"(zw) : "l"(t), "f"(x), "f"(y), "f"(z));
+}
+
 __device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
     uint32_t r; asm("cvt.rn.f16x2.f32 %0, %1, %2;\n" : "=r"(r) : "f"(hi), "f"(lo)); return r;
 }
