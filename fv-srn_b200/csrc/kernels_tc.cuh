@@ -405,7 +405,10 @@ __device__ __forceinline__ void tc_epilogue(const typename Net::Ctx& c) {
 }
 
 template <int H16, int GC16, bool DIR, int VARIANT>
-__global__ void __launch_bounds__(kTcThreads, H16 <= 2 ? 4 : 1)
+// Register budget: 4 CTAs/SM at hidden <= 32 (96 registers); 2 CTAs/SM at hidden 48/64, which needs <= 168 registers
+// because a warp's registers must fit one 16384-entry register-file partition three times over (see
+// tc_blocks_by_regs in launch.cuh) - expressed as (192 threads, 2 blocks), the launch still uses kTcThreads.
+__global__ void __launch_bounds__(H16 <= 2 ? kTcThreads : 192, H16 <= 2 ? 4 : (H16 <= 4 ? 2 : 1))
 dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
     using Net = SrnTc<H16, GC16, DIR, VARIANT>;
     using Core = typename Net::Core;

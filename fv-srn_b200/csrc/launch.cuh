@@ -29,6 +29,15 @@ cudaError_t launch_h4(int, int, int, const NetParams&, const void*, LaunchCfg*, 
 cudaError_t launch_h6(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
 cudaError_t launch_h8(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
 
+// CTAs per SM the register file allows: registers live in four 16384-entry partitions (one per SM sub-partition) and a
+// warp's registers cannot straddle them, so the limit is per partition: floor(16384 / regs per warp) warps each.
+// (A 5-warp CTA at 174 registers: 2 warps per partition -> 8 warps -> ONE CTA, although 2 x 5 x 176 x 32 < 65536.)
+inline int tc_blocks_by_regs(int regs_per_thread, int threads) {
+    const int per_warp = ((regs_per_thread + 7) / 8 * 8) * 32;
+    const int warps_per_partition = 16384 / per_warp;
+    return (4 * warps_per_partition) / ((threads + 31) / 32);
+}
+
 // SS-mode tcgen05 DVR kernel (kernels_ss.cuh): hidden width 32, density networks without direction input
 template <int H16, int GC16, int NS>
 cudaError_t launch_ss_n(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, cudaStream_t s, const void* fn) {
@@ -43,7 +52,7 @@ cudaError_t launch_ss_n(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg,
     cudaFuncAttributes fa;
     e = cudaFuncGetAttributes(&fa, fn);
     if (e != cudaSuccess) return e;
-    const int by_regs = 65536 / (((fa.numRegs + 7) / 8 * 8) * kTcThreads);
+    const int by_regs = tc_blocks_by_regs(fa.numRegs, kTcThreads);
     const int by_smem = int((227 * 1024) / (size_t(smem) + 1024));
     const int by_tmem = 512 / Net::TMEM_COLS;
     const int bps = max(1, min(min(by_regs, by_smem), by_tmem));
@@ -108,7 +117,7 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
         // The occupancy API reports 1 CTA/SM for kernels that allocate TMEM; co-residency is in fact bounded by
         // registers, shared memory (+1 KiB reserved per CTA) and the 512 TMEM columns of an SM (measured:
         // profiles/microbench). Surplus CTAs of the persistent grid would only queue, never deadlock.
-        const int by_regs = 65536 / (((fa.numRegs + 7) / 8 * 8) * threads);
+        const int by_regs = tc_blocks_by_regs(fa.numRegs, threads);
         const int by_smem = int((228 * 1024) / (size_t(smem) + 1024));
         const int by_tmem = 512 / SrnTc<H16, GC16, DIR, 0>::TMEM_COLS;
         bps = max(1, min(min(by_regs, by_smem), min(by_tmem, 16)));

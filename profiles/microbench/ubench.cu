@@ -84,6 +84,28 @@ __global__ void __launch_bounds__(128) fetch_tex_kernel(Tex4 T, int steps, float
     out[i] = r;
 }
 
+// same fetch with the result returned as 2 x f16x2 (tex.3d.v2.f16x2.f32): no F2FP, half the return registers
+__global__ void __launch_bounds__(128) fetch_tex_h2_kernel(Tex4 T, int steps, float* out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    __half2 acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = __float2half2_rn(0.f);
+    for (int s = 0; s < steps; ++s) {
+        float x, y, z; ray_pos(i, s, x, y, z);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            uint32_t a, b;
+            asm("tex.3d.v2.f16x2.f32 {%0, %1}, [%2, {%3, %4, %5, %5}];" : "=r"(a), "=r"(b) : "l"(T.t[g]), "f"(x), "f"(y), "f"(z));
+            acc[2 * g] = __hadd2(acc[2 * g], *reinterpret_cast<__half2*>(&a));
+            acc[2 * g + 1] = __hadd2(acc[2 * g + 1], *reinterpret_cast<__half2*>(&b));
+        }
+    }
+    float r = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r += __low2float(acc[j]) + __high2float(acc[j]);
+    out[i] = r;
+}
+
 __global__ void __launch_bounds__(128) fetch_ldg_kernel(const uint4* __restrict__ grid, int N, int steps, float* out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     __half2 tot[8];
@@ -236,6 +258,13 @@ int main() {
     CK(cudaEventElapsedTime(&ms, e0, e1)); CK(cudaMemcpy(o1.data(), d_out, rays * 4, cudaMemcpyDeviceToHost));
     printf("fetch tex3D half4 x4: %.3f ms, %.3e samples/s, %.2f clk/sample/SM at max clock\n", ms, double(rays) * steps / (ms * 1e-3),
            ms * 1e-3 * clk_khz * 1e3 * sms / (double(rays) * steps));
+    for (int rep = 0; rep < 2; ++rep) {
+        CK(cudaEventRecord(e0)); fetch_tex_h2_kernel<<<rays / 128, 128>>>(T, steps, d_out); CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1)); CK(cudaGetLastError());
+    }
+    CK(cudaEventElapsedTime(&ms, e0, e1)); CK(cudaMemcpy(o2.data(), d_out, rays * 4, cudaMemcpyDeviceToHost));
+    { double md2 = 0; for (int i = 0; i < rays; ++i) md2 = std::max(md2, double(std::fabs(o1[i] - o2[i])));
+      printf("fetch tex3D half4 x4, f16x2 return: %.3f ms, %.3e samples/s, %.2f clk/sample/SM at max clock; max |diff| vs fp32 return + F2FP (sum of 256 steps x 16 ch) %.3e\n",
+             ms, double(rays) * steps / (ms * 1e-3), ms * 1e-3 * clk_khz * 1e3 * sms / (double(rays) * steps), md2); }
     for (int rep = 0; rep < 2; ++rep) {
         CK(cudaEventRecord(e0)); fetch_ldg_kernel<<<rays / 128, 128>>>(d_grid, N, steps, d_out); CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1)); CK(cudaGetLastError());
     }
