@@ -119,7 +119,10 @@ def tf_piecewise(tf: torch.Tensor, d: torch.Tensor, dmin: float, dmax: float, st
     d2 = torch.clamp((d - dmin) * (1.0 / (dmax - dmin)), 0, 1)
     pos = tf[:, 4]; R = pos.shape[0]
     gt = pos[None, 1:R - 1] > d2[:, None]
-    i = torch.where(gt.any(1), gt.float().argmax(1), torch.full_like(d2, R - 2, dtype=torch.long))
+    if R > 2:
+        i = torch.where(gt.any(1), gt.float().argmax(1), torch.full_like(d2, R - 2, dtype=torch.long))
+    else:           # two control points: one interval
+        i = torch.zeros_like(d2, dtype=torch.long)
     p0, p1 = pos[i], pos[i + 1]
     f = (torch.minimum(torch.maximum(d2, p0), p1) - p0) / (p1 - p0)
     c = tf[i, :4] + f[:, None] * (tf[i + 1, :4] - tf[i, :4])

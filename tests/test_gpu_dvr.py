@@ -73,6 +73,32 @@ def test_dvr_texture_tf_alpha_blend_density_range(env, plume_tf):
     _check_steps(ie.last_step_counts.cpu().numpy(), steps)
 
 
+@pytest.mark.parametrize("points", [2, 3, 97, 204])
+def test_dvr_long_irregular_piecewise_tf(env, points):
+    """Piecewise TFs from the minimum of 2 control points to the maximum of 204, with clustered and duplicated positions:
+    the interval the kernels pick (tcgen05: binned start index + scan; mma.sync: linear scan) must be the one the
+    reference's linear search picks (renderer_tf_piecewise.cuh:27-52), for every density."""
+    rng = np.random.default_rng(points)
+    pos = np.sort(np.concatenate([rng.random(points // 2) * 0.1 + 0.3, rng.random(points - points // 2)])).astype(np.float32)
+    if points >= 8:
+        pos[5] = pos[4]                       # a zero-width interval
+        pos[points // 2:points // 2 + 3] = pos[points // 2]
+    pos[0], pos[-1] = 0.0, 1.0
+    # colour / absorption are smooth functions of the position, sampled at the irregular control points (a TF with random
+    # values per point, or non-zero absorption at density 0, would amplify the fp16 noise of the density itself and test
+    # the network, not the search); absorption 0 at density 0 keeps the image continuous across the density-min skip
+    tf = np.zeros((1, points, 5), np.float32)
+    tf[0, :, 0] = 0.5 + 0.5 * np.sin(3.0 * pos); tf[0, :, 1] = pos; tf[0, :, 2] = 1.0 - pos * pos
+    tf[0, :, 3] = 20.0 * pos * pos; tf[0, :, 4] = pos
+    g = Golden("c3_relu_gauss")
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, g.camera, tf, 1 / 64)
+    img = ie.render(48, 40).cpu().numpy()
+    ref, steps, _ = env.oracle.render_dvr(g.net, width=48, height=40, camera=g.camera, fov_y=env.scenes.DEFAULT_FOV_Y, stepsize=1 / 64, tf=tf)
+    assert np.abs(img[:, :4] - ref[:, :4]).max() <= RGBA_TOL
+    _check_steps(ie.last_step_counts.cpu().numpy(), steps)
+
+
 def test_dvr_rgbo_network_skips_tf(env):
     g = Golden("rgbo_32")
     cam = env.scenes.camera_reference_frame(**env.scenes.DEFAULT_CAMERA)
