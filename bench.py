@@ -143,7 +143,7 @@ def run_reference(args):
             "cpu_baseline": {"value": value, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    _emit(line)
     return 0
 
 
@@ -197,6 +197,7 @@ def run_b200(args):
         times = [(rank * V + i) * (T - 1) / max(1, world * V - 1) for i in range(V)]
         vt = (C.c_float * V)(*times); keep_alive.append(vt)
         p.view_times_host = C.cast(vt, C.c_void_p)
+    gathered = torch.empty((world * V, 4, S, S), dtype=torch.float32, device="cuda") if world > 1 else None
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
 
@@ -206,7 +207,7 @@ def run_b200(args):
         if ev: ev[1].record()
         rgba = ie.extract_color(out)
         if world > 1:
-            fdist.gather_views(rgba, world * V)  # one NCCL gather of the finished RGBA views on rank 0
+            fdist.gather_views(rgba, world * V, out=gathered, collective=args.collective)  # one NCCL collective: the finished RGBA views land on rank 0
         if ev: ev[2].record()
         return rgba
 
@@ -296,7 +297,7 @@ def run_b200(args):
             "metric": "srn_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-            "config": {"workload": f"{args.workload}: {w['desc']}", "views_per_step": world * V, "samples_per_pixel": int(w.get("spp", 1)), "sharding": "one view per GPU, RGBA gathered on rank 0 (NCCL)" if world > 1 else "single GPU",
+            "config": {"workload": f"{args.workload}: {w['desc']}", "views_per_step": world * V, "samples_per_pixel": int(w.get("spp", 1)), "sharding": f"{V} view(s) per GPU, RGBA collected on rank 0 (NCCL {args.collective})" if world > 1 else "single GPU",
                        "l2": "256 MiB buffer written between timed steps (outside the per-step CUDA-event pairs)",
                        "useful_samples_per_frame": useful / args.steps / world / V, "executed_samples_per_frame": executed / args.steps / world / V,
                        "kernel": {"block_threads": qi.block_threads, "blocks_per_sm": qi.blocks_per_sm, "grid": qi.grid_blocks,
@@ -338,10 +339,27 @@ def run_b200(args):
         except Exception as e:   # no prebuilt PTX for this network shape
             line["reference_gpu_kernel"] = {"unavailable": str(e)[:200]}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
     return 0
+
+
+_REAL_STDOUT = None
+
+
+def _guard_stdout():
+    """The contract is ONE JSON line on stdout. Libraries print there too (NCCL's version banner at communicator
+    creation): everything except the result line is sent to stderr."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(line):
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, (json.dumps(line) + "\n").encode())
 
 
 def main():
@@ -356,9 +374,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-batch-query", action="store_true", help="skip the C2 world-space batch query measurement")
     ap.add_argument("--no-gpu-reference", action="store_true", help="skip timing the reference's own kernel (oracle/_ref PTX)")
+    ap.add_argument("--collective", default="all_gather", choices=["gather", "all_gather"],
+                    help="N>1: how the finished RGBA views reach rank 0 (fv-srn_b200/dist.py gather_views)")
     ap.add_argument("--kernel-mode", default="tcgen05", choices=["tcgen05", "mma_sync"],
                     help="tcgen05: tcgen05.mma/TMEM kernel (default); mma_sync: reference-precision fp16-accumulate kernel")
     args = ap.parse_args()
+    _guard_stdout()
     if args.impl == "reference":
         return run_reference(args)
     return run_b200(args)

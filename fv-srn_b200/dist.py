@@ -86,12 +86,33 @@ def _scatter_rows(out: torch.Tensor, packed: torch.Tensor, rects: Sequence[Rect]
         y += h
 
 
-def gather_views(local: torch.Tensor, num_views: int, dst: int = 0) -> Optional[torch.Tensor]:
-    """local (v_rank,C,H,W) = this rank's views (partition_views order) -> (num_views,C,H,W) on `dst`."""
+def gather_views(local: torch.Tensor, num_views: int, dst: int = 0, out: Optional[torch.Tensor] = None,
+                 collective: str = "gather") -> Optional[torch.Tensor]:
+    """local (v_rank,C,H,W) = this rank's views (partition_views order) -> (num_views,C,H,W) on `dst` (None elsewhere).
+
+    When every rank owns the same number of views the pieces land directly in `out` (allocated here if None; pass a
+    persistent buffer to avoid the allocation per frame) with no staging copy. `collective`:
+      "gather"      ncclSend/Recv fan-in to `dst` - least traffic, but NCCL gives each peer pair only a few channels;
+      "all_gather"  every rank receives the whole batch (needs `out` on every rank) - rides NCCL's ring / NVLS
+                    all-gather at full NVSwitch bandwidth.
+    Uneven view counts fall back to a padded gather."""
     rank, world = world_info()
     if world == 1:
         return local
     counts = [len(partition_views(num_views, world, r)) for r in range(world)]
+    shape = (num_views,) + tuple(local.shape[1:])
+    if min(counts) == max(counts):
+        local = local.contiguous()
+        if collective == "all_gather":
+            if out is None:
+                out = local.new_empty(shape)
+            dist.all_gather_into_tensor(out, local)
+            return out if rank == dst else None
+        if rank == dst and out is None:
+            out = local.new_empty(shape)
+        pieces = list(out.chunk(world, dim=0)) if rank == dst else None     # contiguous slices of `out`
+        dist.gather(local, pieces, dst=dst)
+        return out if rank == dst else None
     pad = max(counts)
     buf = local.new_zeros((pad,) + tuple(local.shape[1:]))
     buf[:local.shape[0]] = local

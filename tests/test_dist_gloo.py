@@ -51,12 +51,22 @@ def _worker(rank, world, port, width, height, band, views, q):
             ok_views = bool(torch.equal(sweep, want))
         else:
             ok_views = sweep is None
+        if views % world == 0:      # even split: pieces land directly in a caller-provided buffer, both collectives
+            per = views // world
+            mine = torch.cat([render_view(i) for i in range(rank * per, (rank + 1) * per)], dim=0)
+            for coll in ("gather", "all_gather"):
+                buf = torch.full((views,) + tuple(mine.shape[1:]), -1.0)
+                got = fdist.gather_views(mine, views, out=buf, collective=coll)
+                if rank == 0:
+                    ok_views = ok_views and got is buf and bool(torch.equal(buf, want))
+                else:
+                    ok_views = ok_views and got is None
         q.put((rank, ok_frame, ok_views))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,width,height,band,views", [(2, 64, 200, 64, 5), (3, 40, 136, 8, 7), (2, 32, 24, 64, 2)])
+@pytest.mark.parametrize("world,width,height,band,views", [(2, 64, 200, 64, 5), (3, 40, 136, 8, 7), (2, 32, 24, 64, 2), (2, 32, 24, 8, 6)])
 def test_sharded_frame_and_sweep_gloo(world, width, height, band, views):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
