@@ -46,7 +46,7 @@ WORKLOADS = {
                     size=2048, stepsize=1.0 / 512, flop=43008, desc="fV-SRN 64x6, 30 Fourier, 64^3x16 grid; DVR 2048^2, 1 spp"),
     "C5": dict(net=dict(hidden=32, num_layers=4, grid_res=32, activation="ReLU", seed=42, last_gain=6.0, time_keyframes=8),
                size=512, stepsize=1.0 / 512, flop=7168, views=8, desc="time-dependent fV-SRN 32x4 (8 keyframe grids 32^3x16, temporally "
-               "interpolated), 512^2 camera sweep with per-view time, 8 views per GPU per step"),
+               "interpolated per view), 512^2 camera sweep, 8 views per GPU per step"),
 }
 
 
@@ -193,8 +193,9 @@ def run_b200(args):
     cam_dev = ie.camera.get_parameters(); tf_dev = ie.ray_evaluator.tf._tensor()
     p = ie._params(S, S, cam_dev, tf_dev, out.stride())
     p.counters_dev = counters.data_ptr()
-    if T > 1:   # time sweep: view i of the whole sweep is rendered at keyframe time i (T-1) / (views-1)
-        times = [(rank * V + i) * (T - 1) / max(1, world * V - 1) for i in range(V)]
+    if T > 1:   # per-view time: a golden-ratio sequence over the keyframe range, so that every rank's views need the temporal
+        # interpolation of two keyframe grids (the expensive case) in the same proportion at every N
+        times = [(T - 1) * (((rank * V + i) * 0.6180339887) % 1.0) for i in range(V)]
         vt = (C.c_float * V)(*times); keep_alive.append(vt)
         p.view_times_host = C.cast(vt, C.c_void_p)
     gathered = torch.empty((world * V, 4, S, S), dtype=torch.float32, device="cuda") if world > 1 else None
@@ -374,7 +375,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-batch-query", action="store_true", help="skip the C2 world-space batch query measurement")
     ap.add_argument("--no-gpu-reference", action="store_true", help="skip timing the reference's own kernel (oracle/_ref PTX)")
-    ap.add_argument("--collective", default="all_gather", choices=["gather", "all_gather"],
+    ap.add_argument("--collective", default="gather", choices=["gather", "all_gather"],
                     help="N>1: how the finished RGBA views reach rank 0 (fv-srn_b200/dist.py gather_views)")
     ap.add_argument("--kernel-mode", default="tcgen05", choices=["tcgen05", "mma_sync"],
                     help="tcgen05: tcgen05.mma/TMEM kernel (default); mma_sync: reference-precision fp16-accumulate kernel")
