@@ -17,6 +17,12 @@ constexpr int kTcComputeThreads = 128;
 constexpr int kTcThreads = 160;            // + the MMA warp
 constexpr int kTcTileW = 16, kTcTileH = 8;
 constexpr int kTcTfBins = 64;              // piecewise TF search accelerator: one start interval per density bin
+#ifndef FVSRN_LAGGED_VOTE
+#define FVSRN_LAGGED_VOTE 1   // A/B on one B200 (C3): 5.48 ms vs 5.56 ms with a CTA-wide vote every trip
+#endif
+#ifndef FVSRN_NO_SYNCWARP
+#define FVSRN_NO_SYNCWARP 0
+#endif
 constexpr int kTcTfFloats = 2560;          // shared-memory TF: up to 204 piecewise intervals x 12 floats, or 256 x float4 texels
 
 // Transfer function staged in shared memory in evaluation-ready form. Piecewise (reference renderer_tf_piecewise.cuh:
@@ -287,7 +293,7 @@ struct SrnTc {
     static __device__ __forceinline__ void publish(const Ctx& c, int slot) {
         tc::wait_st();
         tc::fence_before_sync();
-        __syncwarp();
+        if (!FVSRN_NO_SYNCWARP) __syncwarp();    // (elect.sync in the arrive converges the warp as well)
         tc::mbar_arrive_elect(c.ready + 8 * slot);
     }
 
@@ -413,6 +419,7 @@ __device__ __forceinline__ typename Net::Ctx tc_prologue(const NetParams& P, TcS
     load_blob(P, sblob);
     const int warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
+        sh->pad[0] = sh->pad[1] = -1;    // trip-vote flags (FVSRN_LAGGED_VOTE)
         tc::mbar_init(smem_u32(&sh->ready[0]), 4); tc::mbar_init(smem_u32(&sh->ready[1]), 4);
         tc::mbar_init(smem_u32(&sh->done[0]), 1); tc::mbar_init(smem_u32(&sh->done[1]), 1);
     }
@@ -472,6 +479,7 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
     const int lx = (warp & 1) * 8 + (lane & 7), ly = ((warp >> 1) & 1) * 4 + (lane >> 3);
 
     unsigned long long n_valid = 0, n_exec = 0;
+    int trip_id = 0;     // trips executed by this CTA (same count in every warp)
     for (;;) {
         if (threadIdx.x == 0) sh->tile = int(atomicAdd(D.tile_counter, 1u));
         __syncthreads();
@@ -490,11 +498,22 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
 
         if (is_mma_warp) {
             // ---------------------------------------------------------------- MMA warp: one elected thread issues
-            for (int s = 0; s < D.spp; ++s)
+            for (int s = 0; s < D.spp; ++s) {
+                if (FVSRN_LAGGED_VOTE) {
+                    // one CTA vote per march; afterwards trip i+1 runs iff some warp had work in trip i (flag written
+                    // before that warp's first arrival of trip i, read after this warp's last ready-wait of trip i)
+                    bool cont = __syncthreads_or(0);
+                    while (cont) {
+                        Net::mlp_issue(P, ctx);
+                        cont = *reinterpret_cast<volatile int*>(&sh->pad[trip_id & 1]) == trip_id;
+                        ++trip_id;
+                    }
+                } else
                 for (;;) {
                     if (!__syncthreads_or(0)) break;
                     Net::mlp_issue(P, ctx);
                 }
+            }
             continue;
         }
         // -------------------------------------------------------------------- compute warps
@@ -516,15 +535,20 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
             // steps are evaluated per trip (slot 0 = step i, slot 1 = step i+1, the second speculatively: whether it is
             // needed is only known after step i has been composited); samples are blended in order, so the result is
             // the sequential one.
+            bool cont = true;
             for (int i = 0;; i += 2) {
                 const float t0 = __fmaf_rn(float(i), D.stepsize, r.tmin);
                 const float t1 = __fmaf_rn(float(i + 1), D.stepsize, r.tmin);
                 const bool alive = !D.early_out || (acc.w < D.alpha_early_out);
                 const bool valid0 = (t0 <= tmax) && alive;
                 const bool in1 = (t1 <= tmax) && alive;
-                if (!__syncthreads_or(valid0 ? 1 : 0)) break;
+                if (FVSRN_LAGGED_VOTE) {
+                    if (i == 0) cont = __syncthreads_or(valid0 ? 1 : 0);
+                    if (!cont) break;
+                } else if (!__syncthreads_or(valid0 ? 1 : 0)) break;
                 // a warp whose 32 rays are all finished keeps the barrier protocol going but skips the arithmetic
                 const bool warp_active = __any_sync(0xffffffffu, valid0);
+                if (FVSRN_LAGGED_VOTE && warp_active && lane == 0) *reinterpret_cast<volatile int*>(&sh->pad[trip_id & 1]) = trip_id;
                 if (warp_active) {
                     float px = 0.f, py = 0.f, pz = 0.f, qx = 0.f, qy = 0.f, qz = 0.f;
                     if (valid0) {
@@ -563,6 +587,10 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
                 }
                 float o0[4], o1[4];
                 Net::mlp_compute(P, ctx, warp_active, o0, o1);
+                if (FVSRN_LAGGED_VOTE) {    // every warp's flag store of this trip precedes the MMAs this warp just waited for
+                    cont = *reinterpret_cast<volatile int*>(&sh->pad[trip_id & 1]) == trip_id;
+                    ++trip_id;
+                }
                 if (lane == 0) n_exec += 64;
                 // both samples are shaded first (independent work, interleaved by the compiler), then composited in order
                 const float4 c0 = tc_shade_sample(P, D, stf, o0), c1 = tc_shade_sample(P, D, stf, o1);
