@@ -40,9 +40,9 @@ WORKLOADS = {
                      size=1024, stepsize=1.0 / 512, flop=7168, desc="as C3 with SnakeAlt:2 activations"),
     "C1": dict(net=dict(hidden=32, num_layers=4, grid_res=16, activation="ReLU", seed=42, last_gain=6.0),
                size=256, stepsize=0.005, flop=7168, desc="fV-SRN 32x4, 16^3x16 grid; DVR 256^2, step 0.005"),
-    "C4": dict(net=dict(hidden=64, num_layers=6, grid_res=64, activation="ReLU", seed=42, last_gain=4.0),
+    "C4": dict(net=dict(hidden=64, num_layers=6, grid_res=64, activation="ReLU", seed=42, hidden_gain=2.0),
                size=2048, stepsize=1.0 / 512, flop=43008, spp=4, desc="fV-SRN 64x6, 30 Fourier, 64^3x16 grid; DVR 2048^2, 4 spp"),
-    "C4-1spp": dict(net=dict(hidden=64, num_layers=6, grid_res=64, activation="ReLU", seed=42, last_gain=4.0),
+    "C4-1spp": dict(net=dict(hidden=64, num_layers=6, grid_res=64, activation="ReLU", seed=42, hidden_gain=2.0),
                     size=2048, stepsize=1.0 / 512, flop=43008, desc="fV-SRN 64x6, 30 Fourier, 64^3x16 grid; DVR 2048^2, 1 spp"),
     "C5": dict(net=dict(hidden=32, num_layers=4, grid_res=32, activation="ReLU", seed=42, last_gain=6.0, time_keyframes=8),
                size=512, stepsize=1.0 / 512, flop=7168, views=8, desc="time-dependent fV-SRN 32x4 (8 keyframe grids 32^3x16, temporally "

@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -23,10 +24,25 @@ int fail(const std::string& msg) { g_last_error = msg; return 1; }
 #define CUDA_OK(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) \
     throw std::runtime_error(std::string(#expr) + " failed: " + cudaGetErrorString(_e)); } while (0)
 
+// Entry points run on the network's device and leave the caller's current device as they found it.
+struct DeviceGuard {
+    int prev = -1; bool switched = false;
+    explicit DeviceGuard(int dev) {
+        if (dev < 0) return;
+        if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; return; }
+        if (prev != dev) { switched = cudaSetDevice(dev) == cudaSuccess; }
+    }
+    ~DeviceGuard() { if (switched && prev >= 0) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard&) = delete;
+    DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+
 struct DeviceGrid {
     __half* data = nullptr; int C = 0, Z = 0, Y = 0, X = 0;   // channel-last fp16 (mma.sync path)
     std::vector<cudaArray_t> arrays;                          // C/4 fp16 RGBA 3-D arrays + texture objects (tcgen05 path)
     std::vector<cudaTextureObject_t> tex;
+    std::vector<cudaArray_t> arrays32;                        // the same (fp16-rounded) texels as fp32 RGBA textures, created on
+    std::vector<cudaTextureObject_t> tex32;                   // first use of the reference-exact mode (the reference's own format)
 };
 } // namespace
 
@@ -47,12 +63,15 @@ struct fvsrn_network {
     int tile_counter_slots = 0, tile_counter_next = 0;
     float* d_scratch = nullptr; size_t scratch_bytes = 0;  // staging for the *_host entry points
     unsigned long long launches = 0;
+    // A handle is used by one host thread at a time (as the reference's modules); concurrent calls on one
+    // handle are serialised here because the work-queue counter ring and the staging buffer are per-handle state.
+    std::mutex mu;
 };
 
 namespace {
 
 void release_gpu(fvsrn_network* h) {
-    if (h->device >= 0) cudaSetDevice(h->device);
+    DeviceGuard guard(h->device);
     if (h->d_blob) cudaFree(h->d_blob);
     if (h->d_tc_blob) cudaFree(h->d_tc_blob);
     h->d_tc_blob = nullptr;
@@ -61,6 +80,8 @@ void release_gpu(fvsrn_network* h) {
             if (g.data) cudaFree(g.data);
             for (auto t : g.tex) cudaDestroyTextureObject(t);
             for (auto a : g.arrays) cudaFreeArray(a);
+            for (auto t : g.tex32) cudaDestroyTextureObject(t);
+            for (auto a : g.arrays32) cudaFreeArray(a);
         }
     if (h->d_tile_counter) cudaFree(h->d_tile_counter);
     if (h->d_scratch) cudaFree(h->d_scratch);
@@ -185,11 +206,43 @@ void build_tc_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
 }
 
 launch_fn pick_launcher(int H16) {
+#ifdef FVSRN_ONLY_H2     // kernel-tuning builds (make FAST=1)
+    return H16 == 2 ? launch_h2 : nullptr;
+#else
     switch (H16) {
         case 2: return launch_h2; case 3: return launch_h3; case 4: return launch_h4;
         case 6: return launch_h6; case 8: return launch_h8;
     }
     return nullptr;
+#endif
+}
+
+// fp32 RGBA textures of one latent grid for the reference-exact mode: LatentGrid::GPUArray as the reference creates it
+// (volume_interpolation_network.cpp:470-504), holding the fp16-rounded voxel values every kernel family of this
+// library sees
+void ensure_tex32(DeviceGrid& d, const LatentGrid& g) {
+    if (!d.tex32.empty()) return;
+    std::vector<float> sub(size_t(g.Z) * g.Y * g.X * 4);
+    for (int q = 0; q < g.C / 4; ++q) {
+        for (int z = 0; z < g.Z; ++z) for (int y = 0; y < g.Y; ++y) for (int x = 0; x < g.X; ++x)
+            for (int c = 0; c < 4; ++c)
+                sub[((size_t(z) * g.Y + y) * g.X + x) * 4 + c] = f16_to_f32(f32_to_f16(g.decoded(q * 4 + c, z, y, x)));
+        cudaChannelFormatDesc fd = cudaCreateChannelDesc<float4>();
+        cudaArray_t arr = nullptr;
+        CUDA_OK(cudaMalloc3DArray(&arr, &fd, make_cudaExtent(g.X, g.Y, g.Z)));
+        d.arrays32.push_back(arr);
+        cudaMemcpy3DParms cp = {};
+        cp.srcPtr = make_cudaPitchedPtr(sub.data(), size_t(g.X) * 16, g.X, g.Y);
+        cp.dstArray = arr; cp.extent = make_cudaExtent(g.X, g.Y, g.Z); cp.kind = cudaMemcpyHostToDevice;
+        CUDA_OK(cudaMemcpy3D(&cp));
+        cudaResourceDesc rd = {}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+        cudaTextureDesc td = {};
+        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 1;
+        cudaTextureObject_t t = 0;
+        CUDA_OK(cudaCreateTextureObject(&t, &rd, &td, nullptr));
+        d.tex32.push_back(t);
+    }
 }
 
 // device-side view of the network for a given absolute time / ensemble (reference fillConstantMemory :1290-1352)
@@ -215,17 +268,22 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
             P.time_value = t;
             const DeviceGrid& A = h->d_time[lo]; const DeviceGrid& B = h->d_time[hi];
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
+            const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && !A.tex32.empty() && !B.tex32.empty();
             for (int i = 0; i < A.C / 16; ++i, ++g) {
                 P.groups[g] = GridGroup{A.data + 16 * i, B.data + 16 * i, frac, A.C * 2 / 16};
-                for (int q = 0; q < 4; ++q) { P.tex_a[4 * g + q] = A.tex[4 * i + q]; P.tex_b[4 * g + q] = B.tex[4 * i + q]; }
+                for (int q = 0; q < 4; ++q) {
+                    P.tex_a[4 * g + q] = exact ? A.tex32[4 * i + q] : A.tex[4 * i + q];
+                    P.tex_b[4 * g + q] = exact ? B.tex32[4 * i + q] : B.tex[4 * i + q];
+                }
             }
         }
         if (!h->d_ens.empty()) {
             const DeviceGrid& A = h->d_ens[n.interpolate_ensemble(ensemble)];
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
+            const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && !A.tex32.empty();
             for (int i = 0; i < A.C / 16; ++i, ++g) {
                 P.groups[g] = GridGroup{A.data + 16 * i, A.data + 16 * i, 0.f, A.C * 2 / 16};
-                for (int q = 0; q < 4; ++q) P.tex_a[4 * g + q] = P.tex_b[4 * g + q] = A.tex[4 * i + q];
+                for (int q = 0; q < 4; ++q) P.tex_a[4 * g + q] = P.tex_b[4 * g + q] = exact ? A.tex32[4 * i + q] : A.tex[4 * i + q];
             }
         }
     }
@@ -249,15 +307,12 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
         for (int k = 0; k < last.cin && k < 128; ++k) w[k] = last.w(0, k);
         P.blast = f16_to_f32(last.bias[0]);
     }
-    static const int dbg = [] { const char* e = std::getenv("FVSRN_TC_DEBUG"); return e ? std::atoi(e) : 0; }();
-    P.dbg_flags = dbg;
     return P;
 }
 
 void require_prepared(fvsrn_network* h) {
     if (!h) throw std::runtime_error("null network handle");
     if (!h->prepared) throw std::runtime_error("network is not prepared: call fvsrn_network_prepare first");
-    CUDA_OK(cudaSetDevice(h->device));
 }
 
 unsigned int* next_tile_counter(fvsrn_network* h, cudaStream_t s) {
@@ -431,7 +486,7 @@ int fvsrn_network_set_time_and_ensemble(fvsrn_network* net, float time, int ense
 
 int fvsrn_network_set_kernel_mode(fvsrn_network* net, int mode) {
     if (!net) return fail("null network handle");
-    if (mode != FVSRN_KERNEL_MMA_SYNC && mode != FVSRN_KERNEL_TCGEN05) return fail("unknown kernel mode");
+    if (mode != FVSRN_KERNEL_MMA_SYNC && mode != FVSRN_KERNEL_TCGEN05 && mode != FVSRN_KERNEL_REFERENCE_EXACT) return fail("unknown kernel mode");
     net->kernel_mode = mode;
     return 0;
 }
@@ -463,10 +518,11 @@ int fvsrn_network_prepare(fvsrn_network* net, int device, void* stream) {
     if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
         return fail("no CUDA device available: the fV-SRN B200 path has no CPU fallback");
     if (device < 0 || device >= count) return fail("invalid device index");
+    std::lock_guard<std::mutex> lock(net->mu);
     release_gpu(net);
     std::vector<uint8_t> blob;
     build_blob(net, blob);
-    CUDA_OK(cudaSetDevice(device));
+    DeviceGuard guard(device);
     net->device = device;
     cudaDeviceProp prop;
     CUDA_OK(cudaGetDeviceProperties(&prop, device));
@@ -528,6 +584,7 @@ int fvsrn_network_prepare(fvsrn_network* net, int device, void* stream) {
 
 int fvsrn_network_clear_gpu_resources(fvsrn_network* net) {
     if (!net) return fail("null network handle");
+    std::lock_guard<std::mutex> lock(net->mu);
     release_gpu(net);
     return 0;
 }
@@ -559,6 +616,7 @@ void do_evaluate(fvsrn_network* h, const float* pos, const float* dir, float* ou
     if (n == 0) return;
     if (!pos || !out) throw std::runtime_error("null device pointer");
     if (h->net.has_direction && !dir) throw std::runtime_error("the network uses directions, but no directions were passed");
+    if (h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT) throw std::runtime_error("the reference-exact kernel mode covers the DVR frame only");
     // reference volume_interpolation.cpp:45-48: positions are in the unit cube
     const NetParams P = make_net_params(h, h->net.current_time, h->net.current_ensemble, true);
     EvalParams E{pos, dir, out, (long long)n, kOutputModeChannelsOut[h->net.output_mode]};
@@ -586,7 +644,6 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         if (floats > kTfSmemFloats) throw std::runtime_error("transfer function too large for the fused kernel (max 204 control points / 256 texels)");
         if (p->tf_batch != 1 && p->tf_batch != p->batch) throw std::runtime_error("transfer function batch must be 1 or equal to the camera batch");
     }
-    if (h->net.has_direction && false) {}
     int spp = p->samples_per_pixel <= 0 ? 1 : p->samples_per_pixel;
     int side = int(std::lround(std::sqrt(double(spp))));
     if (side * side != spp) throw std::runtime_error("samples_per_pixel must be a square number (1, 4, 9, ...)");
@@ -597,10 +654,10 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     D.th = p->tile_h > 0 ? p->tile_h : p->height - p->tile_y0;
     if (D.x0 < 0 || D.y0 < 0 || D.tw <= 0 || D.th <= 0 || D.x0 + D.tw > D.W || D.y0 + D.th > D.H) throw std::runtime_error("tile rectangle outside the image");
     D.cam = p->camera_matrix_dev;
-    D.tan_half_fovy = std::tan(p->fov_y_radians * 0.5f);
+    D.fov_y = p->fov_y_radians;
     D.aspect = float(double(p->width) / double(p->height)); // camera->setAspectRatio, image_evaluator_simple.cpp:204
     D.stepsize = p->stepsize; D.alpha_early_out = p->alpha_early_out;
-    D.dmin = p->density_min; D.inv_range = 1.0f / (p->density_max - p->density_min);
+    D.dmin = p->density_min; D.dmax = p->density_max; D.inv_range = 1.0f / (p->density_max - p->density_min);
     D.early_out = p->early_out; D.blend_mode = p->blend_mode;
     D.tf_kind = is_rgbo ? 2 : p->tf_kind; D.tf_R = p->tf_resolution; D.tf_batch = is_rgbo ? 1 : p->tf_batch;
     D.tf = is_rgbo ? reinterpret_cast<const float*>(h->d_blob) : p->tf_dev; // rgbo networks skip the TF; any readable pointer
@@ -608,6 +665,15 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     D.out = out; D.sb = p->out_stride_b; D.sc = p->out_stride_c; D.sy = p->out_stride_y; D.sx = p->out_stride_x;
     D.step_count = p->step_count_dev; D.counters = p->counters_dev;
     const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05;
+    const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT;
+    if (exact) {    // the shapes the reference kernels this mode is validated against cover (kernels_exact.cuh)
+        const Network& n = h->net;
+        if (n.output_mode != OUT_DENSITY_DIRECT || n.has_time || n.has_direction || h->GC16 != 1)
+            throw std::runtime_error("reference-exact mode: density:direct networks with one 16-channel latent grid, without time/direction input");
+        if (p->tf_kind != FVSRN_TF_PIECEWISE && p->tf_kind != FVSRN_TF_TEXTURE) throw std::runtime_error("reference-exact mode: piecewise or texture transfer function");
+        for (size_t i = 0; i < h->d_time.size(); ++i) ensure_tex32(h->d_time[i], n.time_grids[i]);
+        for (size_t i = 0; i < h->d_ens.size(); ++i) ensure_tex32(h->d_ens[i], n.ensemble_grids[i]);
+    }
     const int tile_w = tc ? kTcTileW : kTileW, tile_h = tc ? kTcTileH : kTileH;
     D.tiles_x = (D.tw + tile_w - 1) / tile_w; D.tiles_y = (D.th + tile_h - 1) / tile_h;
     launch_fn fn = pick_launcher(h->H16);
@@ -619,7 +685,8 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         d.tile_counter = next_tile_counter(h, s);
         LaunchCfg cfg; cfg.sm_count = h->sm_count;
         cfg.max_blocks = tc ? d.num_tiles : (d.num_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
-        CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, s));
+        if (exact) CUDA_OK(launch_exact(h->H16, P, d, &cfg, s));
+        else CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, s));
         h->launches++;
     };
     if (p->view_times_host) { // one launch per view: every view selects its own keyframe pair (time sweeps)
@@ -637,6 +704,9 @@ extern "C" {
 int fvsrn_evaluate(fvsrn_network* net, const float* positions_dev, const float* directions_dev, float* out_dev,
                    int64_t n, void* stream) {
     FV_TRY
+    if (!net) return fail("null network handle");
+    std::lock_guard<std::mutex> lock(net->mu);
+    DeviceGuard guard(net->device);
     do_evaluate(net, positions_dev, directions_dev, out_dev, n, static_cast<cudaStream_t>(stream));
     return 0;
     FV_CATCH
@@ -645,6 +715,9 @@ int fvsrn_evaluate(fvsrn_network* net, const float* positions_dev, const float* 
 int fvsrn_evaluate_host(fvsrn_network* net, const float* positions_host, const float* directions_host, float* out_host,
                         int64_t n, void* stream) {
     FV_TRY
+    if (!net) return fail("null network handle");
+    std::lock_guard<std::mutex> lock(net->mu);
+    DeviceGuard guard(net->device);
     require_prepared(net);
     if (n <= 0) return n == 0 ? 0 : fail("negative sample count");
     if (!positions_host || !out_host) return fail("null host pointer");
@@ -667,6 +740,9 @@ int fvsrn_evaluate_host(fvsrn_network* net, const float* positions_host, const f
 
 int fvsrn_render_dvr(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_dev, void* stream) {
     FV_TRY
+    if (!net) return fail("null network handle");
+    std::lock_guard<std::mutex> lock(net->mu);
+    DeviceGuard guard(net->device);
     do_render(net, p, out_dev, static_cast<cudaStream_t>(stream));
     return 0;
     FV_CATCH
@@ -674,6 +750,9 @@ int fvsrn_render_dvr(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_d
 
 int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_host, void* stream) {
     FV_TRY
+    if (!net) return fail("null network handle");
+    std::lock_guard<std::mutex> lock(net->mu);
+    DeviceGuard guard(net->device);
     require_prepared(net);
     if (!p || !out_host) return fail("null argument");
     if (p->out_stride_x != 1 || p->out_stride_y != p->width || p->out_stride_c != (int64_t)p->width * p->height ||
@@ -716,6 +795,9 @@ int fvsrn_extract_color(const float* img_dev, float* out_dev, int batch, int hei
 
 int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     FV_TRY
+    if (!net) return fail("null network handle");
+    std::lock_guard<std::mutex> lock(net->mu);
+    DeviceGuard guard(net->device);
     require_prepared(net);
     if (!info) return fail("null argument");
     const NetParams P = make_net_params(net, net->net.current_time, net->net.current_ensemble, false);
@@ -724,7 +806,8 @@ int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     if (!fn) return fail("no kernel for this hidden width");
     const bool tc = net->kernel_mode == FVSRN_KERNEL_TCGEN05;
     DvrParams dq{}; dq.tf_kind = 0; dq.tf_R = 8;   // a typical piecewise TF: the DVR kernels size their shared memory from it
-    CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, kernel == 0 ? &dq : nullptr, &cfg, nullptr));
+    if (net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact(net->H16, P, dq, &cfg, nullptr));
+    else CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, kernel == 0 ? &dq : nullptr, &cfg, nullptr));
     info->device = net->device; info->sm_count = net->sm_count;
     info->block_threads = cfg.threads; info->blocks_per_sm = cfg.blocks_per_sm; info->grid_blocks = cfg.grid;
     info->smem_bytes_per_block = cfg.smem; info->regs_per_thread = cfg.regs;

@@ -20,8 +20,8 @@ struct DvrParams {
     int x0, y0, tw, th;       // rendered sub-rectangle
     int b0, nb;               // first batch index and number of batches of this launch
     const float* cam;         // (B,3,3)
-    float tan_half_fovy, aspect;
-    float stepsize, alpha_early_out, dmin, inv_range;
+    float fov_y, aspect;       // fovY in radians; tan(fovY/2) is taken on the device as the reference does
+    float stepsize, alpha_early_out, dmin, inv_range, dmax;
     int early_out, blend_mode;
     int tf_kind, tf_R, tf_batch;
     const float* tf;
@@ -75,18 +75,39 @@ __device__ __forceinline__ float4 tf_texture(const float* tf, int R, float d) { 
 struct Ray { float3 eye, dir; float tmin, tmax; };
 struct CamFrame { float3 eye, right, up, front; float tan_x, tan_y; };
 
-// camera frame, reference renderer_camera.cuh:34-52
+// fp32 operations exactly as the reference kernel executes them. The reference is compiled with --use_fast_math
+// (kernel_loader.cpp:229-241): flush-to-zero arithmetic, div.approx / rcp.approx / rsqrt.approx / sin.approx /
+// cos.approx / ex2.approx. Spelled as PTX here so that this file's results do not depend on its own compile flags.
+// Ray setup decides per ray how many steps fall inside the box (t <= tmax); with these operations in the
+// reference's order that count is bit-identical to the reference kernel's for every ray.
+namespace rf {
+#define FV_RF2(name, ptx) __device__ __forceinline__ float name(float a, float b) { float r; asm(ptx " %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+#define FV_RF1(name, ptx) __device__ __forceinline__ float name(float a) { float r; asm(ptx " %0, %1;" : "=f"(r) : "f"(a)); return r; }
+FV_RF2(add, "add.ftz.f32") FV_RF2(sub, "sub.ftz.f32") FV_RF2(mul, "mul.ftz.f32") FV_RF2(div, "div.approx.ftz.f32")
+FV_RF2(fmin, "min.ftz.f32") FV_RF2(fmax, "max.ftz.f32")
+FV_RF1(rcp, "rcp.approx.ftz.f32") FV_RF1(rsqrt, "rsqrt.approx.ftz.f32") FV_RF1(sin, "sin.approx.ftz.f32")
+FV_RF1(cos, "cos.approx.ftz.f32") FV_RF1(ex2, "ex2.approx.ftz.f32") FV_RF1(floor, "cvt.rmi.ftz.f32.f32")
+__device__ __forceinline__ float fma(float a, float b, float c) { float r; asm("fma.rn.ftz.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+// (a < b) ? a : b and (a > b) ? a : b as the reference's fminf/fmaxf-free helper_math compiles (setp + selp)
+__device__ __forceinline__ float sel_lt(float a, float b) { return (a < b) ? a : b; }
+__device__ __forceinline__ float sel_gt(float a, float b) { return (a > b) ? a : b; }
+#undef FV_RF1
+#undef FV_RF2
+} // namespace rf
+
+// camera frame, reference renderer_camera.cuh:34-52 (operation order of the compiled reference kernel)
 __device__ __forceinline__ CamFrame load_camera(const DvrParams& D, int b) {
     CamFrame c;
     const float* cm = D.cam + (size_t)b * 9;
     c.eye = make_float3(__ldg(cm + 0), __ldg(cm + 1), __ldg(cm + 2));
     c.right = make_float3(__ldg(cm + 3), __ldg(cm + 4), __ldg(cm + 5));
     c.up = make_float3(__ldg(cm + 6), __ldg(cm + 7), __ldg(cm + 8));
-    // explicit rounding order (no compiler FMA contraction) so that the CPU oracle reproduces ray setup bit for bit
-    c.front = make_float3(__fmaf_rn(c.up.y, c.right.z, -__fmul_rn(c.up.z, c.right.y)),
-                          __fmaf_rn(c.up.z, c.right.x, -__fmul_rn(c.up.x, c.right.z)),
-                          __fmaf_rn(c.up.x, c.right.y, -__fmul_rn(c.up.y, c.right.x))); // cross(up, right)
-    c.tan_y = D.tan_half_fovy; c.tan_x = __fmul_rn(c.tan_y, D.aspect);
+    c.front = make_float3(rf::sub(rf::mul(c.right.z, c.up.y), rf::mul(c.right.y, c.up.z)),
+                          rf::sub(rf::mul(c.right.x, c.up.z), rf::mul(c.right.z, c.up.x)),
+                          rf::sub(rf::mul(c.right.y, c.up.x), rf::mul(c.right.x, c.up.y))); // cross(up, right)
+    const float half_fov = rf::div(D.fov_y, 2.0f);
+    c.tan_y = rf::div(rf::sin(half_fov), rf::cos(half_fov));      // tanf under fast math
+    c.tan_x = rf::mul(c.tan_y, D.aspect);
     return c;
 }
 
@@ -94,27 +115,28 @@ __device__ __forceinline__ CamFrame load_camera(const DvrParams& D, int b) {
 // and its box interval (renderer_utils.cuh:91-105, renderer_ray_evaluation_stepping_dvr.cuh:66-71)
 __device__ __forceinline__ Ray make_ray(const DvrParams& D, const CamFrame& c, int x, int y, int s, float3 bmin, float3 bsize) {
     float nx = float(x), ny = float(y);
-    if (D.spp > 1) {                // deterministic stratified sub-pixel offsets
+    if (D.spp > 1) {                // deterministic stratified sub-pixel offsets (no reference counterpart)
         nx = __fadd_rn(nx, __fsub_rn(__fdiv_rn(float(s % D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
         ny = __fadd_rn(ny, __fsub_rn(__fdiv_rn(float(s / D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
     }
-    const float ndc_x = __fsub_rn(__fdiv_rn(2.f * (nx + 0.5f), float(D.W)), 1.f);
-    const float ndc_y = __fsub_rn(__fdiv_rn(2.f * (ny + 0.5f), float(D.H)), 1.f);
-    const float sx = __fmul_rn(ndc_x, c.tan_x), sy = __fmul_rn(ndc_y, c.tan_y);
-    float3 dir = make_float3(__fmaf_rn(sy, c.up.x, __fmaf_rn(sx, c.right.x, c.front.x)),
-                             __fmaf_rn(sy, c.up.y, __fmaf_rn(sx, c.right.y, c.front.y)),
-                             __fmaf_rn(sy, c.up.z, __fmaf_rn(sx, c.right.z, c.front.z)));
-    const float len2 = __fmaf_rn(dir.z, dir.z, __fmaf_rn(dir.y, dir.y, __fmul_rn(dir.x, dir.x)));
-    const float inv_len = __fdiv_rn(1.0f, __fsqrt_rn(len2));
-    dir.x = __fmul_rn(dir.x, inv_len); dir.y = __fmul_rn(dir.y, inv_len); dir.z = __fmul_rn(dir.z, inv_len);
+    const float hx = rf::add(nx, 0.5f), hy = rf::add(ny, 0.5f);
+    const float ndc_x = rf::add(rf::div(rf::add(hx, hx), float(D.W)), -1.0f);
+    const float ndc_y = rf::add(rf::div(rf::add(hy, hy), float(D.H)), -1.0f);
+    const float sx = rf::mul(ndc_x, c.tan_x), sy = rf::mul(ndc_y, c.tan_y);
+    float3 dir = make_float3(rf::fma(sy, c.up.x, rf::fma(sx, c.right.x, c.front.x)),
+                             rf::fma(sy, c.up.y, rf::fma(sx, c.right.y, c.front.y)),
+                             rf::fma(sy, c.up.z, rf::fma(sx, c.right.z, c.front.z)));
+    const float len2 = rf::fma(dir.z, dir.z, rf::fma(dir.x, dir.x, rf::mul(dir.y, dir.y)));
+    const float inv_len = rf::rsqrt(len2);
+    dir.x = rf::mul(inv_len, dir.x); dir.y = rf::mul(inv_len, dir.y); dir.z = rf::mul(inv_len, dir.z);
     const float3 eye = c.eye;
-    const float ix = __fdiv_rn(1.0f, dir.x), iy = __fdiv_rn(1.0f, dir.y), iz = __fdiv_rn(1.0f, dir.z);
-    const float t1 = __fmul_rn(__fsub_rn(bmin.x, eye.x), ix), t2 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.x, bsize.x), eye.x), ix);
-    const float t3 = __fmul_rn(__fsub_rn(bmin.y, eye.y), iy), t4 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.y, bsize.y), eye.y), iy);
-    const float t5 = __fmul_rn(__fsub_rn(bmin.z, eye.z), iz), t6 = __fmul_rn(__fsub_rn(__fadd_rn(bmin.z, bsize.z), eye.z), iz);
+    const float ix = rf::div(1.0f, dir.x), iy = rf::div(1.0f, dir.y), iz = rf::div(1.0f, dir.z);
+    const float t1 = rf::mul(rf::sub(bmin.x, eye.x), ix), t2 = rf::mul(ix, rf::sub(rf::add(bmin.x, bsize.x), eye.x));
+    const float t3 = rf::mul(rf::sub(bmin.y, eye.y), iy), t4 = rf::mul(iy, rf::sub(rf::add(bmin.y, bsize.y), eye.y));
+    const float t5 = rf::mul(rf::sub(bmin.z, eye.z), iz), t6 = rf::mul(rf::sub(rf::add(bmin.z, bsize.z), eye.z), iz);
     Ray r; r.eye = eye; r.dir = dir;
-    r.tmin = fmaxf(fmaxf(fmaxf(fminf(t1, t2), fminf(t3, t4)), fminf(t5, t6)), 0.f);
-    r.tmax = fminf(fminf(fminf(fmaxf(t1, t2), fmaxf(t3, t4)), fmaxf(t5, t6)), FLT_MAX);
+    r.tmin = rf::fmax(rf::sel_gt(rf::sel_gt(rf::sel_lt(t1, t2), rf::sel_lt(t3, t4)), rf::sel_lt(t5, t6)), 0.f);
+    r.tmax = rf::fmin(rf::sel_lt(rf::sel_lt(rf::sel_gt(t1, t2), rf::sel_gt(t3, t4)), rf::sel_gt(t5, t6)), FLT_MAX);
     return r;
 }
 

@@ -1,0 +1,296 @@
+// Reference-exact mode (FVSRN_KERNEL_REFERENCE_EXACT): the DVR frame with the arithmetic of the reference's compiled
+// kernel, operation for operation, so that images AND early-termination step counts are bit-identical to
+// ImageEvaluatorSimpleKernel + RayEvaluationSteppingDvr + VolumeInterpolationTensorcores run on the same GPU
+// (north_star: "early-termination step counts bit-exact against the reference's tensor-core kernel when it is run
+// with the same precision"). It is the validation mode, not the fast path.
+//
+// What "same arithmetic" means here (reference file:line; the operation order is that of the reference kernel as NVRTC
+// compiles it with --use_fast_math, kernel_loader.cpp:229-241):
+//   * ray setup, stepping, position: rf:: operations (flush-to-zero, div.approx, rsqrt.approx, sin/cos.approx), kernels.cuh
+//   * p = (pos - boxMin) / boxSize with div.approx (renderer_volume_tensorcores.cuh:746); fp16 inputs by cvt.rn (:768-771)
+//   * Fourier features: fp16 phase chain hmul, hfma, hfma, then hcos / hsin of cuda_fp16.hpp (:795-807)
+//   * latent vector: tex3D<float4> on FP32 textures, both keyframes always fetched, v = vA + frac(t)*(vB - vA) as
+//     sub + fma, then cvt.rn.f16 (:573-605)
+//   * layers: HMMA m16n8k16 with fp16 accumulators, accumulator preloaded with the bias, K consumed 16 at a time,
+//     Fourier block first, then the latent chunk (:839-910, 956-995: wmma m16n16k16 = two HMMA.16816.F16 per op)
+//   * activations on the fp16 accumulator elements with the reference's formulas for __CUDA_ARCH__ < 800 - the kernel is
+//     built for compute_75 (renderer_activations.cuh:39-341)
+//   * last layer: one sequential fp16 fma chain over the hidden channels, starting from the bias (:1138-1143)
+//   * density range, piecewise / texture TF, Beer-Lambert / alpha blending and the output normalisation in the
+//     reference's fp32 operation order (renderer_ray_evaluation_stepping_dvr.cuh:84-154, renderer_tf_piecewise.cuh:27-62,
+//     renderer_tf_texture.cuh:46-56, renderer_blending.cuh:36-51, renderer_image_evaluator_simple.cuh:96-124)
+// Scope: density networks ("density:direct"), Fourier features, one 16-channel latent grid group (static, time
+// keyframes or ensemble), no direction / time input - the shapes the reference kernels in oracle/_ref are built for.
+#pragma once
+#include "kernels.cuh"
+
+namespace fvsrn {
+
+template <int H16>
+struct SrnExact {
+    using Core = Srn<H16, 1, false>;
+    static constexpr int H = Core::H, K0 = Core::K0, NF = Core::NF, FOFF = Core::FOFF, NT = Core::NT, KT0 = Core::KT0, KTH = Core::KTH;
+    static constexpr int RS_CHUNKS = Core::RS_CHUNKS, ROW_CHUNKS = Core::ROW_CHUNKS;
+
+    struct Act {        // per-network constants of the hidden activation, as the reference forms them per call
+        __half p;       // Sine / Snake: half(param)
+        __half q;       // Snake: half(1/param) (fast-math division); SnakeAlt: half(2*param)
+        __half one;
+    };
+    static __device__ __forceinline__ Act make_act(int act, float param) {
+        Act a;
+        a.p = __float2half(param);
+        a.q = (act == D_ACT_SNAKE) ? __float2half(rf::div(1.0f, param)) : __float2half(rf::mul(param, 2.0f));
+        a.one = __float2half(1.0f);
+        return a;
+    }
+    static __device__ __forceinline__ __half act1(int act, const Act& a, __half v) {
+        if (act == D_ACT_RELU) return __float2half(rf::fmax(0.f, __half2float(v)));          // :46
+        if (act == D_ACT_SINE) return hsin(__hmul(v, a.p));                                   // :103
+        if (act == D_ACT_SNAKE) { const __half s = hsin(__hmul(a.p, v)); return __hadd(v, __hmul(a.q, __hmul(s, s))); }   // :266-269
+        if (act == D_ACT_SNAKEALT) { const __half x0 = hcos(__hmul(a.q, v)); return __hdiv(__hsub(__hadd(v, a.one), x0), a.q); }  // :333-337
+        return v;
+    }
+    static __device__ __forceinline__ void activate(uint32_t (&r)[2][NT][2], int act, const Act& a) {
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const __half2 v = u2h(r[mt][nt][j]);
+                    r[mt][nt][j] = h2u(__halves2half2(act1(act, a, __low2half(v)), act1(act, a, __high2half(v))));
+                }
+    }
+
+    // layer-0 inputs of the sample owned by this lane: [px,py,pz,0, cos x NF, sin x NF, latent x 16]
+    static __device__ __forceinline__ void build_row(const NetParams& P, float px, float py, float pz, float tfrac, uint32_t (&row)[K0 / 2]) {
+        const __half vx = __float2half(px), vy = __float2half(py), vz = __float2half(pz);
+        row[0] = h2u(__halves2half2(vx, vy));
+        row[1] = h2u(__halves2half2(vz, __float2half(0.f)));
+        const __half* F = reinterpret_cast<const __half*>(P.fourier2);
+        __half cs[NF], sn[NF];
+#pragma unroll
+        for (int i = 0; i < NF; ++i) {
+            __half c = __hmul(vx, F[i]);
+            c = __hfma(vy, F[i + NF], c);
+            c = __hfma(vz, F[i + 2 * NF], c);
+            cs[i] = hcos(c); sn[i] = hsin(c);
+        }
+#pragma unroll
+        for (int i = 0; i < NF; i += 2) {
+            row[FOFF / 2 + i / 2] = h2u(__halves2half2(cs[i], cs[i + 1]));
+            row[FOFF / 2 + NF / 2 + i / 2] = h2u(__halves2half2(sn[i], sn[i + 1]));
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float4 a = tex3D<float4>(P.tex_a[q], px, py, pz);
+            const float4 b = tex3D<float4>(P.tex_b[q], px, py, pz);
+            const float x = rf::fma(rf::sub(b.x, a.x), tfrac, a.x), y = rf::fma(rf::sub(b.y, a.y), tfrac, a.y);
+            const float z = rf::fma(rf::sub(b.z, a.z), tfrac, a.z), w = rf::fma(rf::sub(b.w, a.w), tfrac, a.w);
+            row[H / 2 + 2 * q] = h2u(__halves2half2(__float2half(x), __float2half(y)));
+            row[H / 2 + 2 * q + 1] = h2u(__halves2half2(__float2half(z), __float2half(w)));
+        }
+    }
+
+    // network output (raw last-layer value, fp16) of the sample owned by this lane; all 32 lanes call
+    static __device__ __forceinline__ __half forward(const NetParams& P, uint32_t sblob, uint4* stage, const Act& ac,
+                                                     float px, float py, float pz, float tfrac) {
+        const int lane = threadIdx.x & 31;
+        __syncwarp();
+        uint32_t row[K0 / 2];
+        build_row(P, px, py, pz, tfrac, row);
+#pragma unroll
+        for (int j = 0; j < ROW_CHUNKS; ++j)
+            stage[lane * RS_CHUNKS + j] = make_uint4(row[4 * j], row[4 * j + 1], row[4 * j + 2], row[4 * j + 3]);
+        __syncwarp();
+        const uint32_t stage_addr = smem_u32(stage);
+        const uint32_t bias_addr = sblob + P.off_bias;
+        uint32_t acc[2][NT][2];
+        {
+            const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8;
+            const int lcol = lane >> 4;
+            Core::template dense<KT0>(acc, sblob + P.off_w0, bias_addr, lane, [&](int kt, uint32_t (&a)[2][4]) {
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt)
+                    ldmatrix_x4(a[mt], stage_addr + ((mt * 16 + lrow) * RS_CHUNKS + kt * 2 + lcol) * 16);
+            });
+        }
+        activate(acc, P.activation, ac);
+#pragma unroll 1
+        for (int l = 0; l < P.num_hidden; ++l) {
+            uint32_t nxt[2][NT][2];
+            Core::template dense<KTH>(nxt, sblob + P.off_wh + l * Core::wh_bytes(), bias_addr + (1 + l) * H * 2, lane,
+                                      [&](int kt, uint32_t (&a)[2][4]) {
+#pragma unroll
+                                          for (int mt = 0; mt < 2; ++mt) {
+                                              a[mt][0] = acc[mt][2 * kt][0]; a[mt][1] = acc[mt][2 * kt][1];
+                                              a[mt][2] = acc[mt][2 * kt + 1][0]; a[mt][3] = acc[mt][2 * kt + 1][1];
+                                          }
+                                      });
+            activate(nxt, P.activation, ac);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) { acc[mt][nt][0] = nxt[mt][nt][0]; acc[mt][nt][1] = nxt[mt][nt][1]; }
+        }
+        // activations back to one row per sample (the reference's store_matrix_sync to shared memory, :1018-1023):
+        // accumulator register j of tile (mt, nt) holds sample mt*16 + lane/4 + 8*j, channels nt*8 + 2*(lane%4) + {0,1}
+        __syncwarp();
+        uint32_t* st32 = reinterpret_cast<uint32_t*>(stage);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+                    st32[(mt * 16 + (lane >> 2) + 8 * j) * (RS_CHUNKS * 4) + nt * 4 + (lane & 3)] = acc[mt][nt][j];
+        __syncwarp();
+        // last layer, :1138-1143: out = bias; out = hfma(x[c], w[c], out) for c = 0..H-1
+        const __half* wl = reinterpret_cast<const __half*>(P.wlast2);
+        __half out = __float2half(P.blast);
+#pragma unroll
+        for (int c4 = 0; c4 < H / 8; ++c4) {
+            const uint4 v = stage[lane * RS_CHUNKS + c4];
+            const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                out = __hfma(__low2half(u2h(u[k])), wl[c4 * 8 + 2 * k], out);
+                out = __hfma(__high2half(u2h(u[k])), wl[c4 * 8 + 2 * k + 1], out);
+            }
+        }
+        return out;
+    }
+};
+
+// transfer functions in the reference's operation order
+__device__ __forceinline__ float4 exact_tf_piecewise(const float* tf, int R, float d, float stepsize) {   // renderer_tf_piecewise.cuh:27-62
+    int i = 0;
+    for (; i < R - 2; ++i)
+        if (tf[(i + 1) * 5 + 4] > d) break;
+    const float* v0 = tf + i * 5;
+    const float* v1 = v0 + 5;
+    const float p0 = v0[4], p1 = v1[4];
+    const float dc = rf::fmax(p0, rf::fmin(d, p1));
+    const float f = rf::div(rf::sub(dc, p0), rf::sub(p1, p0));
+    float4 c;
+    c.x = rf::fma(rf::sub(v1[0], v0[0]), f, v0[0]);
+    c.y = rf::fma(rf::sub(v1[1], v0[1]), f, v0[1]);
+    c.z = rf::fma(rf::sub(v1[2], v0[2]), f, v0[2]);
+    c.w = rf::mul(stepsize, rf::fma(rf::sub(v1[3], v0[3]), f, v0[3]));
+    return c;
+}
+__device__ __forceinline__ float4 exact_tf_texture(const float* tf, int R, float d, float stepsize) {     // renderer_tf_texture.cuh:46-56
+    const float x = rf::fma(d, float(R), -0.5f);
+    const float fl = rf::floor(x);
+    const int di = int(fl);
+    const float df = rf::sub(x, float(di));
+    const float* v0 = tf + 4 * min(max(di, 0), R - 1);
+    const float* v1 = tf + 4 * min(max(di + 1, 0), R - 1);
+    float4 c;
+    c.x = rf::fma(df, rf::sub(v1[0], v0[0]), v0[0]);
+    c.y = rf::fma(df, rf::sub(v1[1], v0[1]), v0[1]);
+    c.z = rf::fma(df, rf::sub(v1[2], v0[2]), v0[2]);
+    c.w = rf::mul(rf::fma(df, rf::sub(v1[3], v0[3]), v0[3]), stepsize);
+    return c;
+}
+
+template <int H16>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
+    using Net = SrnExact<H16>;
+    using Core = typename Net::Core;
+    extern __shared__ uint4 smem[];
+    uint4* sblob = smem;
+    const int blob16 = (P.blob_bytes + 15) / 16;
+    float* stf = reinterpret_cast<float*>(smem + blob16);
+    uint4* stage_all = smem + blob16 + kTfSmemFloats / 4;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint4* stage = stage_all + warp * (Core::STAGE_BYTES / 16);
+
+    load_blob(P, sblob);
+    const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : D.tf_R * 4;
+    if (D.tf_batch == 1)
+        for (int i = threadIdx.x; i < tf_floats; i += blockDim.x) stf[i] = __ldg(D.tf + i);
+    __syncthreads();
+
+    const uint32_t sblob_addr = smem_u32(sblob);
+    const typename Net::Act ac = Net::make_act(P.activation, P.act_param);
+    const float3 bmin = make_float3(P.box_min[0], P.box_min[1], P.box_min[2]);
+    const float3 bsize = make_float3(P.box_size[0], P.box_size[1], P.box_size[2]);
+    const float tfrac = rf::sub(P.time_value, rf::floor(P.time_value));       // fracf(time), :596-597
+    const float inv_range = rf::rcp(rf::sub(D.dmax, D.dmin));                 // 1 / (densityMax - densityMin), fast math
+    unsigned long long n_valid = 0, n_exec = 0;
+    for (;;) {
+        int tile = 0;
+        if (lane == 0) tile = int(atomicAdd(D.tile_counter, 1u));
+        tile = __shfl_sync(0xffffffffu, tile, 0);
+        if (tile >= D.num_tiles) break;
+        const int tiles_per_img = D.tiles_x * D.tiles_y;
+        const int bl = tile / tiles_per_img;
+        const int trem = tile - bl * tiles_per_img;
+        const int ty = trem / D.tiles_x, tx = trem - ty * D.tiles_x;
+        const int b = D.b0 + bl;
+        const int x = D.x0 + tx * kTileW + (lane & (kTileW - 1));
+        const int y = D.y0 + ty * kTileH + (lane / kTileW);
+        const bool in_img = (x < D.x0 + D.tw) && (y < D.y0 + D.th);
+        const float* tfp = (D.tf_batch == 1) ? stf : (D.tf + (size_t)b * tf_floats);
+        const CamFrame cf = load_camera(D, b);
+
+        float4 pix = make_float4(0.f, 0.f, 0.f, 0.f);
+        float pix_depth = 0.f;
+        int last_steps = 0;
+        for (int s = 0; s < D.spp; ++s) {
+            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize);
+            const float tmax = in_img ? r.tmax : -1.f;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            float acc_depth = 0.f;
+            int steps = 0;
+            for (int i = 0;; ++i) {     // renderer_ray_evaluation_stepping_dvr.cuh:84-154
+                const float t = rf::fma(D.stepsize, float(i), r.tmin);
+                bool valid = (t <= tmax);
+                if (D.early_out) valid = valid && (acc.w < D.alpha_early_out);
+                if (!__any_sync(0xffffffffu, valid)) break;
+                n_exec += 32;
+                const float wx = rf::fma(r.dir.x, t, r.eye.x), wy = rf::fma(r.dir.y, t, r.eye.y), wz = rf::fma(r.dir.z, t, r.eye.z);
+                const float px = rf::div(rf::sub(wx, bmin.x), bsize.x), py = rf::div(rf::sub(wy, bmin.y), bsize.y),
+                            pz = rf::div(rf::sub(wz, bmin.z), bsize.z);
+                const float value = __half2float(Net::forward(P, sblob_addr, stage, ac, px, py, pz, tfrac));
+                float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (valid && value >= D.dmin) {
+                    const float d2 = rf::fmax(0.f, rf::fmin(rf::mul(inv_range, rf::sub(value, D.dmin)), 1.0f));
+                    c = D.tf_kind == 0 ? exact_tf_piecewise(tfp, D.tf_R, d2, D.stepsize) : exact_tf_texture(tfp, D.tf_R, d2, D.stepsize);
+                }
+                steps += valid ? 1 : 0;
+                if (c.w > 0.f && valid) {   // renderer_blending.cuh:36-51
+                    const float a = (D.blend_mode == 1) ? rf::sub(1.0f, rf::ex2(rf::mul(c.w, -1.4426950408889634f))) : rf::fmin(1.0f, c.w);
+                    const float om = rf::sub(1.0f, acc.w);
+                    acc.x = rf::fma(rf::mul(om, c.x), a, acc.x);
+                    acc.y = rf::fma(rf::mul(om, c.y), a, acc.y);
+                    acc.z = rf::fma(rf::mul(om, c.z), a, acc.z);
+                    acc.w = rf::fma(om, a, acc.w);
+                    acc_depth = rf::fma(rf::mul(om, t), a, acc_depth);
+                }
+            }
+            n_valid += steps;
+            last_steps = steps;
+            pix.x = rf::add(pix.x, acc.x); pix.y = rf::add(pix.y, acc.y); pix.z = rf::add(pix.z, acc.z); pix.w = rf::add(pix.w, acc.w);
+            pix_depth = rf::fma(acc.w, acc_depth, pix_depth);       // renderer_image_evaluator_simple.cuh:101-103
+        }
+        if (in_img) {       // :105-124: depth /= alpha first, then colour /= samples
+            const float ns = float(D.spp);
+            float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
+            o[0 * D.sc] = rf::div(pix.x, ns); o[1 * D.sc] = rf::div(pix.y, ns); o[2 * D.sc] = rf::div(pix.z, ns);
+            o[3 * D.sc] = rf::div(pix.w, ns);
+            o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
+            o[7 * D.sc] = rf::div(pix_depth, pix.w);
+            if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
+        }
+    }
+    if (D.counters) {
+        for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);
+        if (lane == 0) { atomicAdd(D.counters + 0, n_valid); atomicAdd(D.counters + 1, n_exec); }
+    }
+}
+
+} // namespace fvsrn

@@ -2,9 +2,15 @@
 // Replaces the run-time NVRTC assembly of reference renderer/kernel_loader.cpp:197-273 by ahead-of-time
 // sm_100a instantiations selected from the network's shape (hidden width, latent channels, direction input).
 #pragma once
+#include "kernels_tc.cuh"
+#ifdef FVSRN_EXPERIMENTS   // measured dead ends kept for reference (SS-mode tcgen05 kernel): not in the product build
 #include "kernels_ss.cuh"
+#endif
 #include <cstdlib>
 #include <cuda_runtime.h>
+#include <map>
+#include <mutex>
+#include <utility>
 
 namespace fvsrn {
 
@@ -28,6 +34,8 @@ cudaError_t launch_h3(int, int, int, const NetParams&, const void*, LaunchCfg*, 
 cudaError_t launch_h4(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
 cudaError_t launch_h6(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
 cudaError_t launch_h8(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
+// reference-exact DVR kernel (kernels_exact.cuh, inst_exact.cu)
+cudaError_t launch_exact(int h16, const NetParams& P, const DvrParams& D, LaunchCfg* cfg, cudaStream_t s);
 
 // CTAs per SM the register file allows: registers live in four 16384-entry partitions (one per SM sub-partition) and a
 // warp's registers cannot straddle them, so the limit is per partition: floor(16384 / regs per warp) warps each.
@@ -38,6 +46,7 @@ inline int tc_blocks_by_regs(int regs_per_thread, int threads) {
     return (4 * warps_per_partition) / ((threads + 31) / 32);
 }
 
+#ifdef FVSRN_EXPERIMENTS
 // SS-mode tcgen05 DVR kernel (kernels_ss.cuh): hidden width 32, density networks without direction input
 template <int H16, int GC16, int NS>
 cudaError_t launch_ss_n(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, cudaStream_t s, const void* fn) {
@@ -82,29 +91,24 @@ cudaError_t launch_ss(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, c
     }
     return cudaSuccess;
 }
+#endif  // FVSRN_EXPERIMENTS
 
-template <int H16, int GC16, bool DIR>
-cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s) {
-    using Net = Srn<H16, GC16, DIR>;
-    if (kind == KIND_DVR_TC && kp != nullptr) {
-        bool handled = false;
-        const cudaError_t e = launch_ss<H16, GC16, DIR>(P, *static_cast<const DvrParams*>(kp), cfg, s, &handled);
-        if (e != cudaSuccess || handled) return e;
+// Per-kernel launch facts (dynamic-smem opt-in done, registers, co-resident CTAs per SM), queried once per
+// (kernel, shared-memory size) instead of three runtime-API calls on every launch.
+struct KernelFacts { int regs = 0; int bps = 0; };
+inline cudaError_t kernel_facts(const void* fn, int threads, int smem, bool is_tc, int tmem_cols, KernelFacts* out) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, std::pair<int, int>>, KernelFacts> cache;   // key: kernel, (smem, device)
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    const auto key = std::make_pair(fn, std::make_pair(smem, dev));
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        auto it = cache.find(key);
+        if (it != cache.end()) { *out = it->second; return cudaSuccess; }
     }
-    const bool is_tc = kind >= KIND_DVR_TC, is_dvr = (kind == KIND_DVR || kind == KIND_DVR_TC);
-    const int blob = ((P.blob_bytes + 15) / 16) * 16;
-    const int threads = is_tc ? kTcThreads : kWarpsPerBlock * 32;
-    const int smem = blob + (is_dvr ? (is_tc ? kTcTfFloats : kTfSmemFloats) * 4 : 0) + (is_tc ? int(sizeof(TcShared)) : kWarpsPerBlock * Net::STAGE_BYTES);
-    // tcgen05 kernels: the common cases (ReLU, NeRF-style Fourier matrix) get their own instantiations
-    const int variant = (P.activation == D_ACT_RELU ? 1 : 0) | ((P.fourier_nerf && !DIR) ? 2 : 0);
-    const void* tc_dvr[4] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1>,
-                             (const void*)dvr_tc_kernel<H16, GC16, DIR, DIR ? 0 : 2>, (const void*)dvr_tc_kernel<H16, GC16, DIR, DIR ? 1 : 3>};
-    const void* tc_eval[4] = {(const void*)eval_tc_kernel<H16, GC16, DIR, 0>, (const void*)eval_tc_kernel<H16, GC16, DIR, 1>,
-                              (const void*)eval_tc_kernel<H16, GC16, DIR, DIR ? 0 : 2>, (const void*)eval_tc_kernel<H16, GC16, DIR, DIR ? 1 : 3>};
-    const void* fn = kind == KIND_DVR ? (const void*)dvr_kernel<H16, GC16, DIR>
-                   : kind == KIND_EVAL ? (const void*)eval_kernel<H16, GC16, DIR>
-                   : kind == KIND_DVR_TC ? tc_dvr[variant] : tc_eval[variant];
-    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     int bps = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, fn, threads, smem);
@@ -119,13 +123,49 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
         // profiles/microbench). Surplus CTAs of the persistent grid would only queue, never deadlock.
         const int by_regs = tc_blocks_by_regs(fa.numRegs, threads);
         const int by_smem = int((228 * 1024) / (size_t(smem) + 1024));
-        const int by_tmem = 512 / SrnTc<H16, GC16, DIR, 0>::TMEM_COLS;
+        const int by_tmem = 512 / tmem_cols;
         bps = max(1, min(min(by_regs, by_smem), min(by_tmem, 16)));
     }
+    KernelFacts f; f.regs = fa.numRegs; f.bps = bps;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        cache[key] = f;
+    }
+    *out = f;
+    return cudaSuccess;
+}
+
+template <int H16, int GC16, bool DIR>
+cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s) {
+    using Net = Srn<H16, GC16, DIR>;
+#ifdef FVSRN_EXPERIMENTS
+    if (kind == KIND_DVR_TC && kp != nullptr) {
+        bool handled = false;
+        const cudaError_t e = launch_ss<H16, GC16, DIR>(P, *static_cast<const DvrParams*>(kp), cfg, s, &handled);
+        if (e != cudaSuccess || handled) return e;
+    }
+#endif
+    const bool is_tc = kind >= KIND_DVR_TC, is_dvr = (kind == KIND_DVR || kind == KIND_DVR_TC);
+    const int blob = ((P.blob_bytes + 15) / 16) * 16;
+    const int threads = is_tc ? kTcThreads : kWarpsPerBlock * 32;
+    const int smem = blob + (is_dvr ? (is_tc ? kTcTfFloats : kTfSmemFloats) * 4 : 0) + (is_tc ? int(sizeof(TcShared)) : kWarpsPerBlock * Net::STAGE_BYTES);
+    // tcgen05 kernels: the common cases (ReLU, NeRF-style Fourier matrix) get their own instantiations
+    const int variant = (P.activation == D_ACT_RELU ? 1 : 0) | ((P.fourier_nerf && !DIR) ? 2 : 0);
+    const void* tc_dvr[4] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1>,
+                             (const void*)dvr_tc_kernel<H16, GC16, DIR, DIR ? 0 : 2>, (const void*)dvr_tc_kernel<H16, GC16, DIR, DIR ? 1 : 3>};
+    const void* tc_eval[4] = {(const void*)eval_tc_kernel<H16, GC16, DIR, 0>, (const void*)eval_tc_kernel<H16, GC16, DIR, 1>,
+                              (const void*)eval_tc_kernel<H16, GC16, DIR, DIR ? 0 : 2>, (const void*)eval_tc_kernel<H16, GC16, DIR, DIR ? 1 : 3>};
+    const void* fn = kind == KIND_DVR ? (const void*)dvr_kernel<H16, GC16, DIR>
+                   : kind == KIND_EVAL ? (const void*)eval_kernel<H16, GC16, DIR>
+                   : kind == KIND_DVR_TC ? tc_dvr[variant] : tc_eval[variant];
+    KernelFacts kf;
+    const cudaError_t e = kernel_facts(fn, threads, smem, is_tc, SrnTc<H16, GC16, DIR, 0>::TMEM_COLS, &kf);
+    if (e != cudaSuccess) return e;
+    const int bps = kf.bps;
     long long grid = (long long)bps * cfg->sm_count;
     if (cfg->max_blocks > 0 && grid > cfg->max_blocks) grid = cfg->max_blocks;
     if (grid < 1) grid = 1;
-    cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = fa.numRegs; cfg->threads = threads;
+    cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = kf.regs; cfg->threads = threads;
     if (cfg->query_only) return cudaSuccess;
     if (is_tc) {
         void* args[2] = {const_cast<NetParams*>(&P), const_cast<void*>(kp)};

@@ -54,7 +54,6 @@ struct NetParams {
     int fourier_nerf;     // Fourier matrix has the NeRF layout (see SrnTc::build_row)
     uint32_t wlast2[64];  // density networks: last-layer weights as fp16x2 pairs (k, k+1) and its bias, for the in-thread dot product
     float blast;
-    int dbg_flags;       // bring-up switches (env FVSRN_TC_DEBUG): bit0 = swap LBO/SBO of the UMMA weight descriptors
 };
 
 // ------------------------------------------------------------------ small PTX wrappers

@@ -25,7 +25,7 @@ from ._lib import check
 
 # Kernel family used by networks created from now on (B200 addition, see fvsrn_network_set_kernel_mode):
 # "tcgen05" (default; tcgen05.mma + TMEM, fp32 accumulate) or "mma_sync" (reference-precision fp16-accumulate mode).
-KERNEL_MODES = {"mma_sync": 0, "tcgen05": 1}
+KERNEL_MODES = {"mma_sync": 0, "tcgen05": 1, "reference_exact": 2}
 DEFAULT_KERNEL_MODE = __import__("os").environ.get("FVSRN_KERNEL_MODE", "tcgen05")
 
 

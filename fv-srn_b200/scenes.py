@@ -111,11 +111,19 @@ def texture_tf_from_piecewise(tf: np.ndarray, resolution: int = 256) -> np.ndarr
 def make_network(hidden: int = 32, num_layers: int = 4, grid_res: int = 32, grid_channels: int = 16, activation: str = "ReLU",
                  fourier: str = "nerf", fourier_std: float = 1.0, output_mode: str = "density:direct", seed: int = 42,
                  grid_std: float = 0.5, time_keyframes: int = 0, has_direction: bool = False, pass_time: bool = False,
-                 box_min=(-0.5, -0.5, -0.5), box_size=(1.0, 1.0, 1.0), last_gain: float = 1.0) -> volnet.SceneNetwork:
+                 box_min=(-0.5, -0.5, -0.5), box_size=(1.0, 1.0, 1.0), last_gain: float = 1.0,
+                 last_bias: float | None = None, hidden_gain: float = 1.0) -> volnet.SceneNetwork:
     """Random-init SRN shaped like the reference's SceneRepresentationNetwork (network.py:653-770):
     ``num_layers`` linear layers (``--layers h:h:..`` has num_layers-1 entries), Fourier count (hidden-4)/2
     (collect_possible_layers.py:50), nn.Linear default init U(-1/sqrt(fan_in), 1/sqrt(fan_in)), grid ~ N(0, grid_std).
-    time_keyframes > 0 creates that many time-dependent latent grids (volumetric_features_time_dependent)."""
+    time_keyframes > 0 creates that many time-dependent latent grids (volumetric_features_time_dependent).
+    last_gain / last_bias scale the last layer's weights and replace its bias: a random-init network's output is a narrow
+    band around some mean (deep ReLU networks more so), these two place that band across the transfer function so
+    that the synthetic frame has content (the same reason the latent grid uses std 0.5 instead of 0.01).
+    hidden_gain scales the weights of every layer but the last: nn.Linear's default init shrinks the signal by ~0.4 per
+    ReLU layer, so a 6-layer random network's output varies by 1e-2 of its activations and only a large last_gain (which
+    amplifies fp16 noise as much as signal) would make it visible; hidden_gain = sqrt(6) (He-uniform) keeps the signal
+    O(1) through the layers, like trained weights do."""
     rng = np.random.default_rng(seed)
     foff = 8 if has_direction else 4
     nf = (hidden - foff) // 2
@@ -139,11 +147,13 @@ def make_network(hidden: int = 32, num_layers: int = 4, grid_res: int = 32, grid
     last = cin
     for s in sizes:
         k = 1.0 / math.sqrt(last)
-        net.add_layer(rng.uniform(-k, k, (s, last)), rng.uniform(-k, k, (s,)), act_name, act_param)
+        net.add_layer(rng.uniform(-k, k, (s, last)) * hidden_gain, rng.uniform(-k, k, (s,)), act_name, act_param)
         last = s
     k = 1.0 / math.sqrt(last)
     w_last = rng.uniform(-k, k, (cout, last)) * last_gain
     b_last = rng.uniform(-k, k, (cout,))
+    if last_bias is not None:
+        b_last = np.full((cout,), float(last_bias))
     if cout == 4:
         b_last = np.abs(b_last) + 1.0  # network.py:405-406
     net.add_layer(w_last, b_last, "None", 1.0)

@@ -113,8 +113,13 @@ int  fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info);
 /* Which sm_100a kernel family evaluates the SRN (no reference analogue; the reference picks wmma by NVRTC defines):
  *   FVSRN_KERNEL_TCGEN05  (default) tcgen05.mma with TMEM accumulators (fp32 accumulate), 128 rays per CTA in lock-step
  *   FVSRN_KERNEL_MMA_SYNC reference-precision mode: mma.sync m16n8k16 with fp16 accumulation in the reference's
- *                         K order (renderer_volume_tensorcores.cuh:856-910), 32 rays per warp - used for step-count parity */
-enum { FVSRN_KERNEL_MMA_SYNC = 0, FVSRN_KERNEL_TCGEN05 = 1 };
+ *                         K order (renderer_volume_tensorcores.cuh:856-910), 32 rays per warp
+ *   FVSRN_KERNEL_REFERENCE_EXACT  validation mode (DVR frame only): every fp16 and fp32 operation of the reference's
+ *                         compiled kernel in the reference's order - tex3D<float4> latent fetch, hsin/hcos/__hdiv of
+ *                         cuda_fp16.hpp, fp16-accumulate HMMA with the bias preloaded, sequential fp16 last layer, fast-math
+ *                         fp32 ray setup / TF / blending - so that images and early-termination step counts are
+ *                         bit-identical to ImageEvaluatorSimpleKernel on the same GPU (csrc/kernels_exact.cuh) */
+enum { FVSRN_KERNEL_MMA_SYNC = 0, FVSRN_KERNEL_TCGEN05 = 1, FVSRN_KERNEL_REFERENCE_EXACT = 2 };
 int  fvsrn_network_set_kernel_mode(fvsrn_network* net, int mode);
 int  fvsrn_network_get_kernel_mode(const fvsrn_network* net);
 

@@ -38,26 +38,35 @@ template<int N, typename V, typename I> __host__ __device__ fvar<double4, N> mak
 """
 
 NAMES = ["ImageEvaluatorSimpleKernel", "&cameraReferenceFrameParameters", "&volumeInterpolationTensorcoresParameters",
-         "&rayEvaluationSteppingDvrParameters", "&transferFunctionPiecewiseParameters"]
+         "&rayEvaluationSteppingDvrParameters"]
+TF_NAMES = {"piecewise": "&transferFunctionPiecewiseParameters", "texture": "&transferFunctionTextureParameters"}
+TF_TYPES = {"piecewise": ("::kernel::TransferFunctionPiecewise", "renderer_tf_piecewise.cuh"),
+            "texture": ("::kernel::TransferFunctionTexture", "renderer_tf_texture.cuh")}
 
 
-def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, early_out=1, blend_mode=1, first_last_shared=0):
-    """The translation unit IImageEvaluator::getKernel + ImageEvaluatorSimple::render assemble (SURVEY App. F)."""
+def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, early_out=1, blend_mode=1, first_last_shared=0,
+                encoding=0, tf="piecewise"):
+    """The translation unit IImageEvaluator::getKernel + ImageEvaluatorSimple::render assemble (SURVEY App. F).
+    encoding: LATENT_GRID_ENCODING 0 float / 1 byte-linear / 2 byte-gaussian (volume_interpolation_network.cpp:1211);
+    tf "texture": TransferFunctionTexture in its tensor form (transfer_function_texture.cpp: TRANSFER_FUNCTION_TEXTURE__USE_TENSOR,
+    pre-integration off)."""
     d = [
         ("KERNEL_DOUBLE_PRECISION", 0), ("KERNEL_SYNCHRONIZED_TRACING", 1), ("BLOCK_SIZE", block_size),
         ("NUM_HIDDEN_LAYERS", num_hidden), ("HIDDEN_CHANNELS_DIV16", hidden16), ("HAS_FOURIER_FEATURES", 1),
         ("NUM_FOURIER_FEATURES", nf), ("USE_DIRECTION", 0), ("ACTIVATION", activation), ("OUTPUT_MODE", output_mode),
-        ("FIRST_AND_LAST_IN_SHARED_MEMORY", first_last_shared), ("LATENT_GRID_CHANNELS_DIV16", 1), ("LATENT_GRID_ENCODING", 0),
+        ("FIRST_AND_LAST_IN_SHARED_MEMORY", first_last_shared), ("LATENT_GRID_CHANNELS_DIV16", 1), ("LATENT_GRID_ENCODING", encoding),
         ("PASS_TIME_TO_NETWORK", 0), ("GRADIENT_MODE", 0),
         ("RAY_EVALUATION_STEPPING__VOLUME_INTERPOLATION_T", "::kernel::VolumeInterpolationTensorcores"),
-        ("RAY_EVALUATION_STEPPING__TRANSFER_FUNCTION_T", "::kernel::TransferFunctionPiecewise"),
+        ("RAY_EVALUATION_STEPPING__TRANSFER_FUNCTION_T", TF_TYPES[tf][0]),
         ("RAY_EVALUATION_STEPPING__BLENDING_T", "::kernel::Blending"),
         ("RAY_EVALUATION_STEPPING__BRDF_T", "::kernel::BRDFLambert"),
         ("RAY_EVALUATION_STEPPING__ENABLE_EARLY_OUT", early_out), ("RAY_EVALUATION_STEPPING__SKIP_TRANSFER_FUNCTION", 0),
         ("BLENDING_MODE", blend_mode), ("BRDF_LAMBERT_LIGHT_TYPE", 1),
     ]
+    if tf == "texture":
+        d += [("TRANSFER_FUNCTION_TEXTURE__USE_TENSOR", 1), ("TRANSFER_FUNCTION_TEXTURE__PREINTEGRATION_MODE", 0)]
     src = "".join(f"#define {k} {v}\n" for k, v in d)
-    for h in ("renderer_camera.cuh", "renderer_volume_tensorcores.cuh", "renderer_tf_piecewise.cuh", "renderer_blending.cuh",
+    for h in ("renderer_camera.cuh", "renderer_volume_tensorcores.cuh", TF_TYPES[tf][1], "renderer_blending.cuh",
               "renderer_brdf_lambert.cuh", "renderer_ray_evaluation_stepping_dvr.cuh"):
         src += f'#include "{h}"\n'
     src += "#define IMAGE_EVALUATOR__CAMERA_T ::kernel::CameraReferenceFrame\n"
@@ -82,7 +91,7 @@ STEP_PATCHES = {
 }
 
 
-def compile_ptx(src, patch_steps=False):
+def compile_ptx(src, patch_steps=False, tf="piecewise"):
     from cuda.bindings import nvrtc
 
     def ck(r):
@@ -104,7 +113,8 @@ def compile_ptx(src, patch_steps=False):
     headers += [SHIM_FORWARD.encode(), b"#pragma once\n"]
     names += [b"forward.h", b"forward_vector.h"]
     prog = ck(nvrtc.nvrtcCreateProgram(src.encode(), b"main.cu", len(headers), headers, names))
-    for n in NAMES:
+    names_all = NAMES + [TF_NAMES[tf]]
+    for n in names_all:
         ck(nvrtc.nvrtcAddNameExpression(prog, n.encode()))
     cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
     opts = [b"--std=c++17", b"--use_fast_math", b"--generate-line-info", b"--gpu-architecture=compute_75",
@@ -116,7 +126,7 @@ def compile_ptx(src, patch_steps=False):
         raise RuntimeError("NVRTC failed:\n" + log.decode(errors="replace")[-4000:])
     n = ck(nvrtc.nvrtcGetPTXSize(prog)); ptx = b" " * n
     ck(nvrtc.nvrtcGetPTX(prog, ptx))
-    lowered = {nm: ck(nvrtc.nvrtcGetLoweredName(prog, nm.encode())).decode() for nm in NAMES}
+    lowered = {nm: ck(nvrtc.nvrtcGetLoweredName(prog, nm.encode())).decode() for nm in names_all}
     return ptx.rstrip(b"\x00 "), lowered
 
 
@@ -124,7 +134,16 @@ CONFIGS = {
     # name: hidden16, num_hidden (linear layers - 2), nf, activation, output_mode (1 = density:direct), block size
     "h32x4_relu": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256),
     "h32x4_snakealt": dict(hidden16=2, num_hidden=2, nf=14, activation="SnakeAlt", output_mode=1, block_size=256),
+    # BASELINE C4 network: 64x6, 30 Fourier features; computeMaxWarps (volume_interpolation_network.cpp:987-1041) leaves
+    # (48 KiB - 43648 B weights) / (64*2*32 B per warp) = 1 warp per block
+    "h64x6_relu": dict(hidden16=4, num_hidden=4, nf=30, activation="ReLU", output_mode=1, block_size=32),
+    # texture transfer function (tensor form), byte-encoded latent grids
+    "h32x4_relu_textf": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, tf="texture"),
+    "h32x4_relu_bytelinear": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, encoding=1),
+    "h32x4_relu_bytegauss": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, encoding=2),
 }
+# (time-interpolated grids, C5, need no build of their own: cLatentGridB != A and cLatentGridInterpolation = t are
+# constants of the same h32x4 kernels, renderer_volume_tensorcores.cuh:590-604)
 
 
 def main():
@@ -135,7 +154,7 @@ def main():
     meta = {}
     for base, cfg in CONFIGS.items():
         for name, patch in ((base, False), (base + "_steps", True)):
-            ptx, lowered = compile_ptx(main_source(**cfg), patch_steps=patch)
+            ptx, lowered = compile_ptx(main_source(**cfg), patch_steps=patch, tf=cfg.get("tf", "piecewise"))
             open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
             meta[name] = dict(cfg, lowered=lowered, ptx=name + ".ptx", step_count_patch=patch)
             print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['ImageEvaluatorSimpleKernel']}")

@@ -1,0 +1,66 @@
+"""
+TEST INFRASTRUCTURE — parity of the B200 kernels against the REFERENCE's own tensor-core kernel at the BASELINE configs.
+
+The reference kernel (oracle/_ref/*.ptx, built by oracle/build_ref_ptx.py from the unmodified renderer/*.cuh) and the
+product kernels render the same frame on the same GPU from the same .volnet weights, fp16-rounded latent grid, camera
+and transfer function; this module returns the numbers north_star gates: RGBA max-abs (<= 2e-3), PSNR (>= 50 dB) and
+the fraction of rays whose early-termination step count differs (reference kernel patched, test-only, to export it).
+Used by tests/test_gpu_baseline_configs.py and by bench.py's `parity` sub-object. Nothing here is product code.
+"""
+import numpy as np
+
+RGBA_TOL = 2e-3
+PSNR_MIN = 50.0
+
+
+def psnr(a, b):
+    mse = float(np.mean((np.asarray(a, np.float64) - np.asarray(b, np.float64)) ** 2))
+    return 200.0 if mse == 0 else 10.0 * np.log10(1.0 / mse)
+
+
+def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0, time=None, tile=None, spp=1):
+    """One frame through the product path (pyrenderer mirror -> C ABI) -> (img (B,8,H,W) numpy, steps (B,H,W) numpy)."""
+    import torch
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import pyrenderer as pr
+    sn = pr.SceneNetwork.from_bytes(net_bytes); sn.kernel_mode = mode
+    if time is not None:
+        sn.set_time_and_ensemble(float(time), 0)
+    vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
+    ie = pr.ImageEvaluatorSimple(); ie.volume = vol
+    ie.camera.set_parameters(torch.from_numpy(np.ascontiguousarray(camera, np.float32)))
+    if tf_kind == 1:
+        ie.ray_evaluator.tf = pr.TransferFunctionTexture()
+    ie.ray_evaluator.tf.tensor.value = torch.from_numpy(np.ascontiguousarray(tf, np.float32)).cuda()
+    ie.ray_evaluator.stepsize = stepsize
+    ie.samples_per_pixel = spp
+    ie.collect_statistics = True
+    ie.tile = tile
+    img = ie.render(width, height).cpu().numpy()
+    return img, ie.last_step_counts.cpu().numpy()
+
+
+def render_reference(net, width, height, camera, fov_y, tf, stepsize, tf_kind=0, time=0.0, timing_iters=0):
+    """The same frame with the reference's kernel -> (rgba8 image, step counts, ms or None)."""
+    import ref_kernel
+    tfname = "texture" if tf_kind == 1 else "piecewise"
+    rk = ref_kernel.ReferenceDvrKernel(net, time=time, tf=tfname)
+    ms = None
+    if timing_iters > 0:
+        want, ms = rk.render(width, height, camera, fov_y, stepsize, tf, timing_iters=timing_iters)
+    else:
+        want = rk.render(width, height, camera, fov_y, stepsize, tf)
+    want = want.cpu().numpy()
+    counted = ref_kernel.ReferenceDvrKernel(net, patched_steps=True, time=time, tf=tfname).render(
+        width, height, camera, fov_y, stepsize, tf).cpu().numpy()
+    assert np.array_equal(want[:, :4], counted[:, :4]), "the step-count patch must not touch the image"
+    return want, np.rint(counted[:, 4]).astype(np.int32), ms
+
+
+def compare(img, steps, want, want_steps):
+    """-> dict with the gated numbers."""
+    d = np.abs(img[:, :4] - want[:, :4])
+    mism = steps != want_steps
+    return {"rgba_max_abs": float(d.max()), "psnr_db": float(psnr(img[:, :4], want[:, :4])),
+            "step_count_mismatch_frac": float(mism.mean()), "step_count_max_diff": int(np.abs(steps - want_steps).max()),
+            "rays": int(mism.size), "total_steps_ref": int(want_steps.sum()), "total_steps": int(steps.sum())}

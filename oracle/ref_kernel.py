@@ -63,25 +63,31 @@ def _read3(t, broadcast=True):
 
 
 class ReferenceDvrKernel:
-    """One JIT-loaded reference kernel bound to one network (density network, Fourier features, one static 16-channel
-    latent grid, no direction/time input — the paper-default shape)."""
+    """One JIT-loaded reference kernel bound to one network (density network, Fourier features, one 16-channel latent
+    grid group, no direction/time *input*). Covers the paper-default shape, the 64x6 network of C4,
+    time-interpolated keyframe grids (C5: cLatentGridB != A, cLatentGridInterpolation = t), byte-encoded grids and the
+    texture transfer function (tensor form)."""
 
-    def __init__(self, net, variant=None, patched_steps=False):
+    def __init__(self, net, variant=None, patched_steps=False, time=0.0, tf="piecewise"):
         import torch
         from cuda.bindings import driver
         self.torch, self.drv = torch, driver
         meta = json.load(open(os.path.join(REF_DIR, "ref_kernels.json")))
         act = net.layers[0].activation
         H = net.input_channels_out()
+        grids = net.time_grids or net.ensemble_grids
+        enc = grids[0].encoding
         if variant is None:
-            variant = f"h{H}x{len(net.layers)}_{act.lower()}" + ("_steps" if patched_steps else "")
+            variant = f"h{H}x{len(net.layers)}_{act.lower()}" + {0: "", 1: "_bytelinear", 2: "_bytegauss"}[enc] \
+                      + ("_textf" if tf == "texture" else "") + ("_steps" if patched_steps else "")
         if variant not in meta:
             raise RuntimeError(f"no prebuilt reference PTX for {variant} (have {sorted(meta)})")
         m = meta[variant]
         assert m["hidden16"] * 16 == H and m["num_hidden"] == len(net.layers) - 2 and m["nf"] == net.num_fourier
         assert net.latent_channels() == 16 and not net.has_direction and not net.has_time
         assert net.output_mode == {0: "density", 1: "density:direct"}[m["output_mode"]]
-        self.meta, self.block = m, m["block_size"]
+        assert m.get("encoding", 0) == enc and m.get("tf", "piecewise") == tf
+        self.meta, self.block, self.tf_kind = m, m["block_size"], tf
         torch.cuda.init(); torch.zeros(1, device="cuda")         # primary context current
         ptx = open(os.path.join(REF_DIR, m["ptx"]), "rb").read() + b"\0"
         self.module = _ck(driver.cuModuleLoadData(ptx))          # JIT compute_75 PTX -> sm_100 SASS
@@ -90,34 +96,37 @@ class ReferenceDvrKernel:
         self.g_cam = _ck(driver.cuModuleGetGlobal(self.module, low["&cameraReferenceFrameParameters"].encode()))
         self.g_vol = _ck(driver.cuModuleGetGlobal(self.module, low["&volumeInterpolationTensorcoresParameters"].encode()))
         self.g_dvr = _ck(driver.cuModuleGetGlobal(self.module, low["&rayEvaluationSteppingDvrParameters"].encode()))
-        self.g_tf = _ck(driver.cuModuleGetGlobal(self.module, low["&transferFunctionPiecewiseParameters"].encode()))
+        tf_sym = "&transferFunctionTextureParameters" if tf == "texture" else "&transferFunctionPiecewiseParameters"
+        self.g_tf = _ck(driver.cuModuleGetGlobal(self.module, low[tf_sym].encode()))
         self._keep = []
-        self._upload_network(net)
+        self._upload_network(net, float(time))
         sms = torch.cuda.get_device_properties(0).multi_processor_count
         bps = _ck(driver.cuOccupancyMaxActiveBlocksPerMultiprocessor(self.func, self.block, 0))
         self.max_grid = max(1, bps) * sms
         self.blocks_per_sm = bps
 
-    # ---- latent grid -> C/4 float4 3-D textures
+    # ---- latent grid -> C/4 4-channel 3-D textures (LatentGrid::GPUArray, volume_interpolation_network.cpp:470-504)
     def _texture(self, vol4):
-        """vol4: (Z,Y,X,4) float32."""
+        """vol4: (Z,Y,X,4) float32 (element-type read) or uint8 (normalised-float read)."""
         d = self.drv
         Z, Y, X, _ = vol4.shape
+        is_float = vol4.dtype != np.uint8
+        bpt = 4 if is_float else 1
         desc = d.CUDA_ARRAY3D_DESCRIPTOR()
         desc.Width, desc.Height, desc.Depth = X, Y, Z
-        desc.Format = d.CUarray_format.CU_AD_FORMAT_FLOAT
+        desc.Format = d.CUarray_format.CU_AD_FORMAT_FLOAT if is_float else d.CUarray_format.CU_AD_FORMAT_UNSIGNED_INT8
         desc.NumChannels = 4
         desc.Flags = 0
         arr = _ck(d.cuArray3DCreate(desc))
-        host = np.ascontiguousarray(vol4, np.float32)
+        host = np.ascontiguousarray(vol4, np.float32 if is_float else np.uint8)
         cp = d.CUDA_MEMCPY3D()
         cp.srcMemoryType = d.CUmemorytype.CU_MEMORYTYPE_HOST
         cp.srcHost = host.ctypes.data
-        cp.srcPitch = X * 16
+        cp.srcPitch = X * 4 * bpt
         cp.srcHeight = Y
         cp.dstMemoryType = d.CUmemorytype.CU_MEMORYTYPE_ARRAY
         cp.dstArray = arr
-        cp.WidthInBytes = X * 16
+        cp.WidthInBytes = X * 4 * bpt
         cp.Height = Y
         cp.Depth = Z
         _ck(d.cuMemcpy3D(cp))
@@ -127,26 +136,40 @@ class ReferenceDvrKernel:
         td = d.CUDA_TEXTURE_DESC()
         td.addressMode = [d.CUaddress_mode.CU_TR_ADDRESS_MODE_CLAMP] * 3
         td.filterMode = d.CUfilter_mode.CU_TR_FILTER_MODE_LINEAR
-        td.flags = d.CU_TRSF_NORMALIZED_COORDINATES
+        td.flags = d.CU_TRSF_NORMALIZED_COORDINATES      # (no CU_TRSF_READ_AS_INTEGER: 8-bit texels read as normalised floats)
         tex = _ck(d.cuTexObjectCreate(res, td, None))
         self._keep.append((arr, host))
         return int(tex)
 
-    def _upload_network(self, net):
+    def _grid_textures(self, grid):
+        if grid.encoding == 0:
+            # the same fp16-rounded texels every other implementation sees, stored as fp32 like the reference
+            vals = grid.values.astype(np.float32).astype(np.float16).astype(np.float32)     # (C,Z,Y,X)
+        else:
+            vals = grid.raw.astype(np.uint8)
+        return [self._texture(np.ascontiguousarray(np.transpose(vals[4 * i:4 * i + 4], (1, 2, 3, 0)))) for i in range(4)]
+
+    def _upload_network(self, net, time):
         H, nf = net.input_channels_out(), net.num_fourier
-        grid = (net.time_grids or net.ensemble_grids)[0]
-        # the same fp16-rounded texels every other implementation sees, stored as fp32 like the reference
-        vals = grid.values.astype(np.float32).astype(np.float16).astype(np.float32)     # (C,Z,Y,X)
-        texs = [self._texture(np.ascontiguousarray(np.transpose(vals[4 * i:4 * i + 4], (1, 2, 3, 0)))) for i in range(4)]
+        grids = net.time_grids or net.ensemble_grids
+        # keyframe selection as SceneNetwork::setTimeAndEnsemble / fillConstantMemory (:1290-1352): `time` is the keyframe index
+        T = len(grids)
+        lo = min(int(time), T - 1); hi = min(lo + 1, T - 1)
+        gA, gB = grids[lo], grids[hi]
+        texA = self._grid_textures(gA)
+        texB = texA if hi == lo else self._grid_textures(gB)
         b = bytearray()
 
         def add(x):
             _pad32(b); b.extend(x)
 
         add(np.ascontiguousarray(net.fourier.T, np.float16).tobytes())                  # cWeightsFourier [cin][nf]
-        add(np.array(texs, np.uint64).tobytes())                                        # cLatentGridA
-        add(np.array(texs, np.uint64).tobytes())                                        # cLatentGridB
-        add(np.zeros(16, np.float32).tobytes())                                         # cLatentGridInterpolation (time index 0)
+        add(np.array(texA, np.uint64).tobytes())                                        # cLatentGridA
+        add(np.array(texB, np.uint64).tobytes())                                        # cLatentGridB
+        if gA.encoding != 0:                                                            # HAS_LATENT_GRID_OFFSET_SCALE
+            add(np.asarray(gA.offset_or_mean, np.float32).tobytes()); add(np.asarray(gB.offset_or_mean, np.float32).tobytes())
+            add(np.asarray(gA.scale_or_std, np.float32).tobytes()); add(np.asarray(gB.scale_or_std, np.float32).tobytes())
+        add(np.full(16, time, np.float32).tobytes())                                    # cLatentGridInterpolation (kernel takes frac)
         add(np.ascontiguousarray(net.layers[0].weights, np.float16).tobytes())          # cWeightsLatentGrid [H][H+C]
         add(np.ascontiguousarray(net.layers[0].bias, np.float16).tobytes())
         add(np.ascontiguousarray(np.stack([l.weights for l in net.layers[1:-1]]), np.float16).tobytes())
@@ -160,18 +183,20 @@ class ReferenceDvrKernel:
         add(np.array([0.01], np.float32).tobytes())                                     # latentGridDifferencesStepSize (unused)
         _pad32(b)
         dptr, size = self.g_vol
-        if H == 32 and nf == 14:
+        if H == 32 and nf == 14 and gA.encoding == 0:
             assert len(b) == 7840, len(b)                                               # sizeof for C3
         assert len(b) == int(size), (len(b), int(size))
         _ck(self.drv.cuMemcpyHtoD(dptr, bytes(b), len(b)))
 
     def render(self, width, height, camera, fov_y, stepsize, tf, alpha_early_out=1 - 1e-5, density_min=0.0, density_max=1.0,
                out=None, timing_iters=0):
-        """-> (B,8,H,W) float32 CUDA tensor; with timing_iters > 0 also the mean kernel time in ms (CUDA events)."""
+        """-> (B,8,H,W) float32 CUDA tensor; with timing_iters > 0 also the mean kernel time in ms (CUDA events).
+        tf: (1|B,R,5) piecewise or (1|B,R,4) texture tensor, matching the variant this kernel was built with."""
         torch, d = self.torch, self.drv
         cam = torch.as_tensor(np.ascontiguousarray(camera, np.float32)).reshape(-1, 3, 3).cuda()
         tft = torch.as_tensor(np.ascontiguousarray(tf, np.float32)).cuda()
         tft = tft.reshape(-1, tft.shape[-2], tft.shape[-1])
+        assert tft.shape[-1] == (4 if self.tf_kind == "texture" else 5)
         B = cam.shape[0]
         if (width * height * B) % 32:
             raise RuntimeError("the reference requires W*H*B to be a multiple of 32 (image_evaluator_simple.cpp:254-264)")
