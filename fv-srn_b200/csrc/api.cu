@@ -56,6 +56,7 @@ struct fvsrn_network {
     // tcgen05 path: K-major UMMA weight tiles (+ bias chunks) and the Fourier matrix
     uint4* d_tc_blob = nullptr; int tc_blob_bytes = 0;
     int tc_off_w0 = 0, tc_off_wh = 0, tc_off_wlast = 0, tc_off_fourier = 0;
+    int tc_activation = 0;      // activation code the tcgen05 kernels run (SnakeAlt may become its pre-scaled form)
     int kernel_mode = FVSRN_KERNEL_TCGEN05;
     int H16 = 0, GC16 = 0, dir = 0, num_hidden = 0, activation = 0; float act_param = 1.f;
     std::vector<DeviceGrid> d_time, d_ens;
@@ -178,24 +179,40 @@ void build_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
 void build_tc_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
     const Network& n = h->net;
     const int H = 16 * h->H16, GC = 16 * h->GC16, L = int(n.layers.size());
-    auto put_layer = [&](const Layer& l, int K, int N, int Npad, bool bias_in_col3) {
+    // SnakeAlt evaluates cos(q*v), q = 2*param. When q is a power of two the weights and biases of every activated layer
+    // are multiplied by q here - exact in fp16 - so that the accumulators hold q*v and the epilogue saves the multiply
+    // (srn_tc.cuh, D_ACT_SNAKEALT_PRE).
+    float pre = 1.f;
+    h->tc_activation = h->activation;
+    if (h->activation == ACT_SNAKEALT) {
+        const float q = 2.f * h->act_param;
+        int e = 0;
+        bool ok = q >= 1.f && q <= 16.f && std::frexp(q, &e) == 0.5f;
+        for (int i = 0; ok && i + 1 < L; ++i) {
+            for (uint16_t w : n.layers[i].weights) ok = ok && std::fabs(f16_to_f32(w) * q) < 60000.f;
+            for (uint16_t b : n.layers[i].bias) ok = ok && std::fabs(f16_to_f32(b) * q) < 60000.f;
+        }
+        if (ok) { pre = q; h->tc_activation = 6; }
+    }
+    auto put_layer = [&](const Layer& l, int K, int N, int Npad, bool bias_in_col3, float scale) {
         const size_t base = blob.size();
         blob.resize(base + size_t(K + 16) * Npad * 2, 0);
         uint16_t* dst = reinterpret_cast<uint16_t*>(blob.data() + base);
         auto at = [&](int nn, int kk) -> uint16_t& { return dst[size_t(kk / 8) * (Npad / 8) * 64 + size_t(nn / 8) * 64 + (nn % 8) * 8 + (kk % 8)]; };
+        auto sc = [&](uint16_t v) -> uint16_t { return scale == 1.f ? v : f32_to_f16(f16_to_f32(v) * scale); };
         for (int nn = 0; nn < N; ++nn) {
-            for (int kk = 0; kk < K; ++kk) at(nn, kk) = l.w(nn, kk);
-            if (bias_in_col3) at(nn, 3) = l.bias[nn];
-            else at(nn, K) = l.bias[nn];
+            for (int kk = 0; kk < K; ++kk) at(nn, kk) = sc(l.w(nn, kk));
+            if (bias_in_col3) at(nn, 3) = sc(l.bias[nn]);
+            else at(nn, K) = sc(l.bias[nn]);
         }
     };
     blob.clear();
     h->tc_off_w0 = 0;
-    put_layer(n.layers[0], H + GC, H, H, !n.has_time);
+    put_layer(n.layers[0], H + GC, H, H, !n.has_time, pre);
     h->tc_off_wh = int(blob.size());
-    for (int i = 1; i + 1 < L; ++i) put_layer(n.layers[i], H, H, H, false);
+    for (int i = 1; i + 1 < L; ++i) put_layer(n.layers[i], H, H, H, false, pre);
     h->tc_off_wlast = int(blob.size());
-    put_layer(n.layers[L - 1], H, n.layers[L - 1].cout, 16, false);
+    put_layer(n.layers[L - 1], H, n.layers[L - 1].cout, 16, false, 1.f);
     h->tc_off_fourier = int(blob.size());
     {
         const uint8_t* p = reinterpret_cast<const uint8_t*>(n.fourier.data());
@@ -256,7 +273,8 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
         P.blob = h->d_blob; P.blob_bytes = h->blob_bytes;
         P.off_w0 = h->off_w0; P.off_wh = h->off_wh; P.off_wlast = h->off_wlast; P.off_bias = h->off_bias; P.off_fourier = h->off_fourier;
     }
-    P.num_hidden = h->num_hidden; P.activation = h->activation; P.act_param = h->act_param;
+    P.num_hidden = h->num_hidden; P.act_param = h->act_param;
+    P.activation = h->kernel_mode == FVSRN_KERNEL_TCGEN05 ? h->tc_activation : h->activation;
     P.output_mode = n.output_mode; P.has_time = n.has_time ? 1 : 0; P.dir_in_fourier = n.direction_in_fourier ? 1 : 0;
     P.time_value = 0.f;
     int g = 0;
@@ -674,17 +692,13 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         for (size_t i = 0; i < h->d_time.size(); ++i) ensure_tex32(h->d_time[i], n.time_grids[i]);
         for (size_t i = 0; i < h->d_ens.size(); ++i) ensure_tex32(h->d_ens[i], n.ensemble_grids[i]);
     }
-    const int tile_w = tc ? kTcTileW : kTileW, tile_h = tc ? kTcTileH : kTileH;
-    D.tiles_x = (D.tw + tile_w - 1) / tile_w; D.tiles_y = (D.th + tile_h - 1) / tile_h;
     launch_fn fn = pick_launcher(h->H16);
     if (!fn) throw std::runtime_error("no kernel for this hidden width");
     auto launch = [&](int b0, int nb, float time_abs) {
         const NetParams P = make_net_params(h, time_abs, h->net.current_ensemble, false);
-        DvrParams d = D; d.b0 = b0; d.nb = nb;
-        d.num_tiles = d.tiles_x * d.tiles_y * nb;
+        DvrParams d = D; d.b0 = b0; d.nb = nb;      // the launcher lays the tile raster of its kernel over the rectangle
         d.tile_counter = next_tile_counter(h, s);
         LaunchCfg cfg; cfg.sm_count = h->sm_count;
-        cfg.max_blocks = tc ? d.num_tiles : (d.num_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
         if (exact) CUDA_OK(launch_exact(h->H16, P, d, &cfg, s));
         else CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, s));
         h->launches++;
@@ -806,12 +820,14 @@ int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     if (!fn) return fail("no kernel for this hidden width");
     const bool tc = net->kernel_mode == FVSRN_KERNEL_TCGEN05;
     DvrParams dq{}; dq.tf_kind = 0; dq.tf_R = 8;   // a typical piecewise TF: the DVR kernels size their shared memory from it
+    dq.tw = 1024; dq.th = 1024; dq.nb = 1;
     if (net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact(net->H16, P, dq, &cfg, nullptr));
     else CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, kernel == 0 ? &dq : nullptr, &cfg, nullptr));
     info->device = net->device; info->sm_count = net->sm_count;
     info->block_threads = cfg.threads; info->blocks_per_sm = cfg.blocks_per_sm; info->grid_blocks = cfg.grid;
     info->smem_bytes_per_block = cfg.smem; info->regs_per_thread = cfg.regs;
-    info->rays_per_warp_tile_x = tc ? kTcTileW : kTileW; info->rays_per_warp_tile_y = tc ? kTcTileH : kTileH;
+    info->rays_per_warp_tile_x = cfg.tile_w ? cfg.tile_w : (tc ? kTcTileW : kTileW);
+    info->rays_per_warp_tile_y = cfg.tile_h ? cfg.tile_h : (tc ? kTcTileH : kTileH);
     info->kernel_launches = net->launches;
     return 0;
     FV_CATCH

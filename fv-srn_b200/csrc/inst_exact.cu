@@ -6,8 +6,12 @@
 namespace fvsrn {
 
 template <int H16>
-static cudaError_t launch_exact_h(const NetParams& P, const DvrParams& D, LaunchCfg* cfg, cudaStream_t s) {
+static cudaError_t launch_exact_h(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, cudaStream_t s) {
     using Core = Srn<H16, 1, false>;
+    DvrParams D = D0;
+    set_tiles(D, kTileW, kTileH);
+    cfg->tile_w = kTileW; cfg->tile_h = kTileH;
+    cfg->max_blocks = (D.num_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
     const int threads = kWarpsPerBlock * 32;
     const int smem = blob + kTfSmemFloats * 4 + kWarpsPerBlock * Core::STAGE_BYTES;

@@ -113,9 +113,9 @@ __device__ __forceinline__ CamFrame load_camera(const DvrParams& D, int b) {
 
 // ray through pixel (x,y), sub-sample s (reference renderer_image_evaluator_simple.cuh:84-86, renderer_camera.cuh:41-51)
 // and its box interval (renderer_utils.cuh:91-105, renderer_ray_evaluation_stepping_dvr.cuh:66-71)
-__device__ __forceinline__ Ray make_ray(const DvrParams& D, const CamFrame& c, int x, int y, int s, float3 bmin, float3 bsize) {
+__device__ __forceinline__ Ray make_ray(const DvrParams& D, const CamFrame& c, int x, int y, int s, float3 bmin, float3 bsize, int spp) {
     float nx = float(x), ny = float(y);
-    if (D.spp > 1) {                // deterministic stratified sub-pixel offsets (no reference counterpart)
+    if (spp > 1) {                // deterministic stratified sub-pixel offsets (no reference counterpart)
         nx = __fadd_rn(nx, __fsub_rn(__fdiv_rn(float(s % D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
         ny = __fadd_rn(ny, __fsub_rn(__fdiv_rn(float(s / D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
     }
@@ -171,18 +171,18 @@ __device__ __forceinline__ void blend_sample(const DvrParams& D, float4 c, float
     }
 }
 // the same compositing step without divergent branches: `on` = this sample exists (valid step of a live ray)
-__device__ __forceinline__ void blend_sample_pred(const DvrParams& D, bool on, float4 c, float t, float4& acc, float& acc_depth) {
+__device__ __forceinline__ void blend_sample_pred(const DvrParams& D, int blend_mode, bool on, float4 c, float t, float4& acc, float& acc_depth) {
     float e;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(c.w * -1.4426950408889634f));
-    const float a = (D.blend_mode == 1) ? 1.f - e : fminf(1.f, c.w);
+    const float a = (blend_mode == 1) ? 1.f - e : fminf(1.f, c.w);
     const float k = (on && c.w > 0.f) ? (1.f - acc.w) * a : 0.f;
     acc.x = fmaf(k, c.x, acc.x); acc.y = fmaf(k, c.y, acc.y); acc.z = fmaf(k, c.z, acc.z);
     acc_depth = fmaf(k, t, acc_depth);
     acc.w += k;
 }
 // pixel write, reference renderer_image_evaluator_simple.cuh:101-124
-__device__ __forceinline__ void write_pixel(const DvrParams& D, int b, int x, int y, float4 pix_color, float pix_depth, int last_steps) {
-    const float inv_s = 1.f / float(D.spp);
+__device__ __forceinline__ void write_pixel(const DvrParams& D, int b, int x, int y, float4 pix_color, float pix_depth, int last_steps, int spp) {
+    const float inv_s = 1.f / float(spp);
     float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
     const float depth = pix_depth / pix_color.w;    // NaN for empty pixels, as in the reference
     o[0 * D.sc] = pix_color.x * inv_s; o[1 * D.sc] = pix_color.y * inv_s; o[2 * D.sc] = pix_color.z * inv_s;
@@ -237,7 +237,7 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
         float pix_depth = 0.f;
         int last_steps = 0;
         for (int s = 0; s < D.spp; ++s) {   // warp-uniform trip count
-            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize);
+            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize, D.spp);
             const float3 eye = r.eye, dir = r.dir;
             const float tmin = r.tmin;
             const float tmax = in_img ? r.tmax : -1.f;  // lanes outside the image never become valid
@@ -269,7 +269,7 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
             pix_color.x += acc.x; pix_color.y += acc.y; pix_color.z += acc.z; pix_color.w += acc.w;
             pix_depth += acc_depth * acc.w;     // reference renderer_image_evaluator_simple.cuh:101-103
         }
-        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps);
+        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps, D.spp);
     }
     if (D.counters) {
         for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);

@@ -241,7 +241,7 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
         float pix_depth = 0.f;
         int last_steps = 0;
         for (int s = 0; s < D.spp; ++s) {
-            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize);
+            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize, D.spp);
             const float tmax = in_img ? r.tmax : -1.f;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             float acc_depth = 0.f;

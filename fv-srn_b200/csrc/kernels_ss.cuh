@@ -237,7 +237,7 @@ dvr_ss_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
         float pix_depth = 0.f;
         int last_steps = 0;
         for (int s = 0; s < D.spp; ++s) {
-            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize);
+            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize, D.spp);
             const float tmax = in_img ? r.tmax : -1.f;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             float acc_depth = 0.f;
@@ -288,7 +288,7 @@ dvr_ss_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
             pix_color.x += acc.x; pix_color.y += acc.y; pix_color.z += acc.z; pix_color.w += acc.w;
             pix_depth += acc_depth * acc.w;
         }
-        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps);
+        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps, D.spp);
     }
     if (D.counters && !is_mma_warp) {
         for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);

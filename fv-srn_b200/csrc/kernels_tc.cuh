@@ -13,6 +13,24 @@
 
 namespace fvsrn {
 
+// SPEC (template parameter of the DVR kernel and of SrnTc): compile-time specialisation of launch-uniform parameters.
+// The march loop tests them per sample or per trip; as run-time values they cost branches and keep the compiler from
+// scheduling across them. Measured on C3 (A/B on one B200, r02c): 5.49 ms generic, 4.69 ms with them frozen.
+//   0  generic: everything at run time
+//   1  the common DVR configuration: density:direct network without time input, piecewise TF shared by all views,
+//      Beer-Lambert blending, early termination on, one sample per pixel, static latent grid (no temporal interpolation)
+//   2  as 1 with temporally interpolated latent grids (both keyframes always fetched and blended)
+template <int SPEC>
+struct TcSpec {
+    static constexpr bool FAST = SPEC != 0;
+    static __device__ __forceinline__ int output_mode(const NetParams& P) { return FAST ? int(D_OUT_DENSITY_DIRECT) : P.output_mode; }
+    static __device__ __forceinline__ int has_time(const NetParams& P) { return FAST ? 0 : P.has_time; }
+    static __device__ __forceinline__ int tf_kind(const DvrParams& D) { return FAST ? 0 : D.tf_kind; }
+    static __device__ __forceinline__ int tf_batch(const DvrParams& D) { return FAST ? 1 : D.tf_batch; }
+    static __device__ __forceinline__ int early_out(const DvrParams& D) { return FAST ? 1 : D.early_out; }
+    static __device__ __forceinline__ int blend_mode(const DvrParams& D) { return FAST ? 1 : D.blend_mode; }
+    static __device__ __forceinline__ int spp(const DvrParams& D) { return FAST ? 1 : D.spp; }
+};
 constexpr int kTcComputeThreads = 128;
 constexpr int kTcThreads = 160;            // + the MMA warp
 constexpr int kTcTileW = 16, kTcTileH = 8;
@@ -23,14 +41,19 @@ constexpr int kTcTfBins = 64;              // piecewise TF search accelerator: o
 #ifndef FVSRN_NO_SYNCWARP
 #define FVSRN_NO_SYNCWARP 0
 #endif
+#ifndef FVSRN_TC_ACC16
+#define FVSRN_TC_ACC16 0   // 1: fp16 accumulators in TMEM (kind::f16 with D = F16; still one 32-bit column each), read back packed (tcgen05.ld .pack::16b): no fp32 -> fp16 packs in the layer epilogues. A/B on one B200 (C3, r02c): 5.42 vs 5.49 ms - within 1.2 %, kept opt-in
+#endif
 constexpr int kTcTfFloats = 2560;          // shared-memory TF: up to 204 piecewise intervals x 12 floats, or 256 x float4 texels
 
 // Transfer function staged in shared memory in evaluation-ready form. Piecewise (reference renderer_tf_piecewise.cuh:
 // 27-52): one record of three float4 per interval i = (p_i, p_{i+1}, 1/(p_{i+1}-p_i), -), v_i, v_{i+1}-v_i, so that a
 // sample costs the interval search plus three LDS.128 and four FFMA. Texture / identity TFs are copied verbatim.
+template <int SPEC = 0>
 __device__ __forceinline__ void tc_stage_tf(const DvrParams& D, int b, float* stf) {
-    if (D.tf_kind == 0) {
-        const float* src = D.tf + (D.tf_batch == 1 ? 0 : (size_t)b * D.tf_R * 5);
+    using TS = TcSpec<SPEC>;
+    if (TS::tf_kind(D) == 0) {
+        const float* src = D.tf + (TS::tf_batch(D) == 1 ? 0 : (size_t)b * D.tf_R * 5);
         for (int i = threadIdx.x; i < D.tf_R - 1; i += blockDim.x) {
             const float* v0 = src + i * 5; const float* v1 = v0 + 5;
             const float p0 = __ldg(v0 + 4), p1 = __ldg(v1 + 4);
@@ -53,8 +76,8 @@ __device__ __forceinline__ void tc_stage_tf(const DvrParams& D, int b, float* st
             bins[bin] = uint8_t(i);
         }
     } else {
-        const int n = D.tf_kind == 1 ? D.tf_R * 4 : 2;
-        const float* src = D.tf + (D.tf_batch == 1 ? 0 : (size_t)b * n);
+        const int n = TS::tf_kind(D) == 1 ? D.tf_R * 4 : 2;
+        const float* src = D.tf + (TS::tf_batch(D) == 1 ? 0 : (size_t)b * n);
         for (int i = threadIdx.x; i < n; i += blockDim.x) stf[i] = __ldg(src + i);
     }
 }
@@ -69,19 +92,21 @@ __device__ __forceinline__ float4 tc_tf_piecewise(const float* stf, int R, float
     return make_float4(fmaf(f, dv.x, v0.x), fmaf(f, dv.y, v0.y), fmaf(f, dv.z, v0.z), fmaf(f, dv.w, v0.w));
 }
 // network output -> colour + absorption of one sample; same contract as shade_sample (kernels.cuh), TF from shared memory
+template <int SPEC = 0>
 __device__ __forceinline__ float4 tc_shade_sample(const NetParams& P, const DvrParams& D, const float* stf, const float (&o)[4]) {
+    using TS = TcSpec<SPEC>;
     float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (P.output_mode < D_OUT_RGBO) {
-        const float value = (P.output_mode == D_OUT_DENSITY) ? sigmoidf_(o[0]) : o[0];
+    if (TS::output_mode(P) < D_OUT_RGBO) {
+        const float value = (TS::output_mode(P) == D_OUT_DENSITY) ? sigmoidf_(o[0]) : o[0];
         if (value >= D.dmin) {
             const float d2 = fminf(fmaxf((value - D.dmin) * D.inv_range, 0.f), 1.f);
-            if (D.tf_kind == 0) c = tc_tf_piecewise(stf, D.tf_R, d2);
-            else if (D.tf_kind == 1) c = tf_texture(stf, D.tf_R, d2);
+            if (TS::tf_kind(D) == 0) c = tc_tf_piecewise(stf, D.tf_R, d2);
+            else if (TS::tf_kind(D) == 1) c = tf_texture(stf, D.tf_R, d2);
             else c = make_float4(d2 * stf[1], d2 * stf[1], d2 * stf[1], d2 * stf[0]);
             c.w *= D.stepsize;
         }
     } else {    // colour network, SKIP_TRANSFER_FUNCTION path
-        if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
+        if (TS::output_mode(P) == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
         else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
         c.w *= D.stepsize;
     }
@@ -96,11 +121,13 @@ struct TcShared {           // fixed part of the dynamic shared memory, placed f
     int pad[2];
 };
 
-// VARIANT: bit 0 = ReLU hidden activation, bit 1 = NeRF-style Fourier matrix (feature i = axis i%3 times 2^(i/3))
-template <int H16, int GC16, bool DIR, int VARIANT>
+// VARIANT: bit 0 = ReLU hidden activation, bit 1 = NeRF-style Fourier matrix (feature i = axis i%3 times 2^(i/3)),
+// bit 2 = SnakeAlt on pre-scaled accumulators (build_tc_blob; exclusive with bit 0)
+template <int H16, int GC16, bool DIR, int VARIANT, int SPEC = 0>
 struct SrnTc {
     using Core = Srn<H16, GC16, DIR>;
-    static constexpr bool RELU = (VARIANT & 1) != 0, NERF = (VARIANT & 2) != 0;
+    using TS = TcSpec<SPEC>;
+    static constexpr bool RELU = (VARIANT & 1) != 0, NERF = (VARIANT & 2) != 0, SNAKEALT_PRE = (VARIANT & 4) != 0;
     static constexpr int H = Core::H, K0 = Core::K0, KT0 = K0 / 16, KTH = H / 16;
     static constexpr int NLAST = 16;                       // last layer padded to N = 16 (M=128 needs N % 16 == 0)
     // TMEM columns (32-bit): ones chunk | slot 0: D, A | slot 1: D, A
@@ -119,7 +146,7 @@ struct SrnTc {
         uint32_t sblob;       // shared address of the blob
         uint32_t ready, done; // shared addresses of the mbarrier pairs (slot s at +8 s)
         uint32_t phase;       // parity of the next phase to wait for; both slots advance together
-        tc::ActF af;
+        tc::ActF af;          // (af.act: run-time activation code of the generic instantiations)
     };
 
     // Layer-0 inputs of the sample owned by this thread (same channel order and fp16 rounding points as
@@ -131,7 +158,7 @@ struct SrnTc {
     static __device__ __forceinline__ void fetch_latent(const NetParams& P, float px, float py, float pz, uint32_t (&row)[K0 / 2]) {
 #pragma unroll
         for (int g = 0; g < GC16; ++g) {
-            const float frac = P.groups[g].frac;    // grid-uniform
+            const float frac = SPEC == 1 ? 0.f : P.groups[g].frac;    // grid-uniform; SPEC 1: static grid, SPEC 2: two keyframes
 #ifndef FVSRN_TEX_F16
 #define FVSRN_TEX_F16 0   // measured: the f16x2 return path is slower than fp32 return + F2FP (A/B on one B200: 6.05 vs 5.88 ms)
 #endif
@@ -139,7 +166,7 @@ struct SrnTc {
                 float4 v[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) v[q] = tex3D<float4>(P.tex_a[4 * g + q], px, py, pz);
-                if (frac > 0.f)
+                if (SPEC == 2 || frac > 0.f)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const float4 w = tex3D<float4>(P.tex_b[4 * g + q], px, py, pz);
@@ -166,7 +193,7 @@ struct SrnTc {
                                                           float dx, float dy, float dz, uint32_t (&row0)[K0 / 2], uint32_t (&row1)[K0 / 2]) {
         if constexpr (NERF && !DIR) {
             constexpr int FOFF = Core::FOFF, NF = Core::NF;
-            const __half tv = __float2half_rn(P.has_time ? P.time_value : 1.f);
+            const __half tv = __float2half_rn(TS::has_time(P) ? P.time_value : 1.f);
             const __half hp[3] = {__float2half_rn(px), __float2half_rn(py), __float2half_rn(pz)};
             const __half hq[3] = {__float2half_rn(qx), __float2half_rn(qy), __float2half_rn(qz)};
             row0[0] = h2u(__halves2half2(hp[0], hp[1])); row0[1] = h2u(__halves2half2(hp[2], tv));
@@ -205,7 +232,7 @@ struct SrnTc {
         constexpr int FOFF = Core::FOFF, NF = Core::NF;
         const __half hx = __float2half_rn(px), hy = __float2half_rn(py), hz = __float2half_rn(pz);
         row[0] = h2u(__halves2half2(hx, hy));
-        row[1] = h2u(__halves2half2(hz, __float2half_rn(P.has_time ? P.time_value : 1.f)));
+        row[1] = h2u(__halves2half2(hz, __float2half_rn(TS::has_time(P) ? P.time_value : 1.f)));
         __half2 d2x, d2y, d2z;
         if (DIR) {
             const __half hdx = __float2half_rn(dx), hdy = __float2half_rn(dy), hdz = __float2half_rn(dz);
@@ -270,7 +297,7 @@ struct SrnTc {
     // slot's completion barrier.
     // The smem descriptor of K step kt differs from step 0 only in the address field of its low word.
     static __device__ __forceinline__ void issue_layer(const Ctx& c, int slot, uint32_t w_addr, int n, int kt_data, bool bias_chunk) {
-        const uint32_t idesc = tc::make_idesc(128, n);
+        const uint32_t idesc = tc::make_idesc(128, n, FVSRN_TC_ACC16 != 0);
         const uint32_t kstride = uint32_t(n / 8) * 128u;                    // LBO: distance between the two K chunks of a step
         uint32_t lo = ((w_addr >> 4) & 0x3FFFu) | (((kstride >> 4) & 0x3FFFu) << 16);
         const uint32_t hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, descriptor version 1
@@ -305,7 +332,20 @@ struct SrnTc {
     }
 
     // epilogue of one slot: accumulator row -> activation -> fp16 A operand of the next layer
-    static __device__ __forceinline__ void epilogue(const Ctx& c, int slot, int act) {
+    template <int ACT>
+    static __device__ __forceinline__ void epilogue_t(const Ctx& c, int slot) {
+#if FVSRN_TC_ACC16
+#pragma unroll
+        for (int c0 = 0; c0 < H; c0 += 32) {
+            uint32_t v[16];
+            if (H - c0 >= 32) tc::tmem_ld16_pack(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld8_pack(c.tmem_lane + d_col(slot) + c0, v);
+            tc::wait_ld();
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                if (H - c0 >= 32 || j < 8) v[j] = tc::act_h2<ACT>(c.af, v[j]);
+            if (H - c0 >= 32) tc::tmem_st16(c.tmem_lane + a_col(slot) + c0 / 2, v, 0); else tc::tmem_st8(c.tmem_lane + a_col(slot) + c0 / 2, v, 0);
+        }
+#else
 #pragma unroll
         for (int c0 = 0; c0 < H; c0 += 32) {
             uint32_t v[32];
@@ -314,27 +354,41 @@ struct SrnTc {
             uint32_t pk[16];
 #pragma unroll
             for (int j = 0; j < 16; ++j)
-                pk[j] = (H - c0 >= 32 || j < 8) ? (RELU ? tc::pack_relu(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1]))
-                                                        : tc::act_pack(act, c.af, v[2 * j], v[2 * j + 1])) : 0u;
+                pk[j] = (H - c0 >= 32 || j < 8) ? tc::act_pack<ACT>(c.af, v[2 * j], v[2 * j + 1]) : 0u;
             if (H - c0 >= 32) tc::tmem_st16(c.tmem_lane + a_col(slot) + c0 / 2, pk, 0); else tc::tmem_st8(c.tmem_lane + a_col(slot) + c0 / 2, pk, 0);
         }
+#endif
+    }
+    static __device__ __forceinline__ void epilogue(const Ctx& c, int slot, int act) {
+        if constexpr (RELU) epilogue_t<D_ACT_RELU>(c, slot);
+        else if constexpr (SNAKEALT_PRE) epilogue_t<tc::D_ACT_SNAKEALT_PRE>(c, slot);
+        else epilogue_t<-1>(c, slot);       // run-time activation code (c.af.act)
     }
 
     // Last hidden layer's epilogue of a density network (one output): the 1 x H last layer is a dot product of the
     // activations this thread already holds (fp16x2 FMAs in two interleaved chains, summed in fp32), as the reference
     // does it on the CUDA cores (renderer_volume_tensorcores.cuh:1138-1143) - no further tensor-core round trip.
-    static __device__ __forceinline__ float epilogue_dot(const NetParams& P, const Ctx& c, int slot, int act) {
+    template <int ACT>
+    static __device__ __forceinline__ float epilogue_dot_t(const NetParams& P, const Ctx& c, int slot) {
         __half2 a0 = __float2half2_rn(0.f), a1 = a0;
 #pragma unroll
         for (int c0 = 0; c0 < H; c0 += 32) {
+#if FVSRN_TC_ACC16
+            uint32_t v[16];
+            if (H - c0 >= 32) tc::tmem_ld16_pack(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld8_pack(c.tmem_lane + d_col(slot) + c0, v);
+#else
             uint32_t v[32];
             if (H - c0 >= 32) tc::tmem_ld32(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld16(c.tmem_lane + d_col(slot) + c0, v);
+#endif
             tc::wait_ld();
 #pragma unroll
             for (int j = 0; j < 16; j += 2) {
                 if (H - c0 >= 32 || j < 8) {
-                    const uint32_t p0 = RELU ? tc::pack_relu(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])) : tc::act_pack(act, c.af, v[2 * j], v[2 * j + 1]);
-                    const uint32_t p1 = RELU ? tc::pack_relu(__uint_as_float(v[2 * j + 2]), __uint_as_float(v[2 * j + 3])) : tc::act_pack(act, c.af, v[2 * j + 2], v[2 * j + 3]);
+#if FVSRN_TC_ACC16
+                    const uint32_t p0 = tc::act_h2<ACT>(c.af, v[j]), p1 = tc::act_h2<ACT>(c.af, v[j + 1]);
+#else
+                    const uint32_t p0 = tc::act_pack<ACT>(c.af, v[2 * j], v[2 * j + 1]), p1 = tc::act_pack<ACT>(c.af, v[2 * j + 2], v[2 * j + 3]);
+#endif
                     a0 = __hfma2(u2h(p0), u2h(P.wlast2[c0 / 2 + j]), a0);
                     a1 = __hfma2(u2h(p1), u2h(P.wlast2[c0 / 2 + j + 1]), a1);
                 }
@@ -343,12 +397,17 @@ struct SrnTc {
         const float2 f0 = __half22float2(a0), f1 = __half22float2(a1);
         return P.blast + ((f0.x + f0.y) + (f1.x + f1.y));
     }
+    static __device__ __forceinline__ float epilogue_dot(const NetParams& P, const Ctx& c, int slot, int act) {
+        if constexpr (RELU) return epilogue_dot_t<D_ACT_RELU>(P, c, slot);
+        else if constexpr (SNAKEALT_PRE) return epilogue_dot_t<tc::D_ACT_SNAKEALT_PRE>(P, c, slot);
+        else return epilogue_dot_t<-1>(P, c, slot);
+    }
 
     // Compute warps: run the layer chain for the 2 x 128 samples whose layer-0 rows were stored with store_row().
     // A warp that is not `warp_active` (all its rays finished) keeps the barrier protocol going but skips the arithmetic.
     static __device__ __forceinline__ void mlp_compute(const NetParams& P, Ctx& c, bool warp_active, float (&out0)[4], float (&out1)[4]) {
         const int act = P.activation;
-        const bool scalar_last = P.output_mode < D_OUT_RGBO;    // density networks: last layer in registers
+        const bool scalar_last = TS::output_mode(P) < D_OUT_RGBO;    // density networks: last layer in registers
         // hidden-to-hidden hand-overs: accumulator -> activation -> A operand of the next layer
 #pragma unroll 1
         for (int l = scalar_last ? 1 : 0; l <= P.num_hidden; ++l) {
@@ -378,16 +437,25 @@ struct SrnTc {
             float (&out)[4] = slot == 0 ? out0 : out1;
             tc::mbar_wait(c.done + 8 * slot, c.phase);
             tc::fence_after_sync();
-            if (P.output_mode >= D_OUT_RGBO) {
+            if (TS::output_mode(P) >= D_OUT_RGBO) {
                 uint32_t o[4];
                 tc::tmem_ld4(c.tmem_lane + d_col(slot), o);
                 tc::wait_ld();
+#if FVSRN_TC_ACC16
+#pragma unroll
+                for (int k = 0; k < 4; ++k) out[k] = __half2float(__ushort_as_half((unsigned short)(o[k] & 0xffffu)));
+#else
                 out[0] = __uint_as_float(o[0]); out[1] = __uint_as_float(o[1]); out[2] = __uint_as_float(o[2]); out[3] = __uint_as_float(o[3]);
+#endif
             } else {
                 uint32_t o;
                 tc::tmem_ld1(c.tmem_lane + d_col(slot), o);
                 tc::wait_ld();
+#if FVSRN_TC_ACC16
+                out[0] = __half2float(__ushort_as_half((unsigned short)(o & 0xffffu))); out[1] = out[2] = out[3] = 0.f;
+#else
                 out[0] = __uint_as_float(o); out[1] = out[2] = out[3] = 0.f;
+#endif
             }
         }
         c.phase ^= 1u;
@@ -397,14 +465,14 @@ struct SrnTc {
 
     // MMA thread: the matching issue schedule of one trip. `c.phase` here is the parity of the ready barriers.
     static __device__ __forceinline__ void mlp_issue(const NetParams& P, Ctx& c) {
-        const int last = (P.output_mode < D_OUT_RGBO) ? P.num_hidden - 1 : P.num_hidden;   // see epilogue_dot
+        const int last = (TS::output_mode(P) < D_OUT_RGBO) ? P.num_hidden - 1 : P.num_hidden;   // see epilogue_dot
 #pragma unroll 1
         for (int l = -1; l <= last; ++l) {
 #pragma unroll
             for (int slot = 0; slot < 2; ++slot) {
                 tc::mbar_wait(c.ready + 8 * slot, c.phase);
                 tc::fence_after_sync();
-                if (l < 0) issue_layer(c, slot, c.sblob + P.off_w0, H, KT0, P.has_time != 0);
+                if (l < 0) issue_layer(c, slot, c.sblob + P.off_w0, H, KT0, TS::has_time(P) != 0);
                 else if (l < P.num_hidden) issue_layer(c, slot, c.sblob + P.off_wh + l * wh_bytes(), H, KTH, true);
                 else issue_layer(c, slot, c.sblob + P.off_wlast, NLAST, KTH, true);
             }
@@ -452,13 +520,14 @@ __device__ __forceinline__ void tc_epilogue(const typename Net::Ctx& c) {
     if ((threadIdx.x >> 5) == 4) tc::tmem_dealloc(c.tmem_base, Net::TMEM_COLS);
 }
 
-template <int H16, int GC16, bool DIR, int VARIANT>
+template <int H16, int GC16, bool DIR, int VARIANT, int SPEC = 0>
 // Register budget: 4 CTAs/SM at hidden <= 32 (96 registers); 2 CTAs/SM at hidden 48/64, which needs <= 168 registers
 // because a warp's registers must fit one 16384-entry register-file partition three times over (see
 // tc_blocks_by_regs in launch.cuh) - expressed as (192 threads, 2 blocks), the launch still uses kTcThreads.
 __global__ void __launch_bounds__(H16 <= 2 ? kTcThreads : 192, H16 <= 2 ? 4 : (H16 <= 4 ? 2 : 1))
 dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
-    using Net = SrnTc<H16, GC16, DIR, VARIANT>;
+    using Net = SrnTc<H16, GC16, DIR, VARIANT, SPEC>;
+    using TS = TcSpec<SPEC>;
     using Core = typename Net::Core;
     extern __shared__ uint4 smem[];
     TcShared* sh = reinterpret_cast<TcShared*>(smem);
@@ -469,7 +538,7 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
     const bool is_mma_warp = warp == 4;
 
     typename Net::Ctx ctx = tc_prologue<Net>(P, sh, sblob);
-    if (D.tf_batch == 1) tc_stage_tf(D, 0, stf);
+    if (TS::tf_batch(D) == 1) tc_stage_tf<SPEC>(D, 0, stf);
     __syncthreads();
 
     const float3 bmin = make_float3(P.box_min[0], P.box_min[1], P.box_min[2]);
@@ -491,14 +560,14 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
         const int trem = tile - bl * tiles_per_img;
         const int ty = trem / D.tiles_x, tx = trem - ty * D.tiles_x;
         const int b = D.b0 + bl;
-        if (D.tf_batch != 1) {      // per-view transfer function: staged for the view this tile belongs to
-            tc_stage_tf(D, b, stf);
+        if (TS::tf_batch(D) != 1) {      // per-view transfer function: staged for the view this tile belongs to
+            tc_stage_tf<SPEC>(D, b, stf);
             __syncthreads();
         }
 
         if (is_mma_warp) {
             // ---------------------------------------------------------------- MMA warp: one elected thread issues
-            for (int s = 0; s < D.spp; ++s) {
+            for (int s = 0; s < TS::spp(D); ++s) {
                 if (FVSRN_LAGGED_VOTE) {
                     // one CTA vote per march; afterwards trip i+1 runs iff some warp had work in trip i (flag written
                     // before that warp's first arrival of trip i, read after this warp's last ready-wait of trip i)
@@ -525,8 +594,8 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
         float4 pix_color = make_float4(0.f, 0.f, 0.f, 0.f);
         float pix_depth = 0.f;
         int last_steps = 0;
-        for (int s = 0; s < D.spp; ++s) {   // CTA-uniform trip count
-            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize);
+        for (int s = 0; s < TS::spp(D); ++s) {   // CTA-uniform trip count
+            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize, TS::spp(D));
             const float tmax = in_img ? r.tmax : -1.f;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
             float acc_depth = 0.f;
@@ -539,7 +608,7 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
             for (int i = 0;; i += 2) {
                 const float t0 = __fmaf_rn(float(i), D.stepsize, r.tmin);
                 const float t1 = __fmaf_rn(float(i + 1), D.stepsize, r.tmin);
-                const bool alive = !D.early_out || (acc.w < D.alpha_early_out);
+                const bool alive = !TS::early_out(D) || (acc.w < D.alpha_early_out);
                 const bool valid0 = (t0 <= tmax) && alive;
                 const bool in1 = (t1 <= tmax) && alive;
                 if (FVSRN_LAGGED_VOTE) {
@@ -593,19 +662,19 @@ dvr_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrPa
                 }
                 if (lane == 0) n_exec += 64;
                 // both samples are shaded first (independent work, interleaved by the compiler), then composited in order
-                const float4 c0 = tc_shade_sample(P, D, stf, o0), c1 = tc_shade_sample(P, D, stf, o1);
+                const float4 c0 = tc_shade_sample<SPEC>(P, D, stf, o0), c1 = tc_shade_sample<SPEC>(P, D, stf, o1);
                 steps += valid0 ? 1 : 0;
-                blend_sample_pred(D, valid0, c0, t0, acc, acc_depth);
-                const bool valid1 = in1 && (!D.early_out || (acc.w < D.alpha_early_out));
+                blend_sample_pred(D, TS::blend_mode(D), valid0, c0, t0, acc, acc_depth);
+                const bool valid1 = in1 && (!TS::early_out(D) || (acc.w < D.alpha_early_out));
                 steps += valid1 ? 1 : 0;
-                blend_sample_pred(D, valid1, c1, t1, acc, acc_depth);
+                blend_sample_pred(D, TS::blend_mode(D), valid1, c1, t1, acc, acc_depth);
             }
             n_valid += steps;
             last_steps = steps;
             pix_color.x += acc.x; pix_color.y += acc.y; pix_color.z += acc.z; pix_color.w += acc.w;
             pix_depth += acc_depth * acc.w;
         }
-        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps);
+        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps, TS::spp(D));
     }
     if (D.counters && !is_mma_warp) {
         for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);
@@ -618,6 +687,7 @@ template <int H16, int GC16, bool DIR, int VARIANT>
 __global__ void __launch_bounds__(H16 <= 2 ? kTcThreads : 192, H16 <= 2 ? 4 : (H16 <= 4 ? 2 : 1))
 eval_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ EvalParams E) {
     using Net = SrnTc<H16, GC16, DIR, VARIANT>;
+    using TS = TcSpec<0>;
     using Core = typename Net::Core;
     extern __shared__ uint4 smem[];
     TcShared* sh = reinterpret_cast<TcShared*>(smem);
@@ -662,11 +732,11 @@ eval_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Eval
                 const float (&o)[4] = slot == 0 ? o0 : o1;
                 const long long i = idx[slot];
                 // output parametrisation, reference :1054-1072, 1149-1158 (value, not valueNoClamping)
-                if (P.output_mode == D_OUT_DENSITY) E.out[i] = sigmoidf_(o[0]);
-                else if (P.output_mode == D_OUT_DENSITY_DIRECT) E.out[i] = o[0];
+                if (TS::output_mode(P) == D_OUT_DENSITY) E.out[i] = sigmoidf_(o[0]);
+                else if (TS::output_mode(P) == D_OUT_DENSITY_DIRECT) E.out[i] = o[0];
                 else {
                     float4 c;
-                    if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
+                    if (TS::output_mode(P) == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));
                     else c = make_float4(fminf(fmaxf(o[0], 0.f), 1.f), fminf(fmaxf(o[1], 0.f), 1.f), fminf(fmaxf(o[2], 0.f), 1.f), fmaxf(o[3], 0.f));
                     reinterpret_cast<float4*>(E.out)[i] = c;
                 }

@@ -5,6 +5,7 @@
 #include "kernels_tc.cuh"
 #ifdef FVSRN_EXPERIMENTS   // measured dead ends kept for reference (SS-mode tcgen05 kernel): not in the product build
 #include "kernels_ss.cuh"
+#include "kernels_tc8.cuh"
 #endif
 #include <cstdlib>
 #include <cuda_runtime.h>
@@ -22,7 +23,8 @@ struct LaunchCfg {
     int regs = 0;
     int threads = 0;
     int query_only = 0;      // 1: only fill the fields above, do not launch
-    long long max_blocks = 0; // upper bound on useful blocks (0 = none)
+    long long max_blocks = 0; // upper bound on useful blocks (0 = none; DVR launches derive it from the tile raster)
+    int tile_w = 0, tile_h = 0; // DVR kernels: pixels per work-queue tile (filled by the launcher)
 };
 
 enum { KIND_DVR = 0, KIND_EVAL = 1, KIND_DVR_TC = 2, KIND_EVAL_TC = 3 };  // _TC: tcgen05/TMEM kernels (kernels_tc.cuh)
@@ -135,9 +137,62 @@ inline cudaError_t kernel_facts(const void* fn, int threads, int smem, bool is_t
     return cudaSuccess;
 }
 
+// the tile raster of one DVR launch for a kernel whose CTA (tcgen05 kernels) or warp (mma.sync kernels) owns tile_w x tile_h pixels
+inline void set_tiles(DvrParams& d, int tile_w, int tile_h) {
+    d.tiles_x = (d.tw + tile_w - 1) / tile_w; d.tiles_y = (d.th + tile_h - 1) / tile_h;
+    d.num_tiles = d.tiles_x * d.tiles_y * d.nb;
+}
+
+#ifdef FVSRN_EXPERIMENTS
+// Measured dead end (A/B on one B200, C3, profiles/r02c_*): the 8-compute-warp, one-sample-per-thread kernel
+// (kernels_tc8.cuh; 72 registers, 24 compute warps per SM) renders C3 in 7.19 ms against 5.41 ms for dvr_tc_kernel: the
+// march is bound by the latency of its three MMA hand-overs per sample, which only a second sample in flight per
+// thread hides - more warps with one sample each do not.
+#ifndef FVSRN_TC8
+#define FVSRN_TC8 0
+#endif
+template <int H16, int GC16, bool DIR>
+cudaError_t launch_tc8(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, cudaStream_t s, bool* handled) {
+    *handled = false;
+    if constexpr (H16 == 2 && !DIR && FVSRN_TC8 != 0) {
+        if (P.output_mode >= D_OUT_RGBO) return cudaSuccess;
+        *handled = true;
+        using Net = SrnTc<H16, GC16, false, 0>;
+        DvrParams D = D0;
+        set_tiles(D, kTc8TileW, kTc8TileH);
+        const int variant = (P.activation == D_ACT_RELU ? 1 : 0) | (P.fourier_nerf ? 2 : 0);
+        const void* fns[4] = {(const void*)dvr_tc8_kernel<H16, GC16, 0>, (const void*)dvr_tc8_kernel<H16, GC16, 1>,
+                              (const void*)dvr_tc8_kernel<H16, GC16, 2>, (const void*)dvr_tc8_kernel<H16, GC16, 3>};
+        const void* fn = fns[variant];
+        const int blob = ((P.blob_bytes + 15) / 16) * 16;
+        const int smem = int(sizeof(Tc8Shared)) + blob + kTcTfFloats * 4;
+        KernelFacts kf;
+        const cudaError_t e = kernel_facts(fn, kTc8Threads, smem, true, Net::TMEM_COLS, &kf);
+        if (e != cudaSuccess) return e;
+        long long grid = (long long)kf.bps * cfg->sm_count;
+        if (grid > D.num_tiles) grid = D.num_tiles;
+        if (grid < 1) grid = 1;
+        cfg->blocks_per_sm = kf.bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = kf.regs; cfg->threads = kTc8Threads;
+        cfg->tile_w = kTc8TileW; cfg->tile_h = kTc8TileH;
+        if (cfg->query_only) return cudaSuccess;
+        void* args[2] = {const_cast<NetParams*>(&P), &D};
+        return cudaLaunchKernel(fn, dim3(unsigned(grid)), dim3(kTc8Threads), args, size_t(smem), s);
+    }
+    return cudaSuccess;
+}
+
+#endif  // FVSRN_EXPERIMENTS (tc8)
+
 template <int H16, int GC16, bool DIR>
 cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* cfg, cudaStream_t s) {
     using Net = Srn<H16, GC16, DIR>;
+#ifdef FVSRN_EXPERIMENTS
+    if (kind == KIND_DVR_TC && kp != nullptr) {
+        bool handled = false;
+        const cudaError_t e = launch_tc8<H16, GC16, DIR>(P, *static_cast<const DvrParams*>(kp), cfg, s, &handled);
+        if (e != cudaSuccess || handled) return e;
+    }
+#endif
 #ifdef FVSRN_EXPERIMENTS
     if (kind == KIND_DVR_TC && kp != nullptr) {
         bool handled = false;
@@ -149,19 +204,44 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
     const int threads = is_tc ? kTcThreads : kWarpsPerBlock * 32;
     const int smem = blob + (is_dvr ? (is_tc ? kTcTfFloats : kTfSmemFloats) * 4 : 0) + (is_tc ? int(sizeof(TcShared)) : kWarpsPerBlock * Net::STAGE_BYTES);
-    // tcgen05 kernels: the common cases (ReLU, NeRF-style Fourier matrix) get their own instantiations
-    const int variant = (P.activation == D_ACT_RELU ? 1 : 0) | ((P.fourier_nerf && !DIR) ? 2 : 0);
-    const void* tc_dvr[4] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1>,
-                             (const void*)dvr_tc_kernel<H16, GC16, DIR, DIR ? 0 : 2>, (const void*)dvr_tc_kernel<H16, GC16, DIR, DIR ? 1 : 3>};
-    const void* tc_eval[4] = {(const void*)eval_tc_kernel<H16, GC16, DIR, 0>, (const void*)eval_tc_kernel<H16, GC16, DIR, 1>,
-                              (const void*)eval_tc_kernel<H16, GC16, DIR, DIR ? 0 : 2>, (const void*)eval_tc_kernel<H16, GC16, DIR, DIR ? 1 : 3>};
+    // tcgen05 kernels: the common cases (ReLU or pre-scaled SnakeAlt, NeRF-style Fourier matrix) get their own instantiations
+    constexpr int NV = DIR ? 0 : 2;     // the NeRF recurrence is instantiated for networks without direction input only
+    const int variant = (P.activation == D_ACT_RELU ? 1 : (P.activation == tc::D_ACT_SNAKEALT_PRE ? 2 : 0)) + 3 * ((P.fourier_nerf && !DIR) ? 1 : 0);
+    const void* tc_dvr[6] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 4>,
+                             (const void*)dvr_tc_kernel<H16, GC16, DIR, NV>, (const void*)dvr_tc_kernel<H16, GC16, DIR, NV + 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, NV + 4>};
+    const void* tc_eval[6] = {(const void*)eval_tc_kernel<H16, GC16, DIR, 0>, (const void*)eval_tc_kernel<H16, GC16, DIR, 1>, (const void*)eval_tc_kernel<H16, GC16, DIR, 4>,
+                              (const void*)eval_tc_kernel<H16, GC16, DIR, NV>, (const void*)eval_tc_kernel<H16, GC16, DIR, NV + 1>, (const void*)eval_tc_kernel<H16, GC16, DIR, NV + 4>};
+    // ... and, for the network shapes of the BASELINE configs (hidden 32 / 64, one 16-channel grid, no direction input), the
+    // DVR kernel specialised for the common launch configuration (kernels_tc.cuh TcSpec): SPEC 1 static grid, 2 two keyframes
+    const void* tc_dvr_spec = nullptr;
+    if constexpr ((H16 == 2 || H16 == 4) && GC16 == 1 && !DIR) {
+        if (kind == KIND_DVR_TC && kp != nullptr) {
+            const DvrParams& Dq = *static_cast<const DvrParams*>(kp);
+            const bool fast = P.output_mode == D_OUT_DENSITY_DIRECT && !P.has_time && Dq.tf_kind == 0 && Dq.tf_batch == 1 && Dq.early_out && Dq.blend_mode == 1 && Dq.spp == 1;
+            if (fast) {
+                const void* s1[6] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 4, 1>,
+                                     (const void*)dvr_tc_kernel<H16, GC16, DIR, 2, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 3, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 6, 1>};
+                const void* s2[6] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0, 2>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1, 2>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 4, 2>,
+                                     (const void*)dvr_tc_kernel<H16, GC16, DIR, 2, 2>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 3, 2>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 6, 2>};
+                tc_dvr_spec = P.groups[0].frac > 0.f ? s2[variant] : s1[variant];
+            }
+        }
+    }
     const void* fn = kind == KIND_DVR ? (const void*)dvr_kernel<H16, GC16, DIR>
                    : kind == KIND_EVAL ? (const void*)eval_kernel<H16, GC16, DIR>
-                   : kind == KIND_DVR_TC ? tc_dvr[variant] : tc_eval[variant];
+                   : kind == KIND_DVR_TC ? (tc_dvr_spec ? tc_dvr_spec : tc_dvr[variant]) : tc_eval[variant];
     KernelFacts kf;
     const cudaError_t e = kernel_facts(fn, threads, smem, is_tc, SrnTc<H16, GC16, DIR, 0>::TMEM_COLS, &kf);
     if (e != cudaSuccess) return e;
     const int bps = kf.bps;
+    DvrParams dvr;
+    if (is_dvr && kp != nullptr) {
+        dvr = *static_cast<const DvrParams*>(kp);
+        cfg->tile_w = is_tc ? kTcTileW : kTileW; cfg->tile_h = is_tc ? kTcTileH : kTileH;
+        set_tiles(dvr, cfg->tile_w, cfg->tile_h);
+        cfg->max_blocks = is_tc ? dvr.num_tiles : (dvr.num_tiles + kWarpsPerBlock - 1) / kWarpsPerBlock;
+        kp = &dvr;
+    }
     long long grid = (long long)bps * cfg->sm_count;
     if (cfg->max_blocks > 0 && grid > cfg->max_blocks) grid = cfg->max_blocks;
     if (grid < 1) grid = 1;

@@ -119,9 +119,9 @@ __device__ __forceinline__ uint64_t make_b_desc(uint32_t smem_addr, uint32_t lbo
     return uint64_t((smem_addr >> 4) & 0x3FFF) | (uint64_t((lbo_bytes >> 4) & 0x3FFF) << 16) |
            (uint64_t((sbo_bytes >> 4) & 0x3FFF) << 32) | (uint64_t(1) << 46);
 }
-// instruction descriptor: D = F32, A = B = F16, both K-major, dense
-__host__ __device__ constexpr uint32_t make_idesc(int M, int N) {
-    return (1u << 4) | (uint32_t(N >> 3) << 17) | (uint32_t(M >> 4) << 24);
+// instruction descriptor: D = F32 (or F16 when acc16), A = B = F16, both K-major, dense
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, bool acc16 = false) {
+    return (acc16 ? 0u : (1u << 4)) | (uint32_t(N >> 3) << 17) | (uint32_t(M >> 4) << 24);
 }
 
 #define FV_R8(r, o)  "=r"(r[o+0]), "=r"(r[o+1]), "=r"(r[o+2]), "=r"(r[o+3]), "=r"(r[o+4]), "=r"(r[o+5]), "=r"(r[o+6]), "=r"(r[o+7])
@@ -143,6 +143,15 @@ __device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&r)[4]) {
 }
 __device__ __forceinline__ void tmem_ld1(uint32_t taddr, uint32_t& r) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n" : "=r"(r) : "r"(taddr) : "memory");
+}
+// fp16 accumulators (one per 32-bit column): 32 / 16 consecutive columns packed two per register
+__device__ __forceinline__ void tmem_ld16_pack(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+                 : FV_R8(r, 0), FV_R8(r, 8) : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld8_pack(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.pack::16b.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
+                 : FV_R8(r, 0) : "r"(taddr) : "memory");
 }
 template <int N>
 __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[N], int o) {
@@ -169,24 +178,64 @@ __device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
 
 // hidden activation on two fp32 accumulators -> packed fp16x2 (reference renderer_activations.cuh:39-341, evaluated in fp32)
 struct ActF {
-    float p, q, inv_q;   // Sine/Snake: p = param; Snake: q = 1/param; SnakeAlt: q = 2*param, inv_q = 1/q
+    float p, q, inv_q, inv_q2;   // Sine/Snake: p = param; Snake: q = 1/param; SnakeAlt: q = 2*param, inv_q = 1/q, inv_q2 = 1/q^2
+    int act;                     // the activation code itself, for the instantiations that take it at run time (ACT = -1)
 };
+// D_ACT_* plus: SnakeAlt on accumulators that already hold q*v (weights and biases of the producing layer pre-multiplied
+// by q = 2*param when that is a power of two - exact in fp16; see build_tc_blob)
+constexpr int D_ACT_SNAKEALT_PRE = 6;
 __device__ __forceinline__ ActF make_actf(int act, float param) {
-    ActF a; a.p = param;
+    ActF a; a.p = param; a.act = act;
     a.q = (act == D_ACT_SNAKE) ? 1.0f / param : 2.0f * param;
     a.inv_q = 1.0f / a.q;
+    a.inv_q2 = a.inv_q * a.inv_q;
     return a;
 }
-__device__ __forceinline__ float act1(int act, const ActF& a, float v) {
-    if (act == D_ACT_SINE) return __sinf(v * a.p);
-    if (act == D_ACT_SNAKE) { const float s = __sinf(a.p * v); return fmaf(a.q * s, s, v); }
-    /* SnakeAlt */ return (v + 1.0f - __cosf(a.q * v)) * a.inv_q;
+// SnakeAlt (v + 1 - cos(q v)) / q as fma(-cos(q v), 1/q, fma(v, 1/q, 1/q)): 5 issue slots per element instead of 6; on
+// pre-scaled accumulators z = q v: fma(-cos z, 1/q, fma(z, 1/q^2, 1/q)): 4.
+// (Packed-fp32 FMUL2 / FFMA2 forms of these activations were measured slower on B200: 14.57 vs 13.58 ms on C3-snake, r02c.)
+// ACT = -1: the activation code is a.act, uniform at run time (generic instantiations: Sine, Snake, SnakeAlt with a
+// parameter that is no power of two). Measured on C3-snake (r02c, one B200): this three-way run-time chain 12.65 ms; with
+// the pre-scaled form added to the chain 21.0 ms (the compiler stops hoisting it out of the element loop); a switch over
+// per-activation instantiations 13.32 ms; the pre-scaled SnakeAlt as its own kernel instantiation (VARIANT bit 2) 12.1 ms.
+template <int ACT>
+__device__ __forceinline__ float act1(const ActF& a, float v) {
+    if constexpr (ACT == -1) {
+        if (a.act == D_ACT_SINE) return __sinf(v * a.p);
+        if (a.act == D_ACT_SNAKE) { const float s = __sinf(a.p * v); return fmaf(a.q * s, s, v); }
+        /* SnakeAlt */ return fmaf(-__cosf(a.q * v), a.inv_q, fmaf(v, a.inv_q, a.inv_q));
+    }
+    else if constexpr (ACT == D_ACT_SINE) return __sinf(v * a.p);
+    else if constexpr (ACT == D_ACT_SNAKE) { const float s = __sinf(a.p * v); return fmaf(a.q * s, s, v); }
+    else if constexpr (ACT == D_ACT_SNAKEALT) return fmaf(-__cosf(a.q * v), a.inv_q, fmaf(v, a.inv_q, a.inv_q));
+    else if constexpr (ACT == D_ACT_SNAKEALT_PRE) return fmaf(-__cosf(v), a.inv_q, fmaf(v, a.inv_q2, a.inv_q));
+    else return v;
 }
-__device__ __forceinline__ uint32_t act_pack(int act, const ActF& a, uint32_t lo, uint32_t hi) {
+template <int ACT>
+__device__ __forceinline__ uint32_t act_pack(const ActF& a, uint32_t lo, uint32_t hi) {
     const float x = __uint_as_float(lo), y = __uint_as_float(hi);
-    if (act == D_ACT_RELU) return pack_relu(x, y);
-    if (act == D_ACT_NONE) return pack_h2(x, y);
-    return pack_h2(act1(act, a, x), act1(act, a, y));
+    if constexpr (ACT == D_ACT_RELU) return pack_relu(x, y);
+    else if constexpr (ACT == -1) {
+        if (a.act == D_ACT_RELU) return pack_relu(x, y);
+        if (a.act == D_ACT_NONE) return pack_h2(x, y);
+        return pack_h2(act1<ACT>(a, x), act1<ACT>(a, y));
+    }
+    else return pack_h2(act1<ACT>(a, x), act1<ACT>(a, y));
+}
+// the same on a packed fp16x2 accumulator pair (FVSRN_TC_ACC16)
+template <int ACT>
+__device__ __forceinline__ uint32_t act_h2(const ActF& a, uint32_t v) {
+    const __half2 h = u2h(v);
+    if constexpr (ACT == D_ACT_RELU) return h2u(__hmax2(h, __float2half2_rn(0.f)));
+    else if constexpr (ACT == D_ACT_NONE) return v;
+    else {
+        if constexpr (ACT == -1) { if (a.act == D_ACT_RELU) return h2u(__hmax2(h, __float2half2_rn(0.f))); if (a.act == D_ACT_NONE) return v; }
+        const float2 f = __half22float2(h); return pack_h2(act1<ACT>(a, f.x), act1<ACT>(a, f.y));
+    }
+}
+__device__ __forceinline__ uint32_t act_pack(int act, const ActF& a, uint32_t lo, uint32_t hi) {   // run-time form (experiments)
+    ActF b = a; b.act = act;
+    return act_pack<-1>(b, lo, hi);
 }
 
 } // namespace tc
