@@ -16,7 +16,7 @@ SYMBOLS = [
     "fvsrn_network_valid", "fvsrn_network_num_parameters", "fvsrn_network_compute_max_warps",
     "fvsrn_network_set_time_and_ensemble", "fvsrn_network_get_info", "fvsrn_network_set_kernel_mode", "fvsrn_network_get_kernel_mode", "fvsrn_network_prepare",
     "fvsrn_network_clear_gpu_resources", "fvsrn_evaluate", "fvsrn_evaluate_host", "fvsrn_render_dvr",
-    "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_query",
+    "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_extract_color_ex", "fvsrn_query",
 ]
 
 
@@ -39,6 +39,7 @@ class DvrParams(C.Structure):
         ("samples_per_pixel", C.c_int), ("view_times_host", C.c_void_p),
         ("out_stride_b", C.c_int64), ("out_stride_c", C.c_int64), ("out_stride_y", C.c_int64), ("out_stride_x", C.c_int64),
         ("step_count_dev", C.c_void_p), ("counters_dev", C.c_void_p),
+        ("output_format", C.c_int), ("channel_mode", C.c_int), ("tonemap", C.c_int), ("max_exposure", C.c_float),
     ]
 
 
@@ -92,6 +93,7 @@ def lib():
         "fvsrn_render_dvr": [vp, C.POINTER(DvrParams), vp, vp],
         "fvsrn_render_dvr_host": [vp, C.POINTER(DvrParams), vp, vp],
         "fvsrn_extract_color": [vp, vp, i, i, i, vp],
+        "fvsrn_extract_color_ex": [vp, vp, i, i, i, i, i, f, i, vp],
         "fvsrn_query": [vp, i, C.POINTER(QueryInfo)],
     }
     for name, args in sig.items():

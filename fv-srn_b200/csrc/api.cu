@@ -64,6 +64,8 @@ struct fvsrn_network {
     int tile_counter_slots = 0, tile_counter_next = 0;
     float* d_scratch = nullptr; size_t scratch_bytes = 0;  // staging for the *_host entry points
     unsigned long long launches = 0;
+    cudaStream_t aux_stream = nullptr;          // multi-view launches alternate between the caller's stream and this one, so
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // that the next view's CTAs fill the SMs the previous view drains
     // A handle is used by one host thread at a time (as the reference's modules); concurrent calls on one
     // handle are serialised here because the work-queue counter ring and the staging buffer are per-handle state.
     std::mutex mu;
@@ -86,6 +88,10 @@ void release_gpu(fvsrn_network* h) {
         }
     if (h->d_tile_counter) cudaFree(h->d_tile_counter);
     if (h->d_scratch) cudaFree(h->d_scratch);
+    if (h->aux_stream) cudaStreamDestroy(h->aux_stream);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_join) cudaEventDestroy(h->ev_join);
+    h->aux_stream = nullptr; h->ev_fork = h->ev_join = nullptr;
     h->d_blob = nullptr; h->d_time.clear(); h->d_ens.clear(); h->d_tile_counter = nullptr;
     h->d_scratch = nullptr; h->scratch_bytes = 0; h->prepared = false;
 }
@@ -595,6 +601,9 @@ int fvsrn_network_prepare(fvsrn_network* net, int device, void* stream) {
     CUDA_OK(cudaMalloc(&net->d_tile_counter, sizeof(unsigned int) * net->tile_counter_slots));
     CUDA_OK(cudaMemsetAsync(net->d_tile_counter, 0, sizeof(unsigned int) * net->tile_counter_slots, s));
     CUDA_OK(cudaStreamSynchronize(s));
+    CUDA_OK(cudaStreamCreateWithFlags(&net->aux_stream, cudaStreamNonBlocking));
+    CUDA_OK(cudaEventCreateWithFlags(&net->ev_fork, cudaEventDisableTiming));
+    CUDA_OK(cudaEventCreateWithFlags(&net->ev_join, cudaEventDisableTiming));
     net->prepared = true;
     return 0;
     FV_CATCH
@@ -617,6 +626,65 @@ __global__ void extract_color_kernel(const float* __restrict__ img, float* __res
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
         const long long b = i / (4 * hw), r = i - b * 4 * hw;
         out[i] = img[b * 8 * hw + r];
+    }
+}
+
+// IImageEvaluator::ExtractColor on a raw (B,8,H,W) tensor: SelectOutputChannelKernel2 / TonemappingKernel2 and their
+// packed-texture forms (iimage_evaluator_cuda.cu:21-80, 168-260). mm = {min depth, max depth} for ChannelDepth.
+__global__ void extract_color_ex_kernel(const float* __restrict__ img, void* __restrict__ out, long long hw, int batch,
+                                        int channel_mode, int tonemap, float max_exposure, int fmt, const float* __restrict__ mm) {
+    const long long total = hw * batch;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long b = i / hw, px = i - b * hw;
+        const float* p = img + b * 8 * hw + px;
+        const float4 color = make_float4(p[0], p[hw], p[2 * hw], p[3 * hw]);
+        float4 c;
+        if (channel_mode == FVSRN_CHANNEL_DEPTH) {      // iimage_evaluator.cpp:84-94
+            const float mn = mm[0], mx = mm[1];
+            const float scale = 1.f / (mx - mn), offset = -mn / (mx - mn);
+            const float d = p[7 * hw] * scale + offset;
+            c = make_float4(d, d, d, color.w * 0.f + 1.f);
+        } else {
+            c = select_channel(channel_mode, tonemap, max_exposure, color, make_float3(p[4 * hw], p[5 * hw], p[6 * hw]));
+        }
+        if (fmt == FVSRN_OUTPUT_RGBA_F32) {
+            float* o = reinterpret_cast<float*>(out) + b * 4 * hw + px;
+            o[0] = c.x; o[hw] = c.y; o[2 * hw] = c.z; o[3 * hw] = c.w;
+        } else if (fmt == FVSRN_OUTPUT_RGBA8) {
+            reinterpret_cast<unsigned int*>(out)[i] = rgba_to_int(c.x, c.y, c.z, c.w);
+        } else {
+            reinterpret_cast<uint2*>(out)[i] = make_uint2(h2u(__floats2half2_rn(c.x, c.y)), h2u(__floats2half2_rn(c.z, c.w)));
+        }
+    }
+}
+// min / max of the depth plane with torch.min / torch.max semantics (NaN propagates): {min, max} -> mm
+__global__ void depth_minmax_kernel(const float* __restrict__ img, long long hw, int batch, float* mm) {
+    __shared__ float smin[32], smax[32];
+    __shared__ int snan[32];
+    float mn = FLT_MAX, mx = -FLT_MAX; int nan = 0;
+    const long long total = hw * batch;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long b = i / hw, px = i - b * hw;
+        const float d = img[b * 8 * hw + 7 * hw + px];
+        if (d != d) nan = 1; else { mn = fminf(mn, d); mx = fmaxf(mx, d); }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o)); mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        nan |= __shfl_xor_sync(0xffffffffu, nan, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { smin[w] = mn; smax[w] = mx; snan[w] = nan; }
+    __syncthreads();
+    if (w == 0) {
+        const int nw = blockDim.x >> 5;
+        mn = l < nw ? smin[l] : FLT_MAX; mx = l < nw ? smax[l] : -FLT_MAX; nan = l < nw ? snan[l] : 0;
+        for (int o = 16; o > 0; o >>= 1) {
+            mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o)); mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            nan |= __shfl_xor_sync(0xffffffffu, nan, o);
+        }
+        if (l == 0) {   // float atomics through the ordered-int trick are overkill here: one block per call (grid = 1)
+            mm[0] = nan ? __int_as_float(0x7fc00000) : mn; mm[1] = nan ? __int_as_float(0x7fc00000) : mx;
+        }
     }
 }
 
@@ -682,6 +750,13 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     D.spp = spp; D.spp_side = side;
     D.out = out; D.sb = p->out_stride_b; D.sc = p->out_stride_c; D.sy = p->out_stride_y; D.sx = p->out_stride_x;
     D.step_count = p->step_count_dev; D.counters = p->counters_dev;
+    D.out_format = p->output_format; D.channel_mode = p->channel_mode; D.tonemap = p->tonemap; D.max_exposure = p->max_exposure;
+    if (D.out_format < FVSRN_OUTPUT_RAW8_F32 || D.out_format > FVSRN_OUTPUT_RGBA_F16) throw std::runtime_error("unknown output format");
+    if (D.out_format != FVSRN_OUTPUT_RAW8_F32) {
+        if (D.channel_mode == FVSRN_CHANNEL_DEPTH) throw std::runtime_error("ChannelDepth needs the frame's min/max depth: render the raw tensor and call fvsrn_extract_color_ex");
+        if (D.channel_mode < 0 || D.channel_mode > FVSRN_CHANNEL_COLOR) throw std::runtime_error("unknown channel mode");
+        if (D.tonemap && !(D.max_exposure > 0.f)) throw std::runtime_error("tonemapping needs a positive max_exposure");
+    }
     const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05;
     const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT;
     if (exact) {    // the shapes the reference kernels this mode is validated against cover (kernels_exact.cuh)
@@ -694,21 +769,27 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     }
     launch_fn fn = pick_launcher(h->H16);
     if (!fn) throw std::runtime_error("no kernel for this hidden width");
-    auto launch = [&](int b0, int nb, float time_abs) {
+    auto launch = [&](int b0, int nb, float time_abs, cudaStream_t ls) {
         const NetParams P = make_net_params(h, time_abs, h->net.current_ensemble, false);
         DvrParams d = D; d.b0 = b0; d.nb = nb;      // the launcher lays the tile raster of its kernel over the rectangle
-        d.tile_counter = next_tile_counter(h, s);
+        d.tile_counter = next_tile_counter(h, ls);
         LaunchCfg cfg; cfg.sm_count = h->sm_count;
-        if (exact) CUDA_OK(launch_exact(h->H16, P, d, &cfg, s));
-        else CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, s));
+        if (exact) CUDA_OK(launch_exact(h->H16, P, d, &cfg, ls));
+        else CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, ls));
         h->launches++;
     };
-    if (p->view_times_host) { // one launch per view: every view selects its own keyframe pair (time sweeps)
+    if (p->view_times_host) {
+        // One launch per view: every view selects its own keyframe pair (time sweeps). The persistent grid of
+        // a view drains over its last tiles; the views alternate between the caller's stream and an internal one so that
+        // the next view's CTAs become resident on the SMs the previous view is leaving (views write disjoint outputs).
+        const bool overlap = p->batch > 1 && h->aux_stream != nullptr;
+        if (overlap) { CUDA_OK(cudaEventRecord(h->ev_fork, s)); CUDA_OK(cudaStreamWaitEvent(h->aux_stream, h->ev_fork, 0)); }
         for (int b = 0; b < p->batch; ++b) {
             const float t = std::min(std::max(p->view_times_host[b], float(h->net.time_min)), float(h->net.time_max_inclusive()));
-            launch(b, 1, t);
+            launch(b, 1, t, (overlap && (b & 1)) ? h->aux_stream : s);
         }
-    } else launch(0, p->batch, h->net.current_time);
+        if (overlap) { CUDA_OK(cudaEventRecord(h->ev_join, h->aux_stream)); CUDA_OK(cudaStreamWaitEvent(s, h->ev_join, 0)); }
+    } else launch(0, p->batch, h->net.current_time, s);
 }
 
 } // namespace
@@ -769,15 +850,20 @@ int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* 
     DeviceGuard guard(net->device);
     require_prepared(net);
     if (!p || !out_host) return fail("null argument");
-    if (p->out_stride_x != 1 || p->out_stride_y != p->width || p->out_stride_c != (int64_t)p->width * p->height ||
-        p->out_stride_b != 8ll * p->width * p->height)
-        return fail("fvsrn_render_dvr_host needs a contiguous (B,8,H,W) output");
+    // element size and planes of the output format (fvsrn_output_format): planar fp32 (8 or 4 planes) or packed pixels
+    const int fmt = p->output_format;
+    if (fmt < FVSRN_OUTPUT_RAW8_F32 || fmt > FVSRN_OUTPUT_RGBA_F16) return fail("unknown output format");
+    const int planes = fmt == FVSRN_OUTPUT_RAW8_F32 ? 8 : (fmt == FVSRN_OUTPUT_RGBA_F32 ? 4 : 1);
+    const size_t elem = fmt == FVSRN_OUTPUT_RGBA_F16 ? 8 : 4;
+    const int64_t W = p->width, H = p->height;
+    if (p->out_stride_x != 1 || p->out_stride_y != W || (planes > 1 && p->out_stride_c != W * H) || p->out_stride_b != planes * W * H)
+        return fail("fvsrn_render_dvr_host needs a contiguous output: (B,8,H,W) / (B,4,H,W) fp32 or (B,H,W) packed pixels");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     const bool is_rgbo = net->net.output_mode >= OUT_RGBO;
     const size_t cam_b = size_t(p->batch) * 36;
     const int tf_floats = is_rgbo ? 0 : (p->tf_kind == 0 ? p->tf_resolution * 5 : (p->tf_kind == 1 ? p->tf_resolution * 4 : 2)) * p->tf_batch;
     const size_t tf_off = ((cam_b + 15) / 16) * 16, img_off = ((tf_off + size_t(tf_floats) * 4 + 255) / 256) * 256;
-    const size_t img_b = size_t(p->batch) * 8 * p->width * p->height * 4;
+    const size_t img_b = size_t(p->batch) * planes * W * H * elem;
     ensure_scratch(net, img_off + img_b);
     char* base = reinterpret_cast<char*>(net->d_scratch);
     CUDA_OK(cudaMemcpyAsync(base, p->camera_matrix_dev, cam_b, cudaMemcpyHostToDevice, s));
@@ -785,10 +871,34 @@ int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* 
     fvsrn_dvr_params q = *p;
     q.camera_matrix_dev = reinterpret_cast<const float*>(base);
     q.tf_dev = reinterpret_cast<const float*>(base + tf_off);
-    float* d_img = reinterpret_cast<float*>(base + img_off);
-    if (q.tile_w > 0 || q.tile_h > 0 || q.tile_x0 > 0 || q.tile_y0 > 0) CUDA_OK(cudaMemsetAsync(d_img, 0, img_b, s));
-    do_render(net, &q, d_img, s);
-    CUDA_OK(cudaMemcpyAsync(out_host, d_img, img_b, cudaMemcpyDeviceToHost, s));
+    char* d_img = base + img_off;
+    const bool has_rect = q.tile_w > 0 || q.tile_h > 0 || q.tile_x0 > 0 || q.tile_y0 > 0;
+    // A single full frame is rendered as four row bands that alternate between the caller's stream and the internal one:
+    // each band's device-to-host copy follows its kernel on the same stream and overlaps the next band's kernel on the
+    // other, and the next band's CTAs fill the SMs the previous band is draining.
+    const int bands = (p->batch == 1 && !has_rect && !p->view_times_host && H >= 256 && net->aux_stream) ? 4 : 1;
+    if (bands == 1) {
+        if (has_rect) CUDA_OK(cudaMemsetAsync(d_img, 0, img_b, s));
+        do_render(net, &q, reinterpret_cast<float*>(d_img), s);
+        CUDA_OK(cudaMemcpyAsync(out_host, d_img, img_b, cudaMemcpyDeviceToHost, s));
+    } else {
+        CUDA_OK(cudaEventRecord(net->ev_fork, s));
+        CUDA_OK(cudaStreamWaitEvent(net->aux_stream, net->ev_fork, 0));
+        const int rows = int((H + bands - 1) / bands + 7) / 8 * 8;
+        int k = 0;
+        for (int y0 = 0; y0 < H; y0 += rows, ++k) {
+            const int h = int(std::min<int64_t>(rows, H - y0));
+            cudaStream_t bs = (k & 1) ? net->aux_stream : s;
+            q.tile_x0 = 0; q.tile_y0 = y0; q.tile_w = int(W); q.tile_h = h;
+            do_render(net, &q, reinterpret_cast<float*>(d_img), bs);
+            for (int c = 0; c < planes; ++c) {
+                const size_t off = (size_t(c) * W * H + size_t(y0) * W) * elem;
+                CUDA_OK(cudaMemcpyAsync(reinterpret_cast<char*>(out_host) + off, d_img + off, size_t(h) * W * elem, cudaMemcpyDeviceToHost, bs));
+            }
+        }
+        CUDA_OK(cudaEventRecord(net->ev_join, net->aux_stream));
+        CUDA_OK(cudaStreamWaitEvent(s, net->ev_join, 0));
+    }
     CUDA_OK(cudaStreamSynchronize(s));
     return 0;
     FV_CATCH
@@ -803,6 +913,31 @@ int fvsrn_extract_color(const float* img_dev, float* out_dev, int batch, int hei
     const int blocks = int(std::min<long long>((total + threads - 1) / threads, 148 * 16));
     extract_color_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream)>>>(img_dev, out_dev, hw, total);
     CUDA_OK(cudaGetLastError());
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_extract_color_ex(const float* img_dev, void* out_dev, int batch, int height, int width,
+                           int channel_mode, int tonemap, float max_exposure, int output_format, void* stream) {
+    FV_TRY
+    if (!img_dev || !out_dev) return fail("null device pointer");
+    if (output_format < FVSRN_OUTPUT_RGBA_F32 || output_format > FVSRN_OUTPUT_RGBA_F16) return fail("output format must be RGBA_F32, RGBA8 or RGBA_F16");
+    if (channel_mode < 0 || channel_mode > FVSRN_CHANNEL_COLOR) return fail("unknown channel mode");
+    if (tonemap && channel_mode == FVSRN_CHANNEL_COLOR && !(max_exposure > 0.f)) return fail("tonemapping needs a positive max_exposure");
+    const long long hw = (long long)height * width, total = hw * batch;
+    if (total <= 0) return 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    float* mm = nullptr;
+    if (channel_mode == FVSRN_CHANNEL_DEPTH) {
+        CUDA_OK(cudaMallocAsync(&mm, 2 * sizeof(float), s));
+        depth_minmax_kernel<<<1, 1024, 0, s>>>(img_dev, hw, batch, mm);
+        CUDA_OK(cudaGetLastError());
+    }
+    const int threads = 256;
+    const int blocks = int(std::min<long long>((total + threads - 1) / threads, 148 * 16));
+    extract_color_ex_kernel<<<blocks, threads, 0, s>>>(img_dev, out_dev, hw, batch, channel_mode, tonemap, max_exposure, output_format, mm);
+    CUDA_OK(cudaGetLastError());
+    if (mm) CUDA_OK(cudaFreeAsync(mm, s));
     return 0;
     FV_CATCH
 }

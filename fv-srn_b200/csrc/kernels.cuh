@@ -33,6 +33,11 @@ struct DvrParams {
     unsigned int* tile_counter;         // work queue
     int tiles_x, tiles_y, num_tiles;
     int tf_smem_floats;                 // SS-mode tcgen05 kernel: floats reserved for the staged TF (multiple of 4)
+    // fused colour extraction (reference IImageEvaluator::ExtractColor, iimage_evaluator.cpp:26-135, run as a second pass there)
+    int out_format;                     // 0 (B,8,H,W) fp32 raw | 1 (B,4,H,W) fp32 | 2 (B,H,W) packed RGBA8 | 3 (B,H,W) half4
+    int channel_mode;                   // IImageEvaluator::ChannelMode: 0 mask, 1 normal, 3 colour (2 = depth is not fusable)
+    int tonemap;                        // ChannelColor only: ACES filmic curve + gamma (TonemappingKernel)
+    float max_exposure;
 };
 
 struct EvalParams {
@@ -180,16 +185,58 @@ __device__ __forceinline__ void blend_sample_pred(const DvrParams& D, int blend_
     acc_depth = fmaf(k, t, acc_depth);
     acc.w += k;
 }
-// pixel write, reference renderer_image_evaluator_simple.cuh:101-124
+// ACES filmic curve + gamma, reference tonemappingFunction (iimage_evaluator_cuda.cu:145-166; that file is built with
+// --use_fast_math, CMakeLists.txt:44, hence the approximate division and power)
+__device__ __forceinline__ float tonemap1(float v, float max_exposure) {
+    v = rf::div(v, max_exposure);
+    v = rf::div(v * (2.51f * v + 0.03f), v * (2.43f * v + 0.59f) + 0.14f);
+    v = fminf(fmaxf(v, 0.f), 1.f);
+    float l; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(v));
+    return rf::ex2(l * (1.0f / 2.4f));
+}
+// rgbaToInt, renderer_utils.cuh:48-57
+__device__ __forceinline__ unsigned int rgba_to_int(float r, float g, float b, float a) {
+    r = fminf(fmaxf(r * 255.f, 0.f), 255.f); g = fminf(fmaxf(g * 255.f, 0.f), 255.f);
+    b = fminf(fmaxf(b * 255.f, 0.f), 255.f); a = fminf(fmaxf(a * 255.f, 0.f), 255.f);
+    return ((unsigned int)a << 24) | ((unsigned int)b << 16) | ((unsigned int)g << 8) | (unsigned int)r;
+}
+// one pixel of the selected channel: what SelectOutputChannelKernel / TonemappingKernel (iimage_evaluator_cuda.cu:21-80,
+// 168-260) compute from the 8 raw channels, with the channel table of IImageEvaluator::ExtractColor (iimage_evaluator.cpp:52-112)
+__device__ __forceinline__ float4 select_channel(int channel_mode, int tonemap, float max_exposure, float4 color, float3 normal) {
+    if (channel_mode == 3) {        // ChannelColor
+        if (tonemap) return make_float4(tonemap1(color.x, max_exposure), tonemap1(color.y, max_exposure), tonemap1(color.z, max_exposure), color.w);
+        return color;
+    }
+    if (channel_mode == 0) return make_float4(color.w, color.w, color.w, 1.f);                                   // ChannelMask
+    return make_float4(fmaf(normal.x, 0.5f, 0.5f), fmaf(normal.y, 0.5f, 0.5f), fmaf(normal.z, 0.5f, 0.5f), color.w);  // ChannelNormal
+}
+__device__ __forceinline__ void store_rgba(const DvrParams& D, int b, int x, int y, float4 c) {
+    const long long o = (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
+    if (D.out_format == 1) {
+        float* p = D.out + o;
+        p[0 * D.sc] = c.x; p[1 * D.sc] = c.y; p[2 * D.sc] = c.z; p[3 * D.sc] = c.w;
+    } else if (D.out_format == 2) {
+        reinterpret_cast<unsigned int*>(D.out)[o] = rgba_to_int(c.x, c.y, c.z, c.w);
+    } else {
+        const __half2 lo = __floats2half2_rn(c.x, c.y), hi = __floats2half2_rn(c.z, c.w);
+        reinterpret_cast<uint2*>(D.out)[o] = make_uint2(h2u(lo), h2u(hi));
+    }
+}
+// pixel write, reference renderer_image_evaluator_simple.cuh:101-124 (+ the fused colour extraction when requested)
 __device__ __forceinline__ void write_pixel(const DvrParams& D, int b, int x, int y, float4 pix_color, float pix_depth, int last_steps, int spp) {
     const float inv_s = 1.f / float(spp);
+    if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
+    const float4 color = make_float4(pix_color.x * inv_s, pix_color.y * inv_s, pix_color.z * inv_s, pix_color.w * inv_s);
+    if (D.out_format != 0) {
+        store_rgba(D, b, x, y, select_channel(D.channel_mode, D.tonemap, D.max_exposure, color, make_float3(0.f, 0.f, 0.f)));
+        return;
+    }
     float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
     const float depth = pix_depth / pix_color.w;    // NaN for empty pixels, as in the reference
-    o[0 * D.sc] = pix_color.x * inv_s; o[1 * D.sc] = pix_color.y * inv_s; o[2 * D.sc] = pix_color.z * inv_s;
-    o[3 * D.sc] = pix_color.w * inv_s;
+    o[0 * D.sc] = color.x; o[1 * D.sc] = color.y; o[2 * D.sc] = color.z;
+    o[3 * D.sc] = color.w;
     o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
     o[7 * D.sc] = depth;
-    if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
 }
 
 template <int H16, int GC16, bool DIR>

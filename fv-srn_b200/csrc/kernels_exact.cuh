@@ -279,12 +279,17 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
         }
         if (in_img) {       // :105-124: depth /= alpha first, then colour /= samples
             const float ns = float(D.spp);
+            if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
+            if (D.out_format != 0) {
+                store_rgba(D, b, x, y, select_channel(D.channel_mode, D.tonemap, D.max_exposure,
+                                                      make_float4(rf::div(pix.x, ns), rf::div(pix.y, ns), rf::div(pix.z, ns), rf::div(pix.w, ns)), make_float3(0.f, 0.f, 0.f)));
+                continue;
+            }
             float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
             o[0 * D.sc] = rf::div(pix.x, ns); o[1 * D.sc] = rf::div(pix.y, ns); o[2 * D.sc] = rf::div(pix.z, ns);
             o[3 * D.sc] = rf::div(pix.w, ns);
             o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
             o[7 * D.sc] = rf::div(pix_depth, pix.w);
-            if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
         }
     }
     if (D.counters) {

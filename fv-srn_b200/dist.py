@@ -45,6 +45,54 @@ def partition_bands(width: int, height: int, world: int, rank: int, band: int = 
     return rects
 
 
+def partition_rows_by_cost(row_cost: Sequence[float], world: int, align: int = 16) -> List[Tuple[int, int]]:
+    """One contiguous band of rows per rank, (y0, h) for rank 0..world-1, with (nearly) equal summed cost: rows are cut
+    where the running cost passes k/world of the total, rounded to `align` rows (the kernels' pixel-tile height). A rank
+    may get an empty band (h = 0) when the image has fewer aligned row groups than ranks. `row_cost` is any per-row
+    estimate of the march work - scenes.estimate_row_cost sums the box-intersection lengths of a subsampled ray grid."""
+    import numpy as np
+    H = len(row_cost)
+    c = np.maximum(np.asarray(row_cost, np.float64), 0.0) + 1e-9         # empty rows still cost their ray setup
+    cum = np.concatenate([[0.0], np.cumsum(c)])
+    cuts = [0]
+    for k in range(1, world):
+        y = int(np.searchsorted(cum, cum[-1] * k / world))
+        y = int(round(y / align)) * align
+        cuts.append(min(max(y, cuts[-1]), H))
+    cuts.append(H)
+    return [(cuts[k], cuts[k + 1] - cuts[k]) for k in range(world)]
+
+
+def gather_row_bands(local: Optional[torch.Tensor], bands: Sequence[Tuple[int, int]], out: Optional[torch.Tensor], dst: int = 0,
+                     async_op: bool = False):
+    """The finished frame on `dst`: every rank owns one contiguous band of rows (partition_rows_by_cost) of ONE packed-pixel
+    frame - (1,H,W) int32 RGBA8 or (1,H,W,4) fp16 from the fused colour output (fvsrn_dvr_params.output_format). `local` is
+    this rank's band (1,h,W[,4]); `out` the full frame on `dst`, whose own band is already in place (rank `dst` renders
+    straight into its slice). The other bands are received directly into their slices of `out`: no padding, no staging
+    copy, one point-to-point transfer per rank. Returns the work handles when async_op (wait on them before reusing the
+    buffers), else waits."""
+    rank, world = world_info()
+    if world == 1:
+        return []
+    ops = []
+    if rank == dst:
+        if out.shape[0] != 1:
+            raise ValueError("gather_row_bands assembles one frame (batch 1): row bands of a batch are not contiguous")
+        for r, (y0, h) in enumerate(bands):
+            if r != dst and h > 0:
+                ops.append(dist.P2POp(dist.irecv, out[:, y0:y0 + h], r))
+    elif bands[rank][1] > 0:
+        ops.append(dist.P2POp(dist.isend, local.contiguous(), dst))
+    if not ops:
+        return []
+    works = dist.batch_isend_irecv(ops)
+    if async_op:
+        return works
+    for w in works:
+        w.wait()
+    return []
+
+
 def band_rows(rects: Sequence[Rect]) -> int:
     return sum(r[3] for r in rects)
 
@@ -87,7 +135,7 @@ def _scatter_rows(out: torch.Tensor, packed: torch.Tensor, rects: Sequence[Rect]
 
 
 def gather_views(local: torch.Tensor, num_views: int, dst: int = 0, out: Optional[torch.Tensor] = None,
-                 collective: str = "gather") -> Optional[torch.Tensor]:
+                 collective: str = "gather", async_op: bool = False):
     """local (v_rank,C,H,W) = this rank's views (partition_views order) -> (num_views,C,H,W) on `dst` (None elsewhere).
 
     When every rank owns the same number of views the pieces land directly in `out` (allocated here if None; pass a
@@ -95,7 +143,9 @@ def gather_views(local: torch.Tensor, num_views: int, dst: int = 0, out: Optiona
       "gather"      ncclSend/Recv fan-in to `dst` - least traffic, but NCCL gives each peer pair only a few channels;
       "all_gather"  every rank receives the whole batch (needs `out` on every rank) - rides NCCL's ring / NVLS
                     all-gather at full NVSwitch bandwidth.
-    Uneven view counts fall back to a padded gather."""
+    Uneven view counts fall back to a padded gather. With async_op (equal view counts only) the collective is only enqueued and
+    (result, work handle) is returned: the caller renders the next batch into another buffer meanwhile and waits on the
+    handle before it reuses `local` / reads `out`."""
     rank, world = world_info()
     if world == 1:
         return local
@@ -106,13 +156,17 @@ def gather_views(local: torch.Tensor, num_views: int, dst: int = 0, out: Optiona
         if collective == "all_gather":
             if out is None:
                 out = local.new_empty(shape)
-            dist.all_gather_into_tensor(out, local)
-            return out if rank == dst else None
+            work = dist.all_gather_into_tensor(out, local, async_op=async_op)
+            res = out if rank == dst else None
+            return (res, work) if async_op else res
         if rank == dst and out is None:
             out = local.new_empty(shape)
         pieces = list(out.chunk(world, dim=0)) if rank == dst else None     # contiguous slices of `out`
-        dist.gather(local, pieces, dst=dst)
-        return out if rank == dst else None
+        work = dist.gather(local, pieces, dst=dst, async_op=async_op)
+        res = out if rank == dst else None
+        return (res, work) if async_op else res
+    if async_op:
+        raise ValueError("async gather_views needs the same number of views on every rank")
     pad = max(counts)
     buf = local.new_zeros((pad,) + tuple(local.shape[1:]))
     buf[:local.shape[0]] = local

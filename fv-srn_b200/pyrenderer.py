@@ -519,6 +519,18 @@ class CameraOnASphere:
 
 
 # ------------------------------------------------------------------------------------------------ image evaluator
+class ChannelMode(_Enum): pass
+
+
+class IImageEvaluator:
+    """IImageEvaluator::ChannelMode (iimage_evaluator.h:19-26, pybind iimage_evaluator.cpp:335-340)."""
+    ChannelMode = ChannelMode
+    Mask, Normal, Depth, Color = (ChannelMode(n, i) for i, n in enumerate(["Mask", "Normal", "Depth", "Color"]))
+
+
+OUTPUT_FORMATS = {"raw8_f32": 0, "rgba_f32": 1, "rgba8": 2, "rgba_f16": 3}
+
+
 class ImageEvaluatorSimple:
     """renderer::ImageEvaluatorSimple::render (image_evaluator_simple.cpp:198-361) -> torch (B,8,H,W) float32."""
 
@@ -527,7 +539,13 @@ class ImageEvaluatorSimple:
         self.ray_evaluator = RayEvaluationSteppingDvr()
         self.volume: Optional[VolumeInterpolationNetwork] = None
         self.samples_per_pixel = 1
-        self.selected_channel = "ChannelColor"
+        self.selected_channel = IImageEvaluator.Color
+        # tonemapping state, image_evaluator_simple.cpp:21-25, 363-369, pybind :447-451
+        self.use_tonemapping = False
+        self.fix_max_exposure = False
+        self.fixed_max_exposure = 1.0
+        self.tonemapping_shoulder = 1.0
+        self._last_frame: Optional[torch.Tensor] = None
         # B200 additions (all optional): screen-tile sharding, per-view times, statistics
         self.tile = None                     # (x0, y0, w, h)
         self.view_times = None               # list of absolute times, one per camera batch entry
@@ -580,13 +598,77 @@ class ImageEvaluatorSimple:
             self.last_counters = torch.zeros(2, dtype=torch.int64, device="cuda")
             p.step_count_dev = self.last_step_counts.data_ptr(); p.counters_dev = self.last_counters.data_ptr()
         check(_lib.lib().fvsrn_render_dvr(net._h, C.byref(p), out.data_ptr(), _stream_ptr()))
+        self._last_frame = out
         return out
 
-    def extract_color(self, img: torch.Tensor) -> torch.Tensor:
-        """(B,8,H,W) -> (B,4,H,W), iimage_evaluator.cpp:26-135 (ChannelColor)."""
+    # -- colour extraction (IImageEvaluator::ExtractColor, iimage_evaluator.cpp:26-135)
+    @property
+    def last_max_exposure(self) -> float:
+        """max over rgb of the last rendered frame (image_evaluator_simple.cpp:358; computed on demand here instead of a
+        device synchronisation in every render call)."""
+        if self._last_frame is None:
+            return 0.0
+        return float(self._last_frame[:, 0:3].max())
+
+    def get_exposure_for_tonemapping(self) -> float:
+        e = self.fixed_max_exposure if self.fix_max_exposure else self.last_max_exposure
+        return max(0.001, e * self.tonemapping_shoulder)
+
+    def _channel_index(self):
+        c = self.selected_channel
+        if isinstance(c, str):      # "ChannelColor" etc. (json names)
+            c = {"ChannelMask": 0, "ChannelNormal": 1, "ChannelDepth": 2, "ChannelColor": 3}[c]
+        return c.index if isinstance(c, _Enum) else int(c)
+
+    @staticmethod
+    def Extract_color(img: torch.Tensor, use_tonemapping: bool, max_exposure: float, channel, output_format="rgba_f32") -> torch.Tensor:
+        """(B,8,H,W) -> (B,4,H,W) fp32 (or packed RGBA8 (B,H,W) int32 / (B,H,W,4) fp16), ImageEvaluatorSimple::extractColorTorch."""
         if img.dim() != 4 or img.shape[1] != 8:
             raise RuntimeError("expected a (B,8,H,W) tensor")
-        img = img.contiguous()
-        out = torch.empty((img.shape[0], 4, img.shape[2], img.shape[3]), dtype=torch.float32, device=img.device)
-        check(_lib.lib().fvsrn_extract_color(img.data_ptr(), out.data_ptr(), img.shape[0], img.shape[2], img.shape[3], _stream_ptr()))
+        if not img.is_cuda:
+            raise RuntimeError("raw input must reside on the GPU")
+        img = img.to(torch.float32).contiguous()
+        B, _, H, W = img.shape
+        fmt = OUTPUT_FORMATS[output_format]
+        if fmt == 1: out = torch.empty((B, 4, H, W), dtype=torch.float32, device=img.device)
+        elif fmt == 2: out = torch.empty((B, H, W), dtype=torch.int32, device=img.device)
+        elif fmt == 3: out = torch.empty((B, H, W, 4), dtype=torch.float16, device=img.device)
+        else: raise RuntimeError("Extract_color writes rgba_f32, rgba8 or rgba_f16")
+        ch = channel.index if isinstance(channel, _Enum) else int(channel)
+        check(_lib.lib().fvsrn_extract_color_ex(img.data_ptr(), out.data_ptr(), B, H, W, ch, int(bool(use_tonemapping)),
+                                                float(max_exposure), fmt, _stream_ptr()))
+        return out
+
+    def extract_color(self, img: torch.Tensor, output_format="rgba_f32") -> torch.Tensor:
+        """Extracts the selected channel and performs tonemapping (pybind image_evaluator_simple.cpp:463-473)."""
+        return ImageEvaluatorSimple.Extract_color(img, self.use_tonemapping, self.get_exposure_for_tonemapping() if self.use_tonemapping else 1.0,
+                                                  self._channel_index(), output_format)
+
+    def render_color(self, width: int, height: int, output_format="rgba_f32", out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """B200 addition: render + extract_color in ONE kernel - the selected channel (colour / mask / normal; tonemapping
+        with fix_max_exposure) leaves the DVR kernel as (B,4,H,W) fp32, packed RGBA8 (B,H,W) int32 or (B,H,W,4) fp16 instead of
+        the 32 B/pixel raw tensor."""
+        fmt = OUTPUT_FORMATS[output_format]
+        if fmt == 0:
+            return self.render(width, height, out)
+        if self.use_tonemapping and not self.fix_max_exposure:
+            raise RuntimeError("fused tonemapping needs fix_max_exposure (the frame-wide maximum is not known inside the frame)")
+        vol = self._volume(); net = vol._require(); net._ensure_prepared()
+        cam = self.camera.get_parameters()
+        is_rgbo = net._info().channels_out == 4
+        tf = None if is_rgbo else self.ray_evaluator.tf._tensor()
+        B = cam.shape[0]
+        shape, dtype = {1: ((B, 4, height, width), torch.float32), 2: ((B, height, width), torch.int32), 3: ((B, height, width, 4), torch.float16)}[fmt]
+        if out is None or tuple(out.shape) != shape or out.dtype != dtype or not out.is_cuda:
+            out = (torch.empty if self.tile is None else torch.zeros)(shape, dtype=dtype, device="cuda")
+        if fmt == 1: strides = out.stride()
+        else: strides = (out.stride(0) // (4 if fmt == 3 else 1), 0, out.stride(1) // (4 if fmt == 3 else 1), 1)
+        p = self._params(width, height, cam, tf, strides)
+        p.output_format, p.channel_mode = fmt, self._channel_index()
+        p.tonemap, p.max_exposure = int(bool(self.use_tonemapping)), float(self.get_exposure_for_tonemapping() if self.use_tonemapping else 1.0)
+        keep = []
+        if self.view_times is not None:
+            vt = (C.c_float * B)(*[float(t) for t in self.view_times]); keep.append(vt)
+            p.view_times_host = C.cast(vt, C.c_void_p)
+        check(_lib.lib().fvsrn_render_dvr(net._h, C.byref(p), out.data_ptr(), _stream_ptr()))
         return out

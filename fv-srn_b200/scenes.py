@@ -46,6 +46,31 @@ def camera_sweep(n_views: int, **kw) -> np.ndarray:
     return np.concatenate([camera_reference_frame(yaw=yaw0 + a, **base) for a in np.linspace(0, 2 * np.pi, n_views, endpoint=False)])
 
 
+def estimate_row_cost(camera: np.ndarray, fov_y: float, width: int, height: int, box_min=(-0.5, -0.5, -0.5),
+                      box_size=(1.0, 1.0, 1.0), sub: int = 16) -> np.ndarray:
+    """Per-row march cost of one view for screen-band sharding (dist.partition_rows_by_cost): the box-intersection length
+    tmax - max(tmin, 0) of every `sub`-th ray (CameraReferenceFrame::eval + intersectionRayAABB, renderer_camera.cuh:41-51,
+    renderer_utils.cuh:91-105, in NumPy), summed over x and spread over the rows it stands for. -> (height,) float64."""
+    cam = np.asarray(camera, np.float64).reshape(-1, 3, 3)[0]
+    eye, right, up = cam
+    front = np.cross(up, right)
+    tan_y = math.tan(fov_y / 2); tan_x = tan_y * (width / height)
+    xs = np.arange(sub // 2, width, sub); ys = np.arange(sub // 2, height, sub)
+    nx = 2 * (xs + 0.5) / width - 1; ny = 2 * (ys + 0.5) / height - 1
+    d = front[None, None] + (nx * tan_x)[None, :, None] * right[None, None] + (ny * tan_y)[:, None, None] * up[None, None]
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        inv = 1.0 / d
+        t0 = (np.asarray(box_min) - eye) * inv; t1 = (np.asarray(box_min) + np.asarray(box_size) - eye) * inv
+    tmin = np.maximum(np.minimum(t0, t1).max(-1), 0.0); tmax = np.maximum(t0, t1).min(-1)
+    length = np.maximum(tmax - tmin, 0.0).sum(1)                  # per sampled row
+    cost = np.zeros(height)
+    for i, y in enumerate(ys):
+        y0 = y - sub // 2
+        cost[y0:min(y0 + sub, height)] = length[i] / sub
+    return cost
+
+
 # ------------------------------------------------------------------------------------------------ transfer function
 PLUME_COLOR_POINTS = [
     (0.0033444815780967474, (9.999999974752427e-07, 9.999899930335232e-07, 9.999899930335232e-07)),

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FVSRN_ABI_VERSION 1
+#define FVSRN_ABI_VERSION 2
 
 typedef struct fvsrn_network fvsrn_network; /* opaque: renderer::SceneNetwork + its GPU resources */
 
@@ -53,6 +53,16 @@ enum fvsrn_tf_kind {
     FVSRN_TF_TEXTURE = 1,   /* renderer/renderer_tf_texture.cuh:41-60 (tensor variant), (B,R,4) rgba */
     FVSRN_TF_IDENTITY = 2   /* renderer/renderer_tf_identity.cuh: rgb = density*scale_c, absorption = density*scale_a */
 };
+
+/* IImageEvaluator::ChannelMode, renderer/iimage_evaluator.h:19-26 */
+enum fvsrn_channel_mode { FVSRN_CHANNEL_MASK = 0, FVSRN_CHANNEL_NORMAL = 1, FVSRN_CHANNEL_DEPTH = 2, FVSRN_CHANNEL_COLOR = 3 };
+/* what a DVR launch (or fvsrn_extract_color_ex) writes:
+ *   RAW8_F32  the reference's (B,8,H,W) fp32 tensor: rgb, alpha, normal xyz, depth (renderer_image_evaluator_simple.cuh:106-124)
+ *   RGBA_F32  (B,4,H,W) fp32: the selected channel, what extract_color returns (iimage_evaluator.cpp:26-135)
+ *   RGBA8     (B,H,W) uint32 = rgbaToInt (renderer_utils.cuh:48-57): the reference's display format (SelectOutputChannelKernel /
+ *             TonemappingKernel writing the GL texture, iimage_evaluator_cuda.cu:21-38, 168-186)
+ *   RGBA_F16  (B,H,W) 4 x fp16 (B200 addition: half the bytes of RGBA_F32 for the multi-GPU gather) */
+enum fvsrn_output_format { FVSRN_OUTPUT_RAW8_F32 = 0, FVSRN_OUTPUT_RGBA_F32 = 1, FVSRN_OUTPUT_RGBA8 = 2, FVSRN_OUTPUT_RGBA_F16 = 3 };
 
 /* ------------------------------------------------------------------------------------------
  * Network lifetime and .volnet I/O
@@ -180,6 +190,16 @@ typedef struct fvsrn_dvr_params {
     /* optional debug/statistics outputs (may be NULL) */
     int32_t* step_count_dev;        /* (B,H,W) int32 contiguous: valid steps of each ray (last sample of the pixel) */
     unsigned long long* counters_dev; /* [0] += valid samples, [1] += executed (lock-step) samples */
+    /* Fused colour extraction: what every caller runs right after render (inference.py:621) happens in the
+     * pixel write instead of a second pass over a 32 B/pixel tensor. All zero = the reference's raw tensor.
+     *   output_format != RAW8_F32: `out` is the selected channel in that format; the out_stride_* are in elements of it
+     *   (fp32 values for RGBA_F32 with out_stride_c between the 4 channels; uint32 / half4 pixels for RGBA8 / RGBA_F16,
+     *   out_stride_c unused). channel_mode: COLOR (with optional tonemapping at a FIXED exposure, as with the reference's
+     *   fix_max_exposure), MASK or NORMAL; DEPTH needs the frame's min/max depth first -> fvsrn_extract_color_ex. */
+    int   output_format;            /* fvsrn_output_format */
+    int   channel_mode;             /* fvsrn_channel_mode; 0-initialised params with output_format 0 ignore it */
+    int   tonemap;                  /* ImageEvaluatorSimple::useTonemapping_ */
+    float max_exposure;             /* ImageEvaluatorSimple::getExposureForTonemapping(), image_evaluator_simple.cpp:363-369 */
 } fvsrn_dvr_params;
 
 int  fvsrn_render_dvr(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_dev, void* stream);
@@ -193,6 +213,13 @@ int  fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float*
  * SelectOutputChannelKernel, renderer/iimage_evaluator_cuda.cu:21-80 (ChannelColor only). SURVEY f1.
  * ------------------------------------------------------------------------------------------ */
 int  fvsrn_extract_color(const float* img_dev, float* out_dev, int batch, int height, int width, void* stream);
+/* The full IImageEvaluator::ExtractColor (iimage_evaluator.cpp:26-135) on a contiguous (B,8,H,W) fp32 tensor: channel
+ * selection (mask / normal / depth / colour), optional tonemapping of the colour channel (TonemappingKernel2,
+ * iimage_evaluator_cuda.cu:217-260), output as (B,4,H,W) fp32, packed RGBA8 or half4 (fvsrn_output_format, not RAW8).
+ * ChannelDepth normalises by the frame's min / max depth like the reference (a torch min/max there: NaN depth of empty
+ * pixels propagates). */
+int  fvsrn_extract_color_ex(const float* img_dev, void* out_dev, int batch, int height, int width,
+                            int channel_mode, int tonemap, float max_exposure, int output_format, void* stream);
 
 /* Launch diagnostics (stand-in for compute_max_warps / KernelLoader occupancy query) */
 typedef struct fvsrn_query_info {

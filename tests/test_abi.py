@@ -25,14 +25,25 @@ def test_header_and_binding_agree():
 def test_library_exports_every_declared_symbol(built_lib):
     for s in _declared_symbols():
         assert hasattr(built_lib, s), s
-    assert built_lib.fvsrn_abi_version() == 1
+    assert built_lib.fvsrn_abi_version() == 2
 
 
 def test_struct_sizes_match_header(built_lib):
-    # natural C layout of the header structs on LP64
+    # natural C layout of the header structs on LP64 ...
     assert C.sizeof(_lib.NetworkInfo) == 20 * 4
-    assert C.sizeof(_lib.DvrParams) % 8 == 0 and C.sizeof(_lib.DvrParams) == 152
+    assert C.sizeof(_lib.DvrParams) % 8 == 0 and C.sizeof(_lib.DvrParams) == 168
     assert C.sizeof(_lib.QueryInfo) == 48
+    # ... and as the C compiler lays out include/fvsrn_b200.h
+    import subprocess, tempfile
+    with tempfile.TemporaryDirectory() as d:
+        src = os.path.join(d, "s.c")
+        open(src, "w").write('#include <stdio.h>\n#include <stddef.h>\n#include "fvsrn_b200.h"\nint main(void){printf("%zu %zu %zu %zu %zu\\n", '
+                             'sizeof(fvsrn_network_info), sizeof(fvsrn_dvr_params), sizeof(fvsrn_query_info), '
+                             'offsetof(fvsrn_dvr_params, output_format), offsetof(fvsrn_dvr_params, out_stride_b));return 0;}\n')
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), src, "-o", os.path.join(d, "s")])
+        sizes = [int(v) for v in subprocess.check_output([os.path.join(d, "s")]).split()]
+    assert sizes == [C.sizeof(_lib.NetworkInfo), C.sizeof(_lib.DvrParams), C.sizeof(_lib.QueryInfo),
+                     _lib.DvrParams.output_format.offset, _lib.DvrParams.out_stride_b.offset]
 
 
 def _load(built_lib, data):

@@ -61,6 +61,34 @@ def _worker(rank, world, port, width, height, band, views, q):
                     ok_views = ok_views and got is buf and bool(torch.equal(buf, want))
                 else:
                     ok_views = ok_views and got is None
+        # cost-balanced contiguous row bands of ONE packed-pixel frame (RGBA8 / half4), received in place on rank 0, twice
+        # with double-buffered asynchronous transfers (the overlap bench.py --sharding tiles uses)
+        cost = np.linspace(0.0, 3.0, height) ** 2
+        bands = fdist.partition_rows_by_cost(cost, world, align=8)
+        for dtype, tail in ((torch.int32, ()), (torch.float16, (4,))):
+            frames = [(torch.arange(height * width * (4 if tail else 1)).reshape((1, height, width) + tail) % 251 + k).to(dtype) for k in range(3)]
+            bufs = [torch.full_like(frames[0], -1) for _ in range(2)] if rank == 0 else [None, None]
+            pending = [None, None]
+            for k, f in enumerate(frames):
+                slot = k % 2
+                if pending[slot] is not None:
+                    for w in pending[slot][0]: w.wait()
+                    if rank == 0: ok_frame = ok_frame and bool(torch.equal(bufs[slot], pending[slot][1]))
+                y0, h = bands[rank]
+                local = f[:, y0:y0 + h].clone()
+                if rank == 0: bufs[slot][:, y0:y0 + h] = local
+                pending[slot] = (fdist.gather_row_bands(local, bands, bufs[slot], async_op=True), f)
+            for slot in range(2):
+                if pending[slot] is not None:
+                    for w in pending[slot][0]: w.wait()
+                    if rank == 0: ok_frame = ok_frame and bool(torch.equal(bufs[slot], pending[slot][1]))
+        if views % world == 0:      # asynchronous view gather: (result, work handle)
+            per = views // world
+            mine = torch.cat([render_view(i) for i in range(rank * per, (rank + 1) * per)], dim=0)
+            buf = torch.full((views,) + tuple(mine.shape[1:]), -1.0)
+            got, work = fdist.gather_views(mine, views, out=buf, async_op=True)
+            work.wait()
+            ok_views = ok_views and ((got is buf and bool(torch.equal(buf, want))) if rank == 0 else got is None)
         q.put((rank, ok_frame, ok_views))
     finally:
         dist.destroy_process_group()
@@ -94,6 +122,15 @@ def test_partitions_cover_everything_exactly_once():
                     assert x0 == 0 and ww == w and y0 % 8 == 0
                     cover[y0:y0 + hh, x0:x0 + ww] += 1
             assert (cover == 1).all()
+        for h in (8, 90, 2048):
+            cost = np.abs(np.sin(np.arange(h) / 37.0)) * (np.arange(h) > h // 5)
+            bands = fdist.partition_rows_by_cost(cost, world, align=8)
+            assert len(bands) == world and bands[0][0] == 0 and sum(b[1] for b in bands) == h
+            assert all(bands[i][0] + bands[i][1] == bands[i + 1][0] for i in range(world - 1))
+            assert all(y0 % 8 == 0 for y0, _ in bands)
+            if h == 2048 and world > 1:     # equal cost within the rounding to 8 rows
+                shares = [cost[y0:y0 + hh].sum() / cost.sum() for y0, hh in bands]
+                assert max(shares) - min(shares) < 0.02
     with pytest.raises(ValueError):
         fdist.partition_bands(64, 64, 2, 0, band=12)
     with pytest.raises(ValueError):
