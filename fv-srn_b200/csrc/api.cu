@@ -38,7 +38,8 @@ struct DeviceGuard {
 };
 
 struct DeviceGrid {
-    __half* data = nullptr; int C = 0, Z = 0, Y = 0, X = 0;   // channel-last fp16 (mma.sync path)
+    void* data = nullptr; int C = 0, Z = 0, Y = 0, X = 0;     // channel-last fp16 (or bytes, for byte-encoded grids): mma.sync path
+    int encoding = 0; std::vector<float> offset, scale;       // LatentGrid::Encoding and its per-channel constants
     std::vector<cudaArray_t> arrays;                          // C/4 fp16 RGBA 3-D arrays + texture objects (tcgen05 path)
     std::vector<cudaTextureObject_t> tex;
     std::vector<cudaArray_t> arrays32;                        // the same (fp16-rounded) texels as fp32 RGBA textures, created on
@@ -83,7 +84,7 @@ void release_gpu(fvsrn_network* h) {
             if (g.data) cudaFree(g.data);
             for (auto t : g.tex) cudaDestroyTextureObject(t);
             for (auto a : g.arrays) cudaFreeArray(a);
-            for (auto t : g.tex32) cudaDestroyTextureObject(t);
+            if (!g.encoding) for (auto t : g.tex32) cudaDestroyTextureObject(t);
             for (auto a : g.arrays32) cudaFreeArray(a);
         }
     if (h->d_tile_counter) cudaFree(h->d_tile_counter);
@@ -245,6 +246,7 @@ launch_fn pick_launcher(int H16) {
 // library sees
 void ensure_tex32(DeviceGrid& d, const LatentGrid& g) {
     if (!d.tex32.empty()) return;
+    if (g.encoding != GRID_FLOAT) { d.tex32 = d.tex; return; }      // byte grids: the unorm8 textures are the reference's format already
     std::vector<float> sub(size_t(g.Z) * g.Y * g.X * 4);
     for (int q = 0; q < g.C / 4; ++q) {
         for (int z = 0; z < g.Z; ++z) for (int y = 0; y < g.Y; ++y) for (int x = 0; x < g.X; ++x)
@@ -265,6 +267,25 @@ void ensure_tex32(DeviceGrid& d, const LatentGrid& g) {
         cudaTextureObject_t t = 0;
         CUDA_OK(cudaCreateTextureObject(&t, &rd, &td, nullptr));
         d.tex32.push_back(t);
+    }
+}
+
+// channel group i (16 channels) of a channel-last device grid: fp16 halves or bytes
+const __half* grid_ptr(const DeviceGrid& d, int i) {
+    return d.encoding ? reinterpret_cast<const __half*>(static_cast<const uint8_t*>(d.data) + 16 * i)
+                      : static_cast<const __half*>(d.data) + 16 * i;
+}
+// EncodeGridValue constants of latent-channel group g. The reference decodes keyframe B with A's offset / scale
+// (renderer_volume_tensorcores.cuh:586-587, EncodeGridValue<.., false> on both) - a slip that only matters when the
+// keyframes were encoded with different ranges; B's own constants are used here (the reference-exact kernel, which is
+// compared bit for bit with the reference kernel, follows the reference and ignores enc_*_b).
+void fill_encoding(NetParams& P, int g, const DeviceGrid& A, const DeviceGrid& B, int i) {
+    P.grid_encoding = A.encoding;
+    if (!A.encoding) return;
+    if (A.encoding != B.encoding) throw std::runtime_error("all latent grids must share one encoding");
+    for (int c = 0; c < 16; ++c) {
+        P.enc_offset_a[16 * g + c] = A.offset[16 * i + c]; P.enc_scale_a[16 * g + c] = A.scale[16 * i + c];
+        P.enc_offset_b[16 * g + c] = B.offset[16 * i + c]; P.enc_scale_b[16 * g + c] = B.scale[16 * i + c];
     }
 }
 
@@ -294,7 +315,8 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
             const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && !A.tex32.empty() && !B.tex32.empty();
             for (int i = 0; i < A.C / 16; ++i, ++g) {
-                P.groups[g] = GridGroup{A.data + 16 * i, B.data + 16 * i, frac, A.C * 2 / 16};
+                P.groups[g] = GridGroup{grid_ptr(A, i), grid_ptr(B, i), frac, A.encoding ? A.C / 16 : A.C * 2 / 16};
+                fill_encoding(P, g, A, B, i);
                 for (int q = 0; q < 4; ++q) {
                     P.tex_a[4 * g + q] = exact ? A.tex32[4 * i + q] : A.tex[4 * i + q];
                     P.tex_b[4 * g + q] = exact ? B.tex32[4 * i + q] : B.tex[4 * i + q];
@@ -306,7 +328,8 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
             const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && !A.tex32.empty();
             for (int i = 0; i < A.C / 16; ++i, ++g) {
-                P.groups[g] = GridGroup{A.data + 16 * i, A.data + 16 * i, 0.f, A.C * 2 / 16};
+                P.groups[g] = GridGroup{grid_ptr(A, i), grid_ptr(A, i), 0.f, A.encoding ? A.C / 16 : A.C * 2 / 16};
+                fill_encoding(P, g, A, A, i);
                 for (int q = 0; q < 4; ++q) P.tex_a[4 * g + q] = P.tex_b[4 * g + q] = exact ? A.tex32[4 * i + q] : A.tex[4 * i + q];
             }
         }
@@ -560,33 +583,54 @@ int fvsrn_network_prepare(fvsrn_network* net, int device, void* stream) {
     CUDA_OK(cudaMalloc(&net->d_tc_blob, tc_blob.size()));
     CUDA_OK(cudaMemcpyAsync(net->d_tc_blob, tc_blob.data(), tc_blob.size(), cudaMemcpyHostToDevice, s));
     CUDA_OK(cudaStreamSynchronize(s)); // blobs are locals
+    auto make_texture = [&](DeviceGrid& d, const void* host, const cudaChannelFormatDesc& fd, size_t texel_bytes, bool normalized_float, int X, int Y, int Z,
+                            std::vector<cudaArray_t>& arrays, std::vector<cudaTextureObject_t>& texs) {
+        cudaArray_t arr = nullptr;
+        CUDA_OK(cudaMalloc3DArray(&arr, &fd, make_cudaExtent(X, Y, Z)));
+        arrays.push_back(arr);
+        cudaMemcpy3DParms cp = {};
+        cp.srcPtr = make_cudaPitchedPtr(const_cast<void*>(host), size_t(X) * texel_bytes, X, Y);
+        cp.dstArray = arr; cp.extent = make_cudaExtent(X, Y, Z); cp.kind = cudaMemcpyHostToDevice;
+        CUDA_OK(cudaMemcpy3D(&cp));
+        cudaResourceDesc rd = {}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
+        cudaTextureDesc td = {};
+        td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
+        td.filterMode = cudaFilterModeLinear; td.readMode = normalized_float ? cudaReadModeNormalizedFloat : cudaReadModeElementType; td.normalizedCoords = 1;
+        cudaTextureObject_t t = 0;
+        CUDA_OK(cudaCreateTextureObject(&t, &rd, &td, nullptr));
+        texs.push_back(t);
+    };
     auto upload = [&](const LatentGrid& g) {
-        DeviceGrid d; d.C = g.C; d.Z = g.Z; d.Y = g.Y; d.X = g.X;
+        DeviceGrid d; d.C = g.C; d.Z = g.Z; d.Y = g.Y; d.X = g.X; d.encoding = g.encoding;
+        const size_t voxels = size_t(g.Z) * g.Y * g.X;
+        if (g.encoding != GRID_FLOAT) {
+            // Byte-encoded grid: it stays 8-bit on the device. C/4 unorm8 RGBA textures read as normalised floats - the
+            // reference's own layout (LatentGrid::GPUArray with isFloat = false, :470-504) - and a channel-last byte copy
+            // for the mma.sync kernels; decoded after the filter (srn_core.cuh decode_grid_value).
+            std::vector<uint8_t> cl(voxels * g.C);
+            for (int z = 0; z < g.Z; ++z) for (int y = 0; y < g.Y; ++y) for (int x = 0; x < g.X; ++x)
+                for (int c = 0; c < g.C; ++c)
+                    cl[((size_t(z) * g.Y + y) * g.X + x) * g.C + c] = uint8_t(g.data[g.idx(c / 4, z, y, x, c % 4)]);
+            CUDA_OK(cudaMalloc(&d.data, cl.size()));
+            CUDA_OK(cudaMemcpyAsync(d.data, cl.data(), cl.size(), cudaMemcpyHostToDevice, s));
+            CUDA_OK(cudaStreamSynchronize(s));
+            const cudaChannelFormatDesc fd = cudaCreateChannelDesc(8, 8, 8, 8, cudaChannelFormatKindUnsigned);
+            for (int q = 0; q < g.C / 4; ++q)       // storage order of the .volnet grid is already (C/4, Z, Y, X, 4)
+                make_texture(d, g.data.data() + size_t(q) * voxels * 4, fd, 4, true, g.X, g.Y, g.Z, d.arrays, d.tex);
+            d.offset = g.offset_or_mean; d.scale = g.scale_or_std;
+            return d;
+        }
         const std::vector<uint16_t> cl = grid_channel_last(g);
         CUDA_OK(cudaMalloc(&d.data, cl.size() * 2));
         CUDA_OK(cudaMemcpyAsync(d.data, cl.data(), cl.size() * 2, cudaMemcpyHostToDevice, s));
         CUDA_OK(cudaStreamSynchronize(s)); // cl is a temporary
         // the same voxels as C/4 half4 textures: clamp addressing, linear filter, normalised coordinates
         // (reference LatentGrid::GPUArray, volume_interpolation_network.cpp:470-504, with fp16 instead of fp32 texels)
-        std::vector<uint16_t> sub(size_t(g.Z) * g.Y * g.X * 4);
+        std::vector<uint16_t> sub(voxels * 4);
         for (int q = 0; q < g.C / 4; ++q) {
-            for (size_t v = 0; v < size_t(g.Z) * g.Y * g.X; ++v)
+            for (size_t v = 0; v < voxels; ++v)
                 for (int c = 0; c < 4; ++c) sub[v * 4 + c] = cl[v * g.C + q * 4 + c];
-            cudaChannelFormatDesc fd = cudaCreateChannelDescHalf4();
-            cudaArray_t arr = nullptr;
-            CUDA_OK(cudaMalloc3DArray(&arr, &fd, make_cudaExtent(g.X, g.Y, g.Z)));
-            d.arrays.push_back(arr);
-            cudaMemcpy3DParms cp = {};
-            cp.srcPtr = make_cudaPitchedPtr(sub.data(), size_t(g.X) * 8, g.X, g.Y);
-            cp.dstArray = arr; cp.extent = make_cudaExtent(g.X, g.Y, g.Z); cp.kind = cudaMemcpyHostToDevice;
-            CUDA_OK(cudaMemcpy3D(&cp));
-            cudaResourceDesc rd = {}; rd.resType = cudaResourceTypeArray; rd.res.array.array = arr;
-            cudaTextureDesc td = {};
-            td.addressMode[0] = td.addressMode[1] = td.addressMode[2] = cudaAddressModeClamp;
-            td.filterMode = cudaFilterModeLinear; td.readMode = cudaReadModeElementType; td.normalizedCoords = 1;
-            cudaTextureObject_t t = 0;
-            CUDA_OK(cudaCreateTextureObject(&t, &rd, &td, nullptr));
-            d.tex.push_back(t);
+            make_texture(d, sub.data(), cudaCreateChannelDescHalf4(), 8, false, g.X, g.Y, g.Z, d.arrays, d.tex);
         }
         return d;
     };

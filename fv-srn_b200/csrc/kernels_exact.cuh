@@ -84,8 +84,21 @@ struct SrnExact {
         }
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-            const float4 a = tex3D<float4>(P.tex_a[q], px, py, pz);
-            const float4 b = tex3D<float4>(P.tex_b[q], px, py, pz);
+            float4 a = tex3D<float4>(P.tex_a[q], px, py, pz);
+            float4 b = tex3D<float4>(P.tex_b[q], px, py, pz);
+            if (P.grid_encoding != 0) {     // EncodeGridValue<Encoding, false> on BOTH keyframes: the reference decodes B with A's constants (:586-587)
+                float* pa = &a.x; float* pb = &b.x;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    float ta = pa[k], tb = pb[k];
+                    if (P.grid_encoding == 2) {
+                        ta = rf::mul(1.4142135623730951f, erfinvf(rf::mul(rf::add(ta, -0.5f), 2.0f - 1e-4f)));
+                        tb = rf::mul(1.4142135623730951f, erfinvf(rf::mul(rf::add(tb, -0.5f), 2.0f - 1e-4f)));
+                    }
+                    pa[k] = rf::fma(ta, P.enc_scale_a[4 * q + k], P.enc_offset_a[4 * q + k]);
+                    pb[k] = rf::fma(tb, P.enc_scale_a[4 * q + k], P.enc_offset_a[4 * q + k]);
+                }
+            }
             const float x = rf::fma(rf::sub(b.x, a.x), tfrac, a.x), y = rf::fma(rf::sub(b.y, a.y), tfrac, a.y);
             const float z = rf::fma(rf::sub(b.z, a.z), tfrac, a.z), w = rf::fma(rf::sub(b.w, a.w), tfrac, a.w);
             row[H / 2 + 2 * q] = h2u(__halves2half2(__float2half(x), __float2half(y)));

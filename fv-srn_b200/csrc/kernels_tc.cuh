@@ -166,10 +166,27 @@ struct SrnTc {
                 float4 v[4];
 #pragma unroll
                 for (int q = 0; q < 4; ++q) v[q] = tex3D<float4>(P.tex_a[4 * g + q], px, py, pz);
+                if (SPEC == 0 && P.grid_encoding != 0) {        // 8-bit grid (unorm8 textures): decode the filtered texel
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int ch = 16 * g + 4 * q;
+                        v[q].x = decode_grid_value(P.grid_encoding, v[q].x, P.enc_offset_a[ch + 0], P.enc_scale_a[ch + 0]);
+                        v[q].y = decode_grid_value(P.grid_encoding, v[q].y, P.enc_offset_a[ch + 1], P.enc_scale_a[ch + 1]);
+                        v[q].z = decode_grid_value(P.grid_encoding, v[q].z, P.enc_offset_a[ch + 2], P.enc_scale_a[ch + 2]);
+                        v[q].w = decode_grid_value(P.grid_encoding, v[q].w, P.enc_offset_a[ch + 3], P.enc_scale_a[ch + 3]);
+                    }
+                }
                 if (SPEC == 2 || frac > 0.f)
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const float4 w = tex3D<float4>(P.tex_b[4 * g + q], px, py, pz);
+                    float4 w = tex3D<float4>(P.tex_b[4 * g + q], px, py, pz);
+                    if (SPEC == 0 && P.grid_encoding != 0) {
+                        const int ch = 16 * g + 4 * q;
+                        w.x = decode_grid_value(P.grid_encoding, w.x, P.enc_offset_b[ch + 0], P.enc_scale_b[ch + 0]);
+                        w.y = decode_grid_value(P.grid_encoding, w.y, P.enc_offset_b[ch + 1], P.enc_scale_b[ch + 1]);
+                        w.z = decode_grid_value(P.grid_encoding, w.z, P.enc_offset_b[ch + 2], P.enc_scale_b[ch + 2]);
+                        w.w = decode_grid_value(P.grid_encoding, w.w, P.enc_offset_b[ch + 3], P.enc_scale_b[ch + 3]);
+                    }
                     v[q].x = fmaf(frac, w.x - v[q].x, v[q].x); v[q].y = fmaf(frac, w.y - v[q].y, v[q].y);
                     v[q].z = fmaf(frac, w.z - v[q].z, v[q].z); v[q].w = fmaf(frac, w.w - v[q].w, v[q].w);
                 }

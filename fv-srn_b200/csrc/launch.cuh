@@ -217,7 +217,7 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     if constexpr ((H16 == 2 || H16 == 4) && GC16 == 1 && !DIR) {
         if (kind == KIND_DVR_TC && kp != nullptr) {
             const DvrParams& Dq = *static_cast<const DvrParams*>(kp);
-            const bool fast = P.output_mode == D_OUT_DENSITY_DIRECT && !P.has_time && Dq.tf_kind == 0 && Dq.tf_batch == 1 && Dq.early_out && Dq.blend_mode == 1 && Dq.spp == 1;
+            const bool fast = P.output_mode == D_OUT_DENSITY_DIRECT && !P.has_time && Dq.tf_kind == 0 && Dq.tf_batch == 1 && Dq.early_out && Dq.blend_mode == 1 && Dq.spp == 1 && P.grid_encoding == 0;
             if (fast) {
                 const void* s1[6] = {(const void*)dvr_tc_kernel<H16, GC16, DIR, 0, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 1, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 4, 1>,
                                      (const void*)dvr_tc_kernel<H16, GC16, DIR, 2, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 3, 1>, (const void*)dvr_tc_kernel<H16, GC16, DIR, 6, 1>};

@@ -54,7 +54,20 @@ struct NetParams {
     int fourier_nerf;     // Fourier matrix has the NeRF layout (see SrnTc::build_row)
     uint32_t wlast2[64];  // density networks: last-layer weights as fp16x2 pairs (k, k+1) and its bias, for the in-thread dot product
     float blast;
+    // byte-encoded latent grids (LatentGrid::Encoding, volume_interpolation_network.cpp:336-431): the grids stay 8-bit on the
+    // device - unorm8 RGBA textures (tcgen05 / reference-exact kernels) or channel-last bytes (mma.sync kernels, groups[].a/b
+    // then point to uint8) - and are decoded AFTER the trilinear filter as the reference does (EncodeGridValue,
+    // renderer_volume_tensorcores.cuh:341-383): value = offset + scale * x (linear) or offset + scale * sqrt2 * erfinv((2 - 1e-4)(x - 0.5))
+    int grid_encoding;    // 0 float (fp16 on the device), 1 byte-linear, 2 byte-gaussian
+    float enc_offset_a[32], enc_scale_a[32];   // per latent channel, keyframe A
+    float enc_offset_b[32], enc_scale_b[32];   // keyframe B (the reference decodes B with A's constants, :586-587; see make_net_params)
 };
+
+// filtered byte-grid value -> latent value (EncodeGridValue). fast = reference-exact mode: the reference's fast-math operation order.
+__device__ __forceinline__ float decode_grid_value(int encoding, float v, float offset, float scale) {
+    if (encoding == 2) v = 1.4142135623730951f * erfinvf((2.0f - 1e-4f) * (v - 0.5f));
+    return fmaf(v, scale, offset);
+}
 
 // ------------------------------------------------------------------ small PTX wrappers
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -244,6 +257,39 @@ struct Srn {
 #pragma unroll
             for (int g = 0; g < GC16; ++g) {
                 const GridGroup G = P.groups[g];
+                if (P.grid_encoding != 0) {     // 8-bit grid: blend the normalised texels in fp32, decode afterwards, then the temporal lerp
+                    float va[16], vb[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) va[j] = vb[j] = 0.f;
+                    const int nsrc8 = (G.frac > 0.f) ? 2 : 1;
+#pragma unroll 1
+                    for (int s8 = 0; s8 < nsrc8; ++s8) {
+                        const uint4* base8 = reinterpret_cast<const uint4*>(s8 == 0 ? G.a : G.b);
+                        float (&dst)[16] = s8 == 0 ? va : vb;
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const int zi = zs[c >> 2], yi = ys[(c >> 1) & 1], xi = xs[c & 1];
+                            const uint4 t = __ldg(base8 + (size_t)((zi * P.gy + yi) * P.gx + xi) * G.voxel_stride);
+                            const float wc = __fmul_rn(__fmul_rn(wz[c >> 2], wy[(c >> 1) & 1]), wx[c & 1]);
+                            const uint32_t u[4] = {t.x, t.y, t.z, t.w};
+#pragma unroll
+                            for (int j = 0; j < 16; ++j)
+                                dst[j] = fmaf(wc, float((u[j >> 2] >> (8 * (j & 3))) & 0xffu) * (1.0f / 255.0f), dst[j]);
+                        }
+                    }
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) {
+                        float v = decode_grid_value(P.grid_encoding, va[j], P.enc_offset_a[16 * g + j], P.enc_scale_a[16 * g + j]);
+                        if (nsrc8 == 2) {
+                            const float w = decode_grid_value(P.grid_encoding, vb[j], P.enc_offset_b[16 * g + j], P.enc_scale_b[16 * g + j]);
+                            v = fmaf(G.frac, w - v, v);
+                        }
+                        va[j] = v;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) row[H / 2 + g * 8 + j] = h2u(__floats2half2_rn(va[2 * j], va[2 * j + 1]));
+                    continue;
+                }
                 __half2 acc[8];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) acc[j] = __float2half2_rn(0.f);

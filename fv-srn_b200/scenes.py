@@ -194,6 +194,31 @@ def make_network(hidden: int = 32, num_layers: int = 4, grid_res: int = 32, grid
     return net
 
 
+def encode_grids(net: volnet.SceneNetwork, encoding: int) -> volnet.SceneNetwork:
+    """The same network with its latent grids byte-encoded (LatentGrid::Encoding 1 = linear, 2 = gaussian) by the library's
+    own encoder (fvsrn_network_set_*_grid = LatentGrid::initEncodingByte*, volume_interpolation_network.cpp:336-431)."""
+    import ctypes as C
+    from . import _lib
+    L = _lib.lib()
+    data = volnet.dumps(net)
+    h = C.c_void_p()
+    _lib.check(L.fvsrn_network_load_volnet(data, len(data), C.byref(h)))
+    try:
+        for i, g in enumerate(net.time_grids):
+            a = np.ascontiguousarray(g.values, np.float32)
+            _lib.check(L.fvsrn_network_set_time_grid(h, i, a.ctypes.data, *a.shape, int(encoding), None))
+        for i, g in enumerate(net.ensemble_grids):
+            a = np.ascontiguousarray(g.values, np.float32)
+            _lib.check(L.fvsrn_network_set_ensemble_grid(h, i, a.ctypes.data, *a.shape, int(encoding), None))
+        n = C.c_size_t()
+        _lib.check(L.fvsrn_network_save_volnet(h, None, 0, C.byref(n)))
+        buf = C.create_string_buffer(n.value)
+        _lib.check(L.fvsrn_network_save_volnet(h, buf, n.value, C.byref(n)))
+        return volnet.loads(buf.raw[:n.value])
+    finally:
+        L.fvsrn_network_free(h)
+
+
 # BASELINE.json configs (SURVEY §8: C1..C5)
 CONFIGS = {
     "C1": dict(net=dict(hidden=32, num_layers=4, grid_res=16), width=256, height=256, stepsize=0.005, views=1, spp=1),

@@ -36,7 +36,9 @@ class _Net(C.Structure):
         ("wlast", C.c_void_p), ("blast", C.c_void_p),
         ("ngroups", C.c_int32), ("gx", C.c_int32), ("gy", C.c_int32), ("gz", C.c_int32),
         ("ga", C.c_void_p * 4), ("gb", C.c_void_p * 4), ("frac", C.c_float * 4), ("gstride", C.c_int32 * 4),
-        ("box_min", C.c_float * 3), ("box_size", C.c_float * 3), ("tex_filter", C.c_int32), ("acc32", C.c_int32)]
+        ("box_min", C.c_float * 3), ("box_size", C.c_float * 3), ("tex_filter", C.c_int32), ("acc32", C.c_int32),
+        ("encoding", C.c_int32), ("b_uses_a", C.c_int32),
+        ("enc_off_a", C.c_float * 64), ("enc_scale_a", C.c_float * 64), ("enc_off_b", C.c_float * 64), ("enc_scale_b", C.c_float * 64)]
 
 
 class _Dvr(C.Structure):
@@ -61,7 +63,8 @@ def lib():
 class OracleNetwork:
     """Flattens a ``volnet.SceneNetwork`` (parsed .volnet) into the oracle's C struct."""
 
-    def __init__(self, net, time: float = 0.0, ensemble: int = 0, unit_box: bool = False, tex_filter: bool = False, acc32: bool = False):
+    def __init__(self, net, time: float = 0.0, ensemble: int = 0, unit_box: bool = False, tex_filter: bool = False, acc32: bool = False,
+                 b_uses_a: bool = False):
         self.net = net
         self._keep = []
         n = _Net()
@@ -90,9 +93,20 @@ class OracleNetwork:
         n.time_value = 0.0
         g = 0
         if net.has_latent_grid:
-            def chlast(grid):  # (C,Z,Y,X) f32 -> (Z,Y,X,C) f16
-                a = np.ascontiguousarray(np.transpose(grid.values.astype(np.float32).astype(np.float16), (1, 2, 3, 0)))
+            enc = (net.time_grids or net.ensemble_grids)[0].encoding
+            n.encoding, n.b_uses_a = enc, int(b_uses_a)
+            bpe = 1 if enc else 2       # bytes per stored element
+
+            def chlast(grid):  # (C,Z,Y,X) -> (Z,Y,X,C): fp16 values, or the stored bytes of a byte-encoded grid
+                src = grid.raw.astype(np.uint8) if enc else grid.values.astype(np.float32).astype(np.float16)
+                a = np.ascontiguousarray(np.transpose(src, (1, 2, 3, 0)))
                 self._keep.append(a); return a
+
+            def consts(gidx, A, B, i):
+                if not enc: return
+                for c in range(16):
+                    n.enc_off_a[16 * gidx + c] = A.offset_or_mean[16 * i + c]; n.enc_scale_a[16 * gidx + c] = A.scale_or_std[16 * i + c]
+                    n.enc_off_b[16 * gidx + c] = B.offset_or_mean[16 * i + c]; n.enc_scale_b[16 * gidx + c] = B.scale_or_std[16 * i + c]
             if net.time_grids:
                 t = float(np.float32(min(max((np.float32(time) - np.float32(net.time_min)) / np.float32(net.time_step), 0.0), float(net.time_num - 1))))
                 lo = min(int(t), net.time_num - 1); hi = min(lo + 1, net.time_num - 1)
@@ -101,14 +115,16 @@ class OracleNetwork:
                 A, B = chlast(net.time_grids[lo]), chlast(net.time_grids[hi])
                 Cg = A.shape[3]; n.gz, n.gy, n.gx = A.shape[0], A.shape[1], A.shape[2]
                 for i in range(Cg // 16):
-                    n.ga[g] = A.ctypes.data + 32 * i; n.gb[g] = B.ctypes.data + 32 * i
+                    n.ga[g] = A.ctypes.data + 16 * bpe * i; n.gb[g] = B.ctypes.data + 16 * bpe * i
+                    consts(g, net.time_grids[lo], net.time_grids[hi], i)
                     n.frac[g] = frac; n.gstride[g] = Cg; g += 1
             if net.ensemble_grids:
                 e = min(max(ensemble - net.ensemble_min, 0), net.ensemble_num - 1)
                 A = chlast(net.ensemble_grids[e])
                 Cg = A.shape[3]; n.gz, n.gy, n.gx = A.shape[0], A.shape[1], A.shape[2]
                 for i in range(Cg // 16):
-                    n.ga[g] = A.ctypes.data + 32 * i; n.gb[g] = A.ctypes.data + 32 * i
+                    n.ga[g] = A.ctypes.data + 16 * bpe * i; n.gb[g] = A.ctypes.data + 16 * bpe * i
+                    consts(g, net.ensemble_grids[e], net.ensemble_grids[e], i)
                     n.frac[g] = 0.0; n.gstride[g] = Cg; g += 1
         n.ngroups = g
         for i in range(3):

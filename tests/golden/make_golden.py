@@ -100,6 +100,34 @@ def export(net: SceneRepresentationNetwork, opt, box_min, box_size) -> volnet.Sc
     return n
 
 
+def encode_grid(values: np.ndarray, encoding: int) -> volnet.LatentGrid:
+    """LatentGrid::initEncodingByteLinear / initEncodingByteGaussian (volume_interpolation_network.cpp:336-431) in NumPy:
+    (C,Z,Y,X) float32 -> stored bytes + per-channel constants, and the values they DECODE to per voxel
+    (renderer_volume_tensorcores.cuh:341-383)."""
+    from scipy.special import erf, erfinv
+    v = values.astype(np.float32)
+    C_ = v.shape[0]
+    raw = np.empty(v.shape, np.uint8); off = np.empty(C_, np.float32); sc = np.empty(C_, np.float32)
+    for c in range(C_):
+        if encoding == volnet.GRID_BYTE_LINEAR:
+            mn, mx = np.float32(v[c].min()), np.float32(v[c].max())
+            off[c], sc[c] = mn, mx - mn
+            x01 = (v[c] - mn) * (np.float32(1.0) / max(np.float32(1e-5), mx - mn))
+        else:
+            mean, std = np.float32(v[c].mean()), np.float32(v[c].std(ddof=1))          # torch::std_mean: unbiased
+            off[c], sc[c] = mean, std
+            vhat = (v[c] - mean) * (np.float32(1.0) / max(np.float32(1e-5), std))
+            x01 = (np.float32(0.5) * (1 + erf(vhat * np.float32(0.7071067811865475)))).astype(np.float32)
+        raw[c] = np.clip(np.floor(np.float32(255) * x01 + np.float32(0.5)), 0, 255).astype(np.uint8)          # roundf
+    u = raw.astype(np.float32) / np.float32(255)
+    if encoding == volnet.GRID_BYTE_LINEAR:
+        dec = off[:, None, None, None] + u * sc[:, None, None, None]
+    else:
+        t = (np.sqrt(2.0) * erfinv((np.float32(2.0) - np.float32(1e-4)) * (u - np.float32(0.5)))).astype(np.float32)
+        dec = off[:, None, None, None] + t * sc[:, None, None, None]
+    return volnet.LatentGrid(encoding, np.ascontiguousarray(dec.astype(np.float32)), raw, off, sc)
+
+
 # ------------------------------------------------------------------------------------------------ CPU stand-ins
 class _Camera:  # camera.generate_rays: renderer_camera_kernels.cuh:12-43 + renderer_camera.cuh:34-52, fp32
     def __init__(self, matrix, fov_y): self.m, self.fov = matrix.astype(np.float32), np.float32(fov_y)
@@ -193,6 +221,38 @@ def main():
         path = os.path.join(HERE, name + ".npz")
         np.savez_compressed(path, **out)
         print(name, "->", path, os.path.getsize(path) // 1024, "KiB", "world range", world.min(), world.max())
+        if name == "c3_relu_gauss":
+            # byte-encoded latent grids: the same network with its grid stored as 8-bit texels. The reference
+            # encodes in C++ (LatentGrid ctor, restated in encode_grid) and its PyTorch network has no byte mode. The
+            # expected outputs come from the reference network with its latent fetch redirected to what the reference KERNEL
+            # does with such a grid (renderer_volume_tensorcores.cuh:573-605): grid_sample on the normalised texels x/255,
+            # then EncodeGridValue (offset + scale * x, resp. offset + scale * sqrt2 * erfinv((2 - 1e-4)(x - 0.5))).
+            grid_param = net._volumetric_latent_space
+            orig = grid_param.detach().clone()
+            for enc, tag in ((volnet.GRID_BYTE_LINEAR, "bytelinear"), (volnet.GRID_BYTE_GAUSSIAN, "bytegauss")):
+                eg = encode_grid(orig.numpy()[0], enc)
+                vb = export(net, opt, BOX_MIN, BOX_SIZE); vb.time_grids = [eg]
+                import volnet.network as refnet
+                real_sample = refnet.F.grid_sample
+                off_t = torch.from_numpy(eg.offset_or_mean)[None, :, None, None, None]; sc_t = torch.from_numpy(eg.scale_or_std)[None, :, None, None, None]
+
+                def sample_then_decode(inp, grid, **kw):
+                    x = real_sample(inp, grid, **kw)
+                    if enc == volnet.GRID_BYTE_GAUSSIAN:
+                        x = float(np.sqrt(2.0)) * torch.erfinv((2.0 - 1e-4) * (x - 0.5))
+                    return off_t + sc_t * x
+                with torch.no_grad():
+                    grid_param.copy_(torch.from_numpy(eg.raw.astype(np.float32) / np.float32(255))[None])
+                    refnet.F.grid_sample = sample_then_decode
+                    try:
+                        wb = net(pos, *args, 'world').numpy()
+                    finally:
+                        refnet.F.grid_sample = real_sample
+                    grid_param.copy_(orig)
+                pb = os.path.join(HERE, f"{name}_{tag}.npz")
+                np.savez_compressed(pb, volnet=np.frombuffer(volnet.dumps(vb), np.uint8), positions=pos.numpy(), world=wb, screen=wb,
+                                    time=np.float32(0.0), camera=cam, dvr_size=np.int32(48), dvr_step=np.float32(1.0 / 128))
+                print(pb, os.path.getsize(pb) // 1024, "KiB", "max |decoded - float| grid", np.abs(eg.values - orig.numpy()[0]).max())
 
 
 if __name__ == "__main__":

@@ -35,7 +35,23 @@ CASES = {
     "C3_relu_nerf_texture_tf": (dict(C3, activation="ReLU", last_gain=6.0), 1024, 1 / 512, 1, None),
     "C4_relu_nerf_64x6": (dict(hidden=64, num_layers=6, grid_res=64, activation="ReLU", seed=42, hidden_gain=2.0), 2048, 1 / 512, 0, None),
     "C5_time_interpolated": (dict(C3, activation="ReLU", last_gain=6.0, time_keyframes=8), 512, 1 / 512, 0, 2.37),
+    # byte-encoded latent grids kept 8-bit on the device; "encoding" is applied after make_network
+    "C3_relu_nerf_bytelinear": (dict(C3, activation="ReLU", last_gain=6.0, encoding=1), 1024, 1 / 512, 0, None),
+    "C3_relu_nerf_bytegauss": (dict(C3, activation="ReLU", last_gain=6.0, encoding=2), 1024, 1 / 512, 0, None),
+    # two byte-encoded keyframes: the reference kernel decodes keyframe B with A's offset / scale (renderer_volume_tensorcores.cuh:
+    # 586-587), the reference-exact mode follows it bit for bit; the fast modes use B's own constants (api.cu fill_encoding) and
+    # are checked against the oracle instead (test_gpu_dvr.py) - hence the 6-tuple, which keeps this case out of the test below
+    "C5_time_interpolated_bytelinear": (dict(C3, activation="ReLU", last_gain=6.0, time_keyframes=8, encoding=1), 512, 1 / 512, 0, 2.37, 1.0),
 }
+
+
+def make_case_network(kw):
+    """scenes.make_network plus the optional byte encoding of its latent grids."""
+    from fvsrn_b200 import scenes
+    kw = dict(kw)
+    enc = kw.pop("encoding", 0)
+    net = scenes.make_network(**kw)
+    return scenes.encode_grids(net, enc) if enc else net
 MODES = ["tcgen05", "mma_sync"]
 
 
@@ -63,7 +79,7 @@ def test_baseline_config_matches_reference_kernel(ref, name, plume_tf):
     from fvsrn_b200 import scenes, volnet
     kw, size, step, tf_kind, time = CASES[name][:5]
     absorption = CASES[name][5] if len(CASES[name]) > 5 else 1.0
-    net = scenes.make_network(**kw)
+    net = make_case_network(kw)
     cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
     plume_tf = plume_tf.copy(); plume_tf[..., 3] *= absorption
     tf = scenes.texture_tf_from_piecewise(plume_tf, 256) if tf_kind == 1 else plume_tf

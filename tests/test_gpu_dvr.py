@@ -185,6 +185,26 @@ def test_dvr_per_view_times(env, plume_tf):
         assert np.abs(img[b, :4] - ref[0, :4]).max() <= RGBA_TOL, (b, t)
 
 
+@pytest.mark.parametrize("encoding", [1, 2])
+def test_dvr_byte_encoded_time_keyframes(env, plume_tf, encoding):
+    """Byte-encoded latent grids stay 8-bit on the device and are decoded after the trilinear filter; with two keyframes
+    each is decoded with its OWN offset / scale (the reference kernel uses A's for both; oracle b_uses_a=False restates the
+    fixed behaviour, the reference-exact mode the reference's)."""
+    net = env.scenes.encode_grids(env.scenes.make_network(hidden=32, num_layers=4, grid_res=16, seed=5, last_gain=6.0, time_keyframes=3), encoding)
+    assert net.time_grids[0].encoding == encoding and net.time_grids[0].raw is not None
+    cam = env.scenes.camera_reference_frame(**env.scenes.DEFAULT_CAMERA)
+    vol = _volume(env, net)
+    vol.current_network().set_time_and_ensemble(1.4, 0)
+    ie = _evaluator(env, vol, cam, plume_tf, 1 / 64)
+    img = ie.render(40, 32).cpu().numpy()
+    ref, steps, _ = env.oracle.render_dvr(net, width=40, height=32, camera=cam, fov_y=env.scenes.DEFAULT_FOV_Y, stepsize=1 / 64, tf=plume_tf, time=1.4)
+    assert np.abs(img[:, :4] - ref[:, :4]).max() <= RGBA_TOL
+    _check_steps(ie.last_step_counts.cpu().numpy(), steps)
+    pos = np.random.default_rng(3).random((2000, 3), dtype=np.float32)
+    got = vol.evaluate(env.torch.from_numpy(pos).cuda()).cpu().numpy()
+    assert np.abs(got - env.oracle.evaluate(net, pos, time=1.4)).max() < 4e-3
+
+
 def test_dvr_supersampling_matches_oracle(env, plume_tf):
     g = Golden("c3_relu_gauss")
     vol = _volume(env, g.volnet_bytes)

@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 from conftest import Golden
-from test_gpu_baseline_configs import CASES, ref  # noqa: F401
+from test_gpu_baseline_configs import CASES, ref, make_case_network  # noqa: F401
 
 pytestmark = pytest.mark.gpu
 
@@ -32,7 +32,7 @@ def test_reference_exact_mode_is_bit_identical_at_baseline_configs(ref, name, pl
     from fvsrn_b200 import scenes, volnet
     kw, size, step, tf_kind, time = CASES[name][:5]
     absorption = CASES[name][5] if len(CASES[name]) > 5 else 1.0
-    net = scenes.make_network(**kw)
+    net = make_case_network(kw)
     cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
     tfp = plume_tf.copy(); tfp[..., 3] *= absorption
     tf = scenes.texture_tf_from_piecewise(tfp, 256) if tf_kind == 1 else tfp
@@ -59,7 +59,7 @@ def test_ray_setup_is_bit_identical_in_every_kernel_mode(ref, plume_tf):
     import parity
     from fvsrn_b200 import scenes, volnet
     kw, size, step = CASES["C3_relu_nerf"][:3]
-    net = scenes.make_network(**kw)
+    net = make_case_network(kw)
     cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
     want, want_steps, _ = parity.render_reference(net, size, size, cam, scenes.DEFAULT_FOV_Y, plume_tf, step)
     assert want[:, 3].max() < 0.9                           # translucent frame: no ray terminates early

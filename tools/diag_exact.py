@@ -10,7 +10,7 @@ for p in (ROOT, os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
 import fvsrn_b200  # noqa
 from fvsrn_b200 import scenes, volnet
 import parity
-from test_gpu_baseline_configs import CASES
+from test_gpu_baseline_configs import CASES, make_case_network
 
 plume = np.load(os.path.join(ROOT, "tests", "golden", "plume_tf.npy"))
 names = sys.argv[1].split(",") if len(sys.argv) > 1 else list(CASES)
@@ -20,7 +20,7 @@ for name in names:
     absorption = CASES[name][5] if len(CASES[name]) > 5 else 1.0
     if size_override:
         size = size_override
-    net = scenes.make_network(**kw)
+    net = make_case_network(kw)
     cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
     tfp = plume.copy(); tfp[..., 3] *= absorption
     tf = scenes.texture_tf_from_piecewise(tfp, 256) if tf_kind == 1 else tfp

@@ -15,7 +15,7 @@ import oracle
 import torch_ref
 
 plume = np.load(os.path.join(ROOT, "tests", "golden", "plume_tf.npy"))
-from test_gpu_baseline_configs import CASES
+from test_gpu_baseline_configs import CASES, make_case_network
 
 names = sys.argv[1].split(",")
 size_override = int(sys.argv[2]) if len(sys.argv) > 2 else 0
@@ -24,7 +24,7 @@ for name in names:
     absorption = CASES[name][5] if len(CASES[name]) > 5 else 1.0
     if size_override:
         size = size_override
-    net = scenes.make_network(**kw)
+    net = make_case_network(kw)
     cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
     tfp = plume.copy(); tfp[..., 3] *= absorption
     tf = scenes.texture_tf_from_piecewise(tfp, 256) if tf_kind == 1 else tfp
