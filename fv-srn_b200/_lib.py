@@ -16,7 +16,7 @@ SYMBOLS = [
     "fvsrn_network_valid", "fvsrn_network_num_parameters", "fvsrn_network_compute_max_warps",
     "fvsrn_network_set_time_and_ensemble", "fvsrn_network_get_info", "fvsrn_network_set_kernel_mode", "fvsrn_network_get_kernel_mode", "fvsrn_network_prepare",
     "fvsrn_network_clear_gpu_resources", "fvsrn_evaluate", "fvsrn_evaluate_host", "fvsrn_render_dvr",
-    "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_extract_color_ex", "fvsrn_query",
+    "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_extract_color_ex", "fvsrn_generate_rays", "fvsrn_evaluate_tf", "fvsrn_query",
 ]
 
 
@@ -94,6 +94,8 @@ def lib():
         "fvsrn_render_dvr_host": [vp, C.POINTER(DvrParams), vp, vp],
         "fvsrn_extract_color": [vp, vp, i, i, i, vp],
         "fvsrn_extract_color_ex": [vp, vp, i, i, i, i, i, f, i, vp],
+        "fvsrn_generate_rays": [vp, i, f, i, i, vp, vp, vp],
+        "fvsrn_evaluate_tf": [i, vp, i, vp, vp, i64, f, f, f, vp],
         "fvsrn_query": [vp, i, C.POINTER(QueryInfo)],
     }
     for name, args in sig.items():

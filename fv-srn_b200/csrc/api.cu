@@ -986,6 +986,31 @@ int fvsrn_extract_color_ex(const float* img_dev, void* out_dev, int batch, int h
     FV_CATCH
 }
 
+int fvsrn_generate_rays(const float* camera_matrix_dev, int batch, float fov_y_radians, int width, int height,
+                        float* ray_start_dev, float* ray_dir_dev, void* stream) {
+    FV_TRY
+    if (!camera_matrix_dev || !ray_start_dev || !ray_dir_dev) return fail("null device pointer");
+    if (batch <= 0 || width <= 0 || height <= 0) return fail("image size and batch must be positive");
+    CUDA_OK(launch_generate_rays(camera_matrix_dev, fov_y_radians, float(double(width) / double(height)), batch, height, width,
+                                 ray_start_dev, ray_dir_dev, static_cast<cudaStream_t>(stream)));
+    return 0;
+    FV_CATCH
+}
+
+int fvsrn_evaluate_tf(int tf_kind, const float* tf_dev, int tf_resolution, const float* densities_dev, float* colors_dev,
+                      int64_t n, float density_min, float density_max, float stepsize, void* stream) {
+    FV_TRY
+    if (n < 0) return fail("negative sample count");
+    if (n == 0) return 0;
+    if (!tf_dev || !densities_dev || !colors_dev) return fail("null device pointer");
+    if (tf_kind < 0 || tf_kind > 2) return fail("unknown transfer function kind");
+    if (tf_kind != FVSRN_TF_IDENTITY && tf_resolution < 2) return fail("transfer function needs at least 2 entries");
+    CUDA_OK(launch_evaluate_tf(tf_kind, tf_dev, tf_resolution, densities_dev, colors_dev, (long long)n, density_min, density_max, stepsize,
+                               static_cast<cudaStream_t>(stream)));
+    return 0;
+    FV_CATCH
+}
+
 int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     FV_TRY
     if (!net) return fail("null network handle");

@@ -101,32 +101,33 @@ __device__ __forceinline__ float sel_gt(float a, float b) { return (a > b) ? a :
 } // namespace rf
 
 // camera frame, reference renderer_camera.cuh:34-52 (operation order of the compiled reference kernel)
-__device__ __forceinline__ CamFrame load_camera(const DvrParams& D, int b) {
+__device__ __forceinline__ CamFrame load_camera(const float* cam, float fov_y, float aspect, int b) {
     CamFrame c;
-    const float* cm = D.cam + (size_t)b * 9;
+    const float* cm = cam + (size_t)b * 9;
     c.eye = make_float3(__ldg(cm + 0), __ldg(cm + 1), __ldg(cm + 2));
     c.right = make_float3(__ldg(cm + 3), __ldg(cm + 4), __ldg(cm + 5));
     c.up = make_float3(__ldg(cm + 6), __ldg(cm + 7), __ldg(cm + 8));
     c.front = make_float3(rf::sub(rf::mul(c.right.z, c.up.y), rf::mul(c.right.y, c.up.z)),
                           rf::sub(rf::mul(c.right.x, c.up.z), rf::mul(c.right.z, c.up.x)),
                           rf::sub(rf::mul(c.right.y, c.up.x), rf::mul(c.right.x, c.up.y))); // cross(up, right)
-    const float half_fov = rf::div(D.fov_y, 2.0f);
+    const float half_fov = rf::div(fov_y, 2.0f);
     c.tan_y = rf::div(rf::sin(half_fov), rf::cos(half_fov));      // tanf under fast math
-    c.tan_x = rf::mul(c.tan_y, D.aspect);
+    c.tan_x = rf::mul(c.tan_y, aspect);
     return c;
 }
+__device__ __forceinline__ CamFrame load_camera(const DvrParams& D, int b) { return load_camera(D.cam, D.fov_y, D.aspect, b); }
 
-// ray through pixel (x,y), sub-sample s (reference renderer_image_evaluator_simple.cuh:84-86, renderer_camera.cuh:41-51)
-// and its box interval (renderer_utils.cuh:91-105, renderer_ray_evaluation_stepping_dvr.cuh:66-71)
-__device__ __forceinline__ Ray make_ray(const DvrParams& D, const CamFrame& c, int x, int y, int s, float3 bmin, float3 bsize, int spp) {
+// direction of the camera ray through pixel (x,y), sub-sample s (reference renderer_image_evaluator_simple.cuh:84-86 =
+// renderer_camera_kernels.cuh:23-30, renderer_camera.cuh:41-51); the origin is c.eye
+__device__ __forceinline__ float3 camera_ray(int W, int H, const CamFrame& c, int x, int y, int s, int spp, int spp_side) {
     float nx = float(x), ny = float(y);
     if (spp > 1) {                // deterministic stratified sub-pixel offsets (no reference counterpart)
-        nx = __fadd_rn(nx, __fsub_rn(__fdiv_rn(float(s % D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
-        ny = __fadd_rn(ny, __fsub_rn(__fdiv_rn(float(s / D.spp_side) + 0.5f, float(D.spp_side)), 0.5f));
+        nx = __fadd_rn(nx, __fsub_rn(__fdiv_rn(float(s % spp_side) + 0.5f, float(spp_side)), 0.5f));
+        ny = __fadd_rn(ny, __fsub_rn(__fdiv_rn(float(s / spp_side) + 0.5f, float(spp_side)), 0.5f));
     }
     const float hx = rf::add(nx, 0.5f), hy = rf::add(ny, 0.5f);
-    const float ndc_x = rf::add(rf::div(rf::add(hx, hx), float(D.W)), -1.0f);
-    const float ndc_y = rf::add(rf::div(rf::add(hy, hy), float(D.H)), -1.0f);
+    const float ndc_x = rf::add(rf::div(rf::add(hx, hx), float(W)), -1.0f);
+    const float ndc_y = rf::add(rf::div(rf::add(hy, hy), float(H)), -1.0f);
     const float sx = rf::mul(ndc_x, c.tan_x), sy = rf::mul(ndc_y, c.tan_y);
     float3 dir = make_float3(rf::fma(sy, c.up.x, rf::fma(sx, c.right.x, c.front.x)),
                              rf::fma(sy, c.up.y, rf::fma(sx, c.right.y, c.front.y)),
@@ -134,6 +135,11 @@ __device__ __forceinline__ Ray make_ray(const DvrParams& D, const CamFrame& c, i
     const float len2 = rf::fma(dir.z, dir.z, rf::fma(dir.x, dir.x, rf::mul(dir.y, dir.y)));
     const float inv_len = rf::rsqrt(len2);
     dir.x = rf::mul(inv_len, dir.x); dir.y = rf::mul(inv_len, dir.y); dir.z = rf::mul(inv_len, dir.z);
+    return dir;
+}
+// the ray and its box interval (renderer_utils.cuh:91-105, renderer_ray_evaluation_stepping_dvr.cuh:66-71)
+__device__ __forceinline__ Ray make_ray(const DvrParams& D, const CamFrame& c, int x, int y, int s, float3 bmin, float3 bsize, int spp) {
+    float3 dir = camera_ray(D.W, D.H, c, x, y, s, spp, D.spp_side);
     const float3 eye = c.eye;
     const float ix = rf::div(1.0f, dir.x), iy = rf::div(1.0f, dir.y), iz = rf::div(1.0f, dir.z);
     const float t1 = rf::mul(rf::sub(bmin.x, eye.x), ix), t2 = rf::mul(ix, rf::sub(rf::add(bmin.x, bsize.x), eye.x));

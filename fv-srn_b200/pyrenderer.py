@@ -390,9 +390,27 @@ class ITransferFunction:
 
     def _tensor(self) -> torch.Tensor: raise NotImplementedError
 
+    def _evaluate(self, density, min_density, max_density, stepsize):
+        if not density.is_cuda:
+            raise RuntimeError("density must reside on the GPU")
+        if density.dim() != 2 or density.shape[1] != 1:
+            raise RuntimeError("density must be of shape (N,1)")
+        d = density.to(torch.float32).contiguous()
+        tf = self._tensor()
+        out = torch.empty((d.shape[0], 4), dtype=torch.float32, device=d.device)
+        check(_lib.lib().fvsrn_evaluate_tf(self.kind, tf.data_ptr(), tf.shape[1] if self.kind != 2 else 0, d.data_ptr(), out.data_ptr(),
+                                           d.shape[0], float(min_density), float(max_density), float(stepsize), _stream_ptr()))
+        return out
+
     def evaluate(self, density, min_density, max_density):
-        """CPU-free convenience used by callers for previews: evaluates with stepsize 1 on the GPU via torch ops."""
-        raise RuntimeError("ITransferFunction.evaluate tensor op is not part of the B200 hot path (SURVEY §8 f2)")
+        """ITransferFunction::evaluate (transfer_function.cpp:123-136 -> EvaluateTF, renderer_tf_kernels.cuh:11-40):
+        density (N,1) -> rgb + absorption (N,4), stepsize 1."""
+        return self._evaluate(density, min_density, max_density, 1.0)
+
+    def evaluate_with_previous(self, density, min_density, max_density, previous_density, stepsize):
+        """ITransferFunction::evaluate_with_previous (EvaluateTFWithPrevious, :42-70); the previous density only enters
+        pre-integrated texture TFs, which are not on the path."""
+        return self._evaluate(density, min_density, max_density, stepsize)
 
 
 class TransferFunctionPiecewiseLinear(ITransferFunction):
@@ -509,6 +527,17 @@ class CameraOnASphere:
         if t.dim() != 3 or t.shape[1:] != (3, 3):
             raise RuntimeError("camera parameters must be of shape (B,3,3)")
         self._matrix = t.to(device="cuda", dtype=torch.float32).contiguous()
+
+    def generate_rays(self, width: int, height: int, double_precision: bool = False):
+        """ICamera::generateRays (camera.cpp:204-209 -> CameraGenerateRayKernel): (ray_start, ray_dir), both (B,H,W,3)."""
+        if double_precision:
+            raise RuntimeError("double precision rays are not part of the B200 path")
+        cam = self.get_parameters()
+        B = cam.shape[0]
+        start = torch.empty((B, height, width, 3), dtype=torch.float32, device="cuda")
+        dirs = torch.empty_like(start)
+        check(_lib.lib().fvsrn_generate_rays(cam.data_ptr(), B, float(self.fovY_radians), width, height, start.data_ptr(), dirs.data_ptr(), _stream_ptr()))
+        return start, dirs
 
     def get_parameters(self) -> torch.Tensor:
         if self._matrix is not None:

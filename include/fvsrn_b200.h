@@ -221,6 +221,20 @@ int  fvsrn_extract_color(const float* img_dev, float* out_dev, int batch, int he
 int  fvsrn_extract_color_ex(const float* img_dev, void* out_dev, int batch, int height, int width,
                             int channel_mode, int tonemap, float max_exposure, int output_format, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Tensor operators beside the fused path: what the reference's PyTorch marcher (applications/volnet/
+ * raytracing.py:103, 150-154) calls per frame / per step, so that it can run against this library on the GPU as well.
+ * ------------------------------------------------------------------------------------------ */
+/* ICamera::generateRays -> CameraGenerateRayKernel, renderer/renderer_camera_kernels.cuh:12-45, camera.cpp:204-209:
+ * camera (B,3,3) -> ray origins and unit directions, both (B,H,W,3) fp32 contiguous */
+int  fvsrn_generate_rays(const float* camera_matrix_dev, int batch, float fov_y_radians, int width, int height,
+                         float* ray_start_dev, float* ray_dir_dev, void* stream);
+/* ITransferFunction::evaluate / evaluate_with_previous -> EvaluateTF*, renderer/renderer_tf_kernels.cuh:11-70,
+ * transfer_function.cpp:123-152: densities (N) -> rgb + absorption*stepsize (N,4); batch 0 of the TF tensor; stepsize = 1
+ * for plain evaluate (the previous density only enters pre-integrated texture TFs, which are off the path) */
+int  fvsrn_evaluate_tf(int tf_kind, const float* tf_dev, int tf_resolution, const float* densities_dev, float* colors_dev,
+                       int64_t n, float density_min, float density_max, float stepsize, void* stream);
+
 /* Launch diagnostics (stand-in for compute_max_warps / KernelLoader occupancy query) */
 typedef struct fvsrn_query_info {
     int device, sm_count;
