@@ -17,6 +17,8 @@ SYMBOLS = [
     "fvsrn_network_set_time_and_ensemble", "fvsrn_network_get_info", "fvsrn_network_set_kernel_mode", "fvsrn_network_get_kernel_mode", "fvsrn_network_prepare",
     "fvsrn_network_clear_gpu_resources", "fvsrn_evaluate", "fvsrn_evaluate_host", "fvsrn_render_dvr",
     "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_extract_color_ex", "fvsrn_generate_rays", "fvsrn_evaluate_tf", "fvsrn_query",
+    "fvsrn_volume_load_cvol", "fvsrn_volume_save_cvol", "fvsrn_volume_from_dense", "fvsrn_volume_get_info", "fvsrn_volume_free",
+    "fvsrn_volume_prepare", "fvsrn_render_dvr_grid", "fvsrn_evaluate_grid",
 ]
 
 
@@ -41,6 +43,11 @@ class DvrParams(C.Structure):
         ("step_count_dev", C.c_void_p), ("counters_dev", C.c_void_p),
         ("output_format", C.c_int), ("channel_mode", C.c_int), ("tonemap", C.c_int), ("max_exposure", C.c_float),
     ]
+
+
+class VolumeInfo(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("num_features", "feature", "size_x", "size_y", "size_z", "channels", "data_type")] + [
+        ("world_size", C.c_float * 3), ("box_min", C.c_float * 3), ("box_size", C.c_float * 3)]
 
 
 class QueryInfo(C.Structure):
@@ -95,13 +102,21 @@ def lib():
         "fvsrn_extract_color": [vp, vp, i, i, i, vp],
         "fvsrn_extract_color_ex": [vp, vp, i, i, i, i, i, f, i, vp],
         "fvsrn_generate_rays": [vp, i, f, i, i, vp, vp, vp],
+        "fvsrn_volume_load_cvol": [C.c_char_p, C.c_size_t, C.POINTER(vp)],
+        "fvsrn_volume_save_cvol": [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)],
+        "fvsrn_volume_from_dense": [vp, i, i, i, C.POINTER(f * 3), C.POINTER(vp)],
+        "fvsrn_volume_get_info": [vp, i, C.POINTER(VolumeInfo)],
+        "fvsrn_volume_free": [vp],
+        "fvsrn_volume_prepare": [vp, i, i, vp],
+        "fvsrn_render_dvr_grid": [vp, C.POINTER(DvrParams), vp, vp],
+        "fvsrn_evaluate_grid": [vp, vp, vp, i64, vp],
         "fvsrn_evaluate_tf": [i, vp, i, vp, vp, i64, f, f, f, vp],
         "fvsrn_query": [vp, i, C.POINTER(QueryInfo)],
     }
     for name, args in sig.items():
         fn = getattr(L, name)
         fn.argtypes = args
-        fn.restype = None if name == "fvsrn_network_free" else C.c_int
+        fn.restype = None if name in ("fvsrn_network_free", "fvsrn_volume_free") else C.c_int
     _lib = L
     return L
 

@@ -371,6 +371,12 @@ unsigned int* next_tile_counter(fvsrn_network* h, cudaStream_t s) {
 
 } // namespace
 
+// shared with api_volume.cu
+namespace fvsrn_api {
+int fail(const std::string& msg) { return ::fail(msg); }
+DvrParams fill_dvr_params(const fvsrn_dvr_params* p, float* out, bool is_rgbo, const void* any_dev);
+}
+
 // =========================================================================================== C ABI
 extern "C" {
 
@@ -759,13 +765,13 @@ void do_evaluate(fvsrn_network* h, const float* pos, const float* dir, float* ou
     h->launches++;
 }
 
-void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStream_t s) {
-    require_prepared(h);
+// fvsrn_dvr_params -> the kernels' launch parameters (validation shared by the SRN and the grid renderer);
+// is_rgbo: colour networks skip the transfer function (SKIP_TRANSFER_FUNCTION), `any_dev` is some readable device pointer
+DvrParams fill_dvr_params(const fvsrn_dvr_params* p, float* out, bool is_rgbo, const void* any_dev) {
     if (!p || !out) throw std::runtime_error("null argument");
     if (p->width <= 0 || p->height <= 0 || p->batch <= 0) throw std::runtime_error("image size and batch must be positive");
     if (!p->camera_matrix_dev) throw std::runtime_error("camera matrix is null");
     if (!(p->stepsize > 0.f)) throw std::runtime_error("stepsize must be positive");
-    const bool is_rgbo = h->net.output_mode >= OUT_RGBO;
     if (!is_rgbo) {
         if (!p->tf_dev) throw std::runtime_error("texture tensor is not defined");
         if (p->tf_kind < 0 || p->tf_kind > 2) throw std::runtime_error("unknown transfer function kind");
@@ -790,7 +796,7 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     D.dmin = p->density_min; D.dmax = p->density_max; D.inv_range = 1.0f / (p->density_max - p->density_min);
     D.early_out = p->early_out; D.blend_mode = p->blend_mode;
     D.tf_kind = is_rgbo ? 2 : p->tf_kind; D.tf_R = p->tf_resolution; D.tf_batch = is_rgbo ? 1 : p->tf_batch;
-    D.tf = is_rgbo ? reinterpret_cast<const float*>(h->d_blob) : p->tf_dev; // rgbo networks skip the TF; any readable pointer
+    D.tf = is_rgbo ? reinterpret_cast<const float*>(any_dev) : p->tf_dev; // rgbo networks skip the TF; any readable pointer
     D.spp = spp; D.spp_side = side;
     D.out = out; D.sb = p->out_stride_b; D.sc = p->out_stride_c; D.sy = p->out_stride_y; D.sx = p->out_stride_x;
     D.step_count = p->step_count_dev; D.counters = p->counters_dev;
@@ -801,6 +807,19 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         if (D.channel_mode < 0 || D.channel_mode > FVSRN_CHANNEL_COLOR) throw std::runtime_error("unknown channel mode");
         if (D.tonemap && !(D.max_exposure > 0.f)) throw std::runtime_error("tonemapping needs a positive max_exposure");
     }
+    return D;
+}
+
+} // namespace
+namespace fvsrn_api {
+DvrParams fill_dvr_params(const fvsrn_dvr_params* p, float* out, bool is_rgbo, const void* any_dev) { return ::fill_dvr_params(p, out, is_rgbo, any_dev); }
+}
+namespace {
+
+void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStream_t s) {
+    require_prepared(h);
+    const bool is_rgbo = h->net.output_mode >= OUT_RGBO;
+    const DvrParams D = fill_dvr_params(p, out, is_rgbo, h->d_blob);
     const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05;
     const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT;
     if (exact) {    // the shapes the reference kernels this mode is validated against cover (kernels_exact.cuh)

@@ -72,6 +72,18 @@ cudaError_t launch_evaluate_tf(int tf_kind, const float* tf, int R, const float*
     return cudaGetLastError();
 }
 
+cudaError_t launch_dvr_grid(const GridVolumeParams& G, const DvrParams& D, int sm_count, cudaStream_t s) {
+    const long long total = (long long)D.tw * D.th * D.nb;
+    if (total <= 0) return cudaSuccess;
+    dvr_grid_kernel<<<int(std::min<long long>((total + 255) / 256, (long long)sm_count * 8)), 256, 0, s>>>(G, D);
+    return cudaGetLastError();
+}
+cudaError_t launch_eval_grid(const GridVolumeParams& G, const float* pos, float* out, long long n, cudaStream_t s) {
+    if (n <= 0) return cudaSuccess;
+    eval_grid_kernel<<<int(std::min<long long>((n + 255) / 256, 148 * 16)), 256, 0, s>>>(G, pos, out, n);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_exact(int h16, const NetParams& P, const DvrParams& D, LaunchCfg* cfg, cudaStream_t s) {
     switch (h16) {
         case 2: return launch_exact_h<2>(P, D, cfg, s);

@@ -40,6 +40,13 @@ struct DvrParams {
     float max_exposure;
 };
 
+// ground-truth density grid (kernels in kernels_exact.cuh)
+struct GridVolumeParams {
+    unsigned long long tex;     // 1-channel 3-D texture: unnormalised coordinates, clamp, linear (volume.cpp:149-160)
+    int rx, ry, rz;             // resolution
+    float box_min[3], box_size[3];
+};
+
 struct EvalParams {
     const float* pos;   // (N,3)
     const float* dir;   // (N,3) or null

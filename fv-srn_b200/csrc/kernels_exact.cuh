@@ -208,6 +208,43 @@ __device__ __forceinline__ float4 exact_tf_texture(const float* tf, int R, float
     return c;
 }
 
+// one sample of the reference marcher after volume.eval: density range + TF (renderer_ray_evaluation_stepping_dvr.cuh:114-133)
+__device__ __forceinline__ float4 exact_shade(const DvrParams& D, const float* tfp, float value, float inv_range, bool valid) {
+    float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (valid && value >= D.dmin) {
+        const float d2 = rf::fmax(0.f, rf::fmin(rf::mul(inv_range, rf::sub(value, D.dmin)), 1.0f));
+        c = D.tf_kind == 0 ? exact_tf_piecewise(tfp, D.tf_R, d2, D.stepsize) : exact_tf_texture(tfp, D.tf_R, d2, D.stepsize);
+    }
+    return c;
+}
+// Blending::eval, renderer_blending.cuh:36-51
+__device__ __forceinline__ void exact_blend(const DvrParams& D, float4 c, float t, bool valid, float4& acc, float& acc_depth) {
+    if (c.w > 0.f && valid) {
+        const float a = (D.blend_mode == 1) ? rf::sub(1.0f, rf::ex2(rf::mul(c.w, -1.4426950408889634f))) : rf::fmin(1.0f, c.w);
+        const float om = rf::sub(1.0f, acc.w);
+        acc.x = rf::fma(rf::mul(om, c.x), a, acc.x);
+        acc.y = rf::fma(rf::mul(om, c.y), a, acc.y);
+        acc.z = rf::fma(rf::mul(om, c.z), a, acc.z);
+        acc.w = rf::fma(om, a, acc.w);
+        acc_depth = rf::fma(rf::mul(om, t), a, acc_depth);
+    }
+}
+// pixel write, renderer_image_evaluator_simple.cuh:105-124: depth /= alpha first, then colour /= samples
+__device__ __forceinline__ void exact_write(const DvrParams& D, int b, int x, int y, float4 pix, float pix_depth, int last_steps) {
+    const float ns = float(D.spp);
+    if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
+    if (D.out_format != 0) {
+        store_rgba(D, b, x, y, select_channel(D.channel_mode, D.tonemap, D.max_exposure,
+                                              make_float4(rf::div(pix.x, ns), rf::div(pix.y, ns), rf::div(pix.z, ns), rf::div(pix.w, ns)), make_float3(0.f, 0.f, 0.f)));
+        return;
+    }
+    float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
+    o[0 * D.sc] = rf::div(pix.x, ns); o[1 * D.sc] = rf::div(pix.y, ns); o[2 * D.sc] = rf::div(pix.z, ns);
+    o[3 * D.sc] = rf::div(pix.w, ns);
+    o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
+    o[7 * D.sc] = rf::div(pix_depth, pix.w);
+}
+
 template <int H16>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
@@ -269,46 +306,86 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
                 const float px = rf::div(rf::sub(wx, bmin.x), bsize.x), py = rf::div(rf::sub(wy, bmin.y), bsize.y),
                             pz = rf::div(rf::sub(wz, bmin.z), bsize.z);
                 const float value = __half2float(Net::forward(P, sblob_addr, stage, ac, px, py, pz, tfrac));
-                float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (valid && value >= D.dmin) {
-                    const float d2 = rf::fmax(0.f, rf::fmin(rf::mul(inv_range, rf::sub(value, D.dmin)), 1.0f));
-                    c = D.tf_kind == 0 ? exact_tf_piecewise(tfp, D.tf_R, d2, D.stepsize) : exact_tf_texture(tfp, D.tf_R, d2, D.stepsize);
-                }
+                const float4 c = exact_shade(D, tfp, value, inv_range, valid);
                 steps += valid ? 1 : 0;
-                if (c.w > 0.f && valid) {   // renderer_blending.cuh:36-51
-                    const float a = (D.blend_mode == 1) ? rf::sub(1.0f, rf::ex2(rf::mul(c.w, -1.4426950408889634f))) : rf::fmin(1.0f, c.w);
-                    const float om = rf::sub(1.0f, acc.w);
-                    acc.x = rf::fma(rf::mul(om, c.x), a, acc.x);
-                    acc.y = rf::fma(rf::mul(om, c.y), a, acc.y);
-                    acc.z = rf::fma(rf::mul(om, c.z), a, acc.z);
-                    acc.w = rf::fma(om, a, acc.w);
-                    acc_depth = rf::fma(rf::mul(om, t), a, acc_depth);
-                }
+                exact_blend(D, c, t, valid, acc, acc_depth);
             }
             n_valid += steps;
             last_steps = steps;
             pix.x = rf::add(pix.x, acc.x); pix.y = rf::add(pix.y, acc.y); pix.z = rf::add(pix.z, acc.z); pix.w = rf::add(pix.w, acc.w);
             pix_depth = rf::fma(acc.w, acc_depth, pix_depth);       // renderer_image_evaluator_simple.cuh:101-103
         }
-        if (in_img) {       // :105-124: depth /= alpha first, then colour /= samples
-            const float ns = float(D.spp);
-            if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
-            if (D.out_format != 0) {
-                store_rgba(D, b, x, y, select_channel(D.channel_mode, D.tonemap, D.max_exposure,
-                                                      make_float4(rf::div(pix.x, ns), rf::div(pix.y, ns), rf::div(pix.z, ns), rf::div(pix.w, ns)), make_float3(0.f, 0.f, 0.f)));
-                continue;
-            }
-            float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
-            o[0 * D.sc] = rf::div(pix.x, ns); o[1 * D.sc] = rf::div(pix.y, ns); o[2 * D.sc] = rf::div(pix.z, ns);
-            o[3 * D.sc] = rf::div(pix.w, ns);
-            o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
-            o[7 * D.sc] = rf::div(pix_depth, pix.w);
-        }
+        if (in_img) exact_write(D, b, x, y, pix, pix_depth, last_steps);
     }
     if (D.counters) {
         for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);
         if (lane == 0) { atomicAdd(D.counters + 0, n_valid); atomicAdd(D.counters + 1, n_exec); }
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Ground-truth density grid through the same marcher: VolumeInterpolationGrid::eval, texture path, trilinear
+// (renderer_volume_grid.cuh:110-139, 196-231) - what the reference renders its comparison images with. The reference traces
+// these rays per thread (KERNEL_SYNCHRONIZED_TRACING 0); operation order as in its compiled kernel.
+__device__ __forceinline__ float grid_eval(const GridVolumeParams& G, float wx, float wy, float wz) {
+    const float px = rf::mul(rf::div(rf::sub(wx, G.box_min[0]), G.box_size[0]), float(G.rx));
+    const float py = rf::mul(rf::div(rf::sub(wy, G.box_min[1]), G.box_size[1]), float(G.ry));
+    const float pz = rf::mul(rf::div(rf::sub(wz, G.box_min[2]), G.box_size[2]), float(G.rz));
+    return tex3D<float>(G.tex, px, py, pz);
+}
+
+__global__ void __launch_bounds__(256)
+dvr_grid_kernel(const __grid_constant__ GridVolumeParams G, const __grid_constant__ DvrParams D) {
+    __shared__ float stf[kTfSmemFloats];
+    const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : D.tf_R * 4;
+    if (D.tf_batch == 1)
+        for (int i = threadIdx.x; i < tf_floats; i += blockDim.x) stf[i] = __ldg(D.tf + i);
+    __syncthreads();
+    const float3 bmin = make_float3(G.box_min[0], G.box_min[1], G.box_min[2]);
+    const float3 bsize = make_float3(G.box_size[0], G.box_size[1], G.box_size[2]);
+    const float inv_range = rf::rcp(rf::sub(D.dmax, D.dmin));
+    unsigned long long n_valid = 0;
+    const long long per_img = (long long)D.tw * D.th, total = per_img * D.nb;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int bl = int(i / per_img);
+        const int rem = int(i - (long long)bl * per_img);
+        const int y = D.y0 + rem / D.tw, x = D.x0 + rem % D.tw, b = D.b0 + bl;
+        const float* tfp = (D.tf_batch == 1) ? stf : (D.tf + (size_t)b * tf_floats);
+        const CamFrame cf = load_camera(D, b);
+        float4 pix = make_float4(0.f, 0.f, 0.f, 0.f);
+        float pix_depth = 0.f;
+        int last_steps = 0;
+        for (int s = 0; s < D.spp; ++s) {
+            const Ray r = make_ray(D, cf, x, y, s, bmin, bsize, D.spp);
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            float acc_depth = 0.f;
+            int steps = 0;
+            for (int k = 0;; ++k) {
+                const float t = rf::fma(D.stepsize, float(k), r.tmin);
+                bool valid = (t <= r.tmax);
+                if (D.early_out) valid = valid && (acc.w < D.alpha_early_out);
+                if (!valid) break;
+                const float value = grid_eval(G, rf::fma(r.dir.x, t, r.eye.x), rf::fma(r.dir.y, t, r.eye.y), rf::fma(r.dir.z, t, r.eye.z));
+                const float4 c = exact_shade(D, tfp, value, inv_range, true);
+                ++steps;
+                exact_blend(D, c, t, true, acc, acc_depth);
+            }
+            n_valid += steps; last_steps = steps;
+            pix.x = rf::add(pix.x, acc.x); pix.y = rf::add(pix.y, acc.y); pix.z = rf::add(pix.z, acc.z); pix.w = rf::add(pix.w, acc.w);
+            pix_depth = rf::fma(acc.w, acc_depth, pix_depth);
+        }
+        exact_write(D, b, x, y, pix, pix_depth, last_steps);
+    }
+    if (D.counters) {
+        for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);
+        if ((threadIdx.x & 31) == 0) { atomicAdd(D.counters + 0, n_valid); atomicAdd(D.counters + 1, n_valid); }
+    }
+}
+
+// IVolumeInterpolation::evaluate for the grid: positions (N,3) in the unit cube -> densities (N) (volume_interpolation.cpp:26-127)
+__global__ void eval_grid_kernel(const __grid_constant__ GridVolumeParams G, const float* __restrict__ pos, float* __restrict__ out, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = grid_eval(G, pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
 }
 
 } // namespace fvsrn

@@ -38,6 +38,9 @@ cudaError_t launch_h6(int, int, int, const NetParams&, const void*, LaunchCfg*, 
 cudaError_t launch_h8(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
 // reference-exact DVR kernel (kernels_exact.cuh, inst_exact.cu)
 cudaError_t launch_exact(int h16, const NetParams& P, const DvrParams& D, LaunchCfg* cfg, cudaStream_t s);
+// ground-truth density grid through the same marcher (kernels_exact.cuh dvr_grid_kernel / eval_grid_kernel)
+cudaError_t launch_dvr_grid(const GridVolumeParams& G, const DvrParams& D, int sm_count, cudaStream_t s);
+cudaError_t launch_eval_grid(const GridVolumeParams& G, const float* pos, float* out, long long n, cudaStream_t s);
 // tensor operators beside the fused path (inst_exact.cu): camera rays, transfer-function evaluation
 cudaError_t launch_generate_rays(const float* cam, float fov_y, float aspect, int B, int H, int W, float* start, float* dir, cudaStream_t s);
 cudaError_t launch_evaluate_tf(int tf_kind, const float* tf, int R, const float* density, float* out, long long n, float dmin, float dmax,

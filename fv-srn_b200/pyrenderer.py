@@ -384,6 +384,107 @@ class VolumeInterpolationNetwork:
         return out
 
 
+# ------------------------------------------------------------------------------------------------ ground-truth volume
+class Volume:
+    """renderer::Volume (volume.h:32-77): the .cvol container. `Volume(path)` loads, `Volume.from_numpy` wraps a density grid."""
+
+    def __init__(self, path: Optional[str] = None, _handle=None):
+        self._h = _handle
+        if path is not None:
+            with open(path, "rb") as f:
+                data = f.read()
+            h = C.c_void_p()
+            check(_lib.lib().fvsrn_volume_load_cvol(data, len(data), C.byref(h)))
+            self._h = h
+        self._prepared = None
+
+    @staticmethod
+    def from_bytes(data: bytes) -> "Volume":
+        h = C.c_void_p()
+        check(_lib.lib().fvsrn_volume_load_cvol(data, len(data), C.byref(h)))
+        return Volume(_handle=h)
+
+    @staticmethod
+    def from_numpy(density: np.ndarray, world_size=(1.0, 1.0, 1.0)) -> "Volume":
+        """density: (Z,Y,X) float32, x fastest (Volume::MipmapLevel::idx, volume.h:126-132)."""
+        a = np.ascontiguousarray(density, np.float32)
+        if a.ndim != 3:
+            raise RuntimeError("expected a (Z,Y,X) density grid")
+        h = C.c_void_p()
+        check(_lib.lib().fvsrn_volume_from_dense(a.ctypes.data, a.shape[2], a.shape[1], a.shape[0], C.byref((C.c_float * 3)(*world_size)), C.byref(h)))
+        return Volume(_handle=h)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                _lib.lib().fvsrn_volume_free(self._h); self._h = None
+        except Exception:
+            pass
+
+    def info(self, feature=0):
+        i = _lib.VolumeInfo()
+        check(_lib.lib().fvsrn_volume_get_info(self._h, feature, C.byref(i)))
+        return i
+
+    def num_features(self): return self.info().num_features
+    def world_size(self): return float3(*self.info().world_size)
+
+    def to_bytes(self) -> bytes:
+        n = C.c_size_t()
+        check(_lib.lib().fvsrn_volume_save_cvol(self._h, None, 0, C.byref(n)))
+        buf = C.create_string_buffer(n.value)
+        check(_lib.lib().fvsrn_volume_save_cvol(self._h, buf, n.value, C.byref(n)))
+        return buf.raw[:n.value]
+
+    def save(self, path, compression=0):
+        if compression:
+            raise RuntimeError("the B200 path writes uncompressed .cvol files")
+        with open(path, "wb") as f:
+            f.write(self.to_bytes())
+
+    def _ensure_prepared(self, feature=0):
+        dev = torch.cuda.current_device() if torch.cuda.is_available() else 0
+        if self._prepared != (dev, feature):
+            check(_lib.lib().fvsrn_volume_prepare(self._h, dev, feature, _stream_ptr() if torch.cuda.is_available() else None))
+            self._prepared = (dev, feature)
+
+
+class VolumeInterpolationGrid:
+    """renderer::VolumeInterpolationGrid with a Volume source, trilinear interpolation (volume_interpolation_grid.cpp:153-198,
+    renderer_volume_grid.cuh): the ground truth the SRN renders are compared with. Assign it to ImageEvaluatorSimple.volume."""
+
+    def __init__(self):
+        self._volume: Optional[Volume] = None
+        self.feature = 0
+
+    def setSource(self, volume: Volume, mipmap: int = 0):
+        if mipmap != 0:
+            raise RuntimeError("mipmap levels are not part of the B200 path")
+        self._volume = volume
+
+    set_source = setSource
+
+    def volume(self): return self._volume
+
+    def _require(self) -> Volume:
+        if self._volume is None:
+            raise RuntimeError("No volume specified, can't render!")
+        return self._volume
+
+    def box_min(self): return float3(*self._require().info(self.feature).box_min)
+    def box_size(self): return float3(*self._require().info(self.feature).box_size)
+
+    def evaluate(self, positions: torch.Tensor, directions=None) -> torch.Tensor:
+        v = self._require()
+        if not positions.is_cuda or positions.dim() != 2 or positions.shape[1] != 3 or positions.dtype != torch.float32:
+            raise RuntimeError("positions must be a CUDA float32 tensor of shape (N,3)")
+        positions = positions.contiguous()
+        v._ensure_prepared(self.feature)
+        out = torch.empty((positions.shape[0], 1), dtype=torch.float32, device=positions.device)
+        check(_lib.lib().fvsrn_evaluate_grid(v._h, positions.data_ptr(), out.data_ptr(), positions.shape[0], _stream_ptr()))
+        return out
+
+
 # ------------------------------------------------------------------------------------------------ TF modules
 class ITransferFunction:
     kind = -1
@@ -606,8 +707,32 @@ class ImageEvaluatorSimple:
         p.out_stride_b, p.out_stride_c, p.out_stride_y, p.out_stride_x = out_strides
         return p
 
+    def _render_grid(self, vol: "VolumeInterpolationGrid", width, height, out, fmt=0):
+        v = vol._require(); v._ensure_prepared(vol.feature)
+        cam = self.camera.get_parameters()
+        tf = self.ray_evaluator.tf._tensor()
+        B = cam.shape[0]
+        shape, dtype = {0: ((B, 8, height, width), torch.float32), 1: ((B, 4, height, width), torch.float32), 2: ((B, height, width), torch.int32),
+                        3: ((B, height, width, 4), torch.float16)}[fmt]
+        if out is None or tuple(out.shape) != shape or out.dtype != dtype or not out.is_cuda:
+            out = (torch.empty if self.tile is None else torch.zeros)(shape, dtype=dtype, device="cuda")
+        strides = out.stride() if fmt <= 1 else (out.stride(0) // (4 if fmt == 3 else 1), 0, out.stride(1) // (4 if fmt == 3 else 1), 1)
+        p = self._params(width, height, cam, tf, strides)
+        p.output_format, p.channel_mode = fmt, self._channel_index()
+        p.tonemap, p.max_exposure = int(bool(self.use_tonemapping)), float(self.get_exposure_for_tonemapping() if self.use_tonemapping else 1.0)
+        if self.collect_statistics:
+            self.last_step_counts = torch.zeros((B, height, width), dtype=torch.int32, device="cuda")
+            self.last_counters = torch.zeros(2, dtype=torch.int64, device="cuda")
+            p.step_count_dev = self.last_step_counts.data_ptr(); p.counters_dev = self.last_counters.data_ptr()
+        check(_lib.lib().fvsrn_render_dvr_grid(v._h, C.byref(p), out.data_ptr(), _stream_ptr()))
+        if fmt == 0:
+            self._last_frame = out
+        return out
+
     def render(self, width: int, height: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         vol = self._volume()
+        if isinstance(vol, VolumeInterpolationGrid):
+            return self._render_grid(vol, width, height, out)
         net = vol._require()
         net._ensure_prepared()
         cam = self.camera.get_parameters()
@@ -682,6 +807,8 @@ class ImageEvaluatorSimple:
             return self.render(width, height, out)
         if self.use_tonemapping and not self.fix_max_exposure:
             raise RuntimeError("fused tonemapping needs fix_max_exposure (the frame-wide maximum is not known inside the frame)")
+        if isinstance(self._volume(), VolumeInterpolationGrid):
+            return self._render_grid(self._volume(), width, height, out, fmt)
         vol = self._volume(); net = vol._require(); net._ensure_prepared()
         cam = self.camera.get_parameters()
         is_rgbo = net._info().channels_out == 4

@@ -235,6 +235,35 @@ int  fvsrn_generate_rays(const float* camera_matrix_dev, int batch, float fov_y_
 int  fvsrn_evaluate_tf(int tf_kind, const float* tf_dev, int tf_resolution, const float* densities_dev, float* colors_dev,
                        int64_t n, float density_min, float density_max, float stepsize, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Ground-truth volume: the .cvol container and the density grid rendered through the SAME marcher - what the
+ * reference's eval scripts compare the SRN renders against.
+ *   replaces renderer::Volume (load / save, renderer/volume.cpp:278-384, 618-800; format renderer/volume.h:42-77),
+ *   VolumeInterpolationGrid (texture path, trilinear; renderer/renderer_volume_grid.cuh:110-139, 196-231; box
+ *   = +-worldSize/2, volume_interpolation_grid.cpp:193-198) and ImageEvaluatorSimple::render with that volume.
+ * ------------------------------------------------------------------------------------------ */
+typedef struct fvsrn_volume fvsrn_volume;   /* opaque: renderer::Volume + the 3-D texture of one feature */
+typedef struct fvsrn_volume_info {
+    int num_features;
+    int feature;                /* the feature the fields below describe */
+    int size_x, size_y, size_z, channels;
+    int data_type;              /* Volume::DataType: 0 uchar, 1 ushort, 2 float */
+    float world_size[3];
+    float box_min[3], box_size[3];
+} fvsrn_volume_info;
+int  fvsrn_volume_load_cvol(const void* bytes, size_t n, fvsrn_volume** out);      /* "CVOL" v1 and legacy "cvol", raw or LZ4 */
+int  fvsrn_volume_save_cvol(const fvsrn_volume* vol, void* buf, size_t cap, size_t* written);  /* two-call pattern; uncompressed */
+/* density (Z,Y,X) fp32, x fastest (Volume::MipmapLevel::idx) */
+int  fvsrn_volume_from_dense(const float* density_host, int size_x, int size_y, int size_z, const float world_size[3], fvsrn_volume** out);
+int  fvsrn_volume_get_info(const fvsrn_volume* vol, int feature, fvsrn_volume_info* info);
+void fvsrn_volume_free(fvsrn_volume* vol);
+/* upload one (1-channel) feature as a 3-D texture: MipmapLevel::copyCpuToGpu, volume.cpp:120-166 */
+int  fvsrn_volume_prepare(fvsrn_volume* vol, int device, int feature, void* stream);
+/* the DVR frame of the prepared feature; same parameters, output formats and step / sample counters as fvsrn_render_dvr */
+int  fvsrn_render_dvr_grid(fvsrn_volume* vol, const fvsrn_dvr_params* p, float* out_dev, void* stream);
+/* IVolumeInterpolation::evaluate for the grid: positions (N,3) in [0,1]^3 -> densities (N) */
+int  fvsrn_evaluate_grid(fvsrn_volume* vol, const float* positions_dev, float* out_dev, int64_t n, void* stream);
+
 /* Launch diagnostics (stand-in for compute_max_warps / KernelLoader occupancy query) */
 typedef struct fvsrn_query_info {
     int device, sm_count;

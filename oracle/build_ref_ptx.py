@@ -44,6 +44,30 @@ TF_TYPES = {"piecewise": ("::kernel::TransferFunctionPiecewise", "renderer_tf_pi
             "texture": ("::kernel::TransferFunctionTexture", "renderer_tf_texture.cuh")}
 
 
+def grid_source(early_out=1, blend_mode=1, tf="piecewise", interpolation=1):
+    """The same DVR kernel over the ground-truth density grid: VolumeInterpolationGrid::getDefines for a .cvol density feature
+    (volume_interpolation_grid.cpp:913-993: texture path, trilinear, new grid-resolution behaviour), per-thread tracing."""
+    d = [
+        ("KERNEL_DOUBLE_PRECISION", 0), ("KERNEL_SYNCHRONIZED_TRACING", 0),
+        ("VOLUME_INTERPOLATION_GRID__INTERPOLATION", interpolation), ("VOLUME_INTERPOLATION_GRID__TEXTURE_TYPE", "float"),
+        ("VOLUME_INTERPOLATION_GRID__TEXTURE_EXTRACTOR", "getDirect"), ("VOLUME_INTERPOLATION_GRID__GRID_RESOLUTION_OLD_BEHAVIOR", 0),
+        ("RAY_EVALUATION_STEPPING__VOLUME_INTERPOLATION_T", "::kernel::VolumeInterpolationGrid"),
+        ("RAY_EVALUATION_STEPPING__TRANSFER_FUNCTION_T", TF_TYPES[tf][0]),
+        ("RAY_EVALUATION_STEPPING__BLENDING_T", "::kernel::Blending"),
+        ("RAY_EVALUATION_STEPPING__BRDF_T", "::kernel::BRDFLambert"),
+        ("RAY_EVALUATION_STEPPING__ENABLE_EARLY_OUT", early_out), ("RAY_EVALUATION_STEPPING__SKIP_TRANSFER_FUNCTION", 0),
+        ("BLENDING_MODE", blend_mode), ("BRDF_LAMBERT_LIGHT_TYPE", 1),
+    ]
+    src = "".join(f"#define {k} {v}\n" for k, v in d)
+    for h in ("renderer_camera.cuh", "renderer_volume_grid.cuh", TF_TYPES[tf][1], "renderer_blending.cuh",
+              "renderer_brdf_lambert.cuh", "renderer_ray_evaluation_stepping_dvr.cuh"):
+        src += f'#include "{h}"\n'
+    src += "#define IMAGE_EVALUATOR__CAMERA_T ::kernel::CameraReferenceFrame\n"
+    src += "#define IMAGE_EVALUATOR__RAY_EVALUATOR_T ::kernel::RayEvaluationSteppingDvr\n"
+    src += '#include "renderer_image_evaluator_simple.cuh"\n'
+    return src
+
+
 def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, early_out=1, blend_mode=1, first_last_shared=0,
                 encoding=0, tf="piecewise"):
     """The translation unit IImageEvaluator::getKernel + ImageEvaluatorSimple::render assemble (SURVEY App. F).
@@ -91,7 +115,7 @@ STEP_PATCHES = {
 }
 
 
-def compile_ptx(src, patch_steps=False, tf="piecewise"):
+def compile_ptx(src, patch_steps=False, tf="piecewise", volume_symbol="&volumeInterpolationTensorcoresParameters"):
     from cuda.bindings import nvrtc
 
     def ck(r):
@@ -113,7 +137,7 @@ def compile_ptx(src, patch_steps=False, tf="piecewise"):
     headers += [SHIM_FORWARD.encode(), b"#pragma once\n"]
     names += [b"forward.h", b"forward_vector.h"]
     prog = ck(nvrtc.nvrtcCreateProgram(src.encode(), b"main.cu", len(headers), headers, names))
-    names_all = NAMES + [TF_NAMES[tf]]
+    names_all = [n if n != "&volumeInterpolationTensorcoresParameters" else volume_symbol for n in NAMES] + [TF_NAMES[tf]]
     for n in names_all:
         ck(nvrtc.nvrtcAddNameExpression(prog, n.encode()))
     cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
@@ -158,6 +182,11 @@ def main():
             open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
             meta[name] = dict(cfg, lowered=lowered, ptx=name + ".ptx", step_count_patch=patch)
             print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['ImageEvaluatorSimpleKernel']}")
+    for name, patch in (("grid_trilinear", False), ("grid_trilinear_steps", True)):
+        ptx, lowered = compile_ptx(grid_source(), patch_steps=patch, volume_symbol="&volumeInterpolationGridParameters")
+        open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
+        meta[name] = dict(grid=True, lowered=lowered, ptx=name + ".ptx", step_count_patch=patch)
+        print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX")
     json.dump(meta, open(os.path.join(OUT, "ref_kernels.json"), "w"), indent=1)
     return 0
 

@@ -231,3 +231,80 @@ class ReferenceDvrKernel:
             e0.record(); launch(); e1.record(); torch.cuda.synchronize()
             ms += e0.elapsed_time(e1)
         return out, ms / timing_iters
+
+
+class ReferenceGridDvrKernel:
+    """The reference's DVR kernel over a ground-truth density grid (VolumeInterpolationGrid, texture path, trilinear;
+    oracle/build_ref_ptx.py grid_source): same camera / DVR / TF constant blocks, volumeInterpolationGridParameters =
+    {tex; int3 resolution-1; float3 boxMin, boxSize, normalStep, normalScale} (renderer_volume_grid.cuh:26-40, host side
+    volume_interpolation_grid.cpp:1050-1110). density: (Z,Y,X) float32 or uint8 (read as normalised float)."""
+
+    def __init__(self, density, world_size=(1.0, 1.0, 1.0), patched_steps=False):
+        import torch
+        from cuda.bindings import driver as d
+        self.torch, self.drv = torch, d
+        meta = json.load(open(os.path.join(REF_DIR, "ref_kernels.json")))
+        m = meta["grid_trilinear_steps" if patched_steps else "grid_trilinear"]
+        torch.cuda.init(); torch.zeros(1, device="cuda")
+        self.module = _ck(d.cuModuleLoadData(open(os.path.join(REF_DIR, m["ptx"]), "rb").read() + b"\0"))
+        low = m["lowered"]
+        self.func = _ck(d.cuModuleGetFunction(self.module, low["ImageEvaluatorSimpleKernel"].encode()))
+        self.g_cam = _ck(d.cuModuleGetGlobal(self.module, low["&cameraReferenceFrameParameters"].encode()))
+        self.g_vol = _ck(d.cuModuleGetGlobal(self.module, low["&volumeInterpolationGridParameters"].encode()))
+        self.g_dvr = _ck(d.cuModuleGetGlobal(self.module, low["&rayEvaluationSteppingDvrParameters"].encode()))
+        self.g_tf = _ck(d.cuModuleGetGlobal(self.module, low["&transferFunctionPiecewiseParameters"].encode()))
+        host = np.ascontiguousarray(density)
+        Z, Y, X = host.shape
+        is_float = host.dtype != np.uint8
+        desc = d.CUDA_ARRAY3D_DESCRIPTOR()
+        desc.Width, desc.Height, desc.Depth = X, Y, Z
+        desc.Format = d.CUarray_format.CU_AD_FORMAT_FLOAT if is_float else d.CUarray_format.CU_AD_FORMAT_UNSIGNED_INT8
+        desc.NumChannels = 1; desc.Flags = 0
+        arr = _ck(d.cuArray3DCreate(desc))
+        bpt = 4 if is_float else 1
+        cp = d.CUDA_MEMCPY3D()
+        cp.srcMemoryType = d.CUmemorytype.CU_MEMORYTYPE_HOST; cp.srcHost = host.ctypes.data; cp.srcPitch = X * bpt; cp.srcHeight = Y
+        cp.dstMemoryType = d.CUmemorytype.CU_MEMORYTYPE_ARRAY; cp.dstArray = arr
+        cp.WidthInBytes = X * bpt; cp.Height = Y; cp.Depth = Z
+        _ck(d.cuMemcpy3D(cp))
+        res = d.CUDA_RESOURCE_DESC(); res.resType = d.CUresourcetype.CU_RESOURCE_TYPE_ARRAY; res.res.array.hArray = arr
+        td = d.CUDA_TEXTURE_DESC()
+        td.addressMode = [d.CUaddress_mode.CU_TR_ADDRESS_MODE_CLAMP] * 3
+        td.filterMode = d.CUfilter_mode.CU_TR_FILTER_MODE_LINEAR
+        td.flags = 0                                        # unnormalised coordinates; integer texels read as normalised floats
+        tex = int(_ck(d.cuTexObjectCreate(res, td, None)))
+        self._keep = [arr, host]
+        ws = np.asarray(world_size, np.float64)
+        voxel = ws / np.array([X, Y, Z], np.float64)
+        b = np.array([tex], np.uint64).tobytes() + np.array([X - 1, Y - 1, Z - 1], np.int32).tobytes() \
+            + (-ws / 2).astype(np.float32).tobytes() + ws.astype(np.float32).tobytes() \
+            + np.ones(3, np.float32).tobytes() + (0.5 / voxel).astype(np.float32).tobytes()
+        b += b"\0" * (int(self.g_vol[1]) - len(b))
+        assert len(b) == int(self.g_vol[1]) and len(b) in (68, 72), len(b)
+        _ck(d.cuMemcpyHtoD(self.g_vol[0], b, len(b)))
+        self.block = 256
+        sms = torch.cuda.get_device_properties(0).multi_processor_count
+        self.max_grid = max(1, _ck(d.cuOccupancyMaxActiveBlocksPerMultiprocessor(self.func, self.block, 0))) * sms
+
+    def render(self, width, height, camera, fov_y, stepsize, tf, alpha_early_out=1 - 1e-5, density_min=0.0, density_max=1.0):
+        torch, d = self.torch, self.drv
+        cam = torch.as_tensor(np.ascontiguousarray(camera, np.float32)).reshape(-1, 3, 3).cuda()
+        tft = torch.as_tensor(np.ascontiguousarray(tf, np.float32)).cuda()
+        tft = tft.reshape(-1, tft.shape[-2], tft.shape[-1])
+        B = cam.shape[0]
+        cp = _CameraParams(); cp.fovY = fov_y; cp.aspect = float(width) / float(height); cp.matrix = _read3(cam)
+        _ck(d.cuMemcpyHtoD(self.g_cam[0], bytes(cp), C.sizeof(cp)))
+        _ck(d.cuMemcpyHtoD(self.g_dvr[0], np.array([stepsize, alpha_early_out, density_min, density_max], np.float32).tobytes(), 16))
+        ta = _read3(tft)
+        _ck(d.cuMemcpyHtoD(self.g_tf[0], bytes(ta), C.sizeof(ta)))
+        out = torch.empty((B, 8, height, width), dtype=torch.float32, device="cuda")
+        oa = _Accessor4(); oa.data = out.data_ptr()
+        for i in range(4):
+            oa.sizes[i] = out.shape[i]; oa.strides[i] = out.stride(i)
+        vs = _Dim3(width, height, B)
+        samples, time, bg = C.c_int(1), C.c_uint(0), _Accessor4()
+        args = (C.c_void_p * 5)(C.addressof(vs), C.addressof(oa), C.addressof(samples), C.addressof(time), C.addressof(bg))
+        grid = min((width * height * B + self.block - 1) // self.block, self.max_grid)
+        _ck(d.cuLaunchKernel(self.func, grid, 1, 1, self.block, 1, 1, 0, torch.cuda.current_stream().cuda_stream, C.addressof(args), 0))
+        torch.cuda.synchronize()
+        return out
