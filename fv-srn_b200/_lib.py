@@ -14,7 +14,7 @@ SYMBOLS = [
     "fvsrn_network_set_output_mode", "fvsrn_network_add_layer", "fvsrn_network_set_latent_grid_layout",
     "fvsrn_network_set_time_grid", "fvsrn_network_set_ensemble_grid", "fvsrn_network_set_box", "fvsrn_network_get_box",
     "fvsrn_network_valid", "fvsrn_network_num_parameters", "fvsrn_network_compute_max_warps",
-    "fvsrn_network_set_time_and_ensemble", "fvsrn_network_get_info", "fvsrn_network_set_kernel_mode", "fvsrn_network_get_kernel_mode", "fvsrn_network_prepare",
+    "fvsrn_network_set_time_and_ensemble", "fvsrn_network_set_gradient_mode", "fvsrn_network_get_info", "fvsrn_network_set_kernel_mode", "fvsrn_network_get_kernel_mode", "fvsrn_network_prepare",
     "fvsrn_network_clear_gpu_resources", "fvsrn_evaluate", "fvsrn_evaluate_host", "fvsrn_render_dvr",
     "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_extract_color_ex", "fvsrn_generate_rays", "fvsrn_evaluate_tf", "fvsrn_query",
     "fvsrn_volume_load_cvol", "fvsrn_volume_save_cvol", "fvsrn_volume_from_dense", "fvsrn_volume_get_info", "fvsrn_volume_free",
@@ -27,7 +27,8 @@ class NetworkInfo(C.Structure):
         "has_time", "has_direction", "num_fourier", "direction_in_fourier", "output_mode", "num_layers",
         "hidden_channels", "latent_channels", "grid_x", "grid_y", "grid_z", "time_min", "time_num", "time_step",
         "ensemble_min", "ensemble_num", "grid_encoding", "activation")] + [
-        ("activation_param", C.c_float), ("channels_out", C.c_int)]
+        ("activation_param", C.c_float), ("channels_out", C.c_int), ("gradient_mode", C.c_int),
+        ("finite_differences_stepsize", C.c_float)]
 
 
 class DvrParams(C.Structure):
@@ -42,6 +43,9 @@ class DvrParams(C.Structure):
         ("out_stride_b", C.c_int64), ("out_stride_c", C.c_int64), ("out_stride_y", C.c_int64), ("out_stride_x", C.c_int64),
         ("step_count_dev", C.c_void_p), ("counters_dev", C.c_void_p),
         ("output_format", C.c_int), ("channel_mode", C.c_int), ("tonemap", C.c_int), ("max_exposure", C.c_float),
+        ("brdf_flags", C.c_int), ("light_type", C.c_int), ("light", C.c_float * 3),
+        ("brdf_magnitude_scaling", C.c_float), ("brdf_ambient", C.c_float), ("brdf_specular", C.c_float),
+        ("brdf_magnitude_center", C.c_float), ("brdf_magnitude_radius", C.c_float), ("brdf_specular_exponent", C.c_int),
     ]
 
 
@@ -90,6 +94,7 @@ def lib():
         "fvsrn_network_num_parameters": [vp],
         "fvsrn_network_compute_max_warps": [vp, i, i],
         "fvsrn_network_set_time_and_ensemble": [vp, f, i],
+        "fvsrn_network_set_gradient_mode": [vp, i, f],
         "fvsrn_network_get_info": [vp, C.POINTER(NetworkInfo)],
         "fvsrn_network_set_kernel_mode": [vp, i],
         "fvsrn_network_get_kernel_mode": [vp],

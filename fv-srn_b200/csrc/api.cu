@@ -59,6 +59,9 @@ struct fvsrn_network {
     int tc_off_w0 = 0, tc_off_wh = 0, tc_off_wlast = 0, tc_off_fourier = 0;
     int tc_activation = 0;      // activation code the tcgen05 kernels run (SnakeAlt may become its pre-scaled form)
     int kernel_mode = FVSRN_KERNEL_TCGEN05;
+    int gradient_mode = FVSRN_GRADIENT_OFF_OR_DIRECT;      // VolumeInterpolationNetwork::gradientMode_ (a module setting, not part of .volnet)
+    float fd_stepsize = 1.f / 256.f;                       // finiteDifferencesStepsize_, volume_interpolation_network.cpp:1423
+    int off_wlast_rows = 0;
     int H16 = 0, GC16 = 0, dir = 0, num_hidden = 0, activation = 0; float act_param = 1.f;
     std::vector<DeviceGrid> d_time, d_ens;
     unsigned int* d_tile_counter = nullptr;   // ring of work-queue counters (one per launch in flight)
@@ -113,7 +116,6 @@ void build_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
     std::string why;
     if (!n.valid(&why)) throw std::runtime_error("scene network is not valid: " + why);
     if (n.num_fourier <= 0) throw std::runtime_error("unsupported on the B200 path: networks without Fourier features");
-    if (n.output_mode > OUT_RGBO_DIRECT) throw std::runtime_error(std::string("unsupported on the B200 path: output mode ") + kOutputModeNames[n.output_mode]);
     const int H = n.input_channels_out();
     const int GC = n.latent_channels();
     if (!(H == 32 || H == 48 || H == 64 || H == 96 || H == 128))
@@ -175,6 +177,14 @@ void build_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
         blob.insert(blob.end(), p, p + 2 * n.fourier.size());
     }
     while (blob.size() % 16) blob.push_back(0);
+    // the last layer once more as plain rows [cin][8 outputs] for the sequential fp16 chains of the reference-exact mode
+    // (4 / 6-output last layers, renderer_volume_tensorcores.cuh:1045-1052, 1106-1115)
+    h->off_wlast_rows = int(blob.size());
+    for (int k = 0; k < H; ++k)
+        for (int o = 0; o < 8; ++o) {
+            const uint16_t v = o < last.cout ? last.w(o, k) : uint16_t(0);
+            blob.push_back(uint8_t(v & 0xff)); blob.push_back(uint8_t(v >> 8));
+        }
     h->blob_bytes = int(blob.size());
 }
 
@@ -290,10 +300,11 @@ void fill_encoding(NetParams& P, int g, const DeviceGrid& A, const DeviceGrid& B
 }
 
 // device-side view of the network for a given absolute time / ensemble (reference fillConstantMemory :1290-1352)
-NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, bool unit_box) {
+NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, bool unit_box, bool tc) {
     const Network& n = h->net;
     NetParams P{};
-    if (h->kernel_mode == FVSRN_KERNEL_TCGEN05) {
+    P.gradient_mode = h->gradient_mode; P.fd_stepsize = h->fd_stepsize; P.off_wlast_rows = h->off_wlast_rows;
+    if (tc) {
         P.blob = h->d_tc_blob; P.blob_bytes = h->tc_blob_bytes;
         P.off_w0 = h->tc_off_w0; P.off_wh = h->tc_off_wh; P.off_wlast = h->tc_off_wlast; P.off_bias = 0; P.off_fourier = h->tc_off_fourier;
     } else {
@@ -301,7 +312,7 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
         P.off_w0 = h->off_w0; P.off_wh = h->off_wh; P.off_wlast = h->off_wlast; P.off_bias = h->off_bias; P.off_fourier = h->off_fourier;
     }
     P.num_hidden = h->num_hidden; P.act_param = h->act_param;
-    P.activation = h->kernel_mode == FVSRN_KERNEL_TCGEN05 ? h->tc_activation : h->activation;
+    P.activation = tc ? h->tc_activation : h->activation;
     P.output_mode = n.output_mode; P.has_time = n.has_time ? 1 : 0; P.dir_in_fourier = n.direction_in_fourier ? 1 : 0;
     P.time_value = 0.f;
     int g = 0;
@@ -537,6 +548,17 @@ int fvsrn_network_set_time_and_ensemble(fvsrn_network* net, float time, int ense
     return 0;
 }
 
+int fvsrn_network_set_gradient_mode(fvsrn_network* net, int gradient_mode, float finite_differences_stepsize) {
+    if (!net) return fail("null network handle");
+    if (gradient_mode == 2) return fail("unsupported on the B200 path: the adjoint gradient mode (use finite differences)");
+    if (gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT && gradient_mode != FVSRN_GRADIENT_FINITE_DIFFERENCES) return fail("unknown gradient mode");
+    if (gradient_mode == FVSRN_GRADIENT_FINITE_DIFFERENCES && !(finite_differences_stepsize > 0.f)) return fail("finite_differences_stepsize must be positive");
+    std::lock_guard<std::mutex> lock(net->mu);
+    net->gradient_mode = gradient_mode;
+    if (finite_differences_stepsize > 0.f) net->fd_stepsize = finite_differences_stepsize;
+    return 0;
+}
+
 int fvsrn_network_set_kernel_mode(fvsrn_network* net, int mode) {
     if (!net) return fail("null network handle");
     if (mode != FVSRN_KERNEL_MMA_SYNC && mode != FVSRN_KERNEL_TCGEN05 && mode != FVSRN_KERNEL_REFERENCE_EXACT) return fail("unknown kernel mode");
@@ -561,6 +583,7 @@ int fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info) {
     info->activation = n.layers.empty() ? ACT_NONE : n.layers[0].activation;
     info->activation_param = n.layers.empty() ? 1.f : n.layers[0].activation_param;
     info->channels_out = kOutputModeChannelsOut[n.output_mode];
+    info->gradient_mode = net->gradient_mode; info->finite_differences_stepsize = net->fd_stepsize;
     return 0;
 }
 
@@ -754,9 +777,10 @@ void do_evaluate(fvsrn_network* h, const float* pos, const float* dir, float* ou
     if (h->net.has_direction && !dir) throw std::runtime_error("the network uses directions, but no directions were passed");
     if (h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT) throw std::runtime_error("the reference-exact kernel mode covers the DVR frame only");
     // reference volume_interpolation.cpp:45-48: positions are in the unit cube
-    const NetParams P = make_net_params(h, h->net.current_time, h->net.current_ensemble, true);
+    // the tcgen05 kernels cover the 1- and 4-channel outputs; gradient / curvature networks run on the mma.sync family
+    const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05 && h->net.output_mode <= OUT_RGBO_DIRECT;
+    const NetParams P = make_net_params(h, h->net.current_time, h->net.current_ensemble, true, tc);
     EvalParams E{pos, dir, out, (long long)n, kOutputModeChannelsOut[h->net.output_mode]};
-    const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05;
     LaunchCfg cfg; cfg.sm_count = h->sm_count;
     cfg.max_blocks = tc ? (n + 2 * kTcComputeThreads - 1) / (2 * kTcComputeThreads) : ((n + 31) / 32 + kWarpsPerBlock - 1) / kWarpsPerBlock;
     launch_fn fn = pick_launcher(h->H16);
@@ -801,6 +825,15 @@ DvrParams fill_dvr_params(const fvsrn_dvr_params* p, float* out, bool is_rgbo, c
     D.out = out; D.sb = p->out_stride_b; D.sc = p->out_stride_c; D.sy = p->out_stride_y; D.sx = p->out_stride_x;
     D.step_count = p->step_count_dev; D.counters = p->counters_dev;
     D.out_format = p->output_format; D.channel_mode = p->channel_mode; D.tonemap = p->tonemap; D.max_exposure = p->max_exposure;
+    if (p->brdf_flags & ~(FVSRN_BRDF_MAGNITUDE_SCALING | FVSRN_BRDF_PHONG)) throw std::runtime_error("unknown BRDF flags");
+    if (p->brdf_flags) {
+        if (is_rgbo) throw std::runtime_error("BRDF shading needs normals: colour networks provide none");
+        if (p->light_type != FVSRN_LIGHT_POINT && p->light_type != FVSRN_LIGHT_DIRECTIONAL) throw std::runtime_error("unknown light type");
+        D.brdf_flags = p->brdf_flags; D.light_type = p->light_type;
+        for (int i = 0; i < 3; ++i) D.light[i] = p->light[i];
+        D.brdf_mag_scaling = p->brdf_magnitude_scaling; D.brdf_ambient = p->brdf_ambient; D.brdf_specular = p->brdf_specular;
+        D.brdf_mag_center = p->brdf_magnitude_center; D.brdf_mag_radius = p->brdf_magnitude_radius; D.brdf_spec_exp = p->brdf_specular_exponent;
+    }
     if (D.out_format < FVSRN_OUTPUT_RAW8_F32 || D.out_format > FVSRN_OUTPUT_RGBA_F16) throw std::runtime_error("unknown output format");
     if (D.out_format != FVSRN_OUTPUT_RAW8_F32) {
         if (D.channel_mode == FVSRN_CHANNEL_DEPTH) throw std::runtime_error("ChannelDepth needs the frame's min/max depth: render the raw tensor and call fvsrn_extract_color_ex");
@@ -818,14 +851,21 @@ namespace {
 
 void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStream_t s) {
     require_prepared(h);
-    const bool is_rgbo = h->net.output_mode >= OUT_RGBO;
-    const DvrParams D = fill_dvr_params(p, out, is_rgbo, h->d_blob);
-    const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05;
+    const int om = h->net.output_mode;
+    const bool is_rgbo = om == OUT_RGBO || om == OUT_RGBO_DIRECT;
+    DvrParams D = fill_dvr_params(p, out, is_rgbo, h->d_blob);
+    // normals: predicted by the network, finite differences, or none (the normal channels stay zero). The
+    // reference runs its finite differences whenever the module asks for them, shaded or not
+    // (volume_interpolation_network.cpp:1146 is commented out) - so do we.
+    if (h->gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT && is_rgbo) throw std::runtime_error("gradient modes need a density network (the reference's evalNormal asserts it)");
+    D.normals = (om >= OUT_DENSITYGRAD || h->gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT || D.brdf_flags) ? 1 : 0;
+    // the tcgen05 kernels march density / colour networks without normals; everything with normals runs on the mma.sync family
+    const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05 && !D.normals;
     const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT;
     if (exact) {    // the shapes the reference kernels this mode is validated against cover (kernels_exact.cuh)
         const Network& n = h->net;
-        if (n.output_mode != OUT_DENSITY_DIRECT || n.has_time || n.has_direction || h->GC16 != 1)
-            throw std::runtime_error("reference-exact mode: density:direct networks with one 16-channel latent grid, without time/direction input");
+        if (is_rgbo || n.has_time || n.has_direction || h->GC16 != 1)
+            throw std::runtime_error("reference-exact mode: density-type networks with one 16-channel latent grid, without time/direction input");
         if (p->tf_kind != FVSRN_TF_PIECEWISE && p->tf_kind != FVSRN_TF_TEXTURE) throw std::runtime_error("reference-exact mode: piecewise or texture transfer function");
         for (size_t i = 0; i < h->d_time.size(); ++i) ensure_tex32(h->d_time[i], n.time_grids[i]);
         for (size_t i = 0; i < h->d_ens.size(); ++i) ensure_tex32(h->d_ens[i], n.ensemble_grids[i]);
@@ -833,7 +873,7 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     launch_fn fn = pick_launcher(h->H16);
     if (!fn) throw std::runtime_error("no kernel for this hidden width");
     auto launch = [&](int b0, int nb, float time_abs, cudaStream_t ls) {
-        const NetParams P = make_net_params(h, time_abs, h->net.current_ensemble, false);
+        const NetParams P = make_net_params(h, time_abs, h->net.current_ensemble, false, tc);
         DvrParams d = D; d.b0 = b0; d.nb = nb;      // the launcher lays the tile raster of its kernel over the rectangle
         d.tile_counter = next_tile_counter(h, ls);
         LaunchCfg cfg; cfg.sm_count = h->sm_count;
@@ -922,7 +962,7 @@ int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* 
     if (p->out_stride_x != 1 || p->out_stride_y != W || (planes > 1 && p->out_stride_c != W * H) || p->out_stride_b != planes * W * H)
         return fail("fvsrn_render_dvr_host needs a contiguous output: (B,8,H,W) / (B,4,H,W) fp32 or (B,H,W) packed pixels");
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    const bool is_rgbo = net->net.output_mode >= OUT_RGBO;
+    const bool is_rgbo = net->net.output_mode == OUT_RGBO || net->net.output_mode == OUT_RGBO_DIRECT;
     const size_t cam_b = size_t(p->batch) * 36;
     const int tf_floats = is_rgbo ? 0 : (p->tf_kind == 0 ? p->tf_resolution * 5 : (p->tf_kind == 1 ? p->tf_resolution * 4 : 2)) * p->tf_batch;
     const size_t tf_off = ((cam_b + 15) / 16) * 16, img_off = ((tf_off + size_t(tf_floats) * 4 + 255) / 256) * 256;
@@ -1037,11 +1077,12 @@ int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     DeviceGuard guard(net->device);
     require_prepared(net);
     if (!info) return fail("null argument");
-    const NetParams P = make_net_params(net, net->net.current_time, net->net.current_ensemble, false);
+    const bool tc = net->kernel_mode == FVSRN_KERNEL_TCGEN05 && net->net.output_mode <= OUT_RGBO_DIRECT &&
+                    (kernel != 0 || net->gradient_mode == FVSRN_GRADIENT_OFF_OR_DIRECT);
+    const NetParams P = make_net_params(net, net->net.current_time, net->net.current_ensemble, false, tc);
     LaunchCfg cfg; cfg.sm_count = net->sm_count; cfg.query_only = 1;
     launch_fn fn = pick_launcher(net->H16);
     if (!fn) return fail("no kernel for this hidden width");
-    const bool tc = net->kernel_mode == FVSRN_KERNEL_TCGEN05;
     DvrParams dq{}; dq.tf_kind = 0; dq.tf_R = 8;   // a typical piecewise TF: the DVR kernels size their shared memory from it
     dq.tw = 1024; dq.th = 1024; dq.nb = 1;
     if (net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact(net->H16, P, dq, &cfg, nullptr));

@@ -38,6 +38,15 @@ struct DvrParams {
     int channel_mode;                   // IImageEvaluator::ChannelMode: 0 mask, 1 normal, 3 colour (2 = depth is not fusable)
     int tonemap;                        // ChannelColor only: ACES filmic curve + gamma (TonemappingKernel)
     float max_exposure;
+    // normals and shading. normals != 0: the launch evaluates normals - a network that predicts them
+    // (densitygrad* / densitycurvature* output modes), finite differences (NetParams::gradient_mode) or a BRDF that needs them
+    int normals;
+    // BRDFLambert, renderer_brdf_lambert.cuh:19-38 (scalar parameters): bit 0 gradient-magnitude scaling, bit 1 Phong
+    int brdf_flags;
+    int light_type;                     // BRDF_LIGHT_POINT 0 / BRDF_LIGHT_DIRECTION 1
+    float light[3];                     // position or direction
+    float brdf_mag_scaling, brdf_ambient, brdf_specular, brdf_mag_center, brdf_mag_radius;
+    int brdf_spec_exp;
 };
 
 // ground-truth density grid (kernels in kernels_exact.cuh)
@@ -99,6 +108,7 @@ FV_RF2(add, "add.ftz.f32") FV_RF2(sub, "sub.ftz.f32") FV_RF2(mul, "mul.ftz.f32")
 FV_RF2(fmin, "min.ftz.f32") FV_RF2(fmax, "max.ftz.f32")
 FV_RF1(rcp, "rcp.approx.ftz.f32") FV_RF1(rsqrt, "rsqrt.approx.ftz.f32") FV_RF1(sin, "sin.approx.ftz.f32")
 FV_RF1(cos, "cos.approx.ftz.f32") FV_RF1(ex2, "ex2.approx.ftz.f32") FV_RF1(floor, "cvt.rmi.ftz.f32.f32")
+FV_RF1(lg2, "lg2.approx.ftz.f32") FV_RF1(neg, "neg.ftz.f32") FV_RF1(abs, "abs.ftz.f32")
 __device__ __forceinline__ float fma(float a, float b, float c) { float r; asm("fma.rn.ftz.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
 // (a < b) ? a : b and (a > b) ? a : b as the reference's fminf/fmaxf-free helper_math compiles (setp + selp)
 __device__ __forceinline__ float sel_lt(float a, float b) { return (a < b) ? a : b; }
@@ -158,12 +168,18 @@ __device__ __forceinline__ Ray make_ray(const DvrParams& D, const CamFrame& c, i
     return r;
 }
 
+// density of a density-type network from its raw first output (renderer_volume_tensorcores.cuh:1073-1158): the plain modes
+// squash it with a sigmoid, the ":direct" / ":cubic" modes pass it on
+__device__ __forceinline__ bool output_mode_is_colour(int m) { return m == D_OUT_RGBO || m == D_OUT_RGBO_DIRECT; }
+__device__ __forceinline__ bool output_mode_has_sigmoid(int m) { return m == D_OUT_DENSITY || m == D_OUT_DENSITY_GRADIENT || m == D_OUT_DENSITY_CURVATURE; }
+__device__ __forceinline__ float density_from_output(int mode, float o0) { return output_mode_has_sigmoid(mode) ? sigmoidf_(o0) : o0; }
+
 // network output -> colour + absorption of one sample (TF or colour network), reference
 // renderer_ray_evaluation_stepping_dvr.cuh:100-140, renderer_volume_tensorcores.cuh:1054-1072, 1149-1158
 __device__ __forceinline__ float4 shade_sample(const NetParams& P, const DvrParams& D, const float* tfp, const float (&o)[4]) {
     float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (P.output_mode < D_OUT_RGBO) {
-        const float value = (P.output_mode == D_OUT_DENSITY) ? sigmoidf_(o[0]) : o[0];
+    if (!output_mode_is_colour(P.output_mode)) {
+        const float value = density_from_output(P.output_mode, o[0]);
         if (value >= D.dmin) {
             const float d2 = fminf(fmaxf((value - D.dmin) * D.inv_range, 0.f), 1.f);
             if (D.tf_kind == 0) c = tf_piecewise(tfp, D.tf_R, d2);
@@ -188,6 +204,59 @@ __device__ __forceinline__ void blend_sample(const DvrParams& D, float4 c, float
         acc.w += k;
     }
 }
+// ---- normals and shading
+// normal predicted by the network next to the density (:1077-1127); densitygrad:cubic stores the cube root
+__device__ __forceinline__ float3 normal_from_output(int mode, const float (&o)[4]) {
+    if (mode == D_OUT_DENSITY_GRADIENT_CUBIC) return make_float3(o[1] * o[1] * o[1], o[2] * o[2] * o[2], o[3] * o[3] * o[3]);
+    return make_float3(o[1], o[2], o[3]);
+}
+// safeNormalize, helper_math.cuh:2443-2448
+__device__ __forceinline__ float3 safe_normalize(float3 v) {
+    const float l2 = v.x * v.x + v.y * v.y + v.z * v.z;
+    if (l2 < 1e-8f) return v;
+    const float inv = rsqrtf(l2);
+    return make_float3(v.x * inv, v.y * inv, v.z * inv);
+}
+// BRDFLambert::eval, renderer_brdf_lambert.cuh:57-103: gradient-magnitude scaling of the absorption and Phong shading of
+// the colour. `gradientNorm` is rsqrt(|g|^2) there (:63) and enters the smoothstep as such - kept.
+__device__ __forceinline__ float4 brdf_lambert(const DvrParams& D, float4 c, float3 wpos, float3 g, float3 dir) {
+    const float g2 = g.x * g.x + g.y * g.y + g.z * g.z;
+    const float ginv = rsqrtf(g2);
+    const float3 n = safe_normalize(g);
+    if (D.brdf_flags & 1) c.w *= 1.f - __expf(-D.brdf_mag_scaling * g2);
+    if (D.brdf_flags & 2) {
+        float3 l = (D.light_type == 1) ? make_float3(-D.light[0], -D.light[1], -D.light[2])
+                                       : make_float3(D.light[0] - wpos.x, D.light[1] - wpos.y, D.light[2] - wpos.z);
+        const float linv = rsqrtf(l.x * l.x + l.y * l.y + l.z * l.z);
+        l.x *= linv; l.y *= linv; l.z *= linv;
+        const float lo = D.brdf_mag_center - D.brdf_mag_radius, hi = D.brdf_mag_center + D.brdf_mag_radius;
+        const float y = fminf(fmaxf(__fdividef(ginv - lo, hi - lo), 0.f), 1.f);
+        const float phong = y * y * (3.f - 2.f * y);                             // smoothstep
+        const float amb = 1.f + phong * (D.brdf_ambient - 1.f);                  // lerp(1, ambient, phong)
+        const float ndl = n.x * l.x + n.y * l.y + n.z * l.z;
+        // reflect(l, -n) = l - 2 (-n) dot(-n, l)
+        const float k = 2.f * ndl;
+        const float3 r = make_float3(l.x - k * n.x, l.y - k * n.y, l.z - k * n.z);
+        const float rd = fmaxf(0.f, dir.x * r.x + dir.y * r.y + dir.z * r.z);
+        const float e = float(D.brdf_spec_exp);
+        const float spec = D.brdf_specular * float(double(e + 2.f) * 0.159155) * __powf(rd, e);
+        const float d = fabsf(ndl);
+        c.x = amb * c.x + (1.f - amb) * (d * c.x + spec);
+        c.y = amb * c.y + (1.f - amb) * (d * c.y + spec);
+        c.z = amb * c.z + (1.f - amb) * (d * c.z + spec);
+    }
+    return c;
+}
+// Blending::eval with the normal channel, renderer_blending.cuh:36-51
+__device__ __forceinline__ void blend_sample_normal(const DvrParams& D, float4 c, float3 n, float t, float4& acc, float3& acc_n, float& acc_depth) {
+    const float a = (D.blend_mode == 1) ? 1.f - __expf(-c.w) : fminf(1.f, c.w);
+    const float k = (1.f - acc.w) * a;
+    acc.x += k * c.x; acc.y += k * c.y; acc.z += k * c.z;
+    acc_n.x += k * n.x; acc_n.y += k * n.y; acc_n.z += k * n.z;
+    acc_depth += k * t;
+    acc.w += k;
+}
+
 // the same compositing step without divergent branches: `on` = this sample exists (valid step of a live ray)
 __device__ __forceinline__ void blend_sample_pred(const DvrParams& D, int blend_mode, bool on, float4 c, float t, float4& acc, float& acc_depth) {
     float e;
@@ -236,24 +305,28 @@ __device__ __forceinline__ void store_rgba(const DvrParams& D, int b, int x, int
     }
 }
 // pixel write, reference renderer_image_evaluator_simple.cuh:101-124 (+ the fused colour extraction when requested)
-__device__ __forceinline__ void write_pixel(const DvrParams& D, int b, int x, int y, float4 pix_color, float pix_depth, int last_steps, int spp) {
+__device__ __forceinline__ void write_pixel(const DvrParams& D, int b, int x, int y, float4 pix_color, float pix_depth, int last_steps, int spp,
+                                            float3 pix_normal = make_float3(0.f, 0.f, 0.f)) {
     const float inv_s = 1.f / float(spp);
     if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
     const float4 color = make_float4(pix_color.x * inv_s, pix_color.y * inv_s, pix_color.z * inv_s, pix_color.w * inv_s);
+    const float3 normal = make_float3(pix_normal.x * inv_s, pix_normal.y * inv_s, pix_normal.z * inv_s);
     if (D.out_format != 0) {
-        store_rgba(D, b, x, y, select_channel(D.channel_mode, D.tonemap, D.max_exposure, color, make_float3(0.f, 0.f, 0.f)));
+        store_rgba(D, b, x, y, select_channel(D.channel_mode, D.tonemap, D.max_exposure, color, normal));
         return;
     }
     float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
     const float depth = pix_depth / pix_color.w;    // NaN for empty pixels, as in the reference
     o[0 * D.sc] = color.x; o[1 * D.sc] = color.y; o[2 * D.sc] = color.z;
     o[3 * D.sc] = color.w;
-    o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
+    o[4 * D.sc] = normal.x; o[5 * D.sc] = normal.y; o[6 * D.sc] = normal.z;
     o[7 * D.sc] = depth;
 }
 
-template <int H16, int GC16, bool DIR>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+// NORMALS: the launch evaluates normals (predicted by the network or finite differences, BRDFLambert shading,
+// normal channels of the output) - its own instantiation, the plain march keeps its registers
+template <int H16, int GC16, bool DIR, bool NORMALS>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, NORMALS ? 2 : 4)
 dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
     using Net = Srn<H16, GC16, DIR>;
     extern __shared__ uint4 smem[];
@@ -294,6 +367,7 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
         const CamFrame cf = load_camera(D, b);
 
         float4 pix_color = make_float4(0.f, 0.f, 0.f, 0.f);
+        float3 pix_normal = make_float3(0.f, 0.f, 0.f);
         float pix_depth = 0.f;
         int last_steps = 0;
         for (int s = 0; s < D.spp; ++s) {   // warp-uniform trip count
@@ -303,6 +377,7 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
             const float tmax = in_img ? r.tmax : -1.f;  // lanes outside the image never become valid
 
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            float3 acc_n = make_float3(0.f, 0.f, 0.f);
             float acc_depth = 0.f;
             int steps = 0;
             // lock-step march, reference renderer_ray_evaluation_stepping_dvr.cuh:84-154
@@ -320,16 +395,52 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
                 }
                 float o[4];
                 Net::forward(P, sblob_addr, stage, ac, px, py, pz, dir.x, dir.y, dir.z, o);
-                if (!valid) continue;
-                ++steps;
-                blend_sample(D, shade_sample(P, D, tfp, o), t, acc, acc_depth);
+                if constexpr (!NORMALS) {
+                    if (!valid) continue;
+                    ++steps;
+                    blend_sample(D, shade_sample(P, D, tfp, o), t, acc, acc_depth);
+                } else {
+                // normals, :114-153: the normal is evaluated when ANY lane of the warp shades its sample
+                const float value = density_from_output(P.output_mode, o[0]);
+                const bool shaded = valid && value >= D.dmin;
+                float3 n = make_float3(0.f, 0.f, 0.f);
+                if (P.gradient_mode == 1) {     // GRADIENT_MODE_FINITE_DIFFERENCES, renderer_volume_tensorcores.cuh:1185-1197
+                    if (__any_sync(0xffffffffu, shaded)) {
+                        const float h = P.fd_stepsize;
+                        float d[6];
+#pragma unroll 1
+                        for (int k = 0; k < 6; ++k) {
+                            const float sgn = (k & 1) ? -h : h;
+                            const float wx = __fmaf_rn(dir.x, t, eye.x) + ((k >> 1) == 0 ? sgn : 0.f);
+                            const float wy = __fmaf_rn(dir.y, t, eye.y) + ((k >> 1) == 1 ? sgn : 0.f);
+                            const float wz = __fmaf_rn(dir.z, t, eye.z) + ((k >> 1) == 2 ? sgn : 0.f);
+                            float q[4];
+                            Net::forward(P, sblob_addr, stage, ac, valid ? (wx - bmin.x) * binv.x : 0.f, valid ? (wy - bmin.y) * binv.y : 0.f,
+                                         valid ? (wz - bmin.z) * binv.z : 0.f, dir.x, dir.y, dir.z, q);
+                            const float v = density_from_output(P.output_mode, q[0]);
+                            if (k == 0) d[0] = v; else if (k == 1) d[1] = v; else if (k == 2) d[2] = v;
+                            else if (k == 3) d[3] = v; else if (k == 4) d[4] = v; else d[5] = v;
+                        }
+                        const float inv2h = __fdividef(1.f, 2.f * h);
+                        n = make_float3((d[0] - d[1]) * inv2h, (d[2] - d[3]) * inv2h, (d[4] - d[5]) * inv2h);
+                    }
+                } else if (P.output_mode >= D_OUT_DENSITY_GRADIENT) n = normal_from_output(P.output_mode, o);
+                if (valid) ++steps;
+                if (!shaded) continue;
+                float4 c = shade_sample(P, D, tfp, o);
+                if (c.w > 0.f) {
+                    if (D.brdf_flags) c = brdf_lambert(D, c, make_float3(__fmaf_rn(dir.x, t, eye.x), __fmaf_rn(dir.y, t, eye.y), __fmaf_rn(dir.z, t, eye.z)), n, dir);
+                    blend_sample_normal(D, c, safe_normalize(n), t, acc, acc_n, acc_depth);
+                }
+                }
             }
             n_valid += steps;
             last_steps = steps;
             pix_color.x += acc.x; pix_color.y += acc.y; pix_color.z += acc.z; pix_color.w += acc.w;
+            pix_normal.x += acc_n.x * acc.w; pix_normal.y += acc_n.y * acc.w; pix_normal.z += acc_n.z * acc.w;
             pix_depth += acc_depth * acc.w;     // reference renderer_image_evaluator_simple.cuh:101-103
         }
-        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps, D.spp);
+        if (in_img) write_pixel(D, b, x, y, pix_color, pix_depth, last_steps, D.spp, pix_normal);
     }
     if (D.counters) {
         for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);
@@ -364,8 +475,7 @@ eval_kernel(const __grid_constant__ NetParams P, const __grid_constant__ EvalPar
         Net::forward(P, sblob_addr, stage, ac, px, py, pz, dx, dy, dz, o);
         if (!valid) continue;
         // output parametrisation, reference :1054-1072, 1149-1158 (value, not valueNoClamping)
-        if (P.output_mode == D_OUT_DENSITY) E.out[i] = sigmoidf_(o[0]);
-        else if (P.output_mode == D_OUT_DENSITY_DIRECT) E.out[i] = o[0];
+        if (!output_mode_is_colour(P.output_mode)) E.out[i] = density_from_output(P.output_mode, o[0]);
         else {
             float4 c;
             if (P.output_mode == D_OUT_RGBO) c = make_float4(sigmoidf_(o[0]), sigmoidf_(o[1]), sigmoidf_(o[2]), softplusf_(o[3]));

@@ -19,8 +19,10 @@
 //   * density range, piecewise / texture TF, Beer-Lambert / alpha blending and the output normalisation in the
 //     reference's fp32 operation order (renderer_ray_evaluation_stepping_dvr.cuh:84-154, renderer_tf_piecewise.cuh:27-62,
 //     renderer_tf_texture.cuh:46-56, renderer_blending.cuh:36-51, renderer_image_evaluator_simple.cuh:96-124)
-// Scope: density networks ("density:direct"), Fourier features, one 16-channel latent grid group (static, time
-// keyframes or ensemble), no direction / time input - the shapes the reference kernels in oracle/_ref are built for.
+// Scope: density-type networks (density[:direct], densitygrad[:direct|:cubic], densitycurvature[:direct]), Fourier
+// features, one 16-channel latent grid group (static, time keyframes or ensemble), no direction / time input; normals
+// predicted by the network or by finite differences, BRDFLambert shading - the shapes the reference kernels
+// in oracle/_ref are built for.
 #pragma once
 #include "kernels.cuh"
 
@@ -106,9 +108,10 @@ struct SrnExact {
         }
     }
 
-    // network output (raw last-layer value, fp16) of the sample owned by this lane; all 32 lanes call
-    static __device__ __forceinline__ __half forward(const NetParams& P, uint32_t sblob, uint4* stage, const Act& ac,
-                                                     float px, float py, float pz, float tfrac) {
+    // network output (raw last-layer values, fp16) of the sample owned by this lane; all 32 lanes call. four = the
+    // 4 / 6-output last layers of the densitygrad* / densitycurvature* modes (o[0] density, o[1..3] predicted gradient)
+    static __device__ __forceinline__ void forward(const NetParams& P, uint32_t sblob, uint4* stage, const Act& ac,
+                                                   float px, float py, float pz, float tfrac, bool four, __half (&o)[4]) {
         const int lane = threadIdx.x & 31;
         __syncwarp();
         uint32_t row[K0 / 2];
@@ -159,6 +162,27 @@ struct SrnExact {
                 for (int j = 0; j < 2; ++j)
                     st32[(mt * 16 + (lane >> 2) + 8 * j) * (RS_CHUNKS * 4) + nt * 4 + (lane & 3)] = acc[mt][nt][j];
         __syncwarp();
+        if (four) {
+            // :1045-1052 (4 outputs) and :1106-1115 (6 outputs, the first four laid out the same): out1 = (bias0, bias1),
+            // out2 = (bias2, bias3); per hidden channel v: out1 = hfma2((v,v), (w0,w1), out1), out2 = hfma2((v,v), (w2,w3), out2)
+            const uint32_t rows = sblob + P.off_wlast_rows;
+            const uint2 bl = lds64(bias_addr + (1 + P.num_hidden) * H * 2);
+            __half2 out1 = u2h(bl.x), out2 = u2h(bl.y);
+#pragma unroll
+            for (int c4 = 0; c4 < H / 8; ++c4) {
+                const uint4 v = stage[lane * RS_CHUNKS + c4];
+                const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const __half lo = __low2half(u2h(u[k])), hi = __high2half(u2h(u[k]));
+                    const uint2 w0 = lds64(rows + (c4 * 8 + 2 * k) * 16), w1 = lds64(rows + (c4 * 8 + 2 * k + 1) * 16);
+                    out1 = __hfma2(__halves2half2(lo, lo), u2h(w0.x), out1); out2 = __hfma2(__halves2half2(lo, lo), u2h(w0.y), out2);
+                    out1 = __hfma2(__halves2half2(hi, hi), u2h(w1.x), out1); out2 = __hfma2(__halves2half2(hi, hi), u2h(w1.y), out2);
+                }
+            }
+            o[0] = __low2half(out1); o[1] = __high2half(out1); o[2] = __low2half(out2); o[3] = __high2half(out2);
+            return;
+        }
         // last layer, :1138-1143: out = bias; out = hfma(x[c], w[c], out) for c = 0..H-1
         const __half* wl = reinterpret_cast<const __half*>(P.wlast2);
         __half out = __float2half(P.blast);
@@ -172,7 +196,7 @@ struct SrnExact {
                 out = __hfma(__high2half(u2h(u[k])), wl[c4 * 8 + 2 * k + 1], out);
             }
         }
-        return out;
+        o[0] = out; o[1] = o[2] = o[3] = __float2half(0.f);
     }
 };
 
@@ -229,20 +253,91 @@ __device__ __forceinline__ void exact_blend(const DvrParams& D, float4 c, float 
         acc_depth = rf::fma(rf::mul(om, t), a, acc_depth);
     }
 }
-// pixel write, renderer_image_evaluator_simple.cuh:105-124: depth /= alpha first, then colour /= samples
-__device__ __forceinline__ void exact_write(const DvrParams& D, int b, int x, int y, float4 pix, float pix_depth, int last_steps) {
+// pixel write, renderer_image_evaluator_simple.cuh:105-124: depth /= alpha first, then colour and normal /= samples
+__device__ __forceinline__ void exact_write(const DvrParams& D, int b, int x, int y, float4 pix, float pix_depth, int last_steps,
+                                            float3 pix_n = make_float3(0.f, 0.f, 0.f)) {
     const float ns = float(D.spp);
     if (D.step_count) D.step_count[((size_t)b * D.H + y) * D.W + x] = last_steps;
+    const float3 nrm = make_float3(rf::div(pix_n.x, ns), rf::div(pix_n.y, ns), rf::div(pix_n.z, ns));
     if (D.out_format != 0) {
         store_rgba(D, b, x, y, select_channel(D.channel_mode, D.tonemap, D.max_exposure,
-                                              make_float4(rf::div(pix.x, ns), rf::div(pix.y, ns), rf::div(pix.z, ns), rf::div(pix.w, ns)), make_float3(0.f, 0.f, 0.f)));
+                                              make_float4(rf::div(pix.x, ns), rf::div(pix.y, ns), rf::div(pix.z, ns), rf::div(pix.w, ns)), nrm));
         return;
     }
     float* o = D.out + (long long)b * D.sb + (long long)y * D.sy + (long long)x * D.sx;
     o[0 * D.sc] = rf::div(pix.x, ns); o[1 * D.sc] = rf::div(pix.y, ns); o[2 * D.sc] = rf::div(pix.z, ns);
     o[3 * D.sc] = rf::div(pix.w, ns);
-    o[4 * D.sc] = 0.f; o[5 * D.sc] = 0.f; o[6 * D.sc] = 0.f;
+    o[4 * D.sc] = nrm.x; o[5 * D.sc] = nrm.y; o[6 * D.sc] = nrm.z;
     o[7 * D.sc] = rf::div(pix_depth, pix.w);
+}
+
+// ---- normals and shading, operation order of the reference kernels oracle/_ref/h32x4_relu_densgrad*.ptx /
+// h32x4_relu_fd_phong.ptx
+// Sigmoid::forward under fast math (renderer_activations.cuh:174): rcp(ex2(-x * log2 e) + 1)
+__device__ __forceinline__ float exact_sigmoid(float x) { return rf::rcp(rf::add(rf::ex2(rf::mul(x, -1.4426950408889634f)), 1.0f)); }
+__device__ __forceinline__ float exact_dot(float3 a, float3 b) { return rf::fma(a.z, b.z, rf::fma(a.x, b.x, rf::mul(a.y, b.y))); }
+// safeNormalize (helper_math.cuh:2443-2448; the threshold compare is done in double): also returns |v|^2 and rsqrt(|v|^2)
+__device__ __forceinline__ float3 exact_safe_normalize(float3 v, float& len2, float& inv) {
+    len2 = exact_dot(v, v);
+    inv = rf::rsqrt(len2);
+    const bool small = double(len2) < 1e-8;
+    return make_float3(small ? v.x : rf::mul(v.x, inv), small ? v.y : rf::mul(v.y, inv), small ? v.z : rf::mul(v.z, inv));
+}
+// BRDFLambert::eval, renderer_brdf_lambert.cuh:57-103; n = safeNormalize(g), g2 = |g|^2, ginv = rsqrt(g2) ("gradientNorm", :63)
+__device__ __forceinline__ float4 exact_brdf(const DvrParams& D, float4 c, float3 wpos, float3 n, float g2, float ginv, float3 dir) {
+    float absorption = c.w;
+    if (D.brdf_flags & 1) absorption = rf::mul(c.w, rf::sub(1.0f, rf::ex2(rf::mul(rf::mul(g2, D.brdf_mag_scaling), -1.4426950408889634f))));
+    if (D.brdf_flags & 2) {
+        float3 l;           // lightDirection
+        float ndl, dnl;     // dot(normal, l) and dot(-normal, l)
+        if (D.light_type == 1) {    // directional: normalize(-lightParameter)
+            const float3 L = make_float3(D.light[0], D.light[1], D.light[2]);
+            const float linv = rf::rsqrt(exact_dot(L, L));
+            const float px = rf::mul(L.x, linv), py = rf::mul(L.y, linv), pz = rf::mul(L.z, linv);
+            l = make_float3(rf::neg(px), rf::neg(py), rf::neg(pz));
+            const float ny = rf::mul(n.y, py);
+            ndl = rf::sub(rf::sub(rf::mul(n.x, l.x), ny), rf::mul(n.z, pz));
+            dnl = rf::fma(n.z, pz, rf::fma(n.x, px, ny));
+        } else {                    // point: normalize(lightParameter - position)
+            const float3 d = make_float3(rf::sub(D.light[0], wpos.x), rf::sub(D.light[1], wpos.y), rf::sub(D.light[2], wpos.z));
+            const float linv = rf::rsqrt(exact_dot(d, d));
+            l = make_float3(rf::mul(d.x, linv), rf::mul(d.y, linv), rf::mul(d.z, linv));
+            const float a = rf::mul(n.x, l.x), b = rf::mul(n.y, l.y), e = rf::mul(n.z, l.z);
+            ndl = rf::add(e, rf::add(a, b));
+            dnl = rf::sub(rf::sub(rf::neg(b), a), e);
+        }
+        const float lo = rf::sub(D.brdf_mag_center, D.brdf_mag_radius);
+        const float range = rf::sub(rf::add(D.brdf_mag_center, D.brdf_mag_radius), lo);
+        const float y = rf::fmax(0.f, rf::fmin(rf::div(rf::sub(ginv, lo), range), 1.0f));
+        const float phong = rf::mul(rf::mul(y, y), rf::sub(3.0f, rf::add(y, y)));                // smoothstep
+        const float amb = rf::fma(rf::add(D.brdf_ambient, -1.0f), phong, 1.0f);                 // lerp(1, ambient, phong)
+        const float3 r = make_float3(rf::sub(l.x, rf::mul(rf::mul(n.x, -2.0f), dnl)), rf::sub(l.y, rf::mul(rf::mul(n.y, -2.0f), dnl)),
+                                     rf::sub(l.z, rf::mul(rf::mul(n.z, -2.0f), dnl)));          // reflect(l, -normal)
+        float rd = exact_dot(dir, r);
+        rd = (rd < 0.f) ? 0.f : rd;
+        const float e = float(D.brdf_spec_exp);
+        const float coef = float(double(rf::add(e, 2.0f)) * 0.159155);
+        const float spec = rf::mul(D.brdf_specular, rf::mul(rf::ex2(rf::mul(rf::lg2(rd), e)), coef));
+        const float om = rf::sub(1.0f, amb), d = rf::abs(ndl);
+        c.x = rf::fma(c.x, amb, rf::mul(om, rf::fma(c.x, d, spec)));
+        c.y = rf::fma(c.y, amb, rf::mul(om, rf::fma(c.y, d, spec)));
+        c.z = rf::fma(c.z, amb, rf::mul(om, rf::fma(c.z, d, spec)));
+    }
+    c.w = absorption;
+    return c;
+}
+// Blending::eval with the normal channel, renderer_blending.cuh:36-51
+__device__ __forceinline__ void exact_blend_normal(const DvrParams& D, float4 c, float3 n, float t, float4& acc, float3& acc_n, float& acc_depth) {
+    const float a = (D.blend_mode == 1) ? rf::sub(1.0f, rf::ex2(rf::mul(c.w, -1.4426950408889634f))) : rf::fmin(1.0f, c.w);
+    const float om = rf::sub(1.0f, acc.w);
+    acc.x = rf::fma(rf::mul(om, c.x), a, acc.x);
+    acc.y = rf::fma(rf::mul(om, c.y), a, acc.y);
+    acc.z = rf::fma(rf::mul(om, c.z), a, acc.z);
+    acc_n.x = rf::fma(rf::mul(om, n.x), a, acc_n.x);
+    acc_n.y = rf::fma(rf::mul(om, n.y), a, acc_n.y);
+    acc_n.z = rf::fma(rf::mul(om, n.z), a, acc_n.z);
+    acc_depth = rf::fma(rf::mul(om, t), a, acc_depth);
+    acc.w = rf::fma(om, a, acc.w);
 }
 
 template <int H16>
@@ -270,6 +365,8 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
     const float3 bsize = make_float3(P.box_size[0], P.box_size[1], P.box_size[2]);
     const float tfrac = rf::sub(P.time_value, rf::floor(P.time_value));       // fracf(time), :596-597
     const float inv_range = rf::rcp(rf::sub(D.dmax, D.dmin));                 // 1 / (densityMax - densityMin), fast math
+    const bool four = P.output_mode >= D_OUT_DENSITY_GRADIENT;                // 4 / 6-output last layer
+    const bool sigm = output_mode_has_sigmoid(P.output_mode);
     unsigned long long n_valid = 0, n_exec = 0;
     for (;;) {
         int tile = 0;
@@ -288,12 +385,14 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
         const CamFrame cf = load_camera(D, b);
 
         float4 pix = make_float4(0.f, 0.f, 0.f, 0.f);
+        float3 pix_n = make_float3(0.f, 0.f, 0.f);
         float pix_depth = 0.f;
         int last_steps = 0;
         for (int s = 0; s < D.spp; ++s) {
             const Ray r = make_ray(D, cf, x, y, s, bmin, bsize, D.spp);
             const float tmax = in_img ? r.tmax : -1.f;
             float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+            float3 acc_n = make_float3(0.f, 0.f, 0.f);
             float acc_depth = 0.f;
             int steps = 0;
             for (int i = 0;; ++i) {     // renderer_ray_evaluation_stepping_dvr.cuh:84-154
@@ -305,17 +404,62 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
                 const float wx = rf::fma(r.dir.x, t, r.eye.x), wy = rf::fma(r.dir.y, t, r.eye.y), wz = rf::fma(r.dir.z, t, r.eye.z);
                 const float px = rf::div(rf::sub(wx, bmin.x), bsize.x), py = rf::div(rf::sub(wy, bmin.y), bsize.y),
                             pz = rf::div(rf::sub(wz, bmin.z), bsize.z);
-                const float value = __half2float(Net::forward(P, sblob_addr, stage, ac, px, py, pz, tfrac));
-                const float4 c = exact_shade(D, tfp, value, inv_range, valid);
+                __half o[4];
+                Net::forward(P, sblob_addr, stage, ac, px, py, pz, tfrac, four, o);
+                float value = __half2float(o[0]);
+                if (sigm) value = exact_sigmoid(value);
                 steps += valid ? 1 : 0;
-                exact_blend(D, c, t, valid, acc, acc_depth);
+                if (!D.normals) {
+                    const float4 c = exact_shade(D, tfp, value, inv_range, valid);
+                    exact_blend(D, c, t, valid, acc, acc_depth);
+                    continue;
+                }
+                // normals, :114-153: evaluated when ANY lane of the warp shades its sample
+                const bool any_shaded = __any_sync(0xffffffffu, valid && value >= D.dmin);
+                float3 g = make_float3(0.f, 0.f, 0.f);
+                if (P.gradient_mode == 1) {     // central differences of valueNoClamping, renderer_volume_tensorcores.cuh:1185-1197
+                    if (any_shaded) {
+                        const float h = P.fd_stepsize;
+                        float d[6];
+#pragma unroll 1
+                        for (int k = 0; k < 6; ++k) {
+                            // position +- h e_axis: the "+" samples add 0 to the other two coordinates, the "-" samples leave them alone
+                            const int axis = k >> 1;
+                            const bool plus = (k & 1) == 0;
+                            const float qx = axis == 0 ? (plus ? rf::add(wx, h) : rf::sub(wx, h)) : (plus ? rf::add(wx, 0.f) : wx);
+                            const float qy = axis == 1 ? (plus ? rf::add(wy, h) : rf::sub(wy, h)) : (plus ? rf::add(wy, 0.f) : wy);
+                            const float qz = axis == 2 ? (plus ? rf::add(wz, h) : rf::sub(wz, h)) : (plus ? rf::add(wz, 0.f) : wz);
+                            __half q[4];
+                            Net::forward(P, sblob_addr, stage, ac, rf::div(rf::sub(qx, bmin.x), bsize.x), rf::div(rf::sub(qy, bmin.y), bsize.y),
+                                         rf::div(rf::sub(qz, bmin.z), bsize.z), tfrac, four, q);
+                            float v = __half2float(q[0]);
+                            if (sigm) v = exact_sigmoid(v);
+                            if (k == 0) d[0] = v; else if (k == 1) d[1] = v; else if (k == 2) d[2] = v;
+                            else if (k == 3) d[3] = v; else if (k == 4) d[4] = v; else d[5] = v;
+                        }
+                        const float h2 = rf::add(h, h);
+                        g = make_float3(rf::div(rf::sub(d[0], d[1]), h2), rf::div(rf::sub(d[2], d[3]), h2), rf::div(rf::sub(d[4], d[5]), h2));
+                    }
+                } else if (four && any_shaded) {
+                    g = make_float3(__half2float(o[1]), __half2float(o[2]), __half2float(o[3]));
+                    if (P.output_mode == D_OUT_DENSITY_GRADIENT_CUBIC)
+                        g = make_float3(rf::mul(rf::mul(g.x, g.x), g.x), rf::mul(rf::mul(g.y, g.y), g.y), rf::mul(rf::mul(g.z, g.z), g.z));
+                }
+                float4 c = exact_shade(D, tfp, value, inv_range, valid);
+                if (c.w > 0.f) {
+                    float g2, ginv;
+                    const float3 n = exact_safe_normalize(g, g2, ginv);
+                    if (D.brdf_flags) c = exact_brdf(D, c, make_float3(wx, wy, wz), n, g2, ginv, r.dir);
+                    if (valid) exact_blend_normal(D, c, n, t, acc, acc_n, acc_depth);
+                }
             }
             n_valid += steps;
             last_steps = steps;
             pix.x = rf::add(pix.x, acc.x); pix.y = rf::add(pix.y, acc.y); pix.z = rf::add(pix.z, acc.z); pix.w = rf::add(pix.w, acc.w);
+            pix_n.x = rf::fma(acc.w, acc_n.x, pix_n.x); pix_n.y = rf::fma(acc.w, acc_n.y, pix_n.y); pix_n.z = rf::fma(acc.w, acc_n.z, pix_n.z);
             pix_depth = rf::fma(acc.w, acc_depth, pix_depth);       // renderer_image_evaluator_simple.cuh:101-103
         }
-        if (in_img) exact_write(D, b, x, y, pix, pix_depth, last_steps);
+        if (in_img) exact_write(D, b, x, y, pix, pix_depth, last_steps, pix_n);
     }
     if (D.counters) {
         for (int off = 16; off > 0; off >>= 1) n_valid += __shfl_xor_sync(0xffffffffu, n_valid, off);

@@ -261,8 +261,10 @@ struct SrnTc {
             // NeRF-style matrix (network.py:55-63): feature i has the single entry B[i][i%3] = 2^(i/3) * B[i%3][i%3]. The
             // reference's fp16 phase of octave k is then exactly 2^k times the octave-0 phase (power-of-two scaling
             // commutes with rounding), so only the three base phases go through the SFU; higher octaves follow from the
-            // double-angle identities in fp32 (error growth 2x per octave, < 1e-5 after 4: far below the fp16 rounding
-            // of the feature). 6 MUFU instead of 2*NF per sample.
+            // double-angle identities in fp32. The error of the seed (sin.approx: ~5e-7 abs) doubles per octave: < 1e-5 after
+            // the 4 doublings of the 32-wide network (NF = 14), ~3e-4 after the 9 of the 64-wide one (NF = 30) - there about
+            // half an fp16 ulp of the feature, measured end to end: C4 frame vs the reference kernel 6.7e-4 RGBA max-abs
+            // (tests/test_gpu_baseline_configs.py C4_relu_nerf_64x6). 6 MUFU instead of 2*NF per sample.
             float cs[NF], sn[NF];
 #pragma unroll
             for (int a = 0; a < 3; ++a) {

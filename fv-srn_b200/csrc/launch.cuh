@@ -234,7 +234,8 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
             }
         }
     }
-    const void* fn = kind == KIND_DVR ? (const void*)dvr_kernel<H16, GC16, DIR>
+    const bool normals = kind == KIND_DVR && kp != nullptr && static_cast<const DvrParams*>(kp)->normals != 0;
+    const void* fn = kind == KIND_DVR ? (normals ? (const void*)dvr_kernel<H16, GC16, DIR, true> : (const void*)dvr_kernel<H16, GC16, DIR, false>)
                    : kind == KIND_EVAL ? (const void*)eval_kernel<H16, GC16, DIR>
                    : kind == KIND_DVR_TC ? (tc_dvr_spec ? tc_dvr_spec : tc_dvr[variant]) : tc_eval[variant];
     KernelFacts kf;
@@ -259,7 +260,10 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
         return cudaLaunchKernel(fn, dim3(unsigned(grid)), dim3(threads), args, size_t(smem), s);
     }
     switch (kind) {
-        case KIND_DVR: dvr_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp)); break;
+        case KIND_DVR:
+            if (normals) dvr_kernel<H16, GC16, DIR, true><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
+            else dvr_kernel<H16, GC16, DIR, false><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
+            break;
         default: eval_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp)); break;
     }
     return cudaGetLastError();

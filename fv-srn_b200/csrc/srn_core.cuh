@@ -22,7 +22,10 @@
 namespace fvsrn {
 
 enum { D_ACT_RELU = 0, D_ACT_SINE = 1, D_ACT_SNAKE = 2, D_ACT_SNAKEALT = 3, D_ACT_NONE = 5 };
-enum { D_OUT_DENSITY = 0, D_OUT_DENSITY_DIRECT = 1, D_OUT_RGBO = 2, D_OUT_RGBO_DIRECT = 3 };
+enum { D_OUT_DENSITY = 0, D_OUT_DENSITY_DIRECT = 1, D_OUT_RGBO = 2, D_OUT_RGBO_DIRECT = 3,
+       // density + predicted gradient (4 last-layer outputs) / + curvature (6), renderer_volume_tensorcores.cuh:96-100
+       D_OUT_DENSITY_GRADIENT = 4, D_OUT_DENSITY_GRADIENT_DIRECT = 5, D_OUT_DENSITY_GRADIENT_CUBIC = 6,
+       D_OUT_DENSITY_CURVATURE = 7, D_OUT_DENSITY_CURVATURE_DIRECT = 8 };
 
 struct GridGroup {       // 16 latent channels
     const __half* a;     // keyframe A, channel-last [Z][Y][X][Cgrid], already offset to this group's first channel
@@ -61,6 +64,11 @@ struct NetParams {
     int grid_encoding;    // 0 float (fp16 on the device), 1 byte-linear, 2 byte-gaussian
     float enc_offset_a[32], enc_scale_a[32];   // per latent channel, keyframe A
     float enc_offset_b[32], enc_scale_b[32];   // keyframe B (the reference decodes B with A's constants, :586-587; see make_net_params)
+    // normals: GRADIENT_MODE of the reference (renderer_volume_tensorcores.cuh:132-134): 0 = none / predicted by
+    // the network, 1 = central finite differences of the density with step fd_stepsize (world units, :1185-1197)
+    int gradient_mode;
+    float fd_stepsize;
+    int off_wlast_rows;   // mma.sync blob: last layer once more as [cin][8 outputs] fp16 rows (reference-exact fp16 chains)
 };
 
 // filtered byte-grid value -> latent value (EncodeGridValue). fast = reference-exact mode: the reference's fast-math operation order.

@@ -335,11 +335,23 @@ class SceneNetwork:
 class VolumeInterpolationNetwork:
     """renderer::VolumeInterpolationNetwork (:1419-1726, pybind :1974-2005) + IVolumeInterpolation::evaluate."""
 
+    class GradientMode(_Enum): pass
+    OFF_OR_DIRECT = GradientMode("OFF_OR_DIRECT", 0)             # no normals, or the ones a densitygrad* network predicts
+    FINITE_DIFFERENCES = GradientMode("FINITE_DIFFERENCES", 1)   # 6 more SRN evaluations per shaded step
+    ADJOINT_METHOD = GradientMode("ADJOINT_METHOD", 2)           # not built on the B200 path (render raises)
+
     def __init__(self):
         self._networks = []
         self._current = None
         self.only_shared_memory = False   # kept for API compatibility; the B200 kernel always pins weights in smem
-        self.gradient_mode = "OFF_OR_DIRECT"
+        self.gradient_mode = VolumeInterpolationNetwork.OFF_OR_DIRECT
+        self.finite_differences_stepsize = 1.0 / 256.0     # volume_interpolation_network.cpp:1423
+
+    def _apply_gradient_mode(self, net: "SceneNetwork"):
+        """Pushes the module's gradient settings to the network handle (the reference passes them as defines / constants per render)."""
+        gm = self.gradient_mode
+        index = gm.index if isinstance(gm, _Enum) else {"OFF_OR_DIRECT": 0, "FINITE_DIFFERENCES": 1, "ADJOINT_METHOD": 2}[str(gm)]
+        check(_lib.lib().fvsrn_network_set_gradient_mode(net._h, index, float(self.finite_differences_stepsize)))
 
     def set_network(self, net: SceneNetwork):
         if net is None or not net.valid():
@@ -575,11 +587,41 @@ class Blending:
 
 
 class BRDFLambert:
-    """Only the pass-through configuration is on the hot path (renderer_brdf_lambert.cuh:61-102)."""
+    """renderer::BRDFLambert with scalar parameters (brdf.cpp:124-135, 204-225, pybind :256-274; kernel renderer_brdf_lambert.cuh:57-103).
+    Both options need normals: a densitygrad* network or VolumeInterpolationNetwork.gradient_mode = FINITE_DIFFERENCES."""
+
+    class LightType(_Enum): pass
+    Point = LightType("Point", 0)
+    Directional = LightType("Directional", 1)
 
     def __init__(self):
-        self.enable_phong = False
         self.enable_magnitude_scaling = False
+        self.enable_phong = False
+        self.magnitude_scaling = 1.0
+        self.ambient = 1.0
+        self.specular = 1.0
+        self.magnitude_center = 1.0
+        self.magnitude_radius = 1.0
+        self.specular_exponent = 1
+        self.light_follows_camera = True
+        self.light_type = BRDFLambert.Directional
+        self.light_position = double3(0, 0, 0)
+        self.light_direction = double3(0, 0, 0)
+
+    def _fill(self, p, cam: torch.Tensor):
+        flags = (1 if self.enable_magnitude_scaling else 0) | (2 if self.enable_phong else 0)
+        if not flags:
+            return
+        pos, direction = tuple(self.light_position), tuple(self.light_direction)
+        if self.light_follows_camera:      # updateLightFromCamera, brdf.cpp:478-497: origin and front of camera 0
+            c = cam[0].detach().cpu().numpy().astype(np.float64)
+            pos = tuple(c[0])
+            direction = tuple(np.cross(c[2], c[1]))     # front = cross(up, right), renderer_camera.cuh:38
+        p.brdf_flags, p.light_type = flags, self.light_type.index
+        p.light = (C.c_float * 3)(*(pos if self.light_type.index == 0 else direction))
+        p.brdf_magnitude_scaling, p.brdf_ambient, p.brdf_specular = float(self.magnitude_scaling), float(self.ambient), float(self.specular)
+        p.brdf_magnitude_center, p.brdf_magnitude_radius = float(self.magnitude_center), float(self.magnitude_radius)
+        p.brdf_specular_exponent = int(self.specular_exponent)
 
 
 class RayEvaluationSteppingDvr:
@@ -705,6 +747,8 @@ class ImageEvaluatorSimple:
             p.tf_resolution, p.tf_batch = (tf.shape[1] if re.tf.kind != 2 else 0), tf.shape[0]
         p.samples_per_pixel = self.samples_per_pixel
         p.out_stride_b, p.out_stride_c, p.out_stride_y, p.out_stride_x = out_strides
+        if re.brdf is not None:
+            re.brdf._fill(p, cam)
         return p
 
     def _render_grid(self, vol: "VolumeInterpolationGrid", width, height, out, fmt=0):
@@ -735,6 +779,7 @@ class ImageEvaluatorSimple:
             return self._render_grid(vol, width, height, out)
         net = vol._require()
         net._ensure_prepared()
+        vol._apply_gradient_mode(net)
         cam = self.camera.get_parameters()
         is_rgbo = net._info().channels_out == 4
         tf = None if is_rgbo else self.ray_evaluator.tf._tensor()
@@ -810,6 +855,7 @@ class ImageEvaluatorSimple:
         if isinstance(self._volume(), VolumeInterpolationGrid):
             return self._render_grid(self._volume(), width, height, out, fmt)
         vol = self._volume(); net = vol._require(); net._ensure_prepared()
+        vol._apply_gradient_mode(net)
         cam = self.camera.get_parameters()
         is_rgbo = net._info().channels_out == 4
         tf = None if is_rgbo else self.ray_evaluator.tf._tensor()

@@ -179,7 +179,7 @@ def make_network(hidden: int = 32, num_layers: int = 4, grid_res: int = 32, grid
     b_last = rng.uniform(-k, k, (cout,))
     if last_bias is not None:
         b_last = np.full((cout,), float(last_bias))
-    if cout == 4:
+    if output_mode.startswith("rgbo"):
         b_last = np.abs(b_last) + 1.0  # network.py:405-406
     net.add_layer(w_last, b_last, "None", 1.0)
     net.box_min, net.box_size = tuple(box_min), tuple(box_size)

@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define FVSRN_ABI_VERSION 2
+#define FVSRN_ABI_VERSION 3
 
 typedef struct fvsrn_network fvsrn_network; /* opaque: renderer::SceneNetwork + its GPU resources */
 
@@ -40,9 +40,21 @@ enum fvsrn_activation {
 };
 /* OutputParametrization::OutputMode, volume_interpolation_network.cpp:165-175 */
 enum fvsrn_output_mode {
-    FVSRN_OUT_DENSITY = 0, FVSRN_OUT_DENSITY_DIRECT = 1, FVSRN_OUT_RGBO = 2, FVSRN_OUT_RGBO_DIRECT = 3
-    /* 4..8 (densitygrad*, densitycurvature*) are parsed/saved but not evaluated: SURVEY §8 row f4 */
+    FVSRN_OUT_DENSITY = 0, FVSRN_OUT_DENSITY_DIRECT = 1, FVSRN_OUT_RGBO = 2, FVSRN_OUT_RGBO_DIRECT = 3,
+    /* the network predicts the gradient next to the density (4 last-layer outputs; ":cubic" stores its cube
+     * root) or gradient + curvature (6 outputs; the DVR path uses density and gradient), renderer_volume_tensorcores.cuh:1073-1127 */
+    FVSRN_OUT_DENSITY_GRADIENT = 4, FVSRN_OUT_DENSITY_GRADIENT_DIRECT = 5, FVSRN_OUT_DENSITY_GRADIENT_CUBIC = 6,
+    FVSRN_OUT_DENSITY_CURVATURE = 7, FVSRN_OUT_DENSITY_CURVATURE_DIRECT = 8
 };
+/* SceneNetwork::GradientMode, volume_interpolation_network.h / renderer_volume_tensorcores.cuh:132-134, 1166-1203 */
+enum fvsrn_gradient_mode {
+    FVSRN_GRADIENT_OFF_OR_DIRECT = 0,       /* no normals, or the ones the network predicts (densitygrad* / densitycurvature*) */
+    FVSRN_GRADIENT_FINITE_DIFFERENCES = 1   /* central differences: 6 more SRN evaluations per shaded step */
+    /* 2 = ADJOINT_METHOD (backward pass through the SRN, :1205-1555) is not built: finite differences cover its use */
+};
+/* BRDFLambert::LightType as the kernel sees it, renderer_brdf_lambert.cuh:6-7 */
+enum fvsrn_light_type { FVSRN_LIGHT_POINT = 0, FVSRN_LIGHT_DIRECTIONAL = 1 };
+enum { FVSRN_BRDF_MAGNITUDE_SCALING = 1, FVSRN_BRDF_PHONG = 2 };
 /* LatentGrid::Encoding, volume_interpolation_network.cpp:564-614 */
 enum fvsrn_grid_encoding { FVSRN_GRID_FLOAT = 0, FVSRN_GRID_BYTE_LINEAR = 1, FVSRN_GRID_BYTE_GAUSSIAN = 2 };
 /* BLENDING_MODE, renderer/renderer_blending.cuh:7-8 */
@@ -103,6 +115,9 @@ int  fvsrn_network_valid(const fvsrn_network* net);                             
 int  fvsrn_network_num_parameters(const fvsrn_network* net);                       /* :1043-1055 */
 int  fvsrn_network_compute_max_warps(const fvsrn_network* net, int only_shared, int adjoint); /* :987-1041 */
 int  fvsrn_network_set_time_and_ensemble(fvsrn_network* net, float time, int ensemble);       /* :923-938 */
+/* VolumeInterpolationNetwork::{gradient_mode, finite_differences_stepsize} (volume_interpolation_network.cpp:1976-1995):
+ * how the DVR frame obtains normals; stepsize in world units (reference default 1/256). Density-type networks only. */
+int  fvsrn_network_set_gradient_mode(fvsrn_network* net, int gradient_mode, float finite_differences_stepsize);
 
 /* Introspection (what a binding needs to expose .input/.output/.latent_grid read-only) */
 typedef struct fvsrn_network_info {
@@ -117,6 +132,8 @@ typedef struct fvsrn_network_info {
     int activation;           /* of the hidden layers */
     float activation_param;
     int channels_out;         /* 1 (density*) or 4 (rgbo*) */
+    int gradient_mode;        /* fvsrn_gradient_mode */
+    float finite_differences_stepsize;
 } fvsrn_network_info;
 int  fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info);
 
@@ -200,6 +217,15 @@ typedef struct fvsrn_dvr_params {
     int   channel_mode;             /* fvsrn_channel_mode; 0-initialised params with output_format 0 ignore it */
     int   tonemap;                  /* ImageEvaluatorSimple::useTonemapping_ */
     float max_exposure;             /* ImageEvaluatorSimple::getExposureForTonemapping(), image_evaluator_simple.cpp:363-369 */
+    /* Shading: BRDFLambert with scalar parameters, renderer_brdf_lambert.cuh:19-103, brdf.cpp:124-135, 372-452.
+     * brdf_flags = 0 is the reference default (colour passes through). Both options need normals: a network that predicts
+     * them or fvsrn_network_set_gradient_mode. light = position (point) or direction (directional); a binding fills it from
+     * the camera when light_follows_camera is set (brdf.cpp:478-497). */
+    int   brdf_flags;               /* FVSRN_BRDF_MAGNITUDE_SCALING | FVSRN_BRDF_PHONG */
+    int   light_type;               /* fvsrn_light_type */
+    float light[3];
+    float brdf_magnitude_scaling, brdf_ambient, brdf_specular, brdf_magnitude_center, brdf_magnitude_radius;
+    int   brdf_specular_exponent;
 } fvsrn_dvr_params;
 
 int  fvsrn_render_dvr(fvsrn_network* net, const fvsrn_dvr_params* p, float* out_dev, void* stream);

@@ -38,7 +38,7 @@ template<int N, typename V, typename I> __host__ __device__ fvar<double4, N> mak
 """
 
 NAMES = ["ImageEvaluatorSimpleKernel", "&cameraReferenceFrameParameters", "&volumeInterpolationTensorcoresParameters",
-         "&rayEvaluationSteppingDvrParameters"]
+         "&rayEvaluationSteppingDvrParameters", "&brdfLambertParameters"]
 TF_NAMES = {"piecewise": "&transferFunctionPiecewiseParameters", "texture": "&transferFunctionTextureParameters"}
 TF_TYPES = {"piecewise": ("::kernel::TransferFunctionPiecewise", "renderer_tf_piecewise.cuh"),
             "texture": ("::kernel::TransferFunctionTexture", "renderer_tf_texture.cuh")}
@@ -69,24 +69,29 @@ def grid_source(early_out=1, blend_mode=1, tf="piecewise", interpolation=1):
 
 
 def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, early_out=1, blend_mode=1, first_last_shared=0,
-                encoding=0, tf="piecewise"):
+                encoding=0, tf="piecewise", gradient_mode=0, brdf=(), light_type=1, steps_variant=True):
     """The translation unit IImageEvaluator::getKernel + ImageEvaluatorSimple::render assemble (SURVEY App. F).
     encoding: LATENT_GRID_ENCODING 0 float / 1 byte-linear / 2 byte-gaussian (volume_interpolation_network.cpp:1211);
     tf "texture": TransferFunctionTexture in its tensor form (transfer_function_texture.cpp: TRANSFER_FUNCTION_TEXTURE__USE_TENSOR,
-    pre-integration off)."""
+    pre-integration off). gradient_mode: GRADIENT_MODE 0 off-or-predicted / 1 finite differences (SURVEY f4);
+    brdf: subset of ("magnitude", "phong") = BRDFLambert::getDefines (brdf.cpp:372-394); light_type 0 point / 1 directional."""
     d = [
         ("KERNEL_DOUBLE_PRECISION", 0), ("KERNEL_SYNCHRONIZED_TRACING", 1), ("BLOCK_SIZE", block_size),
         ("NUM_HIDDEN_LAYERS", num_hidden), ("HIDDEN_CHANNELS_DIV16", hidden16), ("HAS_FOURIER_FEATURES", 1),
         ("NUM_FOURIER_FEATURES", nf), ("USE_DIRECTION", 0), ("ACTIVATION", activation), ("OUTPUT_MODE", output_mode),
         ("FIRST_AND_LAST_IN_SHARED_MEMORY", first_last_shared), ("LATENT_GRID_CHANNELS_DIV16", 1), ("LATENT_GRID_ENCODING", encoding),
-        ("PASS_TIME_TO_NETWORK", 0), ("GRADIENT_MODE", 0),
+        ("PASS_TIME_TO_NETWORK", 0), ("GRADIENT_MODE", gradient_mode),
         ("RAY_EVALUATION_STEPPING__VOLUME_INTERPOLATION_T", "::kernel::VolumeInterpolationTensorcores"),
         ("RAY_EVALUATION_STEPPING__TRANSFER_FUNCTION_T", TF_TYPES[tf][0]),
         ("RAY_EVALUATION_STEPPING__BLENDING_T", "::kernel::Blending"),
         ("RAY_EVALUATION_STEPPING__BRDF_T", "::kernel::BRDFLambert"),
         ("RAY_EVALUATION_STEPPING__ENABLE_EARLY_OUT", early_out), ("RAY_EVALUATION_STEPPING__SKIP_TRANSFER_FUNCTION", 0),
-        ("BLENDING_MODE", blend_mode), ("BRDF_LAMBERT_LIGHT_TYPE", 1),
+        ("BLENDING_MODE", blend_mode), ("BRDF_LAMBERT_LIGHT_TYPE", light_type),
     ]
+    if "magnitude" in brdf:
+        d.append(("BRDF_LAMBERT_ENABLE_MAGNITUDE_SCALING", ""))
+    if "phong" in brdf:
+        d.append(("BRDF_LAMBERT_ENABLE_PHONG", ""))
     if tf == "texture":
         d += [("TRANSFER_FUNCTION_TEXTURE__USE_TENSOR", 1), ("TRANSFER_FUNCTION_TEXTURE__PREINTEGRATION_MODE", 0)]
     src = "".join(f"#define {k} {v}\n" for k, v in d)
@@ -165,6 +170,14 @@ CONFIGS = {
     "h32x4_relu_textf": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, tf="texture"),
     "h32x4_relu_bytelinear": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, encoding=1),
     "h32x4_relu_bytegauss": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, encoding=2),
+    # networks that predict the gradient next to the density (4 = densitygrad, 6 = densitygrad:cubic), finite
+    # differences on a density network, Phong shading and gradient-magnitude scaling of BRDFLambert. The step-count patch
+    # uses the normal channel, so these are built unpatched only.
+    "h32x4_relu_densgrad": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=4, block_size=256, steps_variant=False),
+    "h32x4_relu_densgrad_cubic_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=6, block_size=256,
+                                            brdf=("magnitude", "phong"), light_type=1, steps_variant=False),
+    "h32x4_relu_fd_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, gradient_mode=1,
+                                brdf=("magnitude", "phong"), light_type=0, steps_variant=False),
 }
 # (time-interpolated grids, C5, need no build of their own: cLatentGridB != A and cLatentGridInterpolation = t are
 # constants of the same h32x4 kernels, renderer_volume_tensorcores.cuh:590-604)
@@ -177,17 +190,27 @@ def main():
     os.makedirs(OUT, exist_ok=True)
     meta = {}
     for base, cfg in CONFIGS.items():
+        only = set(sys.argv[1:])
+        if only and base not in only:
+            continue
         for name, patch in ((base, False), (base + "_steps", True)):
+            if patch and not cfg.get("steps_variant", True):
+                continue
             ptx, lowered = compile_ptx(main_source(**cfg), patch_steps=patch, tf=cfg.get("tf", "piecewise"))
             open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
             meta[name] = dict(cfg, lowered=lowered, ptx=name + ".ptx", step_count_patch=patch)
             print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['ImageEvaluatorSimpleKernel']}")
     for name, patch in (("grid_trilinear", False), ("grid_trilinear_steps", True)):
+        if len(sys.argv) > 1 and "grid_trilinear" not in sys.argv[1:]:
+            continue
         ptx, lowered = compile_ptx(grid_source(), patch_steps=patch, volume_symbol="&volumeInterpolationGridParameters")
         open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
         meta[name] = dict(grid=True, lowered=lowered, ptx=name + ".ptx", step_count_patch=patch)
         print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX")
-    json.dump(meta, open(os.path.join(OUT, "ref_kernels.json"), "w"), indent=1)
+    path = os.path.join(OUT, "ref_kernels.json")
+    if len(sys.argv) > 1 and os.path.exists(path):      # partial rebuild: keep the other entries
+        meta = dict(json.load(open(path)), **meta)
+    json.dump(meta, open(path, "w"), indent=1)
     return 0
 
 

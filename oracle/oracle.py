@@ -18,7 +18,8 @@ _LIB_PATH = os.path.join(_HERE, "_build", "libfvsrn_oracle.so")
 _lib = None
 
 ACTIVATIONS = ["ReLU", "Sine", "Snake", "SnakeAlt", "Sigmoid", "None"]
-OUTPUT_MODES = ["density", "density:direct", "rgbo", "rgbo:direct"]
+OUTPUT_MODES = ["density", "density:direct", "rgbo", "rgbo:direct", "densitygrad", "densitygrad:direct", "densitygrad:cubic",
+                "densitycurvature", "densitycurvature:direct"]
 
 
 def build(force: bool = False):
@@ -46,7 +47,10 @@ class _Dvr(C.Structure):
         ("camera", C.c_void_p), ("fov_y", C.c_float), ("stepsize", C.c_float), ("alpha_early_out", C.c_float),
         ("density_min", C.c_float), ("density_max", C.c_float), ("early_out", C.c_int32), ("blend_mode", C.c_int32),
         ("tf_kind", C.c_int32), ("tf_R", C.c_int32), ("tf_batch", C.c_int32), ("tf", C.c_void_p), ("spp", C.c_int32),
-        ("fp32_mode", C.c_int32)]
+        ("fp32_mode", C.c_int32),
+        ("gradient_mode", C.c_int32), ("fd_stepsize", C.c_float), ("brdf_flags", C.c_int32), ("light_type", C.c_int32),
+        ("light", C.c_float * 3), ("brdf_magnitude_scaling", C.c_float), ("brdf_ambient", C.c_float), ("brdf_specular", C.c_float),
+        ("brdf_magnitude_center", C.c_float), ("brdf_magnitude_radius", C.c_float), ("brdf_specular_exponent", C.c_int32)]
 
 
 def lib():
@@ -142,10 +146,11 @@ def evaluate(net, positions, directions=None, time=0.0, ensemble=0, fp32=False, 
     on = OracleNetwork(net, time, ensemble, unit_box=True, tex_filter=tex_filter, acc32=acc32)
     pos = np.ascontiguousarray(positions, dtype=np.float32)
     d = None if directions is None else np.ascontiguousarray(directions, dtype=np.float32)
-    out = np.empty((pos.shape[0], on.cout), np.float32)
+    out = np.zeros((pos.shape[0], on.cout), np.float32)
     lib().oracle_evaluate(C.byref(on.c), pos.ctypes.data, None if d is None else d.ctypes.data, out.ctypes.data,
                           pos.shape[0], int(fp32))
-    return out
+    # densitygrad* / densitycurvature* networks: `evaluate` is the density channel (OutputModeNumChannelsOut = 1)
+    return out[:, :1].copy() if on.c.output_mode >= 4 else out
 
 
 def features(net, positions, time=0.0, ensemble=0, tex_filter=False, acc32=False):
@@ -159,8 +164,10 @@ def features(net, positions, time=0.0, ensemble=0, tex_filter=False, acc32=False
 
 def render_dvr(net, *, width, height, camera, fov_y, stepsize, tf, tf_kind=0, alpha_early_out=1 - 1e-5,
                density_min=0.0, density_max=1.0, early_out=True, blend_mode=1, spp=1, time=0.0, ensemble=0,
-               tile=None, fp32=False, tex_filter=False, acc32=False):
-    """ImageEvaluatorSimple::render restated on the CPU -> (img (B,8,H,W) f32, steps (B,H,W) i32, valid_samples)."""
+               tile=None, fp32=False, tex_filter=False, acc32=False, fd_stepsize=None, brdf=None):
+    """ImageEvaluatorSimple::render restated on the CPU -> (img (B,8,H,W) f32, steps (B,H,W) i32, valid_samples).
+    fd_stepsize: finite-difference normals (GRADIENT_MODE 1); brdf: dict(flags=("magnitude","phong"), light_type, light,
+    magnitude_scaling, ambient, specular, magnitude_center, magnitude_radius, specular_exponent) = BRDFLambert."""
     on = OracleNetwork(net, time, ensemble, unit_box=False, tex_filter=tex_filter, acc32=acc32)
     cam = np.ascontiguousarray(camera, dtype=np.float32).reshape(-1, 3, 3)
     B = cam.shape[0]
@@ -171,6 +178,14 @@ def render_dvr(net, *, width, height, camera, fov_y, stepsize, tf, tf_kind=0, al
     d.camera = cam.ctypes.data; d.fov_y = fov_y
     d.stepsize, d.alpha_early_out, d.density_min, d.density_max = stepsize, alpha_early_out, density_min, density_max
     d.early_out, d.blend_mode, d.spp, d.fp32_mode = int(early_out), blend_mode, spp, int(fp32)
+    if fd_stepsize is not None:
+        d.gradient_mode, d.fd_stepsize = 1, fd_stepsize
+    if brdf is not None:
+        d.brdf_flags = (1 if "magnitude" in brdf["flags"] else 0) | (2 if "phong" in brdf["flags"] else 0)
+        d.light_type = brdf["light_type"]; d.light = (C.c_float * 3)(*brdf["light"])
+        d.brdf_magnitude_scaling, d.brdf_ambient, d.brdf_specular = brdf["magnitude_scaling"], brdf["ambient"], brdf["specular"]
+        d.brdf_magnitude_center, d.brdf_magnitude_radius = brdf["magnitude_center"], brdf["magnitude_radius"]
+        d.brdf_specular_exponent = brdf["specular_exponent"]
     tfa = None
     if tf is not None:
         tfa = np.ascontiguousarray(tf, dtype=np.float32)

@@ -18,8 +18,11 @@ def psnr(a, b):
     return 200.0 if mse == 0 else 10.0 * np.log10(1.0 / mse)
 
 
-def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0, time=None, tile=None, spp=1):
-    """One frame through the product path (pyrenderer mirror -> C ABI) -> (img (B,8,H,W) numpy, steps (B,H,W) numpy)."""
+def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0, time=None, tile=None, spp=1,
+                fd_stepsize=None, brdf=None):
+    """One frame through the product path (pyrenderer mirror -> C ABI) -> (img (B,8,H,W) numpy, steps (B,H,W) numpy).
+    fd_stepsize: finite-difference normals with that step; brdf: dict as ref_kernel.ReferenceDvrKernel.render takes it plus
+    "flags" (subset of "magnitude", "phong") and "light_type" (0 point / 1 directional)."""
     import torch
     import fvsrn_b200  # noqa: F401
     from fvsrn_b200 import pyrenderer as pr
@@ -34,23 +37,38 @@ def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0,
     ie.ray_evaluator.tf.tensor.value = torch.from_numpy(np.ascontiguousarray(tf, np.float32)).cuda()
     ie.ray_evaluator.stepsize = stepsize
     ie.samples_per_pixel = spp
+    if fd_stepsize is not None:
+        vol.gradient_mode = pr.VolumeInterpolationNetwork.FINITE_DIFFERENCES
+        vol.finite_differences_stepsize = fd_stepsize
+    if brdf is not None:
+        b = ie.ray_evaluator.brdf
+        b.enable_magnitude_scaling, b.enable_phong = "magnitude" in brdf["flags"], "phong" in brdf["flags"]
+        b.magnitude_scaling, b.ambient, b.specular = brdf["magnitude_scaling"], brdf["ambient"], brdf["specular"]
+        b.magnitude_center, b.magnitude_radius, b.specular_exponent = brdf["magnitude_center"], brdf["magnitude_radius"], brdf["specular_exponent"]
+        b.light_follows_camera = False
+        b.light_type = pr.BRDFLambert.Point if brdf["light_type"] == 0 else pr.BRDFLambert.Directional
+        b.light_position = b.light_direction = pr.double3(*brdf["light"])
     ie.collect_statistics = True
     ie.tile = tile
     img = ie.render(width, height).cpu().numpy()
     return img, ie.last_step_counts.cpu().numpy()
 
 
-def render_reference(net, width, height, camera, fov_y, tf, stepsize, tf_kind=0, time=0.0, timing_iters=0):
-    """The same frame with the reference's kernel -> (rgba8 image, step counts, ms or None)."""
+def render_reference(net, width, height, camera, fov_y, tf, stepsize, tf_kind=0, time=0.0, timing_iters=0, variant=None,
+                     fd_stepsize=0.01, brdf=None):
+    """The same frame with the reference's kernel -> (rgba8 image, step counts, ms or None). variant: a named build of
+    oracle/build_ref_ptx.py (the gradient / shading kernels; they have no step-count build: steps come back as None)."""
     import ref_kernel
     tfname = "texture" if tf_kind == 1 else "piecewise"
-    rk = ref_kernel.ReferenceDvrKernel(net, time=time, tf=tfname)
+    rk = ref_kernel.ReferenceDvrKernel(net, time=time, tf=tfname, variant=variant, fd_stepsize=fd_stepsize)
     ms = None
     if timing_iters > 0:
-        want, ms = rk.render(width, height, camera, fov_y, stepsize, tf, timing_iters=timing_iters)
+        want, ms = rk.render(width, height, camera, fov_y, stepsize, tf, timing_iters=timing_iters, brdf=brdf)
     else:
-        want = rk.render(width, height, camera, fov_y, stepsize, tf)
+        want = rk.render(width, height, camera, fov_y, stepsize, tf, brdf=brdf)
     want = want.cpu().numpy()
+    if variant is not None:
+        return want, None, ms
     counted = ref_kernel.ReferenceDvrKernel(net, patched_steps=True, time=time, tf=tfname).render(
         width, height, camera, fov_y, stepsize, tf).cpu().numpy()
     assert np.array_equal(want[:, :4], counted[:, :4]), "the step-count patch must not touch the image"

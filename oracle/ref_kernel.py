@@ -68,7 +68,10 @@ class ReferenceDvrKernel:
     time-interpolated keyframe grids (C5: cLatentGridB != A, cLatentGridInterpolation = t), byte-encoded grids and the
     texture transfer function (tensor form)."""
 
-    def __init__(self, net, variant=None, patched_steps=False, time=0.0, tf="piecewise"):
+    OUTPUT_MODES = ["density", "density:direct", "rgbo", "rgbo:direct", "densitygrad", "densitygrad:direct", "densitygrad:cubic",
+                    "densitycurvature", "densitycurvature:direct"]
+
+    def __init__(self, net, variant=None, patched_steps=False, time=0.0, tf="piecewise", fd_stepsize=0.01):
         import torch
         from cuda.bindings import driver
         self.torch, self.drv = torch, driver
@@ -85,7 +88,8 @@ class ReferenceDvrKernel:
         m = meta[variant]
         assert m["hidden16"] * 16 == H and m["num_hidden"] == len(net.layers) - 2 and m["nf"] == net.num_fourier
         assert net.latent_channels() == 16 and not net.has_direction and not net.has_time
-        assert net.output_mode == {0: "density", 1: "density:direct"}[m["output_mode"]]
+        assert net.output_mode == self.OUTPUT_MODES[m["output_mode"]], (net.output_mode, m["output_mode"])
+        self.fd_stepsize = float(fd_stepsize)
         assert m.get("encoding", 0) == enc and m.get("tf", "piecewise") == tf
         self.meta, self.block, self.tf_kind = m, m["block_size"], tf
         torch.cuda.init(); torch.zeros(1, device="cuda")         # primary context current
@@ -98,6 +102,10 @@ class ReferenceDvrKernel:
         self.g_dvr = _ck(driver.cuModuleGetGlobal(self.module, low["&rayEvaluationSteppingDvrParameters"].encode()))
         tf_sym = "&transferFunctionTextureParameters" if tf == "texture" else "&transferFunctionPiecewiseParameters"
         self.g_tf = _ck(driver.cuModuleGetGlobal(self.module, low[tf_sym].encode()))
+        # BRDFLambertParameters (scalar form, renderer_brdf_lambert.cuh:30-38); absent from the module when the BRDF is the pass-through
+        self.g_brdf = None
+        if m.get("brdf") and "&brdfLambertParameters" in low:
+            self.g_brdf = _ck(driver.cuModuleGetGlobal(self.module, low["&brdfLambertParameters"].encode()))
         self._keep = []
         self._upload_network(net, float(time))
         sms = torch.cuda.get_device_properties(0).multi_processor_count
@@ -174,22 +182,22 @@ class ReferenceDvrKernel:
         add(np.ascontiguousarray(net.layers[0].bias, np.float16).tobytes())
         add(np.ascontiguousarray(np.stack([l.weights for l in net.layers[1:-1]]), np.float16).tobytes())
         add(np.ascontiguousarray(np.stack([l.bias for l in net.layers[1:-1]]), np.float16).tobytes())
-        add(np.ascontiguousarray(net.layers[-1].weights, np.float16).tobytes())         # cWeightsLast [H]
+        add(np.ascontiguousarray(np.asarray(net.layers[-1].weights).T, np.float16).tobytes())   # cWeightsLast [H] / half2 [H][cout/2]
         add(np.ascontiguousarray(net.layers[-1].bias, np.float16).tobytes())
         add(np.array(net.box_min, np.float32).tobytes())
         add(np.array(net.box_size, np.float32).tobytes())
         add(np.array([net.layers[0].activation_param], np.float32).tobytes())
-        add(np.array([0.01], np.float32).tobytes())                                     # finiteDifferencesStepsize (unused)
+        add(np.array([self.fd_stepsize], np.float32).tobytes())                         # finiteDifferencesStepsize (GRADIENT_MODE 1)
         add(np.array([0.01], np.float32).tobytes())                                     # latentGridDifferencesStepSize (unused)
         _pad32(b)
         dptr, size = self.g_vol
-        if H == 32 and nf == 14 and gA.encoding == 0:
+        if H == 32 and nf == 14 and gA.encoding == 0 and net.layers[-1].cout == 1:
             assert len(b) == 7840, len(b)                                               # sizeof for C3
         assert len(b) == int(size), (len(b), int(size))
         _ck(self.drv.cuMemcpyHtoD(dptr, bytes(b), len(b)))
 
     def render(self, width, height, camera, fov_y, stepsize, tf, alpha_early_out=1 - 1e-5, density_min=0.0, density_max=1.0,
-               out=None, timing_iters=0):
+               out=None, timing_iters=0, brdf=None):
         """-> (B,8,H,W) float32 CUDA tensor; with timing_iters > 0 also the mean kernel time in ms (CUDA events).
         tf: (1|B,R,5) piecewise or (1|B,R,4) texture tensor, matching the variant this kernel was built with."""
         torch, d = self.torch, self.drv
@@ -205,6 +213,13 @@ class ReferenceDvrKernel:
         _ck(d.cuMemcpyHtoD(self.g_dvr[0], np.array([stepsize, alpha_early_out, density_min, density_max], np.float32).tobytes(), 16))
         ta = _read3(tft)
         _ck(d.cuMemcpyHtoD(self.g_tf[0], bytes(ta), C.sizeof(ta)))
+        if self.g_brdf is not None:
+            # brdf: dict(magnitude_scaling, ambient, specular, magnitude_center, magnitude_radius, specular_exponent, light) - light =
+            # position (point light) or direction (directional), as BRDFLambert::fillConstantMemory packs it (brdf.cpp:417-452)
+            blob = np.array([brdf["magnitude_scaling"], brdf["ambient"], brdf["specular"], brdf["magnitude_center"], brdf["magnitude_radius"]],
+                            np.float32).tobytes() + np.array([brdf["specular_exponent"]], np.int32).tobytes() + np.asarray(brdf["light"], np.float32).tobytes()
+            assert len(blob) == 36 == int(self.g_brdf[1]), (len(blob), int(self.g_brdf[1]))
+            _ck(d.cuMemcpyHtoD(self.g_brdf[0], blob, len(blob)))
         if out is None:
             out = torch.empty((B, 8, height, width), dtype=torch.float32, device="cuda")
         oa = _Accessor4(); oa.data = out.data_ptr()

@@ -25,13 +25,13 @@ def test_header_and_binding_agree():
 def test_library_exports_every_declared_symbol(built_lib):
     for s in _declared_symbols():
         assert hasattr(built_lib, s), s
-    assert built_lib.fvsrn_abi_version() == 2
+    assert built_lib.fvsrn_abi_version() == 3
 
 
 def test_struct_sizes_match_header(built_lib):
     # natural C layout of the header structs on LP64 ...
-    assert C.sizeof(_lib.NetworkInfo) == 20 * 4
-    assert C.sizeof(_lib.DvrParams) % 8 == 0 and C.sizeof(_lib.DvrParams) == 168
+    assert C.sizeof(_lib.NetworkInfo) == 22 * 4
+    assert C.sizeof(_lib.DvrParams) % 8 == 0 and C.sizeof(_lib.DvrParams) == 216
     assert C.sizeof(_lib.QueryInfo) == 48
     # ... and as the C compiler lays out include/fvsrn_b200.h
     import subprocess, tempfile

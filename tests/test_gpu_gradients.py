@@ -1,0 +1,131 @@
+"""
+SURVEY f4 - normals and shading in the DVR frame, against the reference's own kernels (oracle/_ref, built from the unmodified
+renderer/*.cuh with the matching defines): networks that predict the gradient next to the density (densitygrad, densitygrad:cubic),
+finite-difference normals on a density network (GRADIENT_MODE 1, 6 more SRN evaluations per shaded step), BRDFLambert with
+gradient-magnitude scaling and Phong shading (directional and point light), the normal channels 4..6 of the output tensor.
+  * reference-exact kernel mode: all 8 channels bit-identical to the reference kernel;
+  * fast modes (the mma.sync family renders every frame that needs normals, whichever fast mode is selected): RGBA within the
+    north_star tolerance where the normals come from the network; for finite differences the fp16 noise of two evaluations is
+    divided by 2h, so the gate is 3e-3 / 70 dB (measured 1.94e-3 / 85 dB; numbers in gpurun_out/parity_gradients.jsonl).
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+C3 = dict(hidden=32, num_layers=4, grid_res=32, seed=42, activation="ReLU")
+PHONG_DIR = dict(flags=("magnitude", "phong"), light_type=1, light=(0.3, -0.5, -0.8), magnitude_scaling=2.0, ambient=0.3, specular=0.5,
+                 magnitude_center=1.0, magnitude_radius=0.8, specular_exponent=8)
+PHONG_POINT = dict(PHONG_DIR, light_type=0, light=(1.5, 1.0, -2.0))
+# the cubed gradients of the random-init network are small (|g|^2 ~ 0.005, "gradientNorm" = 1/|g| ~ 10): scale the BRDF to that range
+PHONG_DIR_CUBIC = dict(PHONG_DIR, magnitude_scaling=400.0, magnitude_center=8.0, magnitude_radius=6.0)
+CASES = {
+    # name: (network kwargs, reference variant, finite-difference step or None, brdf or None)
+    "densitygrad": (dict(C3, output_mode="densitygrad", last_gain=6.0), "h32x4_relu_densgrad", None, None),
+    "densitygrad_cubic_phong_directional": (dict(C3, output_mode="densitygrad:cubic", last_gain=6.0), "h32x4_relu_densgrad_cubic_phong", None, PHONG_DIR_CUBIC),
+    "finite_differences_phong_point": (dict(C3, output_mode="density:direct", last_gain=6.0), "h32x4_relu_fd_phong", 1.0 / 128.0, PHONG_POINT),
+}
+SIZE, STEP = 512, 1 / 256
+
+
+@pytest.fixture(scope="module")
+def ref():
+    import torch
+    assert torch.cuda.is_available()
+    import ref_kernel
+    if not ref_kernel.available():
+        pytest.skip("oracle/_ref/*.ptx not built (needs /root/reference: python oracle/build_ref_ptx.py)")
+    return ref_kernel
+
+
+def _record(row):
+    d = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(d):
+        with open(os.path.join(d, "parity_gradients.jsonl"), "a") as f:
+            f.write(json.dumps(row) + "\n")
+
+
+def _frames(name, plume_tf, modes):
+    import parity
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import scenes, volnet
+    kw, variant, fd, brdf = CASES[name]
+    net = scenes.make_network(**kw)
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    want, _, _ = parity.render_reference(net, SIZE, SIZE, cam, scenes.DEFAULT_FOV_Y, plume_tf, STEP, variant=variant,
+                                         fd_stepsize=fd if fd else 0.01, brdf=brdf)
+    data = volnet.dumps(net)
+    got = {m: parity.render_ours(data, m, SIZE, SIZE, cam, plume_tf, STEP, fd_stepsize=fd, brdf=brdf)[0] for m in modes}
+    return want, got
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_reference_exact_mode_is_bit_identical_with_normals(ref, name, plume_tf):
+    want, got = _frames(name, plume_tf, ["reference_exact"])
+    img = got["reference_exact"]
+    assert want[:, 3].max() > 0.1 and np.abs(want[:, 4:7]).max() > 0.02        # a frame with content and normals
+    for c, label in enumerate(("r", "g", "b", "alpha", "normal x", "normal y", "normal z", "depth")):
+        same = (img[:, c] == want[:, c]) | (np.isnan(img[:, c]) & np.isnan(want[:, c]))
+        assert same.all(), (name, label, int((~same).sum()), float(np.nanmax(np.abs(img[:, c] - want[:, c]))))
+
+
+@pytest.mark.parametrize("name", list(CASES))
+def test_fast_modes_with_normals(ref, name, plume_tf):
+    import parity
+    want, got = _frames(name, plume_tf, ["mma_sync", "tcgen05"])
+    fd = CASES[name][2] is not None
+    for mode, img in got.items():
+        d = np.abs(img[:, :4] - want[:, :4])
+        dn = np.abs(img[:, 4:7] - want[:, 4:7])
+        row = dict(config=name, kernel_mode=mode, size=SIZE, rgba_max_abs=float(d.max()), psnr_db=float(parity.psnr(img[:, :4], want[:, :4])),
+                   normal_max_abs=float(dn.max()), normal_mean_abs=float(dn.mean()), frac_rgba_over_2e3=float((d.max(1) > 2e-3).mean()))
+        _record(row)
+        if not fd:
+            assert row["rgba_max_abs"] <= parity.RGBA_TOL and row["psnr_db"] >= parity.PSNR_MIN, row
+            assert row["normal_max_abs"] <= 1e-2, row
+        else:
+            # central differences of two fp16-accumulated evaluations, divided by 2h = 1/64: the normal of a sample moves with
+            # the last bits of the network output. Measured on B200: 1.94e-3 RGBA max-abs, 85 dB, normals 1.2e-3 max-abs
+            assert row["psnr_db"] >= 70.0 and row["rgba_max_abs"] <= 3e-3, row
+            assert row["normal_max_abs"] <= 1e-2 and row["normal_mean_abs"] <= 1e-4, row
+
+
+def test_gradient_mode_errors(plume_tf):
+    """adjoint mode is rejected, colour networks have no normals, BRDF flags are validated."""
+    import torch
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import pyrenderer as pr, scenes, volnet
+    sn = pr.SceneNetwork.from_bytes(volnet.dumps(scenes.make_network(**dict(C3, output_mode="rgbo"))))
+    vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
+    ie = pr.ImageEvaluatorSimple(); ie.volume = vol
+    ie.camera.set_parameters(torch.from_numpy(scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)))
+    vol.gradient_mode = pr.VolumeInterpolationNetwork.FINITE_DIFFERENCES
+    with pytest.raises(RuntimeError, match="density network"):
+        ie.render(64, 64)
+    vol.gradient_mode = pr.VolumeInterpolationNetwork.ADJOINT_METHOD
+    with pytest.raises(RuntimeError, match="adjoint"):
+        ie.render(64, 64)
+    vol.gradient_mode = pr.VolumeInterpolationNetwork.OFF_OR_DIRECT
+    ie.ray_evaluator.brdf.enable_phong = True
+    with pytest.raises(RuntimeError, match="normals"):
+        ie.render(64, 64)
+
+
+def test_evaluate_returns_density_for_gradient_networks():
+    """IVolumeInterpolation::evaluate of a densitygrad network is its density channel (1 output, sigmoid applied)."""
+    import torch
+    import fvsrn_b200  # noqa: F401
+    import oracle
+    from fvsrn_b200 import pyrenderer as pr, scenes, volnet
+    net = scenes.make_network(**dict(C3, output_mode="densitygrad", last_gain=6.0))
+    sn = pr.SceneNetwork.from_bytes(volnet.dumps(net))
+    vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
+    pos = torch.rand((4096, 3), device="cuda")
+    got = vol.evaluate(pos).cpu().numpy()
+    assert got.shape == (4096, 1)
+    want = oracle.evaluate(net, pos.cpu().numpy())
+    assert np.abs(got[:, 0] - np.asarray(want).reshape(len(got), -1)[:, 0]).max() <= 2e-3
