@@ -16,7 +16,7 @@ SYMBOLS = [
     "fvsrn_network_valid", "fvsrn_network_num_parameters", "fvsrn_network_compute_max_warps",
     "fvsrn_network_set_time_and_ensemble", "fvsrn_network_set_gradient_mode", "fvsrn_network_get_info", "fvsrn_network_set_kernel_mode", "fvsrn_network_get_kernel_mode", "fvsrn_network_prepare",
     "fvsrn_network_clear_gpu_resources", "fvsrn_evaluate", "fvsrn_evaluate_host", "fvsrn_render_dvr",
-    "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_extract_color_ex", "fvsrn_generate_rays", "fvsrn_evaluate_tf", "fvsrn_query",
+    "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_extract_color_ex", "fvsrn_extract_color_ex_noalloc", "fvsrn_generate_rays", "fvsrn_evaluate_tf", "fvsrn_query",
     "fvsrn_volume_load_cvol", "fvsrn_volume_save_cvol", "fvsrn_volume_from_dense", "fvsrn_volume_get_info", "fvsrn_volume_free",
     "fvsrn_volume_prepare", "fvsrn_render_dvr_grid", "fvsrn_evaluate_grid",
 ]
@@ -106,6 +106,7 @@ def lib():
         "fvsrn_render_dvr_host": [vp, C.POINTER(DvrParams), vp, vp],
         "fvsrn_extract_color": [vp, vp, i, i, i, vp],
         "fvsrn_extract_color_ex": [vp, vp, i, i, i, i, i, f, i, vp],
+        "fvsrn_extract_color_ex_noalloc": [vp, vp, i, i, i, i, i, f, i, vp],
         "fvsrn_generate_rays": [vp, i, f, i, i, vp, vp, vp],
         "fvsrn_volume_load_cvol": [C.c_char_p, C.c_size_t, C.POINTER(vp)],
         "fvsrn_volume_save_cvol": [vp, vp, C.c_size_t, C.POINTER(C.c_size_t)],

@@ -1045,6 +1045,117 @@ int fvsrn_extract_color_ex(const float* img_dev, void* out_dev, int batch, int h
     FV_CATCH
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// fvsrn_extract_color_ex_noalloc: the same pass for callers that cannot allocate (CUDA graph capture, serving loops).
+// fvsrn_extract_color_ex takes the two floats of its ChannelDepth min / max reduction from cudaMallocAsync; this variant keeps
+// its scratch in a file-scope __device__ array instead: one {min, max, saw-NaN} triple per block of kNoAllocPixelsPerPartial
+// pixels, then the reduced {min, max} in the first two floats of the tail. Every GPU that loads the library holds the
+// array (kNoAllocScratchFloats * 4 = 192 KiB + 256 B) until exit. All calls share it: calls that overlap on the GPU (two
+// streams, two host threads) race. Every word a call reads is written by that call first, so nothing has to be cleared.
+} // extern "C"
+namespace {
+constexpr long long kNoAllocPixelsPerPartial = 4096;
+constexpr long long kNoAllocMaxPartials = FVSRN_NOALLOC_MAX_PIXELS / kNoAllocPixelsPerPartial;      // 16384
+constexpr long long kNoAllocScratchFloats = 3 * kNoAllocMaxPartials + 64;
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocScratchFloats];
+
+// device address of g_noalloc_scratch on the current device. In host code the array's name is only a stand-in for the
+// symbol, not a device pointer: the address comes from cudaGetSymbolAddress, once per device, with that device current.
+float* noalloc_scratch_ptr() {
+    static std::mutex mu;
+    static float* ptrs[64] = {};
+    int dev = -1;
+    CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) throw std::runtime_error("device index out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        float* p = nullptr;
+        CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
+        if (!p) throw std::runtime_error("cudaGetSymbolAddress returned a null scratch address");
+        ptrs[dev] = p;
+    }
+    return ptrs[dev];
+}
+
+// stage 1: block k reduces pixels [k * 4096, (k + 1) * 4096) of the depth plane -> partial[3k..3k+2] = {min, max, saw NaN}
+__global__ void __launch_bounds__(256)
+depth_partials_kernel(const float* __restrict__ img, long long hw, long long total, float* __restrict__ partial) {
+    __shared__ float smin[8], smax[8];
+    __shared__ int snan[8];
+    float mn = FLT_MAX, mx = -FLT_MAX; int nan = 0;
+    const long long first = (long long)blockIdx.x * kNoAllocPixelsPerPartial;
+    for (long long i = first + threadIdx.x; i < first + kNoAllocPixelsPerPartial && i < total; i += blockDim.x) {
+        const long long b = i / hw, px = i - b * hw;
+        const float d = img[b * 8 * hw + 7 * hw + px];
+        if (d != d) nan = 1; else { mn = fminf(mn, d); mx = fmaxf(mx, d); }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o)); mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        nan |= __shfl_xor_sync(0xffffffffu, nan, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { smin[w] = mn; smax[w] = mx; snan[w] = nan; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < 8; ++k) { mn = fminf(mn, smin[k]); mx = fmaxf(mx, smax[k]); nan |= snan[k]; }
+        partial[3 * blockIdx.x + 0] = mn; partial[3 * blockIdx.x + 1] = mx; partial[3 * blockIdx.x + 2] = nan ? 1.f : 0.f;
+    }
+}
+// stage 2 (one block): the partials -> mm = {min, max}, NaN when any depth was NaN (torch.min / torch.max semantics)
+__global__ void __launch_bounds__(1024)
+depth_final_kernel(const float* __restrict__ partial, int n, float* __restrict__ mm) {
+    __shared__ float smin[32], smax[32];
+    __shared__ int snan[32];
+    float mn = FLT_MAX, mx = -FLT_MAX; int nan = 0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        mn = fminf(mn, partial[3 * i]); mx = fmaxf(mx, partial[3 * i + 1]); nan |= partial[3 * i + 2] != 0.f;
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o)); mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        nan |= __shfl_xor_sync(0xffffffffu, nan, o);
+    }
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { smin[w] = mn; smax[w] = mx; snan[w] = nan; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < 32; ++k) { mn = fminf(mn, smin[k]); mx = fmaxf(mx, smax[k]); nan |= snan[k]; }
+        mm[0] = nan ? __int_as_float(0x7fc00000) : mn; mm[1] = nan ? __int_as_float(0x7fc00000) : mx;
+    }
+}
+} // namespace
+extern "C" {
+
+int fvsrn_extract_color_ex_noalloc(const float* img_dev, void* out_dev, int batch, int height, int width,
+                                   int channel_mode, int tonemap, float max_exposure, int output_format, void* stream) {
+    FV_TRY
+    if (!img_dev || !out_dev) return fail("null device pointer");
+    if (output_format < FVSRN_OUTPUT_RGBA_F32 || output_format > FVSRN_OUTPUT_RGBA_F16) return fail("output format must be RGBA_F32, RGBA8 or RGBA_F16");
+    if (channel_mode < 0 || channel_mode > FVSRN_CHANNEL_COLOR) return fail("unknown channel mode");
+    if (tonemap && channel_mode == FVSRN_CHANNEL_COLOR && !(max_exposure > 0.f)) return fail("tonemapping needs a positive max_exposure");
+    if (batch < 0 || height < 0 || width < 0) return fail("negative image size");
+    const long long hw = (long long)height * width, total = hw * batch;
+    if (total > FVSRN_NOALLOC_MAX_PIXELS)
+        return fail("fvsrn_extract_color_ex_noalloc: batch * height * width = " + std::to_string(total) + " pixels exceeds the static scratch limit of " +
+                    std::to_string((long long)FVSRN_NOALLOC_MAX_PIXELS) + " (FVSRN_NOALLOC_MAX_PIXELS); use fvsrn_extract_color_ex");
+    if (total <= 0) return 0;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    float* scratch = noalloc_scratch_ptr();
+    float* mm = scratch + 3 * kNoAllocMaxPartials;      // the 64-float tail holds the reduced {min, max}
+    if (channel_mode == FVSRN_CHANNEL_DEPTH) {
+        const int parts = int((total + kNoAllocPixelsPerPartial - 1) / kNoAllocPixelsPerPartial);
+        depth_partials_kernel<<<parts, 256, 0, s>>>(img_dev, hw, total, scratch);
+        CUDA_OK(cudaGetLastError());
+        depth_final_kernel<<<1, 1024, 0, s>>>(scratch, parts, mm);
+        CUDA_OK(cudaGetLastError());
+    }
+    const int threads = 256;
+    const int blocks = int(std::min<long long>((total + threads - 1) / threads, 148 * 16));
+    extract_color_ex_kernel<<<blocks, threads, 0, s>>>(img_dev, out_dev, hw, batch, channel_mode, tonemap, max_exposure, output_format, mm);
+    CUDA_OK(cudaGetLastError());
+    return 0;
+    FV_CATCH
+}
+
 int fvsrn_generate_rays(const float* camera_matrix_dev, int batch, float fov_y_radians, int width, int height,
                         float* ray_start_dev, float* ray_dir_dev, void* stream) {
     FV_TRY

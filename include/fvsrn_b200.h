@@ -247,6 +247,19 @@ int  fvsrn_extract_color(const float* img_dev, float* out_dev, int batch, int he
 int  fvsrn_extract_color_ex(const float* img_dev, void* out_dev, int batch, int height, int width,
                             int channel_mode, int tonemap, float max_exposure, int output_format, void* stream);
 
+/* fvsrn_extract_color_ex without any allocation. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and results as fvsrn_extract_color_ex, which takes the scratch of its ChannelDepth min / max reduction from
+ * cudaMallocAsync; here that scratch is a static __device__ array inside the library (192 KiB, held by every GPU that loads the
+ * library until exit), and the call makes no cudaMalloc / cudaFree / allocating library call.
+ *   - limit: batch * height * width <= FVSRN_NOALLOC_MAX_PIXELS (2^26, e.g. 16 frames of 2048^2); larger inputs are
+ *     rejected with an error, not truncated;
+ *   - ALL calls share the one array: calls that overlap on the GPU (different streams or host threads) race on it - keep
+ *     them on one stream or order them with events. Nothing carries over between calls: each call writes every word it reads. */
+#define FVSRN_NOALLOC_MAX_PIXELS (1 << 26)
+int  fvsrn_extract_color_ex_noalloc(const float* img_dev, void* out_dev, int batch, int height, int width,
+                                    int channel_mode, int tonemap, float max_exposure, int output_format, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Tensor operators beside the fused path: what the reference's PyTorch marcher (applications/volnet/
  * raytracing.py:103, 150-154) calls per frame / per step, so that it can run against this library on the GPU as well.
