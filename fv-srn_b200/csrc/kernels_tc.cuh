@@ -203,6 +203,63 @@ struct SrnTc {
         }
     }
 
+    // The same latent vector through the LSU instead of the texture units, for the world-space batch query (eval_tc_kernel):
+    // random positions miss the texture cache (ncu r02a: L1 hit 8.8 %, 16.9 L2 sectors per sample over the four RGBA
+    // arrays), while the channel-last copy of the grid keeps all 16 channels of a corner in ONE 32-byte sector: 8 sectors
+    // per sample, one 256-bit load (LDG.E.256) per corner = 8 L1 wavefronts per sample. Same addressing and the same 8-bit
+    // fractional weights as the texture unit (unnormalised coordinate p*n - 0.5, clamp, weights rounded to 1/256 - oracle
+    // latent_group_t); the blend runs in packed fp16, one chain per z plane. Float grids only; byte-encoded grids keep
+    // the texture path.
+    static __device__ __forceinline__ void ldg256(const void* p, uint32_t (&r)[8]) {
+        asm volatile("ld.global.nc.v8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "l"(p));
+    }
+    static __device__ __forceinline__ void fetch_latent_lsu(const NetParams& P, float px, float py, float pz, uint32_t (&row)[K0 / 2]) {
+        if (P.grid_encoding != 0) { fetch_latent(P, px, py, pz, row); return; }
+        int i0[3], i1[3]; float w1[3];
+        const float pp[3] = {px, py, pz};
+        const int nn[3] = {P.gx, P.gy, P.gz};
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float u = fmaf(pp[a], float(nn[a]), -0.5f);
+            const float fl = floorf(u);
+            int cell = int(fl);
+            int q = __float2int_rn((u - fl) * 256.0f);
+            if (q >= 256) { q = 0; cell += 1; }
+            i0[a] = min(max(cell, 0), nn[a] - 1);
+            i1[a] = min(max(cell + 1, 0), nn[a] - 1);
+            w1[a] = float(q) * (1.0f / 256.0f);
+        }
+#pragma unroll
+        for (int g = 0; g < GC16; ++g) {
+            const GridGroup& G = P.groups[g];
+            const int nsrc = (SPEC == 1 || !(G.frac > 0.f)) ? 1 : 2;     // grid-uniform
+            __half2 acc[2][8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[0][j] = acc[1][j] = __float2half2_rn(0.f);
+#pragma unroll 1
+            for (int s = 0; s < nsrc; ++s) {
+                const uint4* base = reinterpret_cast<const uint4*>(s == 0 ? G.a : G.b);
+                const float ws = (nsrc == 1) ? 1.f : (s == 0 ? 1.f - G.frac : G.frac);
+                uint32_t v[8][8];
+                __half2 w2[8];
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int zi = (c >> 2) ? i1[2] : i0[2], yi = ((c >> 1) & 1) ? i1[1] : i0[1], xi = (c & 1) ? i1[0] : i0[0];
+                    ldg256(base + (size_t)((zi * P.gy + yi) * P.gx + xi) * G.voxel_stride, v[c]);
+                    const float wc = ((c >> 2) ? w1[2] : 1.f - w1[2]) * (((c >> 1) & 1) ? w1[1] : 1.f - w1[1]) * ((c & 1) ? w1[0] : 1.f - w1[0]);
+                    w2[c] = __float2half2_rn(wc * ws);
+                }
+#pragma unroll
+                for (int c = 0; c < 8; ++c)
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[c >> 2][j] = __hfma2(w2[c], u2h(v[c][j]), acc[c >> 2][j]);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) row[H / 2 + g * 8 + j] = h2u(__hadd2(acc[0][j], acc[1][j]));
+        }
+    }
+
     // Both samples of a trip at once for the NeRF-style matrix without direction input: the double-angle recurrences of
     // the two samples run in the two lanes of packed-fp32 instructions (FADD2 / FMUL2 / FFMA2, sm_100: one issue slot for
     // both samples; IEEE results, bit-identical to the scalar form in build_row). Everything else as build_row.
@@ -732,16 +789,27 @@ eval_tc_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Eval
 #ifndef FVSRN_EVAL_ORDER
 #define FVSRN_EVAL_ORDER 0   // measured on C2 (random positions): 0 = Fourier first, then fetch: 0.844 ms; 1 = both fetches first: 0.861 ms
 #endif
+#ifndef FVSRN_EVAL_LSU
+// latent fetch of the batch query: 1 = channel-last 256-bit loads (8 L2 sectors per sample), 0 = texture units (16.9).
+// A/B on one B200 (C2, 2^24 random positions, r02h): 0.890 ms through the texture units, 0.837 with 16 LDG.128 per sample,
+// 0.660 with 8 LDG.256; with two keyframes 1.568 -> 1.098 ms. A lane-pair variant (even lane x0 corner, odd lane x1 corner of
+// the same sample: 5 instead of 8 L1 wavefronts per sample, partial sums exchanged by SHFL) measured 0.758 - it spills at 96 registers.
+#define FVSRN_EVAL_LSU 1
+#endif
             uint32_t row0[Core::K0 / 2], row1[Core::K0 / 2];
+            auto fetch = [&](int slot, uint32_t (&row)[Core::K0 / 2]) {
+                if (FVSRN_EVAL_LSU) Net::fetch_latent_lsu(P, pos[slot][0], pos[slot][1], pos[slot][2], row);
+                else Net::fetch_latent(P, pos[slot][0], pos[slot][1], pos[slot][2], row);
+            };
             if (FVSRN_EVAL_ORDER == 1) {        // both slots' latent fetches in flight before any other arithmetic
-                Net::fetch_latent(P, pos[0][0], pos[0][1], pos[0][2], row0);
-                Net::fetch_latent(P, pos[1][0], pos[1][1], pos[1][2], row1);
+                fetch(0, row0);
+                fetch(1, row1);
             }
             Net::build_row(P, pos[0][0], pos[0][1], pos[0][2], dir[0][0], dir[0][1], dir[0][2], row0);
-            if (FVSRN_EVAL_ORDER == 0) Net::fetch_latent(P, pos[0][0], pos[0][1], pos[0][2], row0);
+            if (FVSRN_EVAL_ORDER == 0) fetch(0, row0);
             Net::store_row(ctx, 0, row0);
             Net::build_row(P, pos[1][0], pos[1][1], pos[1][2], dir[1][0], dir[1][1], dir[1][2], row1);
-            if (FVSRN_EVAL_ORDER == 0) Net::fetch_latent(P, pos[1][0], pos[1][1], pos[1][2], row1);
+            if (FVSRN_EVAL_ORDER == 0) fetch(1, row1);
             Net::store_row(ctx, 1, row1);
             float o0[4], o1[4];
             Net::mlp_compute(P, ctx, true, o0, o1);
