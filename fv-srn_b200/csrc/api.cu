@@ -976,7 +976,7 @@ int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* 
     q.tf_dev = reinterpret_cast<const float*>(base + tf_off);
     char* d_img = base + img_off;
     const bool has_rect = q.tile_w > 0 || q.tile_h > 0 || q.tile_x0 > 0 || q.tile_y0 > 0;
-    // A single full frame is rendered as four row bands that alternate between the caller's stream and the internal one:
+    // A single full frame is rendered as a few row bands that alternate between the caller's stream and the internal one:
     // each band's device-to-host copy follows its kernel on the same stream and overlaps the next band's kernel on the
     // other, and the next band's CTAs fill the SMs the previous band is draining.
     const int bands = (p->batch == 1 && !has_rect && !p->view_times_host && H >= 256 && net->aux_stream) ? 4 : 1;
@@ -987,10 +987,23 @@ int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* 
     } else {
         CUDA_OK(cudaEventRecord(net->ev_fork, s));
         CUDA_OK(cudaStreamWaitEvent(net->aux_stream, net->ev_fork, 0));
-        const int rows = int((H + bands - 1) / bands + 7) / 8 * 8;
+        // band heights in sixteenths of the frame, largest first: what is left exposed at the end is the LAST band's copy
+        // (and its kernel's drain), so the bands shrink towards the end of the frame. A/B on one B200 (C3, fp32 colour, kernel
+        // 4.67 ms; tools/ab_bands.sh): four equal bands 4.89 ms, 6/5/3/2 4.84, six or seven bands (5/4/3/2/1/1 ...) 4.98-5.01
+        int pattern[16] = {6, 5, 3, 2}, npat = 4;
+#if defined(FVSRN_EXPERIMENTS) || defined(FVSRN_HOST_BANDS_ENV)
+        if (const char* e = std::getenv("FVSRN_HOST_BANDS")) {
+            npat = 0;
+            for (const char* c = e; *c && npat < 16; ++c) if (*c >= '1' && *c <= '9') pattern[npat++] = *c - '0';
+        }
+#endif
+        int y_end[16], acc16 = 0, total16 = 0;
+        for (int i = 0; i < npat; ++i) total16 += pattern[i];
+        for (int i = 0; i < npat; ++i) { acc16 += pattern[i]; y_end[i] = i + 1 == npat ? int(H) : int((int64_t(H) * acc16 / total16 + 7) / 8 * 8); }
         int k = 0;
-        for (int y0 = 0; y0 < H; y0 += rows, ++k) {
-            const int h = int(std::min<int64_t>(rows, H - y0));
+        for (int y0 = 0; k < npat && y0 < H; ++k) {
+            const int h = std::min(y_end[k], int(H)) - y0;
+            if (h <= 0) continue;
             cudaStream_t bs = (k & 1) ? net->aux_stream : s;
             q.tile_x0 = 0; q.tile_y0 = y0; q.tile_w = int(W); q.tile_h = h;
             do_render(net, &q, reinterpret_cast<float*>(d_img), bs);
@@ -998,6 +1011,7 @@ int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* 
                 const size_t off = (size_t(c) * W * H + size_t(y0) * W) * elem;
                 CUDA_OK(cudaMemcpyAsync(reinterpret_cast<char*>(out_host) + off, d_img + off, size_t(h) * W * elem, cudaMemcpyDeviceToHost, bs));
             }
+            y0 += h;
         }
         CUDA_OK(cudaEventRecord(net->ev_join, net->aux_stream));
         CUDA_OK(cudaStreamWaitEvent(s, net->ev_join, 0));

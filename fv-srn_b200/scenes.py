@@ -137,7 +137,7 @@ def make_network(hidden: int = 32, num_layers: int = 4, grid_res: int = 32, grid
                  fourier: str = "nerf", fourier_std: float = 1.0, output_mode: str = "density:direct", seed: int = 42,
                  grid_std: float = 0.5, time_keyframes: int = 0, has_direction: bool = False, pass_time: bool = False,
                  box_min=(-0.5, -0.5, -0.5), box_size=(1.0, 1.0, 1.0), last_gain: float = 1.0,
-                 last_bias: float | None = None, hidden_gain: float = 1.0) -> volnet.SceneNetwork:
+                 last_bias: float | None = None, hidden_gain: float = 1.0, direction_in_fourier: bool = False) -> volnet.SceneNetwork:
     """Random-init SRN shaped like the reference's SceneRepresentationNetwork (network.py:653-770):
     ``num_layers`` linear layers (``--layers h:h:..`` has num_layers-1 entries), Fourier count (hidden-4)/2
     (collect_possible_layers.py:50), nn.Linear default init U(-1/sqrt(fan_in), 1/sqrt(fan_in)), grid ~ N(0, grid_std).
@@ -155,7 +155,7 @@ def make_network(hidden: int = 32, num_layers: int = 4, grid_res: int = 32, grid
     net = volnet.SceneNetwork()
     net.has_direction = has_direction
     net.has_time = bool(pass_time)
-    fc = 3
+    fc = 6 if (has_direction and direction_in_fourier) else 3     # useDirectionInFourierFeatures: B multiplies (position, direction)
     if fourier == "nerf":  # scaled block identity (network.py:55-63)
         blocks = [(2.0 ** i) * np.eye(fc) for i in range(int(math.ceil(nf / fc)))]
         B = np.concatenate(blocks, 0)[:nf]

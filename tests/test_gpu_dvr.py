@@ -111,6 +111,54 @@ def test_dvr_rgbo_network_skips_tf(env):
     assert np.abs(img[:, :4] - ref[:, :4]).max() <= RGBA_TOL
 
 
+@pytest.mark.parametrize("dir_in_fourier", [False, True])
+def test_dvr_network_with_direction_input(env, plume_tf, dir_in_fourier):
+    """The DIR kernels in the DVR frame: the ray direction is a network input (channels 4..6), optionally also inside the
+    Fourier features (USE_DIRECTION 1 / 2, renderer_volume_tensorcores.cuh:768-807) - per ray constant, per pixel different."""
+    net = env.scenes.make_network(hidden=32, num_layers=3, grid_res=8, has_direction=True, fourier="gauss", fourier_std=0.7,
+                                  direction_in_fourier=dir_in_fourier, seed=5, last_gain=4.0)
+    assert net.direction_in_fourier == dir_in_fourier
+    cam = env.scenes.camera_reference_frame(**env.scenes.DEFAULT_CAMERA)
+    vol = _volume(env, net)
+    tf = plume_tf.copy(); tf[..., 3] *= 0.25         # this random network sits high in the TF: keep the frame translucent like the BASELINE scenes
+    ie = _evaluator(env, vol, cam, tf, 1 / 64)
+    img = ie.render(48, 32).cpu().numpy()
+    ref, steps, _ = env.oracle.render_dvr(net, width=48, height=32, camera=cam, fov_y=env.scenes.DEFAULT_FOV_Y, stepsize=1 / 64, tf=tf)
+    assert 0.05 < ref[:, 3].max() < 0.95
+    assert np.abs(img[:, :4] - ref[:, :4]).max() <= RGBA_TOL
+    _check_steps(ie.last_step_counts.cpu().numpy(), steps)
+
+
+def test_dvr_per_view_transfer_functions_with_tiles_and_times(env, plume_tf):
+    """tf_batch == B (one TF per view, re-staged per tile in the tcgen05 kernel) together with per-view latent times and a
+    screen tile - the combination a sharded time sweep with per-view TFs makes."""
+    g = Golden("c5_time")
+    cams = env.scenes.camera_sweep(3)
+    tfs = np.concatenate([plume_tf, plume_tf, plume_tf], 0).copy()
+    tfs[1, :, 3] *= 0.4; tfs[2, :, 3] *= 2.5; tfs[2, :, :3] = tfs[2, :, :3][:, ::-1]
+    times = [0.25, 1.0, 1.75]
+    W, H, tile = 64, 40, (8, 4, 40, 24)
+    vol = _volume(env, g.volnet_bytes)
+    ie = _evaluator(env, vol, cams, tfs, 1 / 64)
+    ie.view_times = times
+    ie.tile = tile
+    img = ie.render(W, H).cpu().numpy()
+    x0, y0, w, h = tile
+    for b, t in enumerate(times):
+        ref, _, _ = env.oracle.render_dvr(g.net, width=W, height=H, camera=cams[b:b + 1], fov_y=env.scenes.DEFAULT_FOV_Y,
+                                          stepsize=1 / 64, tf=tfs[b:b + 1], time=t, tile=tile)
+        assert np.abs(img[b, :4, y0:y0 + h, x0:x0 + w] - ref[0, :4, y0:y0 + h, x0:x0 + w]).max() <= RGBA_TOL, (b, t)
+    assert not np.array_equal(img[0, :4], img[1, :4])
+    # without per-view times: one launch over the batch, every view with its own TF
+    ie.view_times = None
+    vol.current_network().set_time_and_ensemble(1.0, 0)
+    img = ie.render(W, H).cpu().numpy()
+    for b in range(3):
+        ref, _, _ = env.oracle.render_dvr(g.net, width=W, height=H, camera=cams[b:b + 1], fov_y=env.scenes.DEFAULT_FOV_Y,
+                                          stepsize=1 / 64, tf=tfs[b:b + 1], time=1.0, tile=tile)
+        assert np.abs(img[b, :4, y0:y0 + h, x0:x0 + w] - ref[0, :4, y0:y0 + h, x0:x0 + w]).max() <= RGBA_TOL, b
+
+
 def test_dvr_tiles_and_views_compose(env, plume_tf):
     """Screen-tile sharding (C4) and view batches (C5): tiles rendered separately equal the full frame bit for bit."""
     g = Golden("c1_relu_nerf")
