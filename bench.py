@@ -215,7 +215,29 @@ def run_b200(args):
     # ---- this rank's share of a step and where it lands. The DVR kernel writes the selected colour channel in the gather
     # format itself (fused colour extraction, fvsrn_dvr_params.output_format): no second pass, no 32 B/pixel tensor.
     if tiles:   # screen-band sharding of ONE frame: contiguous row bands of (nearly) equal estimated march cost
-        bands = fdist.partition_rows_by_cost(scenes.estimate_row_cost(cam_np, scenes.DEFAULT_FOV_Y, S, S, net.box_min, net.box_size), world, align=16)
+        bands = fdist.partition_rows_by_cost(scenes.estimate_row_cost(cam_np, scenes.DEFAULT_FOV_Y, S, S, net.box_min, net.box_size), world, align=8)
+        if world > 1 and not args.no_rebalance:
+            # feedback: the estimate knows the box, not the data (early termination, empty space). Render the estimated bands,
+            # measure each rank's kernel time, rescale the estimate band by band and cut again - twice.
+            row_cost = scenes.estimate_row_cost(cam_np, scenes.DEFAULT_FOV_Y, S, S, net.box_min, net.box_size)
+            scratch = _alloc_image(torch, fmt, 1, S, S)
+            for it in range(2):
+                y0, bh = bands[rank]
+                q = ie._params(S, S, cam_dev, tf_dev, _image_strides(fmt, scratch, S))
+                q.output_format, q.channel_mode = pr.OUTPUT_FORMATS[fmt], 3
+                q.tile_x0, q.tile_y0, q.tile_w, q.tile_h = 0, y0, S, bh
+                ce = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+                ms = 0.0
+                if bh > 0:
+                    for k in range(3):
+                        if k == 1: ce[0].record()
+                        _lib.check(L.fvsrn_render_dvr(sn._h, C.byref(q), scratch.data_ptr(), C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+                    ce[1].record(); torch.cuda.synchronize()
+                    ms = ce[0].elapsed_time(ce[1]) / 2
+                all_ms = [None] * world
+                dist.all_gather_object(all_ms, float(ms))
+                bands, row_cost = fdist.rebalance_rows_by_time(row_cost, bands, all_ms, align=8)
+            del scratch
         y0, bh = bands[rank]
         frames = [_alloc_image(torch, fmt, 1, S if rank == 0 else max(bh, 1), S) for _ in range(2)]      # rank 0 holds the whole frame
         if fmt == "rgba_f32":
@@ -402,7 +424,7 @@ def run_b200(args):
             "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong" if tiles else "weak",
             "vs_baseline": None, "dtype": "f16", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {w['desc']}", "views_per_step": frames_per_step, "samples_per_pixel": int(w.get("spp", 1)),
-                       "sharding": (f"one frame per step split into {world} contiguous row bands of equal estimated march cost {[b[1] for b in bands]}, "
+                       "sharding": (f"one frame per step split into {world} contiguous row bands of equal {'estimated' if (args.no_rebalance or world == 1) else 'estimated-then-measured'} march cost {[b[1] for b in bands]}, "
                                     f"bands received in place on rank 0 (NCCL send/recv, {fmt})") if tiles else
                                    (f"{V} view(s) per GPU, {fmt} pixels collected on rank 0 (NCCL {args.collective}), transfer of step k overlaps the render of step k+1" if world > 1 else "single GPU"),
                        "output": f"{fmt} colour written by the DVR kernel (fused extract_color)",
@@ -528,6 +550,7 @@ def main():
     ap.add_argument("--no-batch-query", action="store_true", help="skip the C2 world-space batch query measurement")
     ap.add_argument("--no-gpu-reference", action="store_true", help="skip timing the reference's own kernel (oracle/_ref PTX) and the parity check against it")
     ap.add_argument("--no-variants", action="store_true", help="skip the C3 SnakeAlt / Gaussian-Fourier variants")
+    ap.add_argument("--no-rebalance", action="store_true", help="--sharding tiles: keep the box-only cost estimate (no measured feedback)")
     ap.add_argument("--sharding", default="views", choices=["views", "tiles"],
                     help="N GPUs: views = every rank renders its own views per step (weak scaling); tiles = ONE frame per step split "
                          "into cost-balanced row bands (strong scaling, BASELINE C4)")

@@ -63,6 +63,20 @@ def partition_rows_by_cost(row_cost: Sequence[float], world: int, align: int = 1
     return [(cuts[k], cuts[k + 1] - cuts[k]) for k in range(world)]
 
 
+def rebalance_rows_by_time(row_cost: Sequence[float], bands: Sequence[Tuple[int, int]], band_ms: Sequence[float], align: int = 16):
+    """Feedback step for partition_rows_by_cost: `band_ms[r]` is the measured render time of rank r's band (y0, h). The estimate
+    of every band is rescaled so that its rows sum to the measured time - what the estimate misses (early termination, empty
+    space, TF-dependent density) is constant enough within a band - and the frame is cut again. Returns (bands, row_cost): feed the
+    returned row_cost to the next call for a second iteration. Pure host arithmetic, identical on every rank given the same inputs
+    (all-gather the times first)."""
+    import numpy as np
+    c = np.maximum(np.asarray(row_cost, np.float64), 0.0) + 1e-9
+    for (y0, h), ms in zip(bands, band_ms):
+        if h > 0 and ms > 0:
+            c[y0:y0 + h] *= float(ms) / c[y0:y0 + h].sum()
+    return partition_rows_by_cost(c, len(bands), align), c
+
+
 def gather_row_bands(local: Optional[torch.Tensor], bands: Sequence[Tuple[int, int]], out: Optional[torch.Tensor], dst: int = 0,
                      async_op: bool = False):
     """The finished frame on `dst`: every rank owns one contiguous band of rows (partition_rows_by_cost) of ONE packed-pixel
