@@ -394,6 +394,18 @@ def run_b200(args):
         batch_query = {"workload": "C2: 2^24 random positions, same network (fvsrn_evaluate)", "ms": q_ms, "value": n_q / (q_ms * 1e-3),
                        "unit": "samples/s", "tensor_frac_of_peak": n_q * w["flop"] / (q_ms * 1e-3) / 1e12 / peaks()["tflops"],
                        "checksum": float(dens.double().mean())}
+        if world == 1 and not args.no_gpu_reference:
+            # the reference's own batch-query kernel (EvaluateNoBatches + its tensor-core SRN, oracle/_ref PTX) on the same positions
+            try:
+                import ref_kernel
+                if ref_kernel.available():
+                    rk = ref_kernel.ReferenceEvalKernel(net, time=0.0)       # fvsrn_evaluate runs at the handle's current time (0)
+                    ref_d, ref_ms = rk.evaluate(pos, timing_iters=3)
+                    batch_query["reference_gpu_kernel"] = {"ms": ref_ms, "value": n_q / (ref_ms * 1e-3), "speedup_of_this_kernel": ref_ms / q_ms,
+                                                           "max_abs_vs_reference": float((dens - ref_d).abs().max()), "gate": 1e-2}
+                    del ref_d, rk
+            except Exception as e:      # no build for this network shape (e.g. the 64x6 workloads)
+                batch_query["reference_gpu_kernel"] = {"unavailable": str(e)[:200]}
         del pos, dens
 
     red = torch.tensor([total_ms, kernel_ms, e2e_s], dtype=torch.float64, device="cuda")

@@ -104,6 +104,23 @@ def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, e
     return src
 
 
+def eval_source(hidden16, num_hidden, nf, activation, output_mode, block_size, encoding=0, **_):
+    """The translation unit IVolumeInterpolation::evaluate assembles for the world-space batch query (volume_interpolation.cpp:
+    26-127): the network defines of VolumeInterpolationNetwork::getDefines + EvaluateNoBatches (renderer_volume_kernels1.cuh)."""
+    d = [
+        ("KERNEL_DOUBLE_PRECISION", 0), ("KERNEL_SYNCHRONIZED_TRACING", 1), ("BLOCK_SIZE", block_size),
+        ("NUM_HIDDEN_LAYERS", num_hidden), ("HIDDEN_CHANNELS_DIV16", hidden16), ("HAS_FOURIER_FEATURES", 1),
+        ("NUM_FOURIER_FEATURES", nf), ("USE_DIRECTION", 0), ("ACTIVATION", activation), ("OUTPUT_MODE", output_mode),
+        ("FIRST_AND_LAST_IN_SHARED_MEMORY", 0), ("LATENT_GRID_CHANNELS_DIV16", 1), ("LATENT_GRID_ENCODING", encoding),
+        ("PASS_TIME_TO_NETWORK", 0), ("GRADIENT_MODE", 0),
+    ]
+    src = "".join(f"#define {k} {v}\n" for k, v in d)
+    src += '#include "renderer_volume_tensorcores.cuh"\n'
+    src += "#define VOLUME_INTERPOLATION_T ::kernel::VolumeInterpolationTensorcores\n#define OUTPUT_CHANNELS 1\n#define VOLUME_USE_DIRECTION 0\n"
+    src += '#include "renderer_volume_kernels1.cuh"\n'
+    return src
+
+
 # TEST-ONLY patch, applied to the in-memory copy of two headers for the "*_steps" variants (never written anywhere): the
 # reference kernel does not output its per-ray step count (terminationIndex is a local, ..stepping_dvr.cuh:83-84,156), so
 # the count of valid steps is routed through the (otherwise zero) normal.x channel. Arithmetic and control flow of the
@@ -120,7 +137,7 @@ STEP_PATCHES = {
 }
 
 
-def compile_ptx(src, patch_steps=False, tf="piecewise", volume_symbol="&volumeInterpolationTensorcoresParameters"):
+def compile_ptx(src, patch_steps=False, tf="piecewise", volume_symbol="&volumeInterpolationTensorcoresParameters", names_override=None):
     from cuda.bindings import nvrtc
 
     def ck(r):
@@ -142,7 +159,7 @@ def compile_ptx(src, patch_steps=False, tf="piecewise", volume_symbol="&volumeIn
     headers += [SHIM_FORWARD.encode(), b"#pragma once\n"]
     names += [b"forward.h", b"forward_vector.h"]
     prog = ck(nvrtc.nvrtcCreateProgram(src.encode(), b"main.cu", len(headers), headers, names))
-    names_all = [n if n != "&volumeInterpolationTensorcoresParameters" else volume_symbol for n in NAMES] + [TF_NAMES[tf]]
+    names_all = names_override or ([n if n != "&volumeInterpolationTensorcoresParameters" else volume_symbol for n in NAMES] + [TF_NAMES[tf]])
     for n in names_all:
         ck(nvrtc.nvrtcAddNameExpression(prog, n.encode()))
     cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
@@ -189,8 +206,8 @@ def main():
         return 0
     os.makedirs(OUT, exist_ok=True)
     meta = {}
+    only = set(sys.argv[1:])
     for base, cfg in CONFIGS.items():
-        only = set(sys.argv[1:])
         if only and base not in only:
             continue
         for name, patch in ((base, False), (base + "_steps", True)):
@@ -200,6 +217,15 @@ def main():
             open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
             meta[name] = dict(cfg, lowered=lowered, ptx=name + ".ptx", step_count_patch=patch)
             print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['ImageEvaluatorSimpleKernel']}")
+    # the world-space batch query (BASELINE C2) of the two 32x4 networks: EvaluateNoBatches
+    for base in ("h32x4_relu", "h32x4_snakealt"):
+        name = base + "_eval"
+        if only and name not in only:
+            continue
+        ptx, lowered = compile_ptx(eval_source(**CONFIGS[base]), names_override=["EvaluateNoBatches", "&volumeInterpolationTensorcoresParameters"])
+        open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
+        meta[name] = dict(CONFIGS[base], eval=True, lowered=lowered, ptx=name + ".ptx", step_count_patch=False)
+        print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['EvaluateNoBatches']}")
     for name, patch in (("grid_trilinear", False), ("grid_trilinear_steps", True)):
         if len(sys.argv) > 1 and "grid_trilinear" not in sys.argv[1:]:
             continue

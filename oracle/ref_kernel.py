@@ -96,9 +96,15 @@ class ReferenceDvrKernel:
         ptx = open(os.path.join(REF_DIR, m["ptx"]), "rb").read() + b"\0"
         self.module = _ck(driver.cuModuleLoadData(ptx))          # JIT compute_75 PTX -> sm_100 SASS
         low = m["lowered"]
+        self.g_vol = _ck(driver.cuModuleGetGlobal(self.module, low["&volumeInterpolationTensorcoresParameters"].encode()))
+        self._keep = []
+        if m.get("eval"):       # the batch-query build (ReferenceEvalKernel): no camera / marcher / TF constants
+            self.func = _ck(driver.cuModuleGetFunction(self.module, low["EvaluateNoBatches"].encode()))
+            self._upload_network(net, float(time), unit_box=True)
+            self._occupancy()
+            return
         self.func = _ck(driver.cuModuleGetFunction(self.module, low["ImageEvaluatorSimpleKernel"].encode()))
         self.g_cam = _ck(driver.cuModuleGetGlobal(self.module, low["&cameraReferenceFrameParameters"].encode()))
-        self.g_vol = _ck(driver.cuModuleGetGlobal(self.module, low["&volumeInterpolationTensorcoresParameters"].encode()))
         self.g_dvr = _ck(driver.cuModuleGetGlobal(self.module, low["&rayEvaluationSteppingDvrParameters"].encode()))
         tf_sym = "&transferFunctionTextureParameters" if tf == "texture" else "&transferFunctionPiecewiseParameters"
         self.g_tf = _ck(driver.cuModuleGetGlobal(self.module, low[tf_sym].encode()))
@@ -106,10 +112,12 @@ class ReferenceDvrKernel:
         self.g_brdf = None
         if m.get("brdf") and "&brdfLambertParameters" in low:
             self.g_brdf = _ck(driver.cuModuleGetGlobal(self.module, low["&brdfLambertParameters"].encode()))
-        self._keep = []
         self._upload_network(net, float(time))
-        sms = torch.cuda.get_device_properties(0).multi_processor_count
-        bps = _ck(driver.cuOccupancyMaxActiveBlocksPerMultiprocessor(self.func, self.block, 0))
+        self._occupancy()
+
+    def _occupancy(self):
+        sms = self.torch.cuda.get_device_properties(0).multi_processor_count
+        bps = _ck(self.drv.cuOccupancyMaxActiveBlocksPerMultiprocessor(self.func, self.block, 0))
         self.max_grid = max(1, bps) * sms
         self.blocks_per_sm = bps
 
@@ -157,7 +165,7 @@ class ReferenceDvrKernel:
             vals = grid.raw.astype(np.uint8)
         return [self._texture(np.ascontiguousarray(np.transpose(vals[4 * i:4 * i + 4], (1, 2, 3, 0)))) for i in range(4)]
 
-    def _upload_network(self, net, time):
+    def _upload_network(self, net, time, unit_box=False):
         H, nf = net.input_channels_out(), net.num_fourier
         grids = net.time_grids or net.ensemble_grids
         # keyframe selection as SceneNetwork::setTimeAndEnsemble / fillConstantMemory (:1290-1352): `time` is the keyframe index
@@ -184,8 +192,9 @@ class ReferenceDvrKernel:
         add(np.ascontiguousarray(np.stack([l.bias for l in net.layers[1:-1]]), np.float16).tobytes())
         add(np.ascontiguousarray(np.asarray(net.layers[-1].weights).T, np.float16).tobytes())   # cWeightsLast [H] / half2 [H][cout/2]
         add(np.ascontiguousarray(net.layers[-1].bias, np.float16).tobytes())
-        add(np.array(net.box_min, np.float32).tobytes())
-        add(np.array(net.box_size, np.float32).tobytes())
+        # IVolumeInterpolation::evaluate forces the box to the unit cube (volume_interpolation.cpp:45-48)
+        add(np.array((0, 0, 0) if unit_box else net.box_min, np.float32).tobytes())
+        add(np.array((1, 1, 1) if unit_box else net.box_size, np.float32).tobytes())
         add(np.array([net.layers[0].activation_param], np.float32).tobytes())
         add(np.array([self.fd_stepsize], np.float32).tobytes())                         # finiteDifferencesStepsize (GRADIENT_MODE 1)
         add(np.array([0.01], np.float32).tobytes())                                     # latentGridDifferencesStepSize (unused)
@@ -245,6 +254,49 @@ class ReferenceDvrKernel:
             flush.zero_()
             e0.record(); launch(); e1.record(); torch.cuda.synchronize()
             ms += e0.elapsed_time(e1)
+        return out, ms / timing_iters
+
+
+class _Accessor2(C.Structure):   # kernel::Tensor2RW<float>
+    _fields_ = [("data", C.c_uint64), ("sizes", C.c_int32 * 2), ("strides", C.c_int32 * 2)]
+
+
+class ReferenceEvalKernel(ReferenceDvrKernel):
+    """The reference's world-space batch query on the GPU: IVolumeInterpolation::evaluate -> EvaluateNoBatches
+    (volume_interpolation.cpp:26-127, renderer_volume_kernels1.cuh:15-71) with the tensor-core SRN, built by
+    oracle/build_ref_ptx.py as `<network>_eval`. positions (N,3) in the unit cube -> densities (N,1)."""
+
+    def __init__(self, net, time=0.0):
+        act = net.layers[0].activation
+        super().__init__(net, variant=f"h{net.input_channels_out()}x{len(net.layers)}_{act.lower()}_eval", time=time)
+
+    def evaluate(self, positions, timing_iters=0):
+        torch, d = self.torch, self.drv
+        pos = positions if torch.is_tensor(positions) else torch.as_tensor(np.ascontiguousarray(positions, np.float32))
+        pos = pos.to("cuda", torch.float32).contiguous()
+        n = pos.shape[0]
+        out = torch.empty((n, 1), dtype=torch.float32, device="cuda")
+
+        def acc(t):
+            a = _Accessor2(); a.data = t.data_ptr()
+            for i in range(2):
+                a.sizes[i] = t.shape[i]; a.strides[i] = t.stride(i)
+            return a
+        vs, pa, da, oa = _Dim3(n, 1, 1), acc(pos), _Accessor2(), acc(out)
+        args = (C.c_void_p * 4)(C.addressof(vs), C.addressof(pa), C.addressof(da), C.addressof(oa))
+        grid = min((n + self.block - 1) // self.block, self.max_grid)
+        stream = torch.cuda.current_stream().cuda_stream
+
+        def launch():
+            _ck(d.cuLaunchKernel(self.func, grid, 1, 1, self.block, 1, 1, 0, stream, C.addressof(args), 0))
+        launch(); torch.cuda.synchronize()
+        if timing_iters <= 0:
+            return out
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        ms = 0.0
+        for _ in range(timing_iters):
+            flush.zero_(); e0.record(); launch(); e1.record(); torch.cuda.synchronize(); ms += e0.elapsed_time(e1)
         return out, ms / timing_iters
 
 

@@ -100,3 +100,34 @@ def test_baseline_config_matches_reference_kernel(ref, name, plume_tf):
         # crosses 1-1e-5 inside fp16 noise (5% of the saturating rays at most here); never by more than a few steps
         assert r["step_count_mismatch_frac"] <= 0.05 and r["step_count_max_diff"] <= 8, (name, mode, r)
         assert abs(r["total_steps"] - r["total_steps_ref"]) <= 0.002 * r["total_steps_ref"], (name, mode, r)
+
+
+@pytest.mark.parametrize("activation,last_gain", [("ReLU", 6.0), ("SnakeAlt:2", 12.0)])
+def test_batch_query_c2_matches_reference_kernel(ref, activation, last_gain):
+    """BASELINE configs[1] (C2) at its own size - 2^24 random positions through the 32x4 network with the 32^3 x 16 grid - against
+    the reference's own batch-query kernel (IVolumeInterpolation::evaluate -> EvaluateNoBatches with the tensor-core SRN, built from
+    the unmodified renderer/*.cuh)."""
+    import torch
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import pyrenderer as pr, scenes, volnet
+    net = scenes.make_network(**dict(C3, activation=activation, last_gain=last_gain))
+    g = torch.Generator(device="cuda"); g.manual_seed(11)
+    pos = torch.rand((1 << 24, 3), device="cuda", generator=g)
+    pos[:8] = torch.tensor([[0, 0, 0], [1, 1, 1], [0, 1, 0], [1, 0, 0.5], [0.5, 0.5, 0.5], [1e-7, 0.999999, 0.5], [0.25, 0, 1], [1, 1, 0]], device="cuda")
+    want = ref.ReferenceEvalKernel(net).evaluate(pos)
+    assert float(want.std()) > 0.05
+    for mode in MODES:
+        sn = pr.SceneNetwork.from_bytes(volnet.dumps(net)); sn.kernel_mode = mode
+        vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
+        got = vol.evaluate(pos)
+        d = (got - want).abs()
+        # Gate: the bound the reference's own unit test puts on exactly this operator (its tensor-core kernel against its PyTorch
+        # network: 1e-2, unittests/testSRN.cpp:94-208) on the maximum over all 2^24 outputs, and 1e-3 on the mean. Measured
+        # (max / max inside the density range [0,1] the marcher uses / mean): ReLU 3.8e-3 / 2.2e-3 / 2.7e-4 (tcgen05), 3.5e-3 / 2.3e-3 /
+        # 2.7e-4 (mma.sync); SnakeAlt 5.1e-3 / 3.5e-3 / 5.1e-4 and 6.0e-3 / 4.5e-3 / 5.2e-4 - the tail of 1.7e7 fp16 evaluations.
+        inside = (want >= 0) & (want <= 1)
+        row = dict(config=f"C2_{activation}", kernel_mode=mode, n=int(pos.shape[0]), max_abs=float(d.max()), mean_abs=float(d.mean()),
+                   max_abs_inside_density_range=float(d[inside].max()), output_min=float(want.min()), output_max=float(want.max()))
+        _record(row)
+        assert row["max_abs"] <= 1e-2, row
+        assert row["mean_abs"] <= 1e-3, row
