@@ -20,6 +20,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 C3 = dict(hidden=32, num_layers=4, grid_res=32, seed=42)
 CASES = {
     # name: (network kwargs, size, stepsize, tf_kind, time[, absorption factor])
+    # BASELINE configs[0]: the reference's own CPU-runnable case - 16^3 x 16 grid, 256^2, step 0.005
+    "C1_relu_nerf_256": (dict(C3, grid_res=16, activation="ReLU", last_gain=6.0), 256, 0.005, 0, None),
     "C3_relu_nerf": (dict(C3, activation="ReLU", last_gain=6.0), 1024, 1 / 512, 0, None),
     # the bench frame is translucent (max alpha 0.44: no ray terminates early); the same frame with 60x the absorption
     # saturates rays, so that early termination is decided at full size for the NeRF-Fourier networks as well (the
