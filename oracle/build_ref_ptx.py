@@ -69,7 +69,7 @@ def grid_source(early_out=1, blend_mode=1, tf="piecewise", interpolation=1):
 
 
 def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, early_out=1, blend_mode=1, first_last_shared=0,
-                encoding=0, tf="piecewise", gradient_mode=0, brdf=(), light_type=1, steps_variant=True):
+                encoding=0, tf="piecewise", gradient_mode=0, brdf=(), light_type=1, steps_variant=True, skip_tf=0):
     """The translation unit IImageEvaluator::getKernel + ImageEvaluatorSimple::render assemble (SURVEY App. F).
     encoding: LATENT_GRID_ENCODING 0 float / 1 byte-linear / 2 byte-gaussian (volume_interpolation_network.cpp:1211);
     tf "texture": TransferFunctionTexture in its tensor form (transfer_function_texture.cpp: TRANSFER_FUNCTION_TEXTURE__USE_TENSOR,
@@ -85,7 +85,7 @@ def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, e
         ("RAY_EVALUATION_STEPPING__TRANSFER_FUNCTION_T", TF_TYPES[tf][0]),
         ("RAY_EVALUATION_STEPPING__BLENDING_T", "::kernel::Blending"),
         ("RAY_EVALUATION_STEPPING__BRDF_T", "::kernel::BRDFLambert"),
-        ("RAY_EVALUATION_STEPPING__ENABLE_EARLY_OUT", early_out), ("RAY_EVALUATION_STEPPING__SKIP_TRANSFER_FUNCTION", 0),
+        ("RAY_EVALUATION_STEPPING__ENABLE_EARLY_OUT", early_out), ("RAY_EVALUATION_STEPPING__SKIP_TRANSFER_FUNCTION", skip_tf),
         ("BLENDING_MODE", blend_mode), ("BRDF_LAMBERT_LIGHT_TYPE", light_type),
     ]
     if "magnitude" in brdf:
@@ -104,7 +104,7 @@ def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, e
     return src
 
 
-def eval_source(hidden16, num_hidden, nf, activation, output_mode, block_size, encoding=0, **_):
+def eval_source(hidden16, num_hidden, nf, activation, output_mode, block_size, encoding=0, channels=1, **_):
     """The translation unit IVolumeInterpolation::evaluate assembles for the world-space batch query (volume_interpolation.cpp:
     26-127): the network defines of VolumeInterpolationNetwork::getDefines + EvaluateNoBatches (renderer_volume_kernels1.cuh)."""
     d = [
@@ -116,7 +116,7 @@ def eval_source(hidden16, num_hidden, nf, activation, output_mode, block_size, e
     ]
     src = "".join(f"#define {k} {v}\n" for k, v in d)
     src += '#include "renderer_volume_tensorcores.cuh"\n'
-    src += "#define VOLUME_INTERPOLATION_T ::kernel::VolumeInterpolationTensorcores\n#define OUTPUT_CHANNELS 1\n#define VOLUME_USE_DIRECTION 0\n"
+    src += "#define VOLUME_INTERPOLATION_T ::kernel::VolumeInterpolationTensorcores\n#define OUTPUT_CHANNELS %d\n#define VOLUME_USE_DIRECTION 0\n" % channels
     src += '#include "renderer_volume_kernels1.cuh"\n'
     return src
 
@@ -193,6 +193,9 @@ CONFIGS = {
     "h32x4_relu_densgrad": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=4, block_size=256, steps_variant=False),
     "h32x4_relu_densgrad_cubic_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=6, block_size=256,
                                             brdf=("magnitude", "phong"), light_type=1, steps_variant=False),
+    # (colour networks - OUTPUT_MODE rgbo, SKIP_TRANSFER_FUNCTION 1 - do NOT compile in the reference with the tensor-core volume:
+    # renderer_ray_evaluation_stepping_dvr.cuh:109 calls volume.evalNormal(position, rayDir, batch), an overload
+    # VolumeInterpolationTensorcores does not have. Their batch query does: see the *_rgbo_eval build below.)
     "h32x4_relu_fd_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, gradient_mode=1,
                                 brdf=("magnitude", "phong"), light_type=0, steps_variant=False),
 }
@@ -218,13 +221,15 @@ def main():
             meta[name] = dict(cfg, lowered=lowered, ptx=name + ".ptx", step_count_patch=patch)
             print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['ImageEvaluatorSimpleKernel']}")
     # the world-space batch query (BASELINE C2) of the two 32x4 networks: EvaluateNoBatches
-    for base in ("h32x4_relu", "h32x4_snakealt"):
-        name = base + "_eval"
+    for base, name, extra in (("h32x4_relu", "h32x4_relu_eval", {}), ("h32x4_snakealt", "h32x4_snakealt_eval", {}),
+                              ("h32x4_relu", "h32x4_relu_rgbo_eval", dict(output_mode=2, channels=4)),
+                              ("h32x4_relu", "h32x4_relu_rgbo_direct_eval", dict(output_mode=3, channels=4))):
         if only and name not in only:
             continue
-        ptx, lowered = compile_ptx(eval_source(**CONFIGS[base]), names_override=["EvaluateNoBatches", "&volumeInterpolationTensorcoresParameters"])
+        cfg = dict(CONFIGS[base], **extra)
+        ptx, lowered = compile_ptx(eval_source(**cfg), names_override=["EvaluateNoBatches", "&volumeInterpolationTensorcoresParameters"])
         open(os.path.join(OUT, name + ".ptx"), "wb").write(ptx)
-        meta[name] = dict(CONFIGS[base], eval=True, lowered=lowered, ptx=name + ".ptx", step_count_patch=False)
+        meta[name] = dict(cfg, eval=True, lowered=lowered, ptx=name + ".ptx", step_count_patch=False)
         print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['EvaluateNoBatches']}")
     for name, patch in (("grid_trilinear", False), ("grid_trilinear_steps", True)):
         if len(sys.argv) > 1 and "grid_trilinear" not in sys.argv[1:]:

@@ -268,14 +268,16 @@ class ReferenceEvalKernel(ReferenceDvrKernel):
 
     def __init__(self, net, time=0.0):
         act = net.layers[0].activation
-        super().__init__(net, variant=f"h{net.input_channels_out()}x{len(net.layers)}_{act.lower()}_eval", time=time)
+        mode = {"density:direct": "", "rgbo": "_rgbo", "rgbo:direct": "_rgbo_direct"}[net.output_mode]
+        self.channels = 4 if mode else 1
+        super().__init__(net, variant=f"h{net.input_channels_out()}x{len(net.layers)}_{act.lower()}{mode}_eval", time=time)
 
     def evaluate(self, positions, timing_iters=0):
         torch, d = self.torch, self.drv
         pos = positions if torch.is_tensor(positions) else torch.as_tensor(np.ascontiguousarray(positions, np.float32))
         pos = pos.to("cuda", torch.float32).contiguous()
         n = pos.shape[0]
-        out = torch.empty((n, 1), dtype=torch.float32, device="cuda")
+        out = torch.empty((n, self.channels), dtype=torch.float32, device="cuda")
 
         def acc(t):
             a = _Accessor2(); a.data = t.data_ptr()
