@@ -180,6 +180,8 @@ CONFIGS = {
     # name: hidden16, num_hidden (linear layers - 2), nf, activation, output_mode (1 = density:direct), block size
     "h32x4_relu": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256),
     "h32x4_snakealt": dict(hidden16=2, num_hidden=2, nf=14, activation="SnakeAlt", output_mode=1, block_size=256),
+    "h32x4_sine": dict(hidden16=2, num_hidden=2, nf=14, activation="Sine", output_mode=1, block_size=256),
+    "h32x4_snake": dict(hidden16=2, num_hidden=2, nf=14, activation="Snake", output_mode=1, block_size=256),
     # BASELINE C4 network: 64x6, 30 Fourier features; computeMaxWarps (volume_interpolation_network.cpp:987-1041) leaves
     # (48 KiB - 43648 B weights) / (64*2*32 B per warp) = 1 warp per block
     "h64x6_relu": dict(hidden16=4, num_hidden=4, nf=30, activation="ReLU", output_mode=1, block_size=32),
@@ -222,6 +224,7 @@ def main():
             print(f"build_ref_ptx: {name}: {len(ptx)} bytes of PTX, kernel {lowered['ImageEvaluatorSimpleKernel']}")
     # the world-space batch query (BASELINE C2) of the two 32x4 networks: EvaluateNoBatches
     for base, name, extra in (("h32x4_relu", "h32x4_relu_eval", {}), ("h32x4_snakealt", "h32x4_snakealt_eval", {}),
+                              ("h32x4_relu", "h32x4_sine_eval", dict(activation="Sine")), ("h32x4_relu", "h32x4_snake_eval", dict(activation="Snake")),
                               ("h32x4_relu", "h32x4_relu_rgbo_eval", dict(output_mode=2, channels=4)),
                               ("h32x4_relu", "h32x4_relu_rgbo_direct_eval", dict(output_mode=3, channels=4))):
         if only and name not in only:
