@@ -446,9 +446,13 @@ struct SrnTc {
     // does it on the CUDA cores (renderer_volume_tensorcores.cuh:1138-1143) - no further tensor-core round trip.
     template <int ACT>
     static __device__ __forceinline__ float epilogue_dot_t(const NetParams& P, const Ctx& c, int slot) {
-        __half2 a0 = __float2half2_rn(0.f), a1 = a0;
+        // two interleaved fp16x2 chains per block of 32 channels, each block summed into fp32: wide networks (H = 96, 128) do
+        // not accumulate more than 8 products per fp16 lane (W128x2 frame vs the reference kernel: 2.9e-3 with one chain pair
+        // over all 128 channels)
+        float sum = P.blast;
 #pragma unroll
         for (int c0 = 0; c0 < H; c0 += 32) {
+            __half2 a0 = __float2half2_rn(0.f), a1 = a0;
 #if FVSRN_TC_ACC16
             uint32_t v[16];
             if (H - c0 >= 32) tc::tmem_ld16_pack(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld8_pack(c.tmem_lane + d_col(slot) + c0, v);
@@ -469,9 +473,10 @@ struct SrnTc {
                     a1 = __hfma2(u2h(p1), u2h(P.wlast2[c0 / 2 + j + 1]), a1);
                 }
             }
+            const float2 f0 = __half22float2(a0), f1 = __half22float2(a1);
+            sum += (f0.x + f0.y) + (f1.x + f1.y);
         }
-        const float2 f0 = __half22float2(a0), f1 = __half22float2(a1);
-        return P.blast + ((f0.x + f0.y) + (f1.x + f1.y));
+        return sum;
     }
     static __device__ __forceinline__ float epilogue_dot(const NetParams& P, const Ctx& c, int slot, int act) {
         if constexpr (RELU) return epilogue_dot_t<D_ACT_RELU>(P, c, slot);

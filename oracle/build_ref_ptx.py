@@ -180,6 +180,10 @@ CONFIGS = {
     # name: hidden16, num_hidden (linear layers - 2), nf, activation, output_mode (1 = density:direct), block size
     "h32x4_relu": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256),
     "h32x4_snakealt": dict(hidden16=2, num_hidden=2, nf=14, activation="SnakeAlt", output_mode=1, block_size=256),
+    # other widths of the reference's own network sweep (eval_NetworkConfigsGrid.py:35-37); block size from computeMaxWarps
+    "h48x4_relu": dict(hidden16=3, num_hidden=2, nf=22, activation="ReLU", output_mode=1, block_size=256),
+    "h96x3_relu": dict(hidden16=6, num_hidden=1, nf=46, activation="ReLU", output_mode=1, block_size=32),
+    "h128x2_relu": dict(hidden16=8, num_hidden=0, nf=62, activation="ReLU", output_mode=1, block_size=32),
     "h32x4_sine": dict(hidden16=2, num_hidden=2, nf=14, activation="Sine", output_mode=1, block_size=256),
     "h32x4_snake": dict(hidden16=2, num_hidden=2, nf=14, activation="Snake", output_mode=1, block_size=256),
     # BASELINE C4 network: 64x6, 30 Fourier features; computeMaxWarps (volume_interpolation_network.cpp:987-1041) leaves

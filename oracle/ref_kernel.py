@@ -188,8 +188,11 @@ class ReferenceDvrKernel:
         add(np.full(16, time, np.float32).tobytes())                                    # cLatentGridInterpolation (kernel takes frac)
         add(np.ascontiguousarray(net.layers[0].weights, np.float16).tobytes())          # cWeightsLatentGrid [H][H+C]
         add(np.ascontiguousarray(net.layers[0].bias, np.float16).tobytes())
-        add(np.ascontiguousarray(np.stack([l.weights for l in net.layers[1:-1]]), np.float16).tobytes())
-        add(np.ascontiguousarray(np.stack([l.bias for l in net.layers[1:-1]]), np.float16).tobytes())
+        if len(net.layers) > 2:
+            add(np.ascontiguousarray(np.stack([l.weights for l in net.layers[1:-1]]), np.float16).tobytes())
+            add(np.ascontiguousarray(np.stack([l.bias for l in net.layers[1:-1]]), np.float16).tobytes())
+        else:       # NUM_HIDDEN_LAYERS 0: the device struct keeps one element (MIN_ONE, renderer_volume_tensorcores.cuh:223-224)
+            add(np.zeros(1, np.float16).tobytes()); add(np.zeros(1, np.float16).tobytes())
         add(np.ascontiguousarray(np.asarray(net.layers[-1].weights).T, np.float16).tobytes())   # cWeightsLast [H] / half2 [H][cout/2]
         add(np.ascontiguousarray(net.layers[-1].bias, np.float16).tobytes())
         # IVolumeInterpolation::evaluate forces the box to the unit cube (volume_interpolation.cpp:45-48)
