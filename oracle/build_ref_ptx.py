@@ -184,6 +184,8 @@ CONFIGS = {
     "h48x4_relu": dict(hidden16=3, num_hidden=2, nf=22, activation="ReLU", output_mode=1, block_size=256),
     "h96x3_relu": dict(hidden16=6, num_hidden=1, nf=46, activation="ReLU", output_mode=1, block_size=32),
     "h128x2_relu": dict(hidden16=8, num_hidden=0, nf=62, activation="ReLU", output_mode=1, block_size=32),
+    # alpha blending (BLENDING_MODE 0) without early termination: the other values of the two marcher defines
+    "h32x4_relu_alpha_noearly": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, blend_mode=0, early_out=0),
     "h32x4_sine": dict(hidden16=2, num_hidden=2, nf=14, activation="Sine", output_mode=1, block_size=256),
     "h32x4_snake": dict(hidden16=2, num_hidden=2, nf=14, activation="Snake", output_mode=1, block_size=256),
     # BASELINE C4 network: 64x6, 30 Fourier features; computeMaxWarps (volume_interpolation_network.cpp:987-1041) leaves

@@ -19,7 +19,7 @@ def psnr(a, b):
 
 
 def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0, time=None, tile=None, spp=1,
-                fd_stepsize=None, brdf=None):
+                fd_stepsize=None, brdf=None, blend=None, early_out=None, density_range=None):
     """One frame through the product path (pyrenderer mirror -> C ABI) -> (img (B,8,H,W) numpy, steps (B,H,W) numpy).
     fd_stepsize: finite-difference normals with that step; brdf: dict as ref_kernel.ReferenceDvrKernel.render takes it plus
     "flags" (subset of "magnitude", "phong") and "light_type" (0 point / 1 directional)."""
@@ -48,6 +48,12 @@ def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0,
         b.light_follows_camera = False
         b.light_type = pr.BRDFLambert.Point if brdf["light_type"] == 0 else pr.BRDFLambert.Directional
         b.light_position = b.light_direction = pr.double3(*brdf["light"])
+    if blend is not None:
+        ie.ray_evaluator.blending.blendMode = pr.Blending.Alpha if blend == "alpha" else pr.Blending.BeerLambert
+    if early_out is not None:
+        ie.ray_evaluator.early_out = bool(early_out)
+    if density_range is not None:
+        ie.ray_evaluator.min_density, ie.ray_evaluator.max_density = density_range
     ie.collect_statistics = True
     ie.tile = tile
     img = ie.render(width, height).cpu().numpy()
@@ -55,7 +61,7 @@ def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0,
 
 
 def render_reference(net, width, height, camera, fov_y, tf, stepsize, tf_kind=0, time=0.0, timing_iters=0, variant=None,
-                     fd_stepsize=0.01, brdf=None):
+                     fd_stepsize=0.01, brdf=None, density_range=(0.0, 1.0), steps_variant=None):
     """The same frame with the reference's kernel -> (rgba8 image, step counts, ms or None). variant: a named build of
     oracle/build_ref_ptx.py (the gradient / shading kernels; they have no step-count build: steps come back as None)."""
     import ref_kernel
@@ -65,10 +71,15 @@ def render_reference(net, width, height, camera, fov_y, tf, stepsize, tf_kind=0,
     if timing_iters > 0:
         want, ms = rk.render(width, height, camera, fov_y, stepsize, tf, timing_iters=timing_iters, brdf=brdf)
     else:
-        want = rk.render(width, height, camera, fov_y, stepsize, tf, brdf=brdf)
+        want = rk.render(width, height, camera, fov_y, stepsize, tf, brdf=brdf, density_min=density_range[0], density_max=density_range[1])
     want = want.cpu().numpy()
-    if variant is not None:
+    if variant is not None and steps_variant is None:
         return want, None, ms
+    if steps_variant is not None:
+        counted = ref_kernel.ReferenceDvrKernel(net, variant=steps_variant, time=time, tf=tfname).render(
+            width, height, camera, fov_y, stepsize, tf, density_min=density_range[0], density_max=density_range[1]).cpu().numpy()
+        assert np.array_equal(want[:, :4], counted[:, :4]), "the step-count patch must not touch the image"
+        return want, np.rint(counted[:, 4]).astype(np.int32), ms
     counted = ref_kernel.ReferenceDvrKernel(net, patched_steps=True, time=time, tf=tfname).render(
         width, height, camera, fov_y, stepsize, tf).cpu().numpy()
     assert np.array_equal(want[:, :4], counted[:, :4]), "the step-count patch must not touch the image"

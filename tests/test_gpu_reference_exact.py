@@ -80,3 +80,26 @@ def test_reference_exact_mode_rejects_what_it_does_not_cover(plume_tf):
         ie.render(32, 32)
     with pytest.raises(RuntimeError, match="reference-exact"):
         vol.evaluate(torch.rand((64, 3), device="cuda"))
+
+
+def test_alpha_blending_without_early_out_and_a_density_window(ref, plume_tf):
+    """The other values of the marcher's compile-time switches - BLENDING_MODE alpha (renderer_blending.cuh:40-44),
+    RAY_EVALUATION_STEPPING__ENABLE_EARLY_OUT 0 - and a density window [0.05, 0.6] (samples below it are skipped, above it
+    clamped): reference-exact mode bit-identical, fast modes within the image gate."""
+    import parity
+    from fvsrn_b200 import scenes, volnet
+    kw, size, step = CASES["C3_relu_nerf"][:3]
+    size = 512
+    net = make_case_network(kw)
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    rng = (0.05, 0.6)
+    want, want_steps, _ = parity.render_reference(net, size, size, cam, scenes.DEFAULT_FOV_Y, plume_tf, step, variant="h32x4_relu_alpha_noearly",
+                                                  steps_variant="h32x4_relu_alpha_noearly_steps", density_range=rng)
+    assert want[:, 3].max() > 0.3
+    kwargs = dict(blend="alpha", early_out=False, density_range=rng)
+    img, steps = parity.render_ours(volnet.dumps(net), "reference_exact", size, size, cam, plume_tf, step, **kwargs)
+    _assert_identical(img, steps, want, want_steps, "alpha_noearly")
+    for mode in ("tcgen05", "mma_sync"):
+        img, steps = parity.render_ours(volnet.dumps(net), mode, size, size, cam, plume_tf, step, **kwargs)
+        r = parity.compare(img, steps, want, want_steps)
+        assert r["rgba_max_abs"] <= parity.RGBA_TOL and r["psnr_db"] >= parity.PSNR_MIN and r["step_count_mismatch_frac"] == 0.0, (mode, r)
