@@ -103,3 +103,24 @@ def test_alpha_blending_without_early_out_and_a_density_window(ref, plume_tf):
         img, steps = parity.render_ours(volnet.dumps(net), mode, size, size, cam, plume_tf, step, **kwargs)
         r = parity.compare(img, steps, want, want_steps)
         assert r["rgba_max_abs"] <= parity.RGBA_TOL and r["psnr_db"] >= parity.PSNR_MIN and r["step_count_mismatch_frac"] == 0.0, (mode, r)
+
+
+def test_camera_batch_with_per_view_transfer_functions(ref, plume_tf):
+    """B = 3 cameras in one call, one TF per view (the batch index of ImageEvaluatorSimpleKernel selects camera and TF,
+    renderer_image_evaluator_simple.cuh:60-98): reference-exact mode bit-identical, fast modes within the image gate."""
+    import parity
+    from fvsrn_b200 import scenes, volnet
+    kw, _, step = CASES["C3_relu_nerf"][:3]
+    size = 256
+    net = make_case_network(kw)
+    cams = scenes.camera_sweep(3)
+    tfs = np.concatenate([plume_tf, plume_tf, plume_tf], 0).copy()
+    tfs[1, :, 3] *= 0.4; tfs[2, :, 3] *= 2.5; tfs[2, :, :3] = tfs[2, :, :3][:, ::-1]
+    want, want_steps, _ = parity.render_reference(net, size, size, cams, scenes.DEFAULT_FOV_Y, tfs, step)
+    assert want.shape[0] == 3 and not np.array_equal(want[0, :4], want[1, :4])
+    img, steps = parity.render_ours(volnet.dumps(net), "reference_exact", size, size, cams, tfs, step)
+    _assert_identical(img, steps, want, want_steps, "batch3")
+    for mode in ("tcgen05", "mma_sync"):
+        img, steps = parity.render_ours(volnet.dumps(net), mode, size, size, cams, tfs, step)
+        r = parity.compare(img, steps, want, want_steps)
+        assert r["rgba_max_abs"] <= parity.RGBA_TOL and r["psnr_db"] >= parity.PSNR_MIN, (mode, r)
