@@ -69,7 +69,8 @@ def grid_source(early_out=1, blend_mode=1, tf="piecewise", interpolation=1):
 
 
 def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, early_out=1, blend_mode=1, first_last_shared=0,
-                encoding=0, tf="piecewise", gradient_mode=0, brdf=(), light_type=1, steps_variant=True, skip_tf=0):
+                encoding=0, tf="piecewise", gradient_mode=0, brdf=(), light_type=1, steps_variant=True, skip_tf=0,
+                use_direction=0, pass_time=0, grid16=1):
     """The translation unit IImageEvaluator::getKernel + ImageEvaluatorSimple::render assemble (SURVEY App. F).
     encoding: LATENT_GRID_ENCODING 0 float / 1 byte-linear / 2 byte-gaussian (volume_interpolation_network.cpp:1211);
     tf "texture": TransferFunctionTexture in its tensor form (transfer_function_texture.cpp: TRANSFER_FUNCTION_TEXTURE__USE_TENSOR,
@@ -78,9 +79,9 @@ def main_source(hidden16, num_hidden, nf, activation, output_mode, block_size, e
     d = [
         ("KERNEL_DOUBLE_PRECISION", 0), ("KERNEL_SYNCHRONIZED_TRACING", 1), ("BLOCK_SIZE", block_size),
         ("NUM_HIDDEN_LAYERS", num_hidden), ("HIDDEN_CHANNELS_DIV16", hidden16), ("HAS_FOURIER_FEATURES", 1),
-        ("NUM_FOURIER_FEATURES", nf), ("USE_DIRECTION", 0), ("ACTIVATION", activation), ("OUTPUT_MODE", output_mode),
-        ("FIRST_AND_LAST_IN_SHARED_MEMORY", first_last_shared), ("LATENT_GRID_CHANNELS_DIV16", 1), ("LATENT_GRID_ENCODING", encoding),
-        ("PASS_TIME_TO_NETWORK", 0), ("GRADIENT_MODE", gradient_mode),
+        ("NUM_FOURIER_FEATURES", nf), ("USE_DIRECTION", use_direction), ("ACTIVATION", activation), ("OUTPUT_MODE", output_mode),
+        ("FIRST_AND_LAST_IN_SHARED_MEMORY", first_last_shared), ("LATENT_GRID_CHANNELS_DIV16", grid16), ("LATENT_GRID_ENCODING", encoding),
+        ("PASS_TIME_TO_NETWORK", pass_time), ("GRADIENT_MODE", gradient_mode),
         ("RAY_EVALUATION_STEPPING__VOLUME_INTERPOLATION_T", "::kernel::VolumeInterpolationTensorcores"),
         ("RAY_EVALUATION_STEPPING__TRANSFER_FUNCTION_T", TF_TYPES[tf][0]),
         ("RAY_EVALUATION_STEPPING__BLENDING_T", "::kernel::Blending"),
@@ -186,6 +187,12 @@ CONFIGS = {
     "h128x2_relu": dict(hidden16=8, num_hidden=0, nf=62, activation="ReLU", output_mode=1, block_size=32),
     # alpha blending (BLENDING_MODE 0) without early termination: the other values of the two marcher defines
     "h32x4_relu_alpha_noearly": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, blend_mode=0, early_out=0),
+    # network inputs beyond the position: ray direction (USE_DIRECTION 1), direction also inside the Fourier features (2), the
+    # keyframe time (PASS_TIME_TO_NETWORK); 32 latent channels (two 16-channel groups)
+    "h32x4_relu_dir": dict(hidden16=2, num_hidden=2, nf=12, activation="ReLU", output_mode=1, block_size=256, use_direction=1, steps_variant=False),
+    "h32x4_relu_dirfourier": dict(hidden16=2, num_hidden=2, nf=12, activation="ReLU", output_mode=1, block_size=256, use_direction=2, steps_variant=False),
+    "h32x4_relu_time": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, pass_time=1, steps_variant=False),
+    "h32x4_relu_grid32": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, grid16=2, steps_variant=False),
     "h32x4_sine": dict(hidden16=2, num_hidden=2, nf=14, activation="Sine", output_mode=1, block_size=256),
     "h32x4_snake": dict(hidden16=2, num_hidden=2, nf=14, activation="Snake", output_mode=1, block_size=256),
     # BASELINE C4 network: 64x6, 30 Fourier features; computeMaxWarps (volume_interpolation_network.cpp:987-1041) leaves

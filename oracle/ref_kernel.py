@@ -87,7 +87,8 @@ class ReferenceDvrKernel:
             raise RuntimeError(f"no prebuilt reference PTX for {variant} (have {sorted(meta)})")
         m = meta[variant]
         assert m["hidden16"] * 16 == H and m["num_hidden"] == len(net.layers) - 2 and m["nf"] == net.num_fourier
-        assert net.latent_channels() == 16 and not net.has_direction and not net.has_time
+        assert net.latent_channels() == 16 * m.get("grid16", 1) and int(net.has_time) == m.get("pass_time", 0)
+        assert (0 if not net.has_direction else (2 if net.direction_in_fourier else 1)) == m.get("use_direction", 0)
         assert net.output_mode == self.OUTPUT_MODES[m["output_mode"]], (net.output_mode, m["output_mode"])
         self.fd_stepsize = float(fd_stepsize)
         assert m.get("encoding", 0) == enc and m.get("tf", "piecewise") == tf
@@ -163,7 +164,7 @@ class ReferenceDvrKernel:
             vals = grid.values.astype(np.float32).astype(np.float16).astype(np.float32)     # (C,Z,Y,X)
         else:
             vals = grid.raw.astype(np.uint8)
-        return [self._texture(np.ascontiguousarray(np.transpose(vals[4 * i:4 * i + 4], (1, 2, 3, 0)))) for i in range(4)]
+        return [self._texture(np.ascontiguousarray(np.transpose(vals[4 * i:4 * i + 4], (1, 2, 3, 0)))) for i in range(vals.shape[0] // 4)]
 
     def _upload_network(self, net, time, unit_box=False):
         H, nf = net.input_channels_out(), net.num_fourier
@@ -185,7 +186,7 @@ class ReferenceDvrKernel:
         if gA.encoding != 0:                                                            # HAS_LATENT_GRID_OFFSET_SCALE
             add(np.asarray(gA.offset_or_mean, np.float32).tobytes()); add(np.asarray(gB.offset_or_mean, np.float32).tobytes())
             add(np.asarray(gA.scale_or_std, np.float32).tobytes()); add(np.asarray(gB.scale_or_std, np.float32).tobytes())
-        add(np.full(16, time, np.float32).tobytes())                                    # cLatentGridInterpolation (kernel takes frac)
+        add(np.full(net.latent_channels(), time, np.float32).tobytes())                 # cLatentGridInterpolation (kernel takes frac; [0] = the time input)
         add(np.ascontiguousarray(net.layers[0].weights, np.float16).tobytes())          # cWeightsLatentGrid [H][H+C]
         add(np.ascontiguousarray(net.layers[0].bias, np.float16).tobytes())
         if len(net.layers) > 2:
@@ -203,7 +204,7 @@ class ReferenceDvrKernel:
         add(np.array([0.01], np.float32).tobytes())                                     # latentGridDifferencesStepSize (unused)
         _pad32(b)
         dptr, size = self.g_vol
-        if H == 32 and nf == 14 and gA.encoding == 0 and net.layers[-1].cout == 1:
+        if H == 32 and nf == 14 and gA.encoding == 0 and net.layers[-1].cout == 1 and net.latent_channels() == 16:
             assert len(b) == 7840, len(b)                                               # sizeof for C3
         assert len(b) == int(size), (len(b), int(size))
         _ck(self.drv.cuMemcpyHtoD(dptr, bytes(b), len(b)))

@@ -231,3 +231,44 @@ def test_wide_network_is_at_least_as_close_to_fp32_as_the_reference_kernel(ref, 
         _record(row)
         assert row["ours_vs_oracle"] <= parity.RGBA_TOL, row
         assert row["ours_vs_fp32"] <= row["reference_vs_fp32"] + 5e-4, row
+
+
+INPUT_CASES = {
+    # name: (network kwargs, reference build, keyframe time)
+    "direction": (dict(C3, activation="ReLU", has_direction=True, last_gain=6.0), "h32x4_relu_dir", 0.0),
+    "direction_in_fourier": (dict(C3, activation="ReLU", has_direction=True, direction_in_fourier=True, fourier="gauss", fourier_std=0.7, last_gain=6.0),
+                             "h32x4_relu_dirfourier", 0.0),
+    "time_input": (dict(C3, activation="ReLU", pass_time=True, time_keyframes=4, last_gain=6.0), "h32x4_relu_time", 1.37),
+    "latent_32_channels": (dict(C3, activation="ReLU", grid_channels=32, last_gain=6.0), "h32x4_relu_grid32", 0.0),
+}
+
+
+@pytest.mark.parametrize("name", list(INPUT_CASES))
+def test_network_input_variants_match_reference_kernel(ref, name, plume_tf):
+    """The other network inputs of VolumeInterpolationTensorcores::eval (renderer_volume_tensorcores.cuh:768-808, 839-910): the
+    ray direction as input channels 4..6 (USE_DIRECTION 1), also inside the Fourier features (2), the keyframe time as input
+    channel 3 with temporally interpolated grids (PASS_TIME_TO_NETWORK), two 16-channel latent groups - each against the
+    reference kernel built with that define, 512^2 frame, both fast kernel families."""
+    import parity
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import scenes, volnet
+    kw, variant, time = INPUT_CASES[name]
+    net = scenes.make_network(**kw)
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    size, step = 512, 1 / 256
+    tf = plume_tf.copy()
+    want, _, _ = parity.render_reference(net, size, size, cam, scenes.DEFAULT_FOV_Y, tf, step, variant=variant, time=time)
+    for _ in range(3):              # keep the frame translucent (see the opaque cases above): scale the absorption, render again
+        if want[:, 3].max() <= 0.9:
+            break
+        tf[..., 3] *= 0.2
+        want, _, _ = parity.render_reference(net, size, size, cam, scenes.DEFAULT_FOV_Y, tf, step, variant=variant, time=time)
+    assert 0.05 < want[:, 3].max() <= 0.9, float(want[:, 3].max())
+    data = volnet.dumps(net)
+    for mode in MODES:
+        img, _ = parity.render_ours(data, mode, size, size, cam, tf, step, time=time if time else None)
+        d = np.abs(img[:, :4] - want[:, :4])
+        row = dict(config=f"input_{name}", kernel_mode=mode, size=size, rgba_max_abs=float(d.max()), psnr_db=float(parity.psnr(img[:, :4], want[:, :4])),
+                   max_alpha=float(want[:, 3].max()))
+        _record(row)
+        assert row["rgba_max_abs"] <= parity.RGBA_TOL and row["psnr_db"] >= parity.PSNR_MIN, row
