@@ -957,8 +957,8 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT;
     if (exact) {    // the shapes the reference kernels this mode is validated against cover (kernels_exact.cuh)
         const Network& n = h->net;
-        if (is_rgbo || n.has_time || n.has_direction || h->GC16 != 1)
-            throw std::runtime_error("reference-exact mode: density-type networks with one 16-channel latent grid, without time/direction input");
+        if (is_rgbo || n.has_direction || h->GC16 != 1)
+            throw std::runtime_error("reference-exact mode: density-type networks with one 16-channel latent grid, without direction input");
         if (p->tf_kind != FVSRN_TF_PIECEWISE && p->tf_kind != FVSRN_TF_TEXTURE) throw std::runtime_error("reference-exact mode: piecewise or texture transfer function");
         for (size_t i = 0; i < h->d_time.size(); ++i) ensure_tex32(h->d_time[i], n.time_grids[i]);
         for (size_t i = 0; i < h->d_ens.size(); ++i) ensure_tex32(h->d_ens[i], n.ensemble_grids[i]);

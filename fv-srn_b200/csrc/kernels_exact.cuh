@@ -20,7 +20,7 @@
 //     reference's fp32 operation order (renderer_ray_evaluation_stepping_dvr.cuh:84-154, renderer_tf_piecewise.cuh:27-62,
 //     renderer_tf_texture.cuh:46-56, renderer_blending.cuh:36-51, renderer_image_evaluator_simple.cuh:96-124)
 // Scope: density-type networks (density[:direct], densitygrad[:direct|:cubic], densitycurvature[:direct]), Fourier
-// features, one 16-channel latent grid group (static, time keyframes or ensemble), no direction / time input; normals
+// features, one 16-channel latent grid group (static, time keyframes or ensemble), optional time input, no direction input; normals
 // predicted by the network or by finite differences, BRDFLambert shading - the shapes the reference kernels
 // in oracle/_ref are built for.
 #pragma once
@@ -69,7 +69,8 @@ struct SrnExact {
     static __device__ __forceinline__ void build_row(const NetParams& P, float px, float py, float pz, float tfrac, uint32_t (&row)[K0 / 2]) {
         const __half vx = __float2half(px), vy = __float2half(py), vz = __float2half(pz);
         row[0] = h2u(__halves2half2(vx, vy));
-        row[1] = h2u(__halves2half2(vz, __float2half(0.f)));
+        // input channel 3: the keyframe time when PASS_TIME_TO_NETWORK (cLatentGridInterpolation[0].x, :777-779), else 0
+        row[1] = h2u(__halves2half2(vz, __float2half(P.has_time ? P.time_value : 0.f)));
         const __half* F = reinterpret_cast<const __half*>(P.fourier2);
         __half cs[NF], sn[NF];
 #pragma unroll

@@ -191,7 +191,7 @@ CONFIGS = {
     # keyframe time (PASS_TIME_TO_NETWORK); 32 latent channels (two 16-channel groups)
     "h32x4_relu_dir": dict(hidden16=2, num_hidden=2, nf=12, activation="ReLU", output_mode=1, block_size=256, use_direction=1, steps_variant=False),
     "h32x4_relu_dirfourier": dict(hidden16=2, num_hidden=2, nf=12, activation="ReLU", output_mode=1, block_size=256, use_direction=2, steps_variant=False),
-    "h32x4_relu_time": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, pass_time=1, steps_variant=False),
+    "h32x4_relu_time": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, pass_time=1),
     "h32x4_relu_grid32": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, grid16=2, steps_variant=False),
     "h32x4_sine": dict(hidden16=2, num_hidden=2, nf=14, activation="Sine", output_mode=1, block_size=256),
     "h32x4_snake": dict(hidden16=2, num_hidden=2, nf=14, activation="Snake", output_mode=1, block_size=256),

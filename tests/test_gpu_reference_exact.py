@@ -124,3 +124,18 @@ def test_camera_batch_with_per_view_transfer_functions(ref, plume_tf):
         img, steps = parity.render_ours(volnet.dumps(net), mode, size, size, cams, tfs, step)
         r = parity.compare(img, steps, want, want_steps)
         assert r["rgba_max_abs"] <= parity.RGBA_TOL and r["psnr_db"] >= parity.PSNR_MIN, (mode, r)
+
+
+def test_time_input_with_interpolated_keyframes(ref, plume_tf):
+    """PASS_TIME_TO_NETWORK: the keyframe time is network input channel 3 and its fractional part blends the two keyframe
+    grids (renderer_volume_tensorcores.cuh:590-604, 777-779): reference-exact mode bit-identical incl. step counts."""
+    import parity
+    from fvsrn_b200 import scenes, volnet
+    net = scenes.make_network(**dict(CASES["C3_relu_nerf"][0], pass_time=True, time_keyframes=4))
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    size, step, time = 512, 1 / 256, 1.37
+    want, want_steps, _ = parity.render_reference(net, size, size, cam, scenes.DEFAULT_FOV_Y, plume_tf, step, variant="h32x4_relu_time",
+                                                  steps_variant="h32x4_relu_time_steps", time=time)
+    assert want[:, 3].max() > 0.3
+    img, steps = parity.render_ours(volnet.dumps(net), "reference_exact", size, size, cam, plume_tf, step, time=time)
+    _assert_identical(img, steps, want, want_steps, "time_input")
