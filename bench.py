@@ -450,7 +450,9 @@ def run_b200(args):
                     "what": "fvsrn_render_dvr_host, (B,4,H,W) fp32 colour to pinned host memory" if world == 1 else
                             "per step: H2D camera+TF on every rank, render, NCCL collection on rank 0, D2H of the assembled frames on rank 0",
                     "by_format": e2e_formats or None},
-            "gpu_launches": ((V if T > 1 else 1) if (not tiles or bh > 0) else 0) * args.steps,
+            # one DVR kernel per launch; with per-view keyframe times one launch per view, each preceded by the small kernel that
+            # blends the view's keyframe pair (api.cu blend_keyframes; tcgen05 mode)
+            "gpu_launches": ((V * (2 if args.kernel_mode == "tcgen05" else 1) if T > 1 else 1) if (not tiles or bh > 0) else 0) * args.steps,
             "roofline": {"bound": "tensor", "achieved": ach, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": ach / pk["tflops"],
                          "traffic": traffic, "kernel": "dvr_tc_kernel (tcgen05.mma + TMEM)" if args.kernel_mode == "tcgen05" else "dvr_kernel (mma.sync)", "flop_per_sample": w["flop"], "peak_source": pk["source"] + ", burst bf16",
                          "executed_frac": (cnt[1] * w["flop"]) / (kernel_ms * 1e-3) / 1e12 / pk["tflops"], "kernel_ms": kernel_ms / args.steps},
