@@ -957,8 +957,8 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT;
     if (exact) {    // the shapes the reference kernels this mode is validated against cover (kernels_exact.cuh)
         const Network& n = h->net;
-        if (is_rgbo || n.has_direction || h->GC16 != 1)
-            throw std::runtime_error("reference-exact mode: density-type networks with one 16-channel latent grid, without direction input");
+        if (is_rgbo || h->GC16 < 1 || h->GC16 > 2 || ((n.has_direction || h->GC16 == 2) && h->H16 != 2 && h->H16 != 4))
+            throw std::runtime_error("reference-exact mode: density-type networks with a latent grid; direction input or 32 latent channels with hidden width 32 or 64");
         if (p->tf_kind != FVSRN_TF_PIECEWISE && p->tf_kind != FVSRN_TF_TEXTURE) throw std::runtime_error("reference-exact mode: piecewise or texture transfer function");
         for (size_t i = 0; i < h->d_time.size(); ++i) ensure_tex32(h->d_time[i], n.time_grids[i]);
         for (size_t i = 0; i < h->d_ens.size(); ++i) ensure_tex32(h->d_ens[i], n.ensemble_grids[i]);
@@ -971,7 +971,7 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         DvrParams d = D; d.b0 = b0; d.nb = nb;      // the launcher lays the tile raster of its kernel over the rectangle
         d.tile_counter = next_tile_counter(h, ls);
         LaunchCfg cfg; cfg.sm_count = h->sm_count;
-        if (exact) CUDA_OK(launch_exact(h->H16, P, d, &cfg, ls));
+        if (exact) CUDA_OK(launch_exact(h->H16, h->GC16, h->dir, P, d, &cfg, ls));
         else CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, ls));
         if (blended) CUDA_OK(cudaEventRecord(blended->ev_read[ls == h->aux_stream ? 1 : 0], ls));
         h->launches++;
@@ -1305,7 +1305,7 @@ int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     if (!fn) return fail("no kernel for this hidden width");
     DvrParams dq{}; dq.tf_kind = 0; dq.tf_R = 8;   // a typical piecewise TF: the DVR kernels size their shared memory from it
     dq.tw = 1024; dq.th = 1024; dq.nb = 1;
-    if (net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact(net->H16, P, dq, &cfg, nullptr));
+    if (net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact(net->H16, net->GC16, net->dir, P, dq, &cfg, nullptr));
     else CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, kernel == 0 ? &dq : nullptr, &cfg, nullptr));
     info->device = net->device; info->sm_count = net->sm_count;
     info->block_threads = cfg.threads; info->blocks_per_sm = cfg.blocks_per_sm; info->grid_blocks = cfg.grid;

@@ -6,9 +6,9 @@
 #include <algorithm>
 namespace fvsrn {
 
-template <int H16>
+template <int H16, int GC16 = 1, bool DIR = false>
 static cudaError_t launch_exact_h(const NetParams& P, const DvrParams& D0, LaunchCfg* cfg, cudaStream_t s) {
-    using Core = Srn<H16, 1, false>;
+    using Core = Srn<H16, GC16, DIR>;
     DvrParams D = D0;
     set_tiles(D, kTileW, kTileH);
     cfg->tile_w = kTileW; cfg->tile_h = kTileH;
@@ -16,7 +16,7 @@ static cudaError_t launch_exact_h(const NetParams& P, const DvrParams& D0, Launc
     const int blob = ((P.blob_bytes + 15) / 16) * 16;
     const int threads = kWarpsPerBlock * 32;
     const int smem = blob + kTfSmemFloats * 4 + kWarpsPerBlock * Core::STAGE_BYTES;
-    const void* fn = (const void*)dvr_exact_kernel<H16>;
+    const void* fn = (const void*)dvr_exact_kernel<H16, GC16, DIR>;
     KernelFacts kf;
     const cudaError_t e = kernel_facts(fn, threads, smem, false, 512, &kf);
     if (e != cudaSuccess) return e;
@@ -25,7 +25,7 @@ static cudaError_t launch_exact_h(const NetParams& P, const DvrParams& D0, Launc
     if (grid < 1) grid = 1;
     cfg->blocks_per_sm = kf.bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = kf.regs; cfg->threads = threads;
     if (cfg->query_only) return cudaSuccess;
-    dvr_exact_kernel<H16><<<int(grid), threads, smem, s>>>(P, D);
+    dvr_exact_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, D);
     return cudaGetLastError();
 }
 
@@ -84,7 +84,12 @@ cudaError_t launch_eval_grid(const GridVolumeParams& G, const float* pos, float*
     return cudaGetLastError();
 }
 
-cudaError_t launch_exact(int h16, const NetParams& P, const DvrParams& D, LaunchCfg* cfg, cudaStream_t s) {
+cudaError_t launch_exact(int h16, int gc16, int dir, const NetParams& P, const DvrParams& D, LaunchCfg* cfg, cudaStream_t s) {
+    if (gc16 != 1 || dir) {     // two latent groups / direction input: the 32- and 64-wide networks
+        if (gc16 < 1 || gc16 > 2 || (h16 != 2 && h16 != 4)) return cudaErrorInvalidValue;
+        if (h16 == 2) return gc16 == 2 ? (dir ? launch_exact_h<2, 2, true>(P, D, cfg, s) : launch_exact_h<2, 2, false>(P, D, cfg, s)) : launch_exact_h<2, 1, true>(P, D, cfg, s);
+        return gc16 == 2 ? (dir ? launch_exact_h<4, 2, true>(P, D, cfg, s) : launch_exact_h<4, 2, false>(P, D, cfg, s)) : launch_exact_h<4, 1, true>(P, D, cfg, s);
+    }
     switch (h16) {
         case 2: return launch_exact_h<2>(P, D, cfg, s);
         case 3: return launch_exact_h<3>(P, D, cfg, s);

@@ -20,7 +20,8 @@
 //     reference's fp32 operation order (renderer_ray_evaluation_stepping_dvr.cuh:84-154, renderer_tf_piecewise.cuh:27-62,
 //     renderer_tf_texture.cuh:46-56, renderer_blending.cuh:36-51, renderer_image_evaluator_simple.cuh:96-124)
 // Scope: density-type networks (density[:direct], densitygrad[:direct|:cubic], densitycurvature[:direct]), Fourier
-// features, one 16-channel latent grid group (static, time keyframes or ensemble), optional time input, no direction input; normals
+// features, one 16-channel latent grid group (static, time keyframes or ensemble) for every supported width, two groups and / or the ray direction as input (also inside the Fourier
+// features) for the 32- and 64-wide networks, optional time input; normals
 // predicted by the network or by finite differences, BRDFLambert shading - the shapes the reference kernels
 // in oracle/_ref are built for.
 #pragma once
@@ -28,9 +29,9 @@
 
 namespace fvsrn {
 
-template <int H16>
+template <int H16, int GC16 = 1, bool DIR = false>
 struct SrnExact {
-    using Core = Srn<H16, 1, false>;
+    using Core = Srn<H16, GC16, DIR>;
     static constexpr int H = Core::H, K0 = Core::K0, NF = Core::NF, FOFF = Core::FOFF, NT = Core::NT, KT0 = Core::KT0, KTH = Core::KTH;
     static constexpr int RS_CHUNKS = Core::RS_CHUNKS, ROW_CHUNKS = Core::ROW_CHUNKS;
 
@@ -66,11 +67,16 @@ struct SrnExact {
     }
 
     // layer-0 inputs of the sample owned by this lane: [px,py,pz,0, cos x NF, sin x NF, latent x 16]
-    static __device__ __forceinline__ void build_row(const NetParams& P, float px, float py, float pz, float tfrac, uint32_t (&row)[K0 / 2]) {
+    static __device__ __forceinline__ void build_row(const NetParams& P, float px, float py, float pz, float3 dir, float tfrac, uint32_t (&row)[K0 / 2]) {
         const __half vx = __float2half(px), vy = __float2half(py), vz = __float2half(pz);
         row[0] = h2u(__halves2half2(vx, vy));
         // input channel 3: the keyframe time when PASS_TIME_TO_NETWORK (cLatentGridInterpolation[0].x, :777-779), else 0
         row[1] = h2u(__halves2half2(vz, __float2half(P.has_time ? P.time_value : 0.f)));
+        const __half dx = __float2half(dir.x), dy = __float2half(dir.y), dz = __float2half(dir.z);
+        if constexpr (DIR) {            // USE_DIRECTION >= 1: input channels 4..7 = direction, 0 (:784-792)
+            row[2] = h2u(__halves2half2(dx, dy));
+            row[3] = h2u(__halves2half2(dz, __float2half(0.f)));
+        }
         const __half* F = reinterpret_cast<const __half*>(P.fourier2);
         __half cs[NF], sn[NF];
 #pragma unroll
@@ -78,6 +84,11 @@ struct SrnExact {
             __half c = __hmul(vx, F[i]);
             c = __hfma(vy, F[i + NF], c);
             c = __hfma(vz, F[i + 2 * NF], c);
+            if (DIR && P.dir_in_fourier) {      // USE_DIRECTION == 2 (:800-804)
+                c = __hfma(dx, F[i + 3 * NF], c);
+                c = __hfma(dy, F[i + 4 * NF], c);
+                c = __hfma(dz, F[i + 5 * NF], c);
+            }
             cs[i] = hcos(c); sn[i] = hsin(c);
         }
 #pragma unroll
@@ -86,7 +97,7 @@ struct SrnExact {
             row[FOFF / 2 + NF / 2 + i / 2] = h2u(__halves2half2(sn[i], sn[i + 1]));
         }
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
+        for (int q = 0; q < 4 * GC16; ++q) {
             float4 a = tex3D<float4>(P.tex_a[q], px, py, pz);
             float4 b = tex3D<float4>(P.tex_b[q], px, py, pz);
             if (P.grid_encoding != 0) {     // EncodeGridValue<Encoding, false> on BOTH keyframes: the reference decodes B with A's constants (:586-587)
@@ -112,11 +123,11 @@ struct SrnExact {
     // network output (raw last-layer values, fp16) of the sample owned by this lane; all 32 lanes call. four = the
     // 4 / 6-output last layers of the densitygrad* / densitycurvature* modes (o[0] density, o[1..3] predicted gradient)
     static __device__ __forceinline__ void forward(const NetParams& P, uint32_t sblob, uint4* stage, const Act& ac,
-                                                   float px, float py, float pz, float tfrac, bool four, __half (&o)[4]) {
+                                                   float px, float py, float pz, float3 dir, float tfrac, bool four, __half (&o)[4]) {
         const int lane = threadIdx.x & 31;
         __syncwarp();
         uint32_t row[K0 / 2];
-        build_row(P, px, py, pz, tfrac, row);
+        build_row(P, px, py, pz, dir, tfrac, row);
 #pragma unroll
         for (int j = 0; j < ROW_CHUNKS; ++j)
             stage[lane * RS_CHUNKS + j] = make_uint4(row[4 * j], row[4 * j + 1], row[4 * j + 2], row[4 * j + 3]);
@@ -341,10 +352,10 @@ __device__ __forceinline__ void exact_blend_normal(const DvrParams& D, float4 c,
     acc.w = rf::fma(om, a, acc.w);
 }
 
-template <int H16>
+template <int H16, int GC16 = 1, bool DIR = false>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
-    using Net = SrnExact<H16>;
+    using Net = SrnExact<H16, GC16, DIR>;
     using Core = typename Net::Core;
     extern __shared__ uint4 smem[];
     uint4* sblob = smem;
@@ -406,7 +417,7 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
                 const float px = rf::div(rf::sub(wx, bmin.x), bsize.x), py = rf::div(rf::sub(wy, bmin.y), bsize.y),
                             pz = rf::div(rf::sub(wz, bmin.z), bsize.z);
                 __half o[4];
-                Net::forward(P, sblob_addr, stage, ac, px, py, pz, tfrac, four, o);
+                Net::forward(P, sblob_addr, stage, ac, px, py, pz, r.dir, tfrac, four, o);
                 float value = __half2float(o[0]);
                 if (sigm) value = exact_sigmoid(value);
                 steps += valid ? 1 : 0;
@@ -432,7 +443,7 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
                             const float qz = axis == 2 ? (plus ? rf::add(wz, h) : rf::sub(wz, h)) : (plus ? rf::add(wz, 0.f) : wz);
                             __half q[4];
                             Net::forward(P, sblob_addr, stage, ac, rf::div(rf::sub(qx, bmin.x), bsize.x), rf::div(rf::sub(qy, bmin.y), bsize.y),
-                                         rf::div(rf::sub(qz, bmin.z), bsize.z), tfrac, four, q);
+                                         rf::div(rf::sub(qz, bmin.z), bsize.z), r.dir, tfrac, four, q);
                             float v = __half2float(q[0]);
                             if (sigm) v = exact_sigmoid(v);
                             if (k == 0) d[0] = v; else if (k == 1) d[1] = v; else if (k == 2) d[2] = v;

@@ -146,7 +146,8 @@ int  fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info);
  *                         cuda_fp16.hpp, fp16-accumulate HMMA with the bias preloaded, sequential fp16 last layer, fast-math
  *                         fp32 ray setup / TF / blending - so that images and early-termination step counts are
  *                         bit-identical to ImageEvaluatorSimpleKernel on the same GPU (csrc/kernels_exact.cuh). Density-type
- *                         networks with one 16-channel latent group, with or without the time input, no direction input. */
+ *                         networks with a latent grid, with or without the time input; the ray direction as input and 32
+ *                         latent channels for hidden widths 32 and 64. */
 enum { FVSRN_KERNEL_MMA_SYNC = 0, FVSRN_KERNEL_TCGEN05 = 1, FVSRN_KERNEL_REFERENCE_EXACT = 2 };
 int  fvsrn_network_set_kernel_mode(fvsrn_network* net, int mode);
 int  fvsrn_network_get_kernel_mode(const fvsrn_network* net);

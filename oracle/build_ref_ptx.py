@@ -189,10 +189,10 @@ CONFIGS = {
     "h32x4_relu_alpha_noearly": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, blend_mode=0, early_out=0),
     # network inputs beyond the position: ray direction (USE_DIRECTION 1), direction also inside the Fourier features (2), the
     # keyframe time (PASS_TIME_TO_NETWORK); 32 latent channels (two 16-channel groups)
-    "h32x4_relu_dir": dict(hidden16=2, num_hidden=2, nf=12, activation="ReLU", output_mode=1, block_size=256, use_direction=1, steps_variant=False),
-    "h32x4_relu_dirfourier": dict(hidden16=2, num_hidden=2, nf=12, activation="ReLU", output_mode=1, block_size=256, use_direction=2, steps_variant=False),
+    "h32x4_relu_dir": dict(hidden16=2, num_hidden=2, nf=12, activation="ReLU", output_mode=1, block_size=256, use_direction=1),
+    "h32x4_relu_dirfourier": dict(hidden16=2, num_hidden=2, nf=12, activation="ReLU", output_mode=1, block_size=256, use_direction=2),
     "h32x4_relu_time": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, pass_time=1),
-    "h32x4_relu_grid32": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, grid16=2, steps_variant=False),
+    "h32x4_relu_grid32": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, grid16=2),
     "h32x4_sine": dict(hidden16=2, num_hidden=2, nf=14, activation="Sine", output_mode=1, block_size=256),
     "h32x4_snake": dict(hidden16=2, num_hidden=2, nf=14, activation="Snake", output_mode=1, block_size=256),
     # BASELINE C4 network: 64x6, 30 Fourier features; computeMaxWarps (volume_interpolation_network.cpp:987-1041) leaves

@@ -139,3 +139,21 @@ def test_time_input_with_interpolated_keyframes(ref, plume_tf):
     assert want[:, 3].max() > 0.3
     img, steps = parity.render_ours(volnet.dumps(net), "reference_exact", size, size, cam, plume_tf, step, time=time)
     _assert_identical(img, steps, want, want_steps, "time_input")
+
+
+@pytest.mark.parametrize("name", ["direction", "direction_in_fourier", "latent_32_channels"])
+def test_exact_mode_with_direction_input_and_two_latent_groups(ref, name, plume_tf):
+    """USE_DIRECTION 1 / 2 and LATENT_GRID_CHANNELS_DIV16 2 (renderer_volume_tensorcores.cuh:784-804, 839-910): reference-exact
+    mode bit-identical to the reference kernel built with that define, incl. step counts."""
+    import parity
+    from fvsrn_b200 import scenes, volnet
+    from test_gpu_baseline_configs import INPUT_CASES
+    kw, variant, time = INPUT_CASES[name]
+    net = scenes.make_network(**kw)
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    size, step = 512, 1 / 256
+    want, want_steps, _ = parity.render_reference(net, size, size, cam, scenes.DEFAULT_FOV_Y, plume_tf, step, variant=variant,
+                                                  steps_variant=variant + "_steps", time=time)
+    assert want[:, 3].max() > 0.2
+    img, steps = parity.render_ours(volnet.dumps(net), "reference_exact", size, size, cam, plume_tf, step)
+    _assert_identical(img, steps, want, want_steps, name)
