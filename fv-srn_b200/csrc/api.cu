@@ -959,7 +959,6 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         const Network& n = h->net;
         if (is_rgbo || h->GC16 < 1 || h->GC16 > 2 || ((n.has_direction || h->GC16 == 2) && h->H16 != 2 && h->H16 != 4))
             throw std::runtime_error("reference-exact mode: density-type networks with a latent grid; direction input or 32 latent channels with hidden width 32 or 64");
-        if (p->tf_kind != FVSRN_TF_PIECEWISE && p->tf_kind != FVSRN_TF_TEXTURE) throw std::runtime_error("reference-exact mode: piecewise or texture transfer function");
         for (size_t i = 0; i < h->d_time.size(); ++i) ensure_tex32(h->d_time[i], n.time_grids[i]);
         for (size_t i = 0; i < h->d_ens.size(); ++i) ensure_tex32(h->d_ens[i], n.ensemble_grids[i]);
     }

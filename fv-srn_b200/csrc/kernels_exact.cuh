@@ -249,6 +249,10 @@ __device__ __forceinline__ float4 exact_shade(const DvrParams& D, const float* t
     float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
     if (valid && value >= D.dmin) {
         const float d2 = rf::fmax(0.f, rf::fmin(rf::mul(inv_range, rf::sub(value, D.dmin)), 1.0f));
+        if (D.tf_kind == 2) {       // TransferFunctionIdentity::eval, renderer_tf_identity.cuh:36-55: tfp = {scale absorption, scale emission}
+            const float e = rf::mul(d2, tfp[1]);
+            c = make_float4(e, e, e, rf::mul(rf::mul(d2, tfp[0]), D.stepsize));
+        } else
         c = D.tf_kind == 0 ? exact_tf_piecewise(tfp, D.tf_R, d2, D.stepsize) : exact_tf_texture(tfp, D.tf_R, d2, D.stepsize);
     }
     return c;
@@ -366,7 +370,7 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
     uint4* stage = stage_all + warp * (Core::STAGE_BYTES / 16);
 
     load_blob(P, sblob);
-    const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : D.tf_R * 4;
+    const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : (D.tf_kind == 1 ? D.tf_R * 4 : 2);
     if (D.tf_batch == 1)
         for (int i = threadIdx.x; i < tf_floats; i += blockDim.x) stf[i] = __ldg(D.tf + i);
     __syncthreads();
@@ -493,7 +497,7 @@ __device__ __forceinline__ float grid_eval(const GridVolumeParams& G, float wx, 
 __global__ void __launch_bounds__(256)
 dvr_grid_kernel(const __grid_constant__ GridVolumeParams G, const __grid_constant__ DvrParams D) {
     __shared__ float stf[kTfSmemFloats];
-    const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : D.tf_R * 4;
+    const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : (D.tf_kind == 1 ? D.tf_R * 4 : 2);
     if (D.tf_batch == 1)
         for (int i = threadIdx.x; i < tf_floats; i += blockDim.x) stf[i] = __ldg(D.tf + i);
     __syncthreads();

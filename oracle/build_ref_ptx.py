@@ -39,9 +39,11 @@ template<int N, typename V, typename I> __host__ __device__ fvar<double4, N> mak
 
 NAMES = ["ImageEvaluatorSimpleKernel", "&cameraReferenceFrameParameters", "&volumeInterpolationTensorcoresParameters",
          "&rayEvaluationSteppingDvrParameters", "&brdfLambertParameters"]
-TF_NAMES = {"piecewise": "&transferFunctionPiecewiseParameters", "texture": "&transferFunctionTextureParameters"}
+TF_NAMES = {"piecewise": "&transferFunctionPiecewiseParameters", "texture": "&transferFunctionTextureParameters",
+            "identity": "&transferFunctionIdentityParameters"}
 TF_TYPES = {"piecewise": ("::kernel::TransferFunctionPiecewise", "renderer_tf_piecewise.cuh"),
-            "texture": ("::kernel::TransferFunctionTexture", "renderer_tf_texture.cuh")}
+            "texture": ("::kernel::TransferFunctionTexture", "renderer_tf_texture.cuh"),
+            "identity": ("::kernel::TransferFunctionIdentity", "renderer_tf_identity.cuh")}
 
 
 def grid_source(early_out=1, blend_mode=1, tf="piecewise", interpolation=1):
@@ -199,6 +201,7 @@ CONFIGS = {
     # (48 KiB - 43648 B weights) / (64*2*32 B per warp) = 1 warp per block
     "h64x6_relu": dict(hidden16=4, num_hidden=4, nf=30, activation="ReLU", output_mode=1, block_size=32),
     # texture transfer function (tensor form), byte-encoded latent grids
+    "h32x4_relu_identitytf": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, tf="identity"),
     "h32x4_relu_textf": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, tf="texture"),
     "h32x4_relu_bytelinear": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, encoding=1),
     "h32x4_relu_bytegauss": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, encoding=2),

@@ -32,9 +32,12 @@ def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0,
     vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
     ie = pr.ImageEvaluatorSimple(); ie.volume = vol
     ie.camera.set_parameters(torch.from_numpy(np.ascontiguousarray(camera, np.float32)))
-    if tf_kind == 1:
-        ie.ray_evaluator.tf = pr.TransferFunctionTexture()
-    ie.ray_evaluator.tf.tensor.value = torch.from_numpy(np.ascontiguousarray(tf, np.float32)).cuda()
+    if tf_kind == 2:        # identity TF: tf = (scale_absorption, scale_emission)
+        ie.ray_evaluator.tf = pr.TransferFunctionIdentity(float(tf[0]), float(tf[1]))
+    else:
+        if tf_kind == 1:
+            ie.ray_evaluator.tf = pr.TransferFunctionTexture()
+        ie.ray_evaluator.tf.tensor.value = torch.from_numpy(np.ascontiguousarray(tf, np.float32)).cuda()
     ie.ray_evaluator.stepsize = stepsize
     ie.samples_per_pixel = spp
     if fd_stepsize is not None:
@@ -65,7 +68,7 @@ def render_reference(net, width, height, camera, fov_y, tf, stepsize, tf_kind=0,
     """The same frame with the reference's kernel -> (rgba8 image, step counts, ms or None). variant: a named build of
     oracle/build_ref_ptx.py (the gradient / shading kernels; they have no step-count build: steps come back as None)."""
     import ref_kernel
-    tfname = "texture" if tf_kind == 1 else "piecewise"
+    tfname = {1: "texture", 2: "identity"}.get(tf_kind, "piecewise")
     rk = ref_kernel.ReferenceDvrKernel(net, time=time, tf=tfname, variant=variant, fd_stepsize=fd_stepsize)
     ms = None
     if timing_iters > 0:

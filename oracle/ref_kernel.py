@@ -82,7 +82,7 @@ class ReferenceDvrKernel:
         enc = grids[0].encoding
         if variant is None:
             variant = f"h{H}x{len(net.layers)}_{act.lower()}" + {0: "", 1: "_bytelinear", 2: "_bytegauss"}[enc] \
-                      + ("_textf" if tf == "texture" else "") + ("_steps" if patched_steps else "")
+                      + {"piecewise": "", "texture": "_textf", "identity": "_identitytf"}[tf] + ("_steps" if patched_steps else "")
         if variant not in meta:
             raise RuntimeError(f"no prebuilt reference PTX for {variant} (have {sorted(meta)})")
         m = meta[variant]
@@ -107,7 +107,7 @@ class ReferenceDvrKernel:
         self.func = _ck(driver.cuModuleGetFunction(self.module, low["ImageEvaluatorSimpleKernel"].encode()))
         self.g_cam = _ck(driver.cuModuleGetGlobal(self.module, low["&cameraReferenceFrameParameters"].encode()))
         self.g_dvr = _ck(driver.cuModuleGetGlobal(self.module, low["&rayEvaluationSteppingDvrParameters"].encode()))
-        tf_sym = "&transferFunctionTextureParameters" if tf == "texture" else "&transferFunctionPiecewiseParameters"
+        tf_sym = {"texture": "&transferFunctionTextureParameters", "identity": "&transferFunctionIdentityParameters"}.get(tf, "&transferFunctionPiecewiseParameters")
         self.g_tf = _ck(driver.cuModuleGetGlobal(self.module, low[tf_sym].encode()))
         # BRDFLambertParameters (scalar form, renderer_brdf_lambert.cuh:30-38); absent from the module when the BRDF is the pass-through
         self.g_brdf = None
@@ -215,17 +215,24 @@ class ReferenceDvrKernel:
         tf: (1|B,R,5) piecewise or (1|B,R,4) texture tensor, matching the variant this kernel was built with."""
         torch, d = self.torch, self.drv
         cam = torch.as_tensor(np.ascontiguousarray(camera, np.float32)).reshape(-1, 3, 3).cuda()
-        tft = torch.as_tensor(np.ascontiguousarray(tf, np.float32)).cuda()
-        tft = tft.reshape(-1, tft.shape[-2], tft.shape[-1])
-        assert tft.shape[-1] == (4 if self.tf_kind == "texture" else 5)
+        if self.tf_kind == "identity":      # TransferFunctionIdentityParameters {scaleAbsorption, scaleEmission} (renderer_tf_identity.cuh:16-26)
+            tft = None
+            tf_blob = np.asarray(tf, np.float32).reshape(-1)[:2].tobytes()
+        else:
+            tft = torch.as_tensor(np.ascontiguousarray(tf, np.float32)).cuda()
+            tft = tft.reshape(-1, tft.shape[-2], tft.shape[-1])
+            assert tft.shape[-1] == (4 if self.tf_kind == "texture" else 5)
         B = cam.shape[0]
         if (width * height * B) % 32:
             raise RuntimeError("the reference requires W*H*B to be a multiple of 32 (image_evaluator_simple.cpp:254-264)")
         cp = _CameraParams(); cp.fovY = fov_y; cp.aspect = float(width) / float(height); cp.matrix = _read3(cam)
         _ck(d.cuMemcpyHtoD(self.g_cam[0], bytes(cp), C.sizeof(cp)))
         _ck(d.cuMemcpyHtoD(self.g_dvr[0], np.array([stepsize, alpha_early_out, density_min, density_max], np.float32).tobytes(), 16))
-        ta = _read3(tft)
-        _ck(d.cuMemcpyHtoD(self.g_tf[0], bytes(ta), C.sizeof(ta)))
+        if tft is None:
+            _ck(d.cuMemcpyHtoD(self.g_tf[0], tf_blob, 8))
+        else:
+            ta = _read3(tft)
+            _ck(d.cuMemcpyHtoD(self.g_tf[0], bytes(ta), C.sizeof(ta)))
         if self.g_brdf is not None:
             # brdf: dict(magnitude_scaling, ambient, specular, magnitude_center, magnitude_radius, specular_exponent, light) - light =
             # position (point light) or direction (directional), as BRDFLambert::fillConstantMemory packs it (brdf.cpp:417-452)

@@ -157,3 +157,23 @@ def test_exact_mode_with_direction_input_and_two_latent_groups(ref, name, plume_
     assert want[:, 3].max() > 0.2
     img, steps = parity.render_ours(volnet.dumps(net), "reference_exact", size, size, cam, plume_tf, step)
     _assert_identical(img, steps, want, want_steps, name)
+
+
+def test_identity_transfer_function(ref):
+    """TransferFunctionIdentity (renderer_tf_identity.cuh:36-55: rgb = density * scaleEmission, absorption = density *
+    scaleAbsorption * stepsize): reference-exact mode bit-identical, fast modes within the image gate."""
+    import parity
+    from fvsrn_b200 import scenes, volnet
+    kw, _, step = CASES["C3_relu_nerf"][:3]
+    size = 512
+    net = make_case_network(kw)
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    tf = np.array([30.0, 0.8], np.float32)      # scale of the absorption, of the emission
+    want, want_steps, _ = parity.render_reference(net, size, size, cam, scenes.DEFAULT_FOV_Y, tf, step, tf_kind=2)
+    assert 0.2 < want[:, 3].max() < 0.95
+    img, steps = parity.render_ours(volnet.dumps(net), "reference_exact", size, size, cam, tf, step, tf_kind=2)
+    _assert_identical(img, steps, want, want_steps, "identity_tf")
+    for mode in ("tcgen05", "mma_sync"):
+        img, steps = parity.render_ours(volnet.dumps(net), mode, size, size, cam, tf, step, tf_kind=2)
+        r = parity.compare(img, steps, want, want_steps)
+        assert r["rgba_max_abs"] <= parity.RGBA_TOL and r["psnr_db"] >= parity.PSNR_MIN, (mode, r)
