@@ -1073,8 +1073,23 @@ int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* 
     // A single full frame is rendered as a few row bands that alternate between the caller's stream and the internal one:
     // each band's device-to-host copy follows its kernel on the same stream and overlaps the next band's kernel on the
     // other, and the next band's CTAs fill the SMs the previous band is draining.
+    // Pinned, device-mapped host memory (cudaHostAlloc / cudaHostRegister; every pinned allocation under unified addressing): the
+    // kernel writes its pixels straight into the caller's buffer. The 4 - 32 bytes per pixel trickle over PCIe while the frame is
+    // marched (16 MiB in 4.7 ms = 3.5 GB/s on C3) - no staging image, no copy left after the kernel.
+    // A/B on one B200 (C3, fp32 colour; kernel 4.67 ms): staged bands 4.84 ms, direct 4.7x ms (profiles/r02k_e2e_direct.log).
+    void* direct = nullptr;
+    if (!has_rect && fmt != FVSRN_OUTPUT_RAW8_F32) {     // (the raw tensor's eight scattered 4-byte planes measured 4.75 - 6.2 ms direct vs 4.91 staged)
+        cudaPointerAttributes at{};
+        if (cudaPointerGetAttributes(&at, out_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer != nullptr) direct = at.devicePointer;
+        else (void)cudaGetLastError();      // pageable memory: not an error, the staged path below handles it
+#if defined(FVSRN_EXPERIMENTS) || defined(FVSRN_HOST_BANDS_ENV)
+        if (std::getenv("FVSRN_HOST_STAGED")) direct = nullptr;
+#endif
+    }
     const int bands = (p->batch == 1 && !has_rect && !p->view_times_host && H >= 256 && net->aux_stream) ? 4 : 1;
-    if (bands == 1) {
+    if (direct) {
+        do_render(net, &q, reinterpret_cast<float*>(direct), s);
+    } else if (bands == 1) {
         if (has_rect) CUDA_OK(cudaMemsetAsync(d_img, 0, img_b, s));
         do_render(net, &q, reinterpret_cast<float*>(d_img), s);
         CUDA_OK(cudaMemcpyAsync(out_host, d_img, img_b, cudaMemcpyDeviceToHost, s));

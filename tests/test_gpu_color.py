@@ -113,7 +113,7 @@ def test_fused_colour_output_equals_render_then_extract(env, scene, fmt):
 @pytest.mark.parametrize("fmt,planes,dtype", [("raw8_f32", 8, np.float32), ("rgba_f32", 4, np.float32), ("rgba8", 1, np.uint32), ("rgba_f16", 1, np.float16)])
 def test_host_entry_point_formats_and_band_streaming(env, scene, fmt, planes, dtype):
     """fvsrn_render_dvr_host: every output format, at a height that takes the four-band streamed path (H >= 256) and one that
-    does not; the host image equals the device render bit for bit."""
+    does not, into pageable and into pinned host memory; the host image equals the device render bit for bit."""
     g, ie = scene
     cam = np.ascontiguousarray(g.camera, np.float32); tf = np.ascontiguousarray(ie.ray_evaluator.tf._tensor().cpu().numpy())
     net = ie.volume.current_network(); net._ensure_prepared()
@@ -124,6 +124,11 @@ def test_host_entry_point_formats_and_band_streaming(env, scene, fmt, planes, dt
         p.camera_matrix_dev = cam.ctypes.data; p.tf_dev = tf.ctypes.data
         p.output_format = env.pr.OUTPUT_FORMATS[fmt]; p.channel_mode = 3
         shape = (1, planes, H, W) if planes > 1 else ((1, H, W, 4) if fmt == "rgba_f16" else (1, H, W))
-        out = np.zeros(shape, dtype)
+        out = np.zeros(shape, dtype)        # pageable host memory: staged through the device image, copied band by band
         env.lib.check(env.lib.lib().fvsrn_render_dvr_host(net._h, C.byref(p), out.ctypes.data, None))
         assert np.array_equal(np.nan_to_num(out.view(dev.dtype) if fmt == "rgba8" else out), np.nan_to_num(dev)), (fmt, W, H)
+        # pinned (device-mapped) host memory: the fused formats are written by the kernel straight into the caller's buffer
+        tdt = {np.float32: env.torch.float32, np.uint32: env.torch.int32, np.float16: env.torch.float16}[dtype]
+        pinned = env.torch.zeros(shape, dtype=tdt).pin_memory()
+        env.lib.check(env.lib.lib().fvsrn_render_dvr_host(net._h, C.byref(p), pinned.data_ptr(), None))
+        assert np.array_equal(np.nan_to_num(pinned.numpy().view(dev.dtype)), np.nan_to_num(dev)), (fmt, W, H, "pinned")
