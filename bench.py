@@ -167,8 +167,18 @@ def _alloc_image(torch, fmt, n, h, w):
     return torch.empty((n, 4, h, w), dtype=torch.float32, device="cuda")
 
 
+def _image_shape(fmt, n, h, w):
+    return {"rgba8": (n, h, w), "rgba_f16": (n, h, w, 4)}.get(fmt, (n, 4, h, w))
+
+
+def _image_dtype(torch, fmt):
+    return {"rgba8": torch.int32, "rgba_f16": torch.float16}.get(fmt, torch.float32)
+
+
 def _image_strides(fmt, t, w):
-    """out_stride_{b,c,y,x} of fvsrn_dvr_params in elements of the output format for a contiguous image tensor `t`."""
+    """out_stride_{b,c,y,x} of fvsrn_dvr_params in elements of the output format for a contiguous image tensor `t`
+    (None: a full w x w frame that lives in another rank's memory)."""
+    if t is None: return (4 * w * w, w * w, w, 1) if fmt == "rgba_f32" else (w * w, 0, w, 1)
     if fmt == "rgba_f32": return tuple(t.stride())
     per = 4 if fmt == "rgba_f16" else 1
     return (t.stride(0) // per, 0, w, 1)
@@ -195,6 +205,8 @@ def run_b200(args):
     S = w["size"]
     fmt = args.gather_format
     tiles = args.sharding == "tiles"
+    peer_mode = world > 1 and args.collective == "peer"
+    peer = None
     sn = pr.SceneNetwork.from_bytes(volnet.dumps(net))
     sn.kernel_mode = args.kernel_mode
     vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
@@ -239,13 +251,22 @@ def run_b200(args):
                 bands, row_cost = fdist.rebalance_rows_by_time(row_cost, bands, all_ms, align=8)
             del scratch
         y0, bh = bands[rank]
-        frames = [_alloc_image(torch, fmt, 1, S if rank == 0 else max(bh, 1), S) for _ in range(2)]      # rank 0 holds the whole frame
+        if peer_mode:
+            peer = fdist.PeerFrames(_image_shape(fmt, 1, S, S), _image_dtype(torch, fmt), dst=0, slots=2)
+            frames = [peer.tensor(slot) for slot in range(2)]                                          # None on ranks > 0: they hold no image
+        else:
+            frames = [_alloc_image(torch, fmt, 1, S if rank == 0 else max(bh, 1), S) for _ in range(2)]      # rank 0 holds the whole frame
         if fmt == "rgba_f32":
             raise RuntimeError("--sharding tiles gathers packed pixels: use --gather-format rgba8 or rgba_f16")
     else:
         bands = None
-        frames = [_alloc_image(torch, fmt, V, S, S) for _ in range(2)]
-        gathered = [_alloc_image(torch, fmt, world * V, S, S) if (world > 1 and (rank == 0 or args.collective == "all_gather")) else None for _ in range(2)]
+        if peer_mode:
+            peer = fdist.PeerFrames(_image_shape(fmt, world * V, S, S), _image_dtype(torch, fmt), dst=0, slots=2)
+            frames = [None, None]
+            gathered = [peer.tensor(slot) for slot in range(2)]
+        else:
+            frames = [_alloc_image(torch, fmt, V, S, S) for _ in range(2)]
+        gathered = gathered if peer_mode else [_alloc_image(torch, fmt, world * V, S, S) if (world > 1 and (rank == 0 or args.collective == "all_gather")) else None for _ in range(2)]
     params = []
     for slot in range(2):
         t = frames[slot]
@@ -261,7 +282,10 @@ def run_b200(args):
             p.view_times_host = C.cast(vt, C.c_void_p)
         # band sharding: the kernel addresses pixels by their frame coordinates; a rank that only holds its band passes the
         # address its row y0 would have in a full frame
-        base = t.data_ptr() - ((y0 * S * FMT_BYTES[fmt]) if (tiles and rank != 0) else 0)
+        if peer_mode:   # rank 0's frame, mapped into this process: band sharding writes rows [y0, y0 + bh) of frame 0, view sharding
+            base = peer.address(slot, 0 if tiles else rank * V)      # writes views [rank V, (rank + 1) V)
+        else:
+            base = t.data_ptr() - ((y0 * S * FMT_BYTES[fmt]) if (tiles and rank != 0) else 0)
         params.append((p, base))
     stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
@@ -277,12 +301,15 @@ def run_b200(args):
         on rank 0. Steps alternate between two buffers, so the transfer of step k overlaps the render of step k+1."""
         slot = k & 1
         wait(slot)
+        if peer_mode: wait(slot ^ 1)     # rank 0 enqueues signal k-1 behind its reads of this slot's previous frame (PeerFrames protocol)
         p, base = params[slot]
         if ev: ev[0].record()
         if not tiles or bh > 0:
             _lib.check(L.fvsrn_render_dvr(sn._h, C.byref(p), base, stream))
         if ev: ev[1].record()
-        if world > 1:
+        if peer_mode:
+            pending[slot] = [peer.signal(slot)]
+        elif world > 1:
             if tiles:
                 pending[slot] = fdist.gather_row_bands(frames[slot][:, :bh] if rank != 0 else None, bands, frames[slot] if rank == 0 else None, async_op=True)
             else:
@@ -437,8 +464,9 @@ def run_b200(args):
             "vs_baseline": None, "dtype": "f16", "data": "synthetic",
             "config": {"workload": f"{args.workload}: {w['desc']}", "views_per_step": frames_per_step, "samples_per_pixel": int(w.get("spp", 1)),
                        "sharding": (f"one frame per step split into {world} contiguous row bands of equal {'estimated' if (args.no_rebalance or world == 1) else 'estimated-then-measured'} march cost {[b[1] for b in bands]}, "
-                                    f"bands received in place on rank 0 (NCCL send/recv, {fmt})") if tiles else
-                                   (f"{V} view(s) per GPU, {fmt} pixels collected on rank 0 (NCCL {args.collective}), transfer of step k overlaps the render of step k+1" if world > 1 else "single GPU"),
+                                    + (f"every rank's kernel writes its band straight into rank 0's frame over NVLink (CUDA IPC peer memory, {fmt}), 4-byte all-reduce as completion signal" if peer_mode else f"bands received in place on rank 0 (NCCL send/recv, {fmt})")) if tiles else
+                                   (f"{V} view(s) per GPU, {fmt} pixels written by every rank's kernel straight into rank 0's view array over NVLink (CUDA IPC peer memory), 4-byte all-reduce as completion signal" if peer_mode else
+                                    f"{V} view(s) per GPU, {fmt} pixels collected on rank 0 (NCCL {args.collective}), transfer of step k overlaps the render of step k+1" if world > 1 else "single GPU"),
                        "output": f"{fmt} colour written by the DVR kernel (fused extract_color)",
                        "l2": "256 MiB buffer written between timed steps (its device time measured separately and subtracted)",
                        "useful_samples_per_frame": useful / args.steps / frames_per_step, "executed_samples_per_frame": executed / args.steps / frames_per_step,
@@ -448,7 +476,7 @@ def run_b200(args):
             "e2e": {"value": useful / e2e_s, "unit": "samples/s", "ms_per_frame": 1e3 * e2e_s / args.steps / (1 if tiles else V),
                     "h2d_bytes_per_step": int(host_cam.numel() * 4 + host_tf.numel() * 4) * (world if world > 1 else 1), "d2h_bytes_per_step": int(d2h_bytes),
                     "what": "fvsrn_render_dvr_host: camera + TF copied up, the kernel writes the (B,4,H,W) fp32 colour straight into the caller's pinned host buffer" if world == 1 else
-                            "per step: H2D camera+TF on every rank, render, NCCL collection on rank 0, D2H of the assembled frames on rank 0",
+                            "per step: H2D camera+TF on every rank, render, " + ("peer-memory writes into rank 0's frame" if peer_mode else "NCCL collection on rank 0") + ", D2H of the assembled frames on rank 0",
                     "by_format": e2e_formats or None},
             # one DVR kernel per launch; with per-view keyframe times one launch per view, each preceded by the small kernel that
             # blends the view's keyframe pair (api.cu blend_keyframes; tcgen05 mode)
@@ -529,6 +557,9 @@ def run_b200(args):
             pv.counters_dev = counters.data_ptr()
     if rank == 0:
         _emit(line)
+    if peer is not None:
+        frames = gathered = params = res0 = None
+        peer.close()
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
     return 0
@@ -570,8 +601,10 @@ def main():
                          "into cost-balanced row bands (strong scaling, BASELINE C4)")
     ap.add_argument("--gather-format", default="rgba8", choices=["rgba8", "rgba_f16", "rgba_f32"],
                     help="pixel format the DVR kernel writes and NCCL collects (fused colour extraction)")
-    ap.add_argument("--collective", default="gather", choices=["gather", "all_gather"],
-                    help="N>1: how the finished RGBA views reach rank 0 (fv-srn_b200/dist.py gather_views)")
+    ap.add_argument("--collective", default="gather", choices=["gather", "all_gather", "peer"],
+                    help="N>1: how the finished pixels reach rank 0. gather / all_gather: NCCL collective behind the render (fv-srn_b200/dist.py "
+                         "gather_views / gather_row_bands); peer: the DVR kernel of every rank writes its pixels straight into rank 0's frame "
+                         "over NVLink (dist.PeerFrames, CUDA IPC), a 4-byte all-reduce is the completion signal")
     ap.add_argument("--kernel-mode", default="tcgen05", choices=["tcgen05", "mma_sync"],
                     help="tcgen05: tcgen05.mma/TMEM kernel (default); mma_sync: reference-precision fp16-accumulate kernel")
     args = ap.parse_args()

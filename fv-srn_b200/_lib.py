@@ -19,6 +19,7 @@ SYMBOLS = [
     "fvsrn_render_dvr_host", "fvsrn_extract_color", "fvsrn_extract_color_ex", "fvsrn_extract_color_ex_noalloc", "fvsrn_generate_rays", "fvsrn_evaluate_tf", "fvsrn_query",
     "fvsrn_volume_load_cvol", "fvsrn_volume_save_cvol", "fvsrn_volume_from_dense", "fvsrn_volume_get_info", "fvsrn_volume_free",
     "fvsrn_volume_prepare", "fvsrn_render_dvr_grid", "fvsrn_evaluate_grid",
+    "fvsrn_peer_buffer_create", "fvsrn_peer_buffer_open", "fvsrn_peer_buffer_close", "fvsrn_peer_buffer_free",
 ]
 
 
@@ -118,6 +119,10 @@ def lib():
         "fvsrn_evaluate_grid": [vp, vp, vp, i64, vp],
         "fvsrn_evaluate_tf": [i, vp, i, vp, vp, i64, f, f, f, vp],
         "fvsrn_query": [vp, i, C.POINTER(QueryInfo)],
+        "fvsrn_peer_buffer_create": [C.c_size_t, C.POINTER(vp), C.c_char_p],
+        "fvsrn_peer_buffer_open": [C.c_char_p, C.POINTER(vp)],
+        "fvsrn_peer_buffer_close": [vp],
+        "fvsrn_peer_buffer_free": [vp],
     }
     for name, args in sig.items():
         fn = getattr(L, name)

@@ -1279,6 +1279,49 @@ int fvsrn_extract_color_ex_noalloc(const float* img_dev, void* out_dev, int batc
     FV_CATCH
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Peer frame buffers (multi-GPU, one process per GPU): a device buffer on the collecting rank that the other ranks' DVR kernels
+// write their pixels into directly over NVLink (CUDA IPC mapping) - the render and the "gather" become one kernel per rank.
+int fvsrn_peer_buffer_create(size_t bytes, void** dev_ptr, unsigned char handle[64]) {
+    FV_TRY
+    if (!dev_ptr || !handle || bytes == 0) return fail("null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+    void* p = nullptr;
+    CUDA_OK(cudaMalloc(&p, bytes));             // its own allocation: an IPC handle names a whole cudaMalloc block
+    cudaIpcMemHandle_t h;
+    const cudaError_t e = cudaIpcGetMemHandle(&h, p);
+    if (e != cudaSuccess) { cudaFree(p); return fail(std::string("cudaIpcGetMemHandle failed: ") + cudaGetErrorString(e)); }
+    CUDA_OK(cudaMemset(p, 0, bytes));
+    std::memcpy(handle, &h, 64);
+    *dev_ptr = p;
+    return 0;
+    FV_CATCH
+}
+int fvsrn_peer_buffer_open(const unsigned char handle[64], void** dev_ptr) {
+    FV_TRY
+    if (!dev_ptr || !handle) return fail("null argument");
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    void* p = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return fail(std::string("cudaIpcOpenMemHandle failed (peer access between the two GPUs is required): ") + cudaGetErrorString(e));
+    *dev_ptr = p;
+    return 0;
+    FV_CATCH
+}
+int fvsrn_peer_buffer_close(void* dev_ptr) {
+    FV_TRY
+    if (dev_ptr) CUDA_OK(cudaIpcCloseMemHandle(dev_ptr));
+    return 0;
+    FV_CATCH
+}
+int fvsrn_peer_buffer_free(void* dev_ptr) {
+    FV_TRY
+    if (dev_ptr) CUDA_OK(cudaFree(dev_ptr));
+    return 0;
+    FV_CATCH
+}
+
 int fvsrn_generate_rays(const float* camera_matrix_dev, int batch, float fov_y_radians, int width, int height,
                         float* ray_start_dev, float* ray_dir_dev, void* stream) {
     FV_TRY

@@ -191,6 +191,73 @@ def gather_views(local: torch.Tensor, num_views: int, dst: int = 0, out: Optiona
     return torch.cat([pieces[r][:counts[r]] for r in range(world)], dim=0)
 
 
+class _DevicePointer:
+    """Raw device memory as an object torch.as_tensor understands (__cuda_array_interface__ v2)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(int(x) for x in shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class PeerFrames:
+    """Fused render + gather over peer memory (NVLink / NVSwitch), one process per GPU. Rank `dst` owns `slots` frame buffers of
+    `shape` (e.g. (views, H, W) int32 for RGBA8); every other rank maps them (CUDA IPC, fvsrn_peer_buffer_*) and passes
+    `address(slot, index)` - the device address of element `index` along dim 0 - as the output pointer of its DVR launch, so its
+    kernel's pixel writes land in rank dst's frame while the march is still running: no local image, no separate transfer.
+    `signal(slot)` enqueues a 4-byte all-reduce behind the render on every rank; when it has completed on `dst`, all writers'
+    kernels have finished and `tensor(slot)` (rank dst only) holds the frame. NCCL backend with peer access; the CPU (gloo)
+    tests cover gather_views / gather_row_bands, which move the same pixels through the collective instead."""
+
+    _TYPESTR = {torch.int32: "<i4", torch.float16: "<f2", torch.float32: "<f4", torch.uint8: "|u1"}
+
+    def __init__(self, shape, dtype=torch.int32, dst: int = 0, slots: int = 2):
+        import ctypes as C
+        from . import _lib
+        self.rank, self.world = world_info()
+        self.dst, self.shape, self.dtype = dst, tuple(int(x) for x in shape), dtype
+        self.itemsize = torch.empty((), dtype=dtype).element_size()
+        self.stride0 = self.itemsize * int(torch.tensor(self.shape[1:]).prod().item()) if len(self.shape) > 1 else self.itemsize
+        nbytes = self.stride0 * self.shape[0]
+        L = _lib.lib()
+        self._L, self._ptrs, self._owner = L, [], self.rank == dst
+        handles = []
+        if self._owner:
+            for _ in range(slots):
+                p = C.c_void_p(); h = C.create_string_buffer(64)
+                _lib.check(L.fvsrn_peer_buffer_create(nbytes, C.byref(p), h))
+                self._ptrs.append(int(p.value)); handles.append(bytes(h.raw))
+        box = [handles]
+        if self.world > 1:
+            dist.broadcast_object_list(box, src=dst)
+        if not self._owner:
+            for h in box[0]:
+                p = C.c_void_p()
+                _lib.check(L.fvsrn_peer_buffer_open(C.create_string_buffer(h, 64), C.byref(p)))
+                self._ptrs.append(int(p.value))
+        self._flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        self._tensors = [torch.as_tensor(_DevicePointer(p, self.shape, self._TYPESTR[dtype]), device="cuda") for p in self._ptrs] if self._owner else None
+
+    def address(self, slot: int, index: int = 0) -> int:
+        return self._ptrs[slot] + index * self.stride0
+
+    def tensor(self, slot: int) -> Optional[torch.Tensor]:
+        return self._tensors[slot] if self._owner else None
+
+    def signal(self, slot: int, async_op: bool = True):
+        if self.world == 1:
+            return None
+        return dist.all_reduce(self._flag, async_op=async_op)
+
+    def close(self):
+        import ctypes as C
+        from . import _lib
+        if self.world > 1:
+            dist.barrier()
+        self._tensors = None
+        for p in self._ptrs:
+            _lib.check((self._L.fvsrn_peer_buffer_free if self._owner else self._L.fvsrn_peer_buffer_close)(C.c_void_p(p)))
+        self._ptrs = []
+
+
 def render_frame_sharded(render_rect: Callable[[Rect], torch.Tensor], width: int, height: int, band: int = 64,
                          dst: int = 0) -> Optional[torch.Tensor]:
     """One frame across all ranks. `render_rect((x0,y0,w,h))` renders that rectangle into a (B,8,H,W) (or (B,4,H,W))

@@ -305,6 +305,20 @@ int  fvsrn_render_dvr_grid(fvsrn_volume* vol, const fvsrn_dvr_params* p, float* 
 /* IVolumeInterpolation::evaluate for the grid: positions (N,3) in [0,1]^3 -> densities (N) */
 int  fvsrn_evaluate_grid(fvsrn_volume* vol, const float* positions_dev, float* out_dev, int64_t n, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Peer frame buffers (B200 addition, no reference analogue: the reference renders on one GPU). One process per GPU; the collecting
+ * rank creates a device buffer and passes the 64-byte handle to the others (any byte transport: torch.distributed, a pipe); they
+ * open it and pass the mapped address (plus their view / band offset) as `out_dev` of fvsrn_render_dvr: the DVR kernel's pixel
+ * writes travel over NVLink into the collecting GPU's frame while the march is still running - render and gather are one
+ * kernel per rank, no staging image and no separate transfer. Needs peer access between the GPUs (NVSwitch / NVLink).
+ * The collecting rank reads the frame after a stream-ordered signal from every writer (fv-srn_b200/dist.py PeerFrames uses a
+ * 4-byte NCCL all-reduce). create / free on the owner, open / close on the peers.
+ * ------------------------------------------------------------------------------------------ */
+int  fvsrn_peer_buffer_create(size_t bytes, void** dev_ptr, unsigned char handle[64]);
+int  fvsrn_peer_buffer_open(const unsigned char handle[64], void** dev_ptr);
+int  fvsrn_peer_buffer_close(void* dev_ptr);
+int  fvsrn_peer_buffer_free(void* dev_ptr);
+
 /* Launch diagnostics (stand-in for compute_max_warps / KernelLoader occupancy query) */
 typedef struct fvsrn_query_info {
     int device, sm_count;
