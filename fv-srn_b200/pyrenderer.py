@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 from typing import Optional
 
 import numpy as np
@@ -477,6 +478,7 @@ class VolumeInterpolationGrid:
     set_source = setSource
 
     def volume(self): return self._volume
+    def mipmap_level(self): return 0
 
     def _require(self) -> Volume:
         if self._volume is None:
@@ -532,6 +534,24 @@ class TransferFunctionPiecewiseLinear(ITransferFunction):
 
     def __init__(self):
         self.tensor = Parameter(None)
+        self._absorption_scaling = 1.0
+        self._cpu: Optional[np.ndarray] = None
+
+    def load_points(self, color_points, opacity_points, absorption_scaling: float):
+        """TransferFunctionPiecewiseLinear::load + computeTensor (transfer_function_piecewise.cpp:80-91, 166-279): the colorPoints /
+        opacityPoints / absorptionScaling of a settings file -> `tensor`."""
+        from . import settings
+        self._cpu = settings.piecewise_tf_tensor(color_points, opacity_points, absorption_scaling)
+        self._absorption_scaling = float(absorption_scaling)
+        self.tensor = Parameter(torch.from_numpy(self._cpu).to("cuda"))
+
+    def evaluate_scalar(self, density: float):
+        """TransferFunctionPiecewiseLinear::evaluate(double) (:281-285): rgba at one density from the CPU copy of the tensor."""
+        from . import settings
+        t = self._cpu if self._cpu is not None else self._tensor().cpu().numpy()
+        return double4(*(float(v) for v in settings.sample_piecewise(t, density)))
+
+    def get_max_absorption(self): return self._absorption_scaling
 
     def _tensor(self):
         t = self.tensor.value
@@ -551,8 +571,26 @@ class TransferFunctionTexture(ITransferFunction):
     def __init__(self):
         self.tensor = Parameter(None)
         self.preintegration_mode = 0
+        self._absorption_scaling = 10.0          # transfer_function_texture.cpp:17
 
     def switch_to_tensor(self): pass
+
+    def load_points(self, color_points, plot, absorption_scaling: float):
+        """TransferFunctionTexture::load + computeTexture (transfer_function_texture.cpp:215-226, 347-362): colorPoints, the 256
+        opacityPoints and absorptionScaling of a settings file -> the (1,256,4) texture."""
+        from . import settings
+        self._absorption_scaling = float(absorption_scaling)
+        self.tensor = Parameter(torch.from_numpy(settings.texture_tf_tensor(color_points, plot, absorption_scaling)).to("cuda"))
+
+    def paste(self, other: "ITransferFunction"):
+        """TransferFunctionTexture::doPaste (:412-437): resample another TF at the 256 texel centres."""
+        from . import settings
+        if not hasattr(other, "evaluate_scalar"):
+            raise RuntimeError("Copying to texture TF not supported from source TF")
+        cps, plot, scale = settings.paste_into_texture(lambda d: tuple(other.evaluate_scalar(d)), self._absorption_scaling)
+        self.load_points(cps, plot, scale)
+
+    def get_max_absorption(self): return self._absorption_scaling
 
     def _tensor(self):
         if self.preintegration_mode != 0:
@@ -575,6 +613,11 @@ class TransferFunctionIdentity(ITransferFunction):
 
     def _tensor(self):
         return torch.tensor([[[self.absorption_scaling, self.emission_scaling]]], dtype=torch.float32, device="cuda")
+
+    def evaluate_scalar(self, density: float):
+        return double4(density * self.emission_scaling, density * self.emission_scaling, density * self.emission_scaling, density * self.absorption_scaling)
+
+    def get_max_absorption(self): return self.absorption_scaling
 
 
 class Blending:
@@ -639,7 +682,12 @@ class RayEvaluationSteppingDvr:
         self.volume = None
 
     def convert_to_texture_tf(self):
-        raise RuntimeError("convert_to_texture_tf is not part of the B200 hot path")
+        """RayEvaluationSteppingDvr::convertToTextureTF (ray_evaluation_stepping.cpp:757-770)."""
+        if self.tf is None or isinstance(self.tf, TransferFunctionTexture):
+            return
+        new_tf = TransferFunctionTexture()
+        new_tf.paste(self.tf)
+        self.tf = new_tf
 
 
 # ------------------------------------------------------------------------------------------------ camera
@@ -874,3 +922,75 @@ class ImageEvaluatorSimple:
             p.view_times_host = C.cast(vt, C.c_void_p)
         check(_lib.lib().fvsrn_render_dvr(net._h, C.byref(p), out.data_ptr(), _stream_ptr()))
         return out
+
+
+# ------------------------------------------------------------------------------------------------ settings files
+def load_from_json(filename: str) -> ImageEvaluatorSimple:
+    """pyrenderer.load_from_json (renderer/module_registry.cpp:75-99): a scene settings file -> a new ImageEvaluatorSimple with the
+    camera, DVR ray evaluator, transfer function, BRDF and volume the file selects, each loaded as that module's `load` does
+    (fv-srn_b200/settings.py cites them). A `Grid` volume loads its .cvol (path relative to the settings file); an `SRN` volume comes
+    back without networks, as in the reference (set_network / load_network afterwards)."""
+    from . import settings
+    plan = settings.read_settings(filename)
+    ie = ImageEvaluatorSimple()
+    e = plan["evaluator"]
+    ie.selected_channel = (IImageEvaluator.Mask, IImageEvaluator.Normal, IImageEvaluator.Depth, IImageEvaluator.Color)[e["channel"]]
+    ie.samples_per_iteration_log2 = e["samples_per_iteration_log2"]          # progressive refinement of the GUI; render() is one pass
+    ie.use_tonemapping, ie.tonemapping_shoulder = e["use_tonemapping"], e["tonemapping_shoulder"]
+    ie.fix_max_exposure, ie.fixed_max_exposure = e["fix_max_exposure"], e["fixed_max_exposure"]
+    c = plan["camera"]
+    cam = ie.camera
+    cam.orientation = (CameraOnASphere.Xp, CameraOnASphere.Xm, CameraOnASphere.Yp, CameraOnASphere.Ym, CameraOnASphere.Zp, CameraOnASphere.Zm)[c["orientation"]]
+    cam.center = Parameter(double3(*c["center"]))
+    cam.pitchYawDistance = Parameter(double3(c["pitch"], c["yaw"], c["distance"]))
+    cam.fovY_radians = c["fov_y"]
+    cam.zoom_value = c["zoom"]
+    re, d = ie.ray_evaluator, plan["dvr"]
+    re.stepsize, re.min_density, re.max_density, re.early_out = d["stepsize"], d["min_density"], d["max_density"], d["early_out"]
+    t = plan["tf"]
+    if t is None:
+        re.tf = None
+    elif t["kind"] == "Piecewise":
+        re.tf = TransferFunctionPiecewiseLinear()
+        re.tf.load_points(t["color_points"], t["opacity_points"], t["absorption_scaling"])
+    elif t["kind"] == "Texture":
+        re.tf = TransferFunctionTexture()
+        re.tf.preintegration_mode = t["preintegration_mode"]
+        re.tf.load_points(t["color_points"], t["plot"], t["absorption_scaling"])
+    else:
+        re.tf = TransferFunctionIdentity(t["absorption_scaling"], t["emission_scaling"])
+    b = plan["brdf"]
+    if b is None:
+        re.brdf = None
+    else:
+        br = re.brdf = BRDFLambert()
+        br.enable_magnitude_scaling, br.magnitude_scaling = b["enable_magnitude_scaling"], b["magnitude_scaling"]
+        br.enable_phong, br.ambient, br.specular = b["enable_phong"], b["ambient"], b["specular"]
+        br.magnitude_center, br.magnitude_radius, br.specular_exponent = b["magnitude_center"], b["magnitude_radius"], b["specular_exponent"]
+        br.light_follows_camera = b["light_follows_camera"]
+        br.light_type = (BRDFLambert.Point, BRDFLambert.Directional)[b["light_type"]]
+        br.light_position, br.light_direction = double3(*b["light_position"]), double3(*b["light_direction"])
+    v = plan["volume"]
+    if v is None:
+        ie.volume = None
+    elif v["kind"] == "Grid":
+        g = VolumeInterpolationGrid()
+        g.feature = v["density_feature"]
+        if v["path"] is not None:
+            if v["interpolation"] != "TRILINEAR":
+                raise RuntimeError(f"grid interpolation {v['interpolation']} is not part of the B200 path (TRILINEAR is)")
+            if not os.path.isfile(v["path"]):       # the reference prints this and leaves the source EMPTY; rendering then fails with "No volume specified"
+                import sys
+                print(f"Unable to load volume, is the file valid? {v['path']}", file=sys.stderr)
+            elif v["path"].endswith(".json"):
+                raise RuntimeError("ensemble volume lists are not part of the B200 path")
+            else:
+                g.setSource(Volume(v["path"]), v["mipmap_level"])
+        ie.volume = g
+    else:
+        n = VolumeInterpolationNetwork()
+        n.gradient_mode = (VolumeInterpolationNetwork.OFF_OR_DIRECT, VolumeInterpolationNetwork.FINITE_DIFFERENCES,
+                           VolumeInterpolationNetwork.ADJOINT_METHOD)[v["gradient_mode"]]
+        n.finite_differences_stepsize = v["finite_differences_stepsize"]
+        ie.volume = n
+    return ie
