@@ -58,6 +58,7 @@ struct fvsrn_network {
     bool prepared = false;
     int device = -1, sm_count = 0;
     uint4* d_blob = nullptr; int blob_bytes = 0;
+    int blob_bytes_adjoint = 0, off_adj_wh = 0, off_adj_w0f = 0, off_adj_w0g = 0;   // blob + transposed weights of the adjoint pass
     int off_w0 = 0, off_wh = 0, off_wlast = 0, off_bias = 0, off_fourier = 0;
     // tcgen05 path: K-major UMMA weight tiles (+ bias chunks) and the Fourier matrix
     uint4* d_tc_blob = nullptr; int tc_blob_bytes = 0;
@@ -66,6 +67,7 @@ struct fvsrn_network {
     int kernel_mode = FVSRN_KERNEL_TCGEN05;
     int gradient_mode = FVSRN_GRADIENT_OFF_OR_DIRECT;      // VolumeInterpolationNetwork::gradientMode_ (a module setting, not part of .volnet)
     float fd_stepsize = 1.f / 256.f;                       // finiteDifferencesStepsize_, volume_interpolation_network.cpp:1423
+    float adjoint_grid_step = 0.f;                         // adjoint mode: central-difference step through the latent grid; 0 = 1 / (4 * resolution), :1424, 1809-1812
     int off_wlast_rows = 0;
     int H16 = 0, GC16 = 0, dir = 0, num_hidden = 0, activation = 0; float act_param = 1.f;
     std::vector<DeviceGrid> d_time, d_ens;
@@ -149,11 +151,11 @@ void build_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
     h->H16 = H / 16; h->GC16 = GC / 16; h->dir = n.has_direction ? 1 : 0;
     h->num_hidden = L - 2; h->activation = act; h->act_param = l0.activation_param;
 
-    auto frag_layer = [&](const Layer& l, int K, int N, int Npad, std::vector<uint8_t>& dst) {
-        // B fragment of mma.m16n8k16 (col-major B[k][n] = W[n][k]): lane (g = lane/4, t = lane%4) holds
-        // b0 = W[n0+g][k0+2t..2t+1], b1 = W[n0+g][k0+2t+8..2t+9]
+    auto frag_matrix = [&](auto&& at, int K, int N, int Npad, std::vector<uint8_t>& dst) {
+        // B fragment of mma.m16n8k16 (col-major B[k][n] = at(n, k)): lane (g = lane/4, t = lane%4) holds
+        // b0 = at(n0+g, k0+2t..2t+1), b1 = at(n0+g, k0+2t+8..2t+9)
         const int KT = K / 16, NT = Npad / 8;
-        auto W = [&](int nn, int kk) -> uint16_t { return (nn < N) ? l.w(nn, kk) : uint16_t(0); };
+        auto W = [&](int nn, int kk) -> uint16_t { return (nn < N) ? at(nn, kk) : uint16_t(0); };
         for (int kt = 0; kt < KT; ++kt)
             for (int ntp = 0; ntp < (NT + 1) / 2; ++ntp)
                 for (int lane = 0; lane < 32; ++lane)
@@ -164,6 +166,9 @@ void build_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
                         const uint8_t* p = reinterpret_cast<const uint8_t*>(v);
                         dst.insert(dst.end(), p, p + 8);
                     }
+    };
+    auto frag_layer = [&](const Layer& l, int K, int N, int Npad, std::vector<uint8_t>& dst) {
+        frag_matrix([&](int nn, int kk) { return l.w(nn, kk); }, K, N, Npad, dst);
     };
     blob.clear();
     h->off_w0 = 0;
@@ -197,6 +202,21 @@ void build_blob(fvsrn_network* h, std::vector<uint8_t>& blob) {
             blob.push_back(uint8_t(v & 0xff)); blob.push_back(uint8_t(v >> 8));
         }
     h->blob_bytes = int(blob.size());
+    // Adjoint pass (GRADIENT_MODE 2, renderer_volume_tensorcores.cuh:1205-1530): the same layers with the roles of inputs and
+    // outputs exchanged, adj_in[cin] = sum_cout W[cout][cin] adj_out[cout] - hidden layers, then layer 0 split into its first H
+    // inputs (position, time, Fourier features) and its 16-channel latent groups. Kept behind blob_bytes: only the kernel that
+    // runs the adjoint pass copies them to shared memory.
+    h->off_adj_wh = int(blob.size());
+    for (int i = 1; i + 1 < L; ++i) {
+        const Layer& l = n.layers[i];
+        frag_matrix([&](int cin, int cout) { return l.w(cout, cin); }, H, H, H, blob);
+    }
+    h->off_adj_w0f = int(blob.size());
+    frag_matrix([&](int cin, int cout) { return l0.w(cout, cin); }, H, H, H, blob);
+    h->off_adj_w0g = int(blob.size());
+    for (int g = 0; g < GC / 16; ++g)
+        frag_matrix([&](int c, int cout) { return l0.w(cout, H + 16 * g + c); }, H, 16, 16, blob);
+    h->blob_bytes_adjoint = int(blob.size());
 }
 
 // Blob of the tcgen05 path (see srn_tc.cuh / kernels_tc.cuh): per layer the B operand W[n][k] as K-major, no-swizzle
@@ -315,11 +335,19 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
     const Network& n = h->net;
     NetParams P{};
     P.gradient_mode = h->gradient_mode; P.fd_stepsize = h->fd_stepsize; P.off_wlast_rows = h->off_wlast_rows;
+    if (h->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD) {
+        // VolumeInterpolationNetwork::fillConstantMemory, :1809-1812: stepsize = 1 / (float(gridResolution) * scale), scale 4 by default;
+        // it fills both finiteDifferencesStepsize and latentGridDifferencesStepSize (:1409-1410)
+        int res = 1;
+        if (n.has_latent_grid) res = !n.time_grids.empty() ? n.time_grids[0].X : n.ensemble_grids[0].X;
+        P.fd_stepsize = h->adjoint_grid_step > 0.f ? h->adjoint_grid_step : 1.0f / (float(res) * 4.0f);
+    }
     if (tc) {
         P.blob = h->d_tc_blob; P.blob_bytes = h->tc_blob_bytes;
         P.off_w0 = h->tc_off_w0; P.off_wh = h->tc_off_wh; P.off_wlast = h->tc_off_wlast; P.off_bias = 0; P.off_fourier = h->tc_off_fourier;
     } else {
-        P.blob = h->d_blob; P.blob_bytes = h->blob_bytes;
+        P.blob = h->d_blob; P.blob_bytes = h->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD ? h->blob_bytes_adjoint : h->blob_bytes;
+        P.off_adj_wh = h->off_adj_wh; P.off_adj_w0f = h->off_adj_w0f; P.off_adj_w0g = h->off_adj_w0g;
         P.off_w0 = h->off_w0; P.off_wh = h->off_wh; P.off_wlast = h->off_wlast; P.off_bias = h->off_bias; P.off_fourier = h->off_fourier;
     }
     P.num_hidden = h->num_hidden; P.act_param = h->act_param;
@@ -335,7 +363,7 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
             P.time_value = t;
             const DeviceGrid& A = h->d_time[lo]; const DeviceGrid& B = h->d_time[hi];
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
-            const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && !A.tex32.empty() && !B.tex32.empty();
+            const bool exact = (h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT || h->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD) && !A.tex32.empty() && !B.tex32.empty();
             for (int i = 0; i < A.C / 16; ++i, ++g) {
                 P.groups[g] = GridGroup{grid_ptr(A, i), grid_ptr(B, i), frac, A.encoding ? A.C / 16 : A.C * 2 / 16};
                 fill_encoding(P, g, A, B, i);
@@ -348,7 +376,7 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
         if (!h->d_ens.empty()) {
             const DeviceGrid& A = h->d_ens[n.interpolate_ensemble(ensemble)];
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
-            const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && !A.tex32.empty();
+            const bool exact = (h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT || h->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD) && !A.tex32.empty();
             for (int i = 0; i < A.C / 16; ++i, ++g) {
                 P.groups[g] = GridGroup{grid_ptr(A, i), grid_ptr(A, i), 0.f, A.encoding ? A.C / 16 : A.C * 2 / 16};
                 fill_encoding(P, g, A, A, i);
@@ -561,12 +589,13 @@ int fvsrn_network_set_time_and_ensemble(fvsrn_network* net, float time, int ense
 
 int fvsrn_network_set_gradient_mode(fvsrn_network* net, int gradient_mode, float finite_differences_stepsize) {
     if (!net) return fail("null network handle");
-    if (gradient_mode == 2) return fail("unsupported on the B200 path: the adjoint gradient mode (use finite differences)");
-    if (gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT && gradient_mode != FVSRN_GRADIENT_FINITE_DIFFERENCES) return fail("unknown gradient mode");
+    if (gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT && gradient_mode != FVSRN_GRADIENT_FINITE_DIFFERENCES && gradient_mode != FVSRN_GRADIENT_ADJOINT_METHOD)
+        return fail("unknown gradient mode");
     if (gradient_mode == FVSRN_GRADIENT_FINITE_DIFFERENCES && !(finite_differences_stepsize > 0.f)) return fail("finite_differences_stepsize must be positive");
     std::lock_guard<std::mutex> lock(net->mu);
     net->gradient_mode = gradient_mode;
-    if (finite_differences_stepsize > 0.f) net->fd_stepsize = finite_differences_stepsize;
+    if (gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD) net->adjoint_grid_step = finite_differences_stepsize > 0.f ? finite_differences_stepsize : 0.f;
+    else if (finite_differences_stepsize > 0.f) net->fd_stepsize = finite_differences_stepsize;
     return 0;
 }
 
@@ -953,8 +982,19 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     if (h->gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT && is_rgbo) throw std::runtime_error("gradient modes need a density network (the reference's evalNormal asserts it)");
     D.normals = (om >= OUT_DENSITYGRAD || h->gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT || D.brdf_flags) ? 1 : 0;
     // the tcgen05 kernels march density / colour networks without normals; everything with normals runs on the mma.sync family
+    // Adjoint normals (GRADIENT_MODE 2): the backward pass through the network exists in the reference-arithmetic kernel family
+    // only (kernels_exact.cuh, SrnExact::adjoint) - frames that ask for it run there whichever kernel mode is selected.
+    const bool adjoint = h->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD;
+    if (adjoint) {
+        const Network& n = h->net;
+        if (n.has_direction) throw std::runtime_error("adjoint gradient mode: networks with a direction input are not supported (the reference's adjoint ignores the direction, :1478-1504)");
+        if (om == OUT_DENSITYCURV || om == OUT_DENSITYCURV_DIRECT) throw std::runtime_error("adjoint gradient mode: not defined for densitycurvature networks (reference :1262-1264)");
+        if (h->num_hidden > 7) throw std::runtime_error("adjoint gradient mode: at most 7 hidden layers after the first");
+        for (const auto& g : h->d_time) if (g.encoding != GRID_FLOAT) throw std::runtime_error("adjoint gradient mode: float latent grids only");
+        for (const auto& g : h->d_ens) if (g.encoding != GRID_FLOAT) throw std::runtime_error("adjoint gradient mode: float latent grids only");
+    }
     const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05 && !D.normals;
-    const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT;
+    const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT || adjoint;
     if (exact) {    // the shapes the reference kernels this mode is validated against cover (kernels_exact.cuh)
         const Network& n = h->net;
         if (is_rgbo || h->GC16 < 1 || h->GC16 > 2 || ((n.has_direction || h->GC16 == 2) && h->H16 != 2 && h->H16 != 4))
@@ -970,7 +1010,8 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         DvrParams d = D; d.b0 = b0; d.nb = nb;      // the launcher lays the tile raster of its kernel over the rectangle
         d.tile_counter = next_tile_counter(h, ls);
         LaunchCfg cfg; cfg.sm_count = h->sm_count;
-        if (exact) CUDA_OK(launch_exact(h->H16, h->GC16, h->dir, P, d, &cfg, ls));
+        if (adjoint) CUDA_OK(launch_exact_adjoint(h->H16, h->GC16, P, d, &cfg, ls));
+        else if (exact) CUDA_OK(launch_exact(h->H16, h->GC16, h->dir, P, d, &cfg, ls));
         else CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, ls));
         if (blended) CUDA_OK(cudaEventRecord(blended->ev_read[ls == h->aux_stream ? 1 : 0], ls));
         h->launches++;
@@ -1362,7 +1403,8 @@ int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     if (!fn) return fail("no kernel for this hidden width");
     DvrParams dq{}; dq.tf_kind = 0; dq.tf_R = 8;   // a typical piecewise TF: the DVR kernels size their shared memory from it
     dq.tw = 1024; dq.th = 1024; dq.nb = 1;
-    if (net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact(net->H16, net->GC16, net->dir, P, dq, &cfg, nullptr));
+    if (net->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD && kernel == 0) CUDA_OK(launch_exact_adjoint(net->H16, net->GC16, P, dq, &cfg, nullptr));
+    else if (net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact(net->H16, net->GC16, net->dir, P, dq, &cfg, nullptr));
     else CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, kernel == 0 ? &dq : nullptr, &cfg, nullptr));
     info->device = net->device; info->sm_count = net->sm_count;
     info->block_threads = cfg.threads; info->blocks_per_sm = cfg.blocks_per_sm; info->grid_blocks = cfg.grid;

@@ -66,6 +66,36 @@ struct SrnExact {
                 }
     }
 
+    static __device__ __forceinline__ void copy_frag(uint32_t (&dst)[2][NT][2], const uint32_t (&src)[2][NT][2]) {
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt) { dst[mt][nt][0] = src[mt][nt][0]; dst[mt][nt][1] = src[mt][nt][1]; }
+    }
+    // accumulator fragments <-> one row per sample in the warp's staging tile: register j of tile (mt, nt) holds sample
+    // mt*16 + lane/4 + 8*j, channels nt*8 + 2*(lane%4) + {0,1}
+    template <int NTL>
+    static __device__ __forceinline__ void frag_to_rows(uint4* stage, const uint32_t (&f)[2][NTL][2], int lane) {
+        uint32_t* st32 = reinterpret_cast<uint32_t*>(stage);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NTL; ++nt)
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+                    st32[(mt * 16 + (lane >> 2) + 8 * j) * (RS_CHUNKS * 4) + nt * 4 + (lane & 3)] = f[mt][nt][j];
+    }
+    static __device__ __forceinline__ void rows_to_frag(const uint4* stage, uint32_t (&f)[2][NT][2], int lane) {
+        const uint32_t* st32 = reinterpret_cast<const uint32_t*>(stage);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+                    f[mt][nt][j] = st32[(mt * 16 + (lane >> 2) + 8 * j) * (RS_CHUNKS * 4) + nt * 4 + (lane & 3)];
+    }
+
     // layer-0 inputs of the sample owned by this lane: [px,py,pz,0, cos x NF, sin x NF, latent x 16]
     static __device__ __forceinline__ void build_row(const NetParams& P, float px, float py, float pz, float3 dir, float tfrac, uint32_t (&row)[K0 / 2]) {
         const __half vx = __float2half(px), vy = __float2half(py), vz = __float2half(pz);
@@ -122,8 +152,13 @@ struct SrnExact {
 
     // network output (raw last-layer values, fp16) of the sample owned by this lane; all 32 lanes call. four = the
     // 4 / 6-output last layers of the densitygrad* / densitycurvature* modes (o[0] density, o[1..3] predicted gradient)
+    // ADJ: keep the pre-activation accumulators of every activated layer for the adjoint pass (the reference stores them in
+    // sStorageForAdjointHidden, :912-920, 997-1006)
+    static constexpr int MAXL = 8;
+    struct Pre { uint32_t v[MAXL][2][NT][2]; };
+    template <bool ADJ = false>
     static __device__ __forceinline__ void forward(const NetParams& P, uint32_t sblob, uint4* stage, const Act& ac,
-                                                   float px, float py, float pz, float3 dir, float tfrac, bool four, __half (&o)[4]) {
+                                                   float px, float py, float pz, float3 dir, float tfrac, bool four, __half (&o)[4], Pre* pre = nullptr) {
         const int lane = threadIdx.x & 31;
         __syncwarp();
         uint32_t row[K0 / 2];
@@ -144,6 +179,7 @@ struct SrnExact {
                     ldmatrix_x4(a[mt], stage_addr + ((mt * 16 + lrow) * RS_CHUNKS + kt * 2 + lcol) * 16);
             });
         }
+        if constexpr (ADJ) copy_frag(pre->v[0], acc);
         activate(acc, P.activation, ac);
 #pragma unroll 1
         for (int l = 0; l < P.num_hidden; ++l) {
@@ -156,23 +192,14 @@ struct SrnExact {
                                               a[mt][2] = acc[mt][2 * kt + 1][0]; a[mt][3] = acc[mt][2 * kt + 1][1];
                                           }
                                       });
+            if constexpr (ADJ) copy_frag(pre->v[1 + l], nxt);
             activate(nxt, P.activation, ac);
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int nt = 0; nt < NT; ++nt) { acc[mt][nt][0] = nxt[mt][nt][0]; acc[mt][nt][1] = nxt[mt][nt][1]; }
+            copy_frag(acc, nxt);
         }
         // activations back to one row per sample (the reference's store_matrix_sync to shared memory, :1018-1023):
         // accumulator register j of tile (mt, nt) holds sample mt*16 + lane/4 + 8*j, channels nt*8 + 2*(lane%4) + {0,1}
         __syncwarp();
-        uint32_t* st32 = reinterpret_cast<uint32_t*>(stage);
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-            for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-                for (int j = 0; j < 2; ++j)
-                    st32[(mt * 16 + (lane >> 2) + 8 * j) * (RS_CHUNKS * 4) + nt * 4 + (lane & 3)] = acc[mt][nt][j];
+        frag_to_rows<NT>(stage, acc, lane);
         __syncwarp();
         if (four) {
             // :1045-1052 (4 outputs) and :1106-1115 (6 outputs, the first four laid out the same): out1 = (bias0, bias1),
@@ -209,6 +236,164 @@ struct SrnExact {
             }
         }
         o[0] = out; o[1] = o[2] = o[3] = __float2half(0.f);
+    }
+
+    // ------------------------------------------------------------------------------------------------------------------
+    // GRADIENT_MODE 2: d density / d position by one backward pass (_evalNormalAdjoint, renderer_volume_tensorcores.cuh:
+    // 1205-1530), the reference's operations in the reference's order. Samples stay the M dimension of the MMA: the reference
+    // computes adj_in(cin x 32 samples) = W^T * adj_out with wmma, this is its transpose - the same dot products, fp16
+    // accumulators from zero, K (= cout) consumed 16 at a time in ascending order.
+    struct AdjAct { __half p, q2, inv_q2, one; };
+    static __device__ __forceinline__ AdjAct make_adj_act(float param) {
+        AdjAct a;
+        a.p = __float2half(param);
+        const float p2 = rf::add(param, param);
+        a.q2 = __float2half(p2);                    // Snake / SnakeAlt: half(2 * param), renderer_activations.cuh:299, 368
+        a.inv_q2 = __float2half(rf::rcp(p2));       // SnakeAlt: half(1 / (2 * param)), :369 (fast-math reciprocal)
+        a.one = __float2half(1.0f);
+        return a;
+    }
+    // ACTIVATION::adjoint(x, zAdj) of the half overloads, the __CUDA_ARCH__ < 800 branches (the reference builds for compute_75)
+    static __device__ __forceinline__ __half act_adj1(int act, const AdjAct& a, __half x, __half z) {
+        if (act == D_ACT_RELU) return __half2float(x) > 0.f ? z : __float2half(0.f);                         // :66-73
+        if (act == D_ACT_SINE) return __hmul(z, __hmul(a.p, hcos(__hmul(x, a.p))));                         // :123-127
+        if (act == D_ACT_SNAKE) return __hmul(z, __hadd(a.one, hsin(__hmul(a.q2, x))));                     // :295-300
+        if (act == D_ACT_SNAKEALT) return __hmul(z, __hadd(hsin(__hmul(a.q2, x)), a.inv_q2));               // :366-371
+        return z;
+    }
+    static __device__ __forceinline__ void act_adjoint(uint32_t (&z)[2][NT][2], const uint32_t (&x)[2][NT][2], int act, const AdjAct& a) {
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const __half2 zv = u2h(z[mt][nt][j]), xv = u2h(x[mt][nt][j]);
+                    z[mt][nt][j] = h2u(__halves2half2(act_adj1(act, a, __low2half(xv), __low2half(zv)), act_adj1(act, a, __high2half(xv), __high2half(zv))));
+                }
+    }
+    // out(32 x 8*NTL) = X(32 x H) * B, B as fragments at w_addr (api.cu build_blob, adjoint sections)
+    template <int NTL>
+    static __device__ __forceinline__ void dense_t(uint32_t (&out)[2][NTL][2], uint32_t w_addr, int lane, const uint32_t (&x)[2][NT][2]) {
+#pragma unroll
+        for (int kt = 0; kt < KTH; ++kt) {
+            uint32_t a[2][4];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                a[mt][0] = x[mt][2 * kt][0]; a[mt][1] = x[mt][2 * kt][1];
+                a[mt][2] = x[mt][2 * kt + 1][0]; a[mt][3] = x[mt][2 * kt + 1][1];
+            }
+#pragma unroll
+            for (int ntp = 0; ntp < NTL / 2; ++ntp) {
+                const uint4 b = lds128(w_addr + ((kt * (NTL / 2) + ntp) * 32 + lane) * 16);
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) {
+                    if (kt == 0) {
+                        mma16816(out[mt][2 * ntp], a[mt], b.x, b.y, 0u, 0u);
+                        mma16816(out[mt][2 * ntp + 1], a[mt], b.z, b.w, 0u, 0u);
+                    } else {
+                        mma16816(out[mt][2 * ntp], a[mt], b.x, b.y, out[mt][2 * ntp][0], out[mt][2 * ntp][1]);
+                        mma16816(out[mt][2 * ntp + 1], a[mt], b.z, b.w, out[mt][2 * ntp + 1][0], out[mt][2 * ntp + 1][1]);
+                    }
+                }
+            }
+        }
+    }
+    // one axis of LoadVolumetricFeaturesAdjoint (:660-678): central difference of the time-interpolated texel, dotted with the adjoint
+    static __device__ __forceinline__ float latent_axis(const NetParams& P, int q, float xh, float yh, float zh, float xl, float yl, float zl,
+                                                        float tfrac, float s, const float (&adj)[4]) {
+        const float4 ah = tex3D<float4>(P.tex_a[q], xh, yh, zh), al = tex3D<float4>(P.tex_a[q], xl, yl, zl);
+        const float4 bh = tex3D<float4>(P.tex_b[q], xh, yh, zh), bl = tex3D<float4>(P.tex_b[q], xl, yl, zl);
+        const float hx = rf::fma(tfrac, rf::sub(bh.x, ah.x), ah.x), hy = rf::fma(tfrac, rf::sub(bh.y, ah.y), ah.y);
+        const float hz = rf::fma(tfrac, rf::sub(bh.z, ah.z), ah.z), hw = rf::fma(tfrac, rf::sub(bh.w, ah.w), ah.w);
+        const float lx = rf::fma(tfrac, rf::sub(bl.x, al.x), al.x), ly = rf::fma(tfrac, rf::sub(bl.y, al.y), al.y);
+        const float lz = rf::fma(tfrac, rf::sub(bl.z, al.z), al.z), lw = rf::fma(tfrac, rf::sub(bl.w, al.w), al.w);
+        const float gx = rf::mul(s, rf::sub(hx, lx)), gy = rf::mul(s, rf::sub(hy, ly)), gz = rf::mul(s, rf::sub(hz, lz)), gw = rf::mul(s, rf::sub(hw, lw));
+        return rf::fma(adj[3], gw, rf::fma(adj[2], gz, rf::fma(adj[0], gx, rf::mul(adj[1], gy))));      // dot(adjC, grad) as compiled
+    }
+
+    // all 32 lanes call, right after forward<true> of the same position; out_last = the raw density output of this lane's sample
+    static __device__ __forceinline__ float3 adjoint(const NetParams& P, uint32_t sblob, uint4* stage, const AdjAct& aa, float px, float py, float pz,
+                                                     float tfrac, bool sigm, __half out_last, const Pre& pre) {
+        const int lane = threadIdx.x & 31;
+        // adjoint of the output parametrisation, :1233-1246: sigmoid -> Sigmoid::adjoint(float) = ev / (ev + 1)^2 in double; else 1
+        __half adj_out = __float2half(1.0f);
+        if (sigm) {
+            const float ev = rf::ex2(rf::mul(__half2float(out_last), 1.4426950408889634f));
+            const double e = double(ev), e1 = e + 1.0;
+            adj_out = __float2half(float(e / (e1 * e1)));
+        }
+        // adjoint of the last layer, :1248-1262: row[cin] = hmul(wLast[cin] (density output), adjOut)
+        __syncwarp();
+        uint32_t* st32 = reinterpret_cast<uint32_t*>(stage);
+        const __half2 adj2 = __halves2half2(adj_out, adj_out);
+#pragma unroll
+        for (int c2 = 0; c2 < H / 2; ++c2) {
+            // wlast2 = the weights of output 0 (the density; sWeightsLast[cin] or sWeightsLast[2 * cin].x of the 4-output layers)
+            st32[lane * (RS_CHUNKS * 4) + c2] = h2u(__hmul2(u2h(P.wlast2[c2]), adj2));
+        }
+        __syncwarp();
+        uint32_t z[2][NT][2];
+        rows_to_frag(stage, z, lane);
+        // hidden layers, last to first, :1272-1334
+#pragma unroll 1
+        for (int l = P.num_hidden - 1; l >= 0; --l) {
+            act_adjoint(z, pre.v[1 + l], P.activation, aa);
+            uint32_t nxt[2][NT][2];
+            dense_t<NT>(nxt, sblob + P.off_adj_wh + l * Core::wh_bytes(), lane, z);
+            copy_frag(z, nxt);
+        }
+        // layer 0, :1340-1448
+        act_adjoint(z, pre.v[0], P.activation, aa);
+        float3 out = make_float3(0.f, 0.f, 0.f);
+        const float h = P.fd_stepsize;                      // latentGridDifferencesStepSize
+        const float s = rf::rcp(rf::add(h, h));             // 1 / (2 h)
+        const float xh = rf::add(px, h), xl = rf::sub(px, h), yh = rf::add(py, h), yl = rf::sub(py, h), zh = rf::add(pz, h), zl = rf::sub(pz, h);
+#pragma unroll
+        for (int g = 0; g < GC16; ++g) {
+            uint32_t c16[2][2][2];
+            dense_t<2>(c16, sblob + P.off_adj_w0g + g * (H * 16 * 2), lane, z);
+            __syncwarp();
+            frag_to_rows<2>(stage, c16, lane);
+            __syncwarp();
+            const uint4 r0 = stage[lane * RS_CHUNKS], r1 = stage[lane * RS_CHUNKS + 1];
+            const uint32_t u[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+            float3 adjp = make_float3(0.f, 0.f, 0.f);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float adj[4] = {__half2float(__low2half(u2h(u[2 * i]))), __half2float(__high2half(u2h(u[2 * i]))),
+                                      __half2float(__low2half(u2h(u[2 * i + 1]))), __half2float(__high2half(u2h(u[2 * i + 1])))};
+                const int q = 4 * g + i;
+                adjp.x = rf::add(adjp.x, latent_axis(P, q, xh, py, pz, xl, py, pz, tfrac, s, adj));
+                adjp.y = rf::add(adjp.y, latent_axis(P, q, px, yh, pz, px, yl, pz, tfrac, s, adj));
+                adjp.z = rf::add(adjp.z, latent_axis(P, q, px, py, zh, px, py, zl, tfrac, s, adj));
+            }
+            out.x = rf::add(out.x, adjp.x); out.y = rf::add(out.y, adjp.y); out.z = rf::add(out.z, adjp.z);
+        }
+        // the first H inputs: position, (time), Fourier features, :1418-1446 and :1466-1504
+        {
+            uint32_t zf[2][NT][2];
+            dense_t<NT>(zf, sblob + P.off_adj_w0f, lane, z);
+            __syncwarp();
+            frag_to_rows<NT>(stage, zf, lane);
+            __syncwarp();
+        }
+        const __half* row = reinterpret_cast<const __half*>(stage + lane * RS_CHUNKS);
+        out.x = rf::add(out.x, __half2float(row[0])); out.y = rf::add(out.y, __half2float(row[1])); out.z = rf::add(out.z, __half2float(row[2]));
+        const __half vx = __float2half(px), vy = __float2half(py), vz = __float2half(pz);
+        const __half* F = reinterpret_cast<const __half*>(P.fourier2);
+#pragma unroll 2
+        for (int i = 0; i < NF; ++i) {
+            __half c = __hmul(vx, F[i]);
+            c = __hfma(vy, F[i + NF], c);
+            c = __hfma(vz, F[i + 2 * NF], c);
+            const __half adj_c = __hsub(__hmul(row[FOFF + NF + i], hcos(c)), __hmul(row[FOFF + i], hsin(c)));
+            out.x = rf::add(out.x, __half2float(__hmul(F[i], adj_c)));
+            out.y = rf::add(out.y, __half2float(__hmul(F[i + NF], adj_c)));
+            out.z = rf::add(out.z, __half2float(__hmul(F[i + 2 * NF], adj_c)));
+        }
+        __syncwarp();
+        return out;
     }
 };
 
@@ -356,7 +541,8 @@ __device__ __forceinline__ void exact_blend_normal(const DvrParams& D, float4 c,
     acc.w = rf::fma(om, a, acc.w);
 }
 
-template <int H16, int GC16 = 1, bool DIR = false>
+// ADJ: the instantiation that can run the adjoint pass (gradient_mode 2); it keeps the pre-activations of every forward pass
+template <int H16, int GC16 = 1, bool DIR = false, bool ADJ = false>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
 dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParams D) {
     using Net = SrnExact<H16, GC16, DIR>;
@@ -377,6 +563,8 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
 
     const uint32_t sblob_addr = smem_u32(sblob);
     const typename Net::Act ac = Net::make_act(P.activation, P.act_param);
+    const typename Net::AdjAct aa = Net::make_adj_act(P.act_param);
+    typename Net::Pre pre;
     const float3 bmin = make_float3(P.box_min[0], P.box_min[1], P.box_min[2]);
     const float3 bsize = make_float3(P.box_size[0], P.box_size[1], P.box_size[2]);
     const float tfrac = rf::sub(P.time_value, rf::floor(P.time_value));       // fracf(time), :596-597
@@ -421,7 +609,7 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
                 const float px = rf::div(rf::sub(wx, bmin.x), bsize.x), py = rf::div(rf::sub(wy, bmin.y), bsize.y),
                             pz = rf::div(rf::sub(wz, bmin.z), bsize.z);
                 __half o[4];
-                Net::forward(P, sblob_addr, stage, ac, px, py, pz, r.dir, tfrac, four, o);
+                Net::template forward<ADJ>(P, sblob_addr, stage, ac, px, py, pz, r.dir, tfrac, four, o, &pre);
                 float value = __half2float(o[0]);
                 if (sigm) value = exact_sigmoid(value);
                 steps += valid ? 1 : 0;
@@ -456,6 +644,10 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
                         const float h2 = rf::add(h, h);
                         g = make_float3(rf::div(rf::sub(d[0], d[1]), h2), rf::div(rf::sub(d[2], d[3]), h2), rf::div(rf::sub(d[4], d[5]), h2));
                     }
+                } else if (ADJ && P.gradient_mode == 2) {     // the backward pass through the network, :1199-1201
+                    if constexpr (ADJ) {
+                        if (any_shaded) g = Net::adjoint(P, sblob_addr, stage, aa, px, py, pz, tfrac, sigm, o[0], pre);
+                    }
                 } else if (four && any_shaded) {
                     g = make_float3(__half2float(o[1]), __half2float(o[2]), __half2float(o[3]));
                     if (P.output_mode == D_OUT_DENSITY_GRADIENT_CUBIC)
@@ -487,6 +679,7 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
 // Ground-truth density grid through the same marcher: VolumeInterpolationGrid::eval, texture path, trilinear
 // (renderer_volume_grid.cuh:110-139, 196-231) - what the reference renders its comparison images with. The reference traces
 // these rays per thread (KERNEL_SYNCHRONIZED_TRACING 0); operation order as in its compiled kernel.
+#ifndef FVSRN_EXACT_WITHOUT_GRID_KERNELS     // (the second translation unit of this header, inst_exact_adj.cu, leaves the non-template kernels out)
 __device__ __forceinline__ float grid_eval(const GridVolumeParams& G, float wx, float wy, float wz) {
     const float px = rf::mul(rf::div(rf::sub(wx, G.box_min[0]), G.box_size[0]), float(G.rx));
     const float py = rf::mul(rf::div(rf::sub(wy, G.box_min[1]), G.box_size[1]), float(G.ry));
@@ -547,5 +740,6 @@ __global__ void eval_grid_kernel(const __grid_constant__ GridVolumeParams G, con
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         out[i] = grid_eval(G, pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]);
 }
+#endif
 
 } // namespace fvsrn

@@ -38,6 +38,7 @@ cudaError_t launch_h6(int, int, int, const NetParams&, const void*, LaunchCfg*, 
 cudaError_t launch_h8(int, int, int, const NetParams&, const void*, LaunchCfg*, cudaStream_t);
 // reference-exact DVR kernel (kernels_exact.cuh, inst_exact.cu)
 cudaError_t launch_exact(int h16, int gc16, int dir, const NetParams& P, const DvrParams& D, LaunchCfg* cfg, cudaStream_t s);
+cudaError_t launch_exact_adjoint(int h16, int gc16, const NetParams& P, const DvrParams& D, LaunchCfg* cfg, cudaStream_t s);   // inst_exact_adj.cu
 // ground-truth density grid through the same marcher (kernels_exact.cuh dvr_grid_kernel / eval_grid_kernel)
 cudaError_t launch_dvr_grid(const GridVolumeParams& G, const DvrParams& D, int sm_count, cudaStream_t s);
 cudaError_t launch_eval_grid(const GridVolumeParams& G, const float* pos, float* out, long long n, cudaStream_t s);

@@ -69,6 +69,10 @@ struct NetParams {
     int gradient_mode;
     float fd_stepsize;
     int off_wlast_rows;   // mma.sync blob: last layer once more as [cin][8 outputs] fp16 rows (reference-exact fp16 chains)
+    // gradient_mode 2 (adjoint pass, kernels_exact.cuh): transposed weights as B fragments - hidden layers, the first H inputs of
+    // layer 0, its 16-channel latent groups (behind the regular blob; blob_bytes includes them in this mode); fd_stepsize then
+    // holds latentGridDifferencesStepSize
+    int off_adj_wh, off_adj_w0f, off_adj_w0g;
 };
 
 // filtered byte-grid value -> latent value (EncodeGridValue). fast = reference-exact mode: the reference's fast-math operation order.

@@ -339,7 +339,7 @@ class VolumeInterpolationNetwork:
     class GradientMode(_Enum): pass
     OFF_OR_DIRECT = GradientMode("OFF_OR_DIRECT", 0)             # no normals, or the ones a densitygrad* network predicts
     FINITE_DIFFERENCES = GradientMode("FINITE_DIFFERENCES", 1)   # 6 more SRN evaluations per shaded step
-    ADJOINT_METHOD = GradientMode("ADJOINT_METHOD", 2)           # not built on the B200 path (render raises)
+    ADJOINT_METHOD = GradientMode("ADJOINT_METHOD", 2)           # one backward pass through the network per shaded step
 
     def __init__(self):
         self._networks = []
@@ -347,12 +347,17 @@ class VolumeInterpolationNetwork:
         self.only_shared_memory = False   # kept for API compatibility; the B200 kernel always pins weights in smem
         self.gradient_mode = VolumeInterpolationNetwork.OFF_OR_DIRECT
         self.finite_differences_stepsize = 1.0 / 256.0     # volume_interpolation_network.cpp:1423
+        self.adjoint_latent_grid_central_differences_stepsize_scale = 4.0     # :1424, pybind :1997-2004
 
     def _apply_gradient_mode(self, net: "SceneNetwork"):
         """Pushes the module's gradient settings to the network handle (the reference passes them as defines / constants per render)."""
         gm = self.gradient_mode
         index = gm.index if isinstance(gm, _Enum) else {"OFF_OR_DIRECT": 0, "FINITE_DIFFERENCES": 1, "ADJOINT_METHOD": 2}[str(gm)]
-        check(_lib.lib().fvsrn_network_set_gradient_mode(net._h, index, float(self.finite_differences_stepsize)))
+        step = float(self.finite_differences_stepsize)
+        if index == 2:      # fillConstantMemory, :1809-1812: 1 / (float(gridResolution) * scale), computed in float
+            res = int(net._info().grid_x)
+            step = float(np.float32(1.0) / (np.float32(res) * np.float32(self.adjoint_latent_grid_central_differences_stepsize_scale))) if res > 0 else 0.0
+        check(_lib.lib().fvsrn_network_set_gradient_mode(net._h, index, step))
 
     def set_network(self, net: SceneNetwork):
         if net is None or not net.valid():
@@ -766,6 +771,8 @@ class ImageEvaluatorSimple:
         self.fixed_max_exposure = 1.0
         self.tonemapping_shoulder = 1.0
         self._last_frame: Optional[torch.Tensor] = None
+        self._refining_counter = 0
+        self.spp_log2 = 2                    # samplesPerIterationLog2_ (image_evaluator_simple.h): only iterative evaluators use it
         # B200 additions (all optional): screen-tile sharding, per-view times, statistics
         self.tile = None                     # (x0, y0, w, h)
         self.view_times = None               # list of absolute times, one per camera batch entry
@@ -817,6 +824,7 @@ class ImageEvaluatorSimple:
             self.last_counters = torch.zeros(2, dtype=torch.int64, device="cuda")
             p.step_count_dev = self.last_step_counts.data_ptr(); p.counters_dev = self.last_counters.data_ptr()
         check(_lib.lib().fvsrn_render_dvr_grid(v._h, C.byref(p), out.data_ptr(), _stream_ptr()))
+        self._refining_counter = 0
         if fmt == 0:
             self._last_frame = out
         return out
@@ -846,7 +854,36 @@ class ImageEvaluatorSimple:
             p.step_count_dev = self.last_step_counts.data_ptr(); p.counters_dev = self.last_counters.data_ptr()
         check(_lib.lib().fvsrn_render_dvr(net._h, C.byref(p), out.data_ptr(), _stream_ptr()))
         self._last_frame = out
+        self._refining_counter = 0
         return out
+
+    def refine(self, width: int, height: int, previous: torch.Tensor) -> torch.Tensor:
+        """IImageEvaluator.refine (iimage_evaluator.cpp:349-353 -> ImageEvaluatorSimple::render with refine = true,
+        image_evaluator_simple.cpp:288-356): render again and fold the frame into the running mean `previous` holds,
+        `previous + (frame - previous) / n` with n counted since the last render(). DVR draws no random numbers
+        (is_iterative_refining() is False), so every frame equals the first; the bookkeeping is the reference's."""
+        if previous is None or tuple(previous.shape) != (self.camera.get_parameters().shape[0], 8, height, width):
+            raise RuntimeError("refine: `previous` must be the (B,8,H,W) tensor of the preceding render / refine call")
+        counter = self._refining_counter
+        frame = self.render(width, height)      # resets the counter, as a non-refining render does
+        self._refining_counter = counter + 1
+        out = previous + (frame - previous) * (1.0 / self._refining_counter)
+        self._last_frame = out
+        return out
+
+    def is_iterative_refining(self) -> bool:
+        return False                            # RayEvaluationSteppingDvr, ray_evaluation.h: only the Monte-Carlo evaluator refines
+
+    def compute_batch_count(self) -> int:
+        """IImageEvaluator::computeBatchCount (iimage_evaluator.cpp:138-165): the common batch size of camera and TF."""
+        b = self.camera.get_parameters().shape[0]
+        tf = self.ray_evaluator.tf
+        if tf is not None and tf.kind != 2 and getattr(tf, "tensor", None) is not None and tf.tensor.value is not None:
+            tb = tf.tensor.value.shape[0]
+            if tb > 1 and b > 1 and tb != b:
+                raise RuntimeError(f"Batch counts don't match. Module camera has {b} batches, but the current module tf has {tb} batches")
+            b = max(b, tb)
+        return b
 
     # -- colour extraction (IImageEvaluator::ExtractColor, iimage_evaluator.cpp:26-135)
     @property
@@ -935,7 +972,7 @@ def load_from_json(filename: str) -> ImageEvaluatorSimple:
     ie = ImageEvaluatorSimple()
     e = plan["evaluator"]
     ie.selected_channel = (IImageEvaluator.Mask, IImageEvaluator.Normal, IImageEvaluator.Depth, IImageEvaluator.Color)[e["channel"]]
-    ie.samples_per_iteration_log2 = e["samples_per_iteration_log2"]          # progressive refinement of the GUI; render() is one pass
+    ie.spp_log2 = e["samples_per_iteration_log2"]
     ie.use_tonemapping, ie.tonemapping_shoulder = e["use_tonemapping"], e["tonemapping_shoulder"]
     ie.fix_max_exposure, ie.fixed_max_exposure = e["fix_max_exposure"], e["fixed_max_exposure"]
     c = plan["camera"]

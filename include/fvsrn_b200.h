@@ -49,8 +49,12 @@ enum fvsrn_output_mode {
 /* SceneNetwork::GradientMode, volume_interpolation_network.h / renderer_volume_tensorcores.cuh:132-134, 1166-1203 */
 enum fvsrn_gradient_mode {
     FVSRN_GRADIENT_OFF_OR_DIRECT = 0,       /* no normals, or the ones the network predicts (densitygrad* / densitycurvature*) */
-    FVSRN_GRADIENT_FINITE_DIFFERENCES = 1   /* central differences: 6 more SRN evaluations per shaded step */
-    /* 2 = ADJOINT_METHOD (backward pass through the SRN, :1205-1555) is not built: finite differences cover its use */
+    FVSRN_GRADIENT_FINITE_DIFFERENCES = 1,  /* central differences: 6 more SRN evaluations per shaded step */
+    /* the backward pass through the SRN (:1205-1530): d density / d position from one more pass with transposed weights,
+     * the latent grid differentiated by central differences of its texture (step 1 / (4 * grid resolution) by default).
+     * Runs in the reference-arithmetic kernel family whichever kernel mode is selected; density / densitygrad* networks
+     * without direction input, float latent grids. */
+    FVSRN_GRADIENT_ADJOINT_METHOD = 2
 };
 /* BRDFLambert::LightType as the kernel sees it, renderer_brdf_lambert.cuh:6-7 */
 enum fvsrn_light_type { FVSRN_LIGHT_POINT = 0, FVSRN_LIGHT_DIRECTIONAL = 1 };
@@ -116,7 +120,10 @@ int  fvsrn_network_num_parameters(const fvsrn_network* net);                    
 int  fvsrn_network_compute_max_warps(const fvsrn_network* net, int only_shared, int adjoint); /* :987-1041 */
 int  fvsrn_network_set_time_and_ensemble(fvsrn_network* net, float time, int ensemble);       /* :923-938 */
 /* VolumeInterpolationNetwork::{gradient_mode, finite_differences_stepsize} (volume_interpolation_network.cpp:1976-1995):
- * how the DVR frame obtains normals; stepsize in world units (reference default 1/256). Density-type networks only. */
+ * how the DVR frame obtains normals; stepsize in world units (reference default 1/256). Density-type networks only.
+ * With FVSRN_GRADIENT_ADJOINT_METHOD the third argument is the central-difference step through the latent grid in normalised
+ * grid coordinates, i.e. 1 / (resolution * adjoint_latent_grid_central_differences_stepsize_scale) of the reference (:1809-1812);
+ * <= 0 selects the reference default 1 / (resolution * 4). */
 int  fvsrn_network_set_gradient_mode(fvsrn_network* net, int gradient_mode, float finite_differences_stepsize);
 
 /* Introspection (what a binding needs to expose .input/.output/.latent_grid read-only) */

@@ -216,6 +216,12 @@ CONFIGS = {
     # VolumeInterpolationTensorcores does not have. Their batch query does: see the *_rgbo_eval build below.)
     "h32x4_relu_fd_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=256, gradient_mode=1,
                                 brdf=("magnitude", "phong"), light_type=0, steps_variant=False),
+    # GRADIENT_MODE 2: the adjoint pass through the network (renderer_volume_tensorcores.cuh:1205-1530); BLOCK_SIZE 128 because
+    # its activation storage needs (NUM_HIDDEN_LAYERS + 1) * BLOCK_SIZE * HIDDEN_CHANNELS halves more shared memory
+    "h32x4_relu_adjoint_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=128, gradient_mode=2,
+                                     brdf=("magnitude", "phong"), light_type=1, steps_variant=False),
+    "h32x4_snakealt_adjoint_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="SnakeAlt", output_mode=0, block_size=128, gradient_mode=2,
+                                         brdf=("magnitude", "phong"), light_type=0, steps_variant=False),
 }
 # (time-interpolated grids, C5, need no build of their own: cLatentGridB != A and cLatentGridInterpolation = t are
 # constants of the same h32x4 kernels, renderer_volume_tensorcores.cuh:590-604)

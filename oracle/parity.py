@@ -19,7 +19,7 @@ def psnr(a, b):
 
 
 def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0, time=None, tile=None, spp=1,
-                fd_stepsize=None, brdf=None, blend=None, early_out=None, density_range=None):
+                fd_stepsize=None, brdf=None, blend=None, early_out=None, density_range=None, adjoint=False):
     """One frame through the product path (pyrenderer mirror -> C ABI) -> (img (B,8,H,W) numpy, steps (B,H,W) numpy).
     fd_stepsize: finite-difference normals with that step; brdf: dict as ref_kernel.ReferenceDvrKernel.render takes it plus
     "flags" (subset of "magnitude", "phong") and "light_type" (0 point / 1 directional)."""
@@ -43,6 +43,8 @@ def render_ours(net_bytes, mode, width, height, camera, tf, stepsize, tf_kind=0,
     if fd_stepsize is not None:
         vol.gradient_mode = pr.VolumeInterpolationNetwork.FINITE_DIFFERENCES
         vol.finite_differences_stepsize = fd_stepsize
+    if adjoint:             # GRADIENT_MODE 2: backward pass through the network, latent-grid step 1 / (4 * resolution)
+        vol.gradient_mode = pr.VolumeInterpolationNetwork.ADJOINT_METHOD
     if brdf is not None:
         b = ie.ray_evaluator.brdf
         b.enable_magnitude_scaling, b.enable_phong = "magnitude" in brdf["flags"], "phong" in brdf["flags"]

@@ -200,8 +200,14 @@ class ReferenceDvrKernel:
         add(np.array((0, 0, 0) if unit_box else net.box_min, np.float32).tobytes())
         add(np.array((1, 1, 1) if unit_box else net.box_size, np.float32).tobytes())
         add(np.array([net.layers[0].activation_param], np.float32).tobytes())
-        add(np.array([self.fd_stepsize], np.float32).tobytes())                         # finiteDifferencesStepsize (GRADIENT_MODE 1)
-        add(np.array([0.01], np.float32).tobytes())                                     # latentGridDifferencesStepSize (unused)
+        if self.meta.get("gradient_mode", 0) == 2:
+            # VolumeInterpolationNetwork::fillConstantMemory (volume_interpolation_network.cpp:1809-1812): in adjoint mode both slots
+            # get 1 / (float(gridResolution) * adjointLatentGridCentralDifferencesStepsizeScale_), scale 4 (:1424)
+            step = np.float32(1.0) / (np.float32(gA.values.shape[-1]) * np.float32(4.0))
+            add(np.array([step], np.float32).tobytes()); add(np.array([step], np.float32).tobytes())
+        else:
+            add(np.array([self.fd_stepsize], np.float32).tobytes())                     # finiteDifferencesStepsize (GRADIENT_MODE 1)
+            add(np.array([0.01], np.float32).tobytes())                                 # latentGridDifferencesStepSize (unused)
         _pad32(b)
         dptr, size = self.g_vol
         if H == 32 and nf == 14 and gA.encoding == 0 and net.layers[-1].cout == 1 and net.latent_channels() == 16:

@@ -29,6 +29,12 @@ CASES = {
     "densitygrad_cubic_phong_directional": (dict(C3, output_mode="densitygrad:cubic", last_gain=6.0), "h32x4_relu_densgrad_cubic_phong", None, PHONG_DIR_CUBIC),
     "finite_differences_phong_point": (dict(C3, output_mode="density:direct", last_gain=6.0), "h32x4_relu_fd_phong", 1.0 / 128.0, PHONG_POINT),
 }
+# GRADIENT_MODE 2: the adjoint pass through the network (renderer_volume_tensorcores.cuh:1205-1530). ReLU / density:direct and
+# SnakeAlt / density (sigmoid output: its adjoint runs in double, renderer_activations.cuh:204-209)
+ADJOINT_CASES = {
+    "adjoint_relu_phong_directional": (dict(C3, output_mode="density:direct", last_gain=6.0), "h32x4_relu_adjoint_phong", PHONG_DIR),
+    "adjoint_snakealt_sigmoid_phong_point": (dict(C3, activation="SnakeAlt", output_mode="density", last_gain=6.0), "h32x4_snakealt_adjoint_phong", PHONG_POINT),
+}
 SIZE, STEP = 512, 1 / 256
 
 
@@ -94,8 +100,56 @@ def test_fast_modes_with_normals(ref, name, plume_tf):
             assert row["normal_max_abs"] <= 1e-2 and row["normal_mean_abs"] <= 1e-4, row
 
 
+def _adjoint_frames(name, plume_tf, modes, size=SIZE):
+    import parity
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import scenes, volnet
+    kw, variant, brdf = ADJOINT_CASES[name]
+    net = scenes.make_network(**kw)
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    want, _, _ = parity.render_reference(net, size, size, cam, scenes.DEFAULT_FOV_Y, plume_tf, STEP, variant=variant, brdf=brdf)
+    data = volnet.dumps(net)
+    got = {m: parity.render_ours(data, m, size, size, cam, plume_tf, STEP, brdf=brdf, adjoint=(m != "finite_differences"),
+                                 fd_stepsize=(1.0 / 256.0 if m == "finite_differences" else None))[0]
+           for m in modes}
+    return want, got
+
+
+@pytest.mark.parametrize("name", list(ADJOINT_CASES))
+def test_adjoint_gradient_mode_is_bit_identical_to_the_reference_kernel(ref, name, plume_tf):
+    """Frames in adjoint gradient mode run in the reference-arithmetic kernel family whichever kernel mode is selected: all 8
+    channels bit-identical to the reference kernel built with GRADIENT_MODE 2."""
+    want, got = _adjoint_frames(name, plume_tf, ["reference_exact", "tcgen05"])
+    assert want[:, 3].max() > 0.1 and np.abs(want[:, 4:7]).max() > 0.02
+    for mode, img in got.items():
+        for c, label in enumerate(("r", "g", "b", "alpha", "normal x", "normal y", "normal z", "depth")):
+            same = (img[:, c] == want[:, c]) | (np.isnan(img[:, c]) & np.isnan(want[:, c]))
+            assert same.all(), (name, mode, label, int((~same).sum()), float(np.nanmax(np.abs(img[:, c] - want[:, c]))))
+
+
+def test_adjoint_normals_agree_with_finite_differences(plume_tf):
+    """The two ways to the same gradient (no reference needed): the adjoint pass and central differences of the same network
+    shade the frame alike - PSNR of the shaded colour >= 35 dB, mean normal difference small. (They are not equal: fp16 noise in
+    the differences, the latent grid differentiated with a coarse step in the adjoint, and the adjoint is the gradient in unit-box
+    coordinates.)"""
+    import parity
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import scenes, volnet
+    kw, _, brdf = ADJOINT_CASES["adjoint_relu_phong_directional"]
+    net = scenes.make_network(**kw)
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    data = volnet.dumps(net)
+    a = parity.render_ours(data, "mma_sync", 256, 256, cam, plume_tf, STEP, brdf=brdf, adjoint=True)[0]
+    f = parity.render_ours(data, "mma_sync", 256, 256, cam, plume_tf, STEP, brdf=brdf, fd_stepsize=1.0 / 256.0)[0]
+    assert np.abs(a[:, 4:7]).max() > 0.02
+    row = dict(config="adjoint_vs_fd", psnr_db=float(parity.psnr(a[:, :4], f[:, :4])), normal_mean_abs=float(np.abs(a[:, 4:7] - f[:, 4:7]).mean()),
+               normal_max_abs=float(np.abs(a[:, 4:7] - f[:, 4:7]).max()))
+    _record(row)
+    assert row["psnr_db"] >= 35.0 and row["normal_mean_abs"] <= 2e-2, row
+
+
 def test_gradient_mode_errors(plume_tf):
-    """adjoint mode is rejected, colour networks have no normals, BRDF flags are validated."""
+    """colour networks have no normals, adjoint mode refuses what the reference's adjoint does not define, BRDF flags are validated."""
     import torch
     import fvsrn_b200  # noqa: F401
     from fvsrn_b200 import pyrenderer as pr, scenes, volnet
@@ -107,8 +161,15 @@ def test_gradient_mode_errors(plume_tf):
     with pytest.raises(RuntimeError, match="density network"):
         ie.render(64, 64)
     vol.gradient_mode = pr.VolumeInterpolationNetwork.ADJOINT_METHOD
-    with pytest.raises(RuntimeError, match="adjoint"):
+    with pytest.raises(RuntimeError, match="density network"):
         ie.render(64, 64)
+    sd = pr.SceneNetwork.from_bytes(volnet.dumps(scenes.make_network(**dict(C3, has_direction=True))))
+    vd = pr.VolumeInterpolationNetwork(); vd.set_network(sd); vd.gradient_mode = pr.VolumeInterpolationNetwork.ADJOINT_METHOD
+    ie.volume = vd
+    ie.ray_evaluator.tf.tensor.value = torch.from_numpy(plume_tf).cuda()
+    with pytest.raises(RuntimeError, match="direction input"):
+        ie.render(64, 64)
+    ie.volume = vol
     vol.gradient_mode = pr.VolumeInterpolationNetwork.OFF_OR_DIRECT
     ie.ray_evaluator.brdf.enable_phong = True
     with pytest.raises(RuntimeError, match="normals"):

@@ -112,3 +112,31 @@ def test_load_from_json_with_texture_tf_identity_tf_and_srn_volume(scene_dir, pl
         ie.render(32, 32)
     with pytest.raises(RuntimeError, match="not part of the B200 path"):
         pr.load_from_json(_write(root / "configs" / "gauss.json", _settings_dict(RayEvaluation__DVR__selectedTF="Gaussian")))
+
+
+def test_refine_folds_frames_into_a_running_mean(scene_dir):
+    """IImageEvaluator.refine (image_evaluator_simple.cpp:288-356): n-th refinement = previous + (frame - previous) / n; DVR frames are
+    deterministic, so the mean stays the first frame (to fp32 rounding) and the counter restarts with render()."""
+    import torch
+    from fvsrn_b200 import pyrenderer as pr
+    root, vol = scene_dir
+    ie = pr.load_from_json(_write(root / "configs" / "scene.json", _settings_dict(RayEvaluation__DVR__stepsize=1.0)))
+    first = ie.render(96, 64)
+    assert not ie.is_iterative_refining() and ie.compute_batch_count() == 1 and ie.spp_log2 == 3
+    prev = torch.nan_to_num(first, nan=0.0) * 0.5           # a different "previous" shows the weights: 1/1, then 1/2, 1/3
+    r1 = ie.refine(96, 64, prev)
+    torch.testing.assert_close(torch.nan_to_num(r1, nan=0.0), prev + (torch.nan_to_num(first, nan=0.0) - prev), rtol=0, atol=1e-6)
+    r2 = ie.refine(96, 64, prev)
+    f = torch.nan_to_num(first, nan=0.0)
+    torch.testing.assert_close(torch.nan_to_num(r2, nan=0.0), prev + (f - prev) * 0.5, rtol=0, atol=1e-6)
+    ie.render(96, 64)
+    r3 = ie.refine(96, 64, prev)
+    torch.testing.assert_close(torch.nan_to_num(r3, nan=0.0), f, rtol=0, atol=1e-6)
+    with pytest.raises(RuntimeError, match="previous"):
+        ie.refine(96, 64, prev[:, :4])
+    cams = torch.from_numpy(np.concatenate([np.asarray(ie.camera.get_parameters().cpu())] * 3, 0)).cuda()
+    ie.camera.set_parameters(cams)
+    assert ie.compute_batch_count() == 3
+    ie.ray_evaluator.tf.tensor.value = torch.cat([ie.ray_evaluator.tf.tensor.value] * 2, 0)
+    with pytest.raises(RuntimeError, match="Batch counts don't match"):
+        ie.compute_batch_count()
