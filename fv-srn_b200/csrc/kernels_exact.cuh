@@ -646,6 +646,8 @@ dvr_exact_kernel(const __grid_constant__ NetParams P, const __grid_constant__ Dv
                     }
                 } else if (ADJ && P.gradient_mode == 2) {     // the backward pass through the network, :1199-1201
                     if constexpr (ADJ) {
+                        // (measured: repeating the forward pass on shaded steps only, instead of keeping the pre-activations of
+                        // every step, is slower - 133.6 vs 112.8 ms per C3 frame: nearly every step of a warp shades something)
                         if (any_shaded) g = Net::adjoint(P, sblob_addr, stage, aa, px, py, pz, tfrac, sigm, o[0], pre);
                     }
                 } else if (four && any_shaded) {

@@ -220,6 +220,13 @@ CONFIGS = {
     # its activation storage needs (NUM_HIDDEN_LAYERS + 1) * BLOCK_SIZE * HIDDEN_CHANNELS halves more shared memory
     "h32x4_relu_adjoint_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=128, gradient_mode=2,
                                      brdf=("magnitude", "phong"), light_type=1, steps_variant=False),
+    "h32x4_relu_densgrad_adjoint": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=4, block_size=128, gradient_mode=2,
+                                        brdf=("magnitude", "phong"), light_type=1, steps_variant=False),
+    "h32x4_sine_adjoint": dict(hidden16=2, num_hidden=2, nf=14, activation="Sine", output_mode=1, block_size=128, gradient_mode=2, steps_variant=False),
+    "h32x4_snake_adjoint": dict(hidden16=2, num_hidden=2, nf=14, activation="Snake", output_mode=1, block_size=128, gradient_mode=2, steps_variant=False),
+    "h32x4_relu_grid32_adjoint": dict(hidden16=2, num_hidden=2, nf=14, activation="ReLU", output_mode=1, block_size=128, gradient_mode=2, grid16=2,
+                                      steps_variant=False),
+    "h48x4_relu_adjoint": dict(hidden16=3, num_hidden=2, nf=22, activation="ReLU", output_mode=1, block_size=64, gradient_mode=2, steps_variant=False),
     "h32x4_snakealt_adjoint_phong": dict(hidden16=2, num_hidden=2, nf=14, activation="SnakeAlt", output_mode=0, block_size=128, gradient_mode=2,
                                          brdf=("magnitude", "phong"), light_type=0, steps_variant=False),
 }

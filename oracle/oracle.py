@@ -153,6 +153,18 @@ def evaluate(net, positions, directions=None, time=0.0, ensemble=0, fp32=False, 
     return out[:, :1].copy() if on.c.output_mode >= 4 else out
 
 
+def adjoint_gradient(net, positions, time=0.0, ensemble=0, tex_filter=False, latent_step=None):
+    """_evalNormalAdjoint restated on the CPU (fvsrn_oracle.c adjoint_h): positions (N,3) in the unit box -> d density / d position (N,3)
+    in unit-box coordinates. latent_step: central-difference step through the latent grid, default 1 / (4 * resolution)."""
+    on = OracleNetwork(net, time, ensemble, unit_box=True, tex_filter=tex_filter, acc32=False)
+    pos = np.ascontiguousarray(positions, dtype=np.float32)
+    h = float(np.float32(1.0) / (np.float32(on.c.gx) * np.float32(4.0))) if latent_step is None else float(latent_step)
+    out = np.zeros((pos.shape[0], 3), np.float32)
+    lib().oracle_adjoint_gradient.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_int64]
+    lib().oracle_adjoint_gradient(C.byref(on.c), pos.ctypes.data, h, out.ctypes.data, pos.shape[0])
+    return out
+
+
 def features(net, positions, time=0.0, ensemble=0, tex_filter=False, acc32=False):
     on = OracleNetwork(net, time, ensemble, unit_box=True, tex_filter=tex_filter, acc32=acc32)
     pos = np.ascontiguousarray(positions, dtype=np.float32)
@@ -164,7 +176,7 @@ def features(net, positions, time=0.0, ensemble=0, tex_filter=False, acc32=False
 
 def render_dvr(net, *, width, height, camera, fov_y, stepsize, tf, tf_kind=0, alpha_early_out=1 - 1e-5,
                density_min=0.0, density_max=1.0, early_out=True, blend_mode=1, spp=1, time=0.0, ensemble=0,
-               tile=None, fp32=False, tex_filter=False, acc32=False, fd_stepsize=None, brdf=None):
+               tile=None, fp32=False, tex_filter=False, acc32=False, fd_stepsize=None, brdf=None, adjoint=False):
     """ImageEvaluatorSimple::render restated on the CPU -> (img (B,8,H,W) f32, steps (B,H,W) i32, valid_samples).
     fd_stepsize: finite-difference normals (GRADIENT_MODE 1); brdf: dict(flags=("magnitude","phong"), light_type, light,
     magnitude_scaling, ambient, specular, magnitude_center, magnitude_radius, specular_exponent) = BRDFLambert."""
@@ -180,6 +192,8 @@ def render_dvr(net, *, width, height, camera, fov_y, stepsize, tf, tf_kind=0, al
     d.early_out, d.blend_mode, d.spp, d.fp32_mode = int(early_out), blend_mode, spp, int(fp32)
     if fd_stepsize is not None:
         d.gradient_mode, d.fd_stepsize = 1, fd_stepsize
+    if adjoint:     # GRADIENT_MODE 2; the step through the latent grid is 1 / (4 * resolution) (volume_interpolation_network.cpp:1424, 1809-1812)
+        d.gradient_mode, d.fd_stepsize = 2, float(np.float32(1.0) / (np.float32(on.c.gx) * np.float32(4.0)))
     if brdf is not None:
         d.brdf_flags = (1 if "magnitude" in brdf["flags"] else 0) | (2 if "phong" in brdf["flags"] else 0)
         d.light_type = brdf["light_type"]; d.light = (C.c_float * 3)(*brdf["light"])

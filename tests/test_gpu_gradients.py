@@ -34,6 +34,12 @@ CASES = {
 ADJOINT_CASES = {
     "adjoint_relu_phong_directional": (dict(C3, output_mode="density:direct", last_gain=6.0), "h32x4_relu_adjoint_phong", PHONG_DIR),
     "adjoint_snakealt_sigmoid_phong_point": (dict(C3, activation="SnakeAlt", output_mode="density", last_gain=6.0), "h32x4_snakealt_adjoint_phong", PHONG_POINT),
+    # a network that also predicts a gradient: the adjoint differentiates its density output (sWeightsLast[2 * cin].x, :1256-1261)
+    "adjoint_densitygrad_phong": (dict(C3, output_mode="densitygrad", last_gain=6.0), "h32x4_relu_densgrad_adjoint", PHONG_DIR),
+    "adjoint_sine": (dict(C3, activation="Sine:1.5", last_gain=1.5, last_bias=-0.35), "h32x4_sine_adjoint", None),
+    "adjoint_snake": (dict(C3, activation="Snake:2", last_gain=2.5, last_bias=-0.3), "h32x4_snake_adjoint", None),
+    "adjoint_32_latent_channels": (dict(C3, grid_channels=32, last_gain=6.0), "h32x4_relu_grid32_adjoint", None),
+    "adjoint_width_48": (dict(hidden=48, num_layers=4, grid_res=32, seed=42, activation="ReLU", fourier="gauss", last_gain=6.0, last_bias=0.05), "h48x4_relu_adjoint", None),
 }
 SIZE, STEP = 512, 1 / 256
 
@@ -125,6 +131,43 @@ def test_adjoint_gradient_mode_is_bit_identical_to_the_reference_kernel(ref, nam
         for c, label in enumerate(("r", "g", "b", "alpha", "normal x", "normal y", "normal z", "depth")):
             same = (img[:, c] == want[:, c]) | (np.isnan(img[:, c]) & np.isnan(want[:, c]))
             assert same.all(), (name, mode, label, int((~same).sum()), float(np.nanmax(np.abs(img[:, c] - want[:, c]))))
+
+
+def test_adjoint_through_time_interpolated_keyframes(ref, plume_tf):
+    """Between two keyframes the adjoint differentiates the time-interpolated texel (lerp of both grids' central differences,
+    :662-676): bit-identical to the reference kernel at time 1.37 of a 4-keyframe network."""
+    import parity
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import scenes, volnet
+    net = scenes.make_network(**dict(C3, output_mode="density:direct", last_gain=6.0, time_keyframes=4))
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    want, _, _ = parity.render_reference(net, 256, 256, cam, scenes.DEFAULT_FOV_Y, plume_tf, STEP, variant="h32x4_relu_adjoint_phong", brdf=PHONG_DIR, time=1.37)
+    img = parity.render_ours(volnet.dumps(net), "reference_exact", 256, 256, cam, plume_tf, STEP, brdf=PHONG_DIR, adjoint=True, time=1.37)[0]
+    assert want[:, 3].max() > 0.1 and np.abs(want[:, 4:7]).max() > 0.02
+    assert np.array_equal(np.nan_to_num(img, nan=-7.0), np.nan_to_num(want, nan=-7.0))
+
+
+def test_adjoint_frame_against_the_cpu_oracle(plume_tf):
+    """The adjoint frame of the product path against the CPU restatement of the reference's adjoint (oracle/fvsrn_oracle.c adjoint_h)
+    - no reference build needed (this is the check __graft_entry__.smoke() style boxes can run). The oracle's libm cos / sin and
+    exact central-difference samples differ from the kernel's hcos / hsin and fp32-texture fetches in the last fp16 bits, and the
+    Phong term (exponent 8) of a 1/64 step carries a whole sample's weight: RGBA within 5e-3 (measured 2.9e-3), blended normals
+    within 2e-2 max-abs / 5e-4 mean-abs (measured 4.7e-3 / 1.2e-5). The bit-exact pin of this mode is the reference-kernel test above."""
+    import oracle
+    import parity
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import scenes, volnet
+    net = scenes.make_network(**dict(C3, output_mode="density:direct", last_gain=6.0))
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    W = 64
+    want, _, _ = oracle.render_dvr(net, width=W, height=W, camera=cam, fov_y=scenes.DEFAULT_FOV_Y, stepsize=1 / 64, tf=plume_tf, adjoint=True, brdf=PHONG_DIR,
+                                   tex_filter=True)
+    img = parity.render_ours(volnet.dumps(net), "reference_exact", W, W, cam, plume_tf, 1 / 64, brdf=PHONG_DIR, adjoint=True)[0]
+    d = np.abs(img[:, :4] - want[:, :4]); dn = np.abs(img[:, 4:7] - want[:, 4:7])
+    row = dict(config="adjoint_vs_cpu_oracle", rgba_max_abs=float(d.max()), normal_max_abs=float(dn.max()), normal_mean_abs=float(dn.mean()))
+    _record(row)
+    assert np.abs(want[:, 4:7]).max() > 0.02
+    assert row["rgba_max_abs"] <= 5e-3 and row["normal_max_abs"] <= 2e-2 and row["normal_mean_abs"] <= 5e-4, row
 
 
 def test_adjoint_normals_agree_with_finite_differences(plume_tf):
