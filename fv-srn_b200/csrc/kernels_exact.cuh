@@ -29,6 +29,13 @@
 
 namespace fvsrn {
 
+// hcos / hsin of cuda_fp16.hpp (range reduction + polynomial + the special-case fix-ups, ~40 instructions each) as out-of-line
+// functions: inlined at each of their ~100 call sites they made the kernels 150 KB of code and the march instruction-fetch bound
+// (ncu r02n: stall no_instruction 14.7 per issue). Same instructions, same results.
+static __device__ __noinline__ __half exact_hcos(__half x) { return hcos(x); }
+static __device__ __noinline__ __half exact_hsin(__half x) { return hsin(x); }
+static __device__ __noinline__ float exact_erfinv(float x) { return erfinvf(x); }     // byte-gaussian grids: 32 call sites per latent group
+
 template <int H16, int GC16 = 1, bool DIR = false>
 struct SrnExact {
     using Core = Srn<H16, GC16, DIR>;
@@ -49,9 +56,9 @@ struct SrnExact {
     }
     static __device__ __forceinline__ __half act1(int act, const Act& a, __half v) {
         if (act == D_ACT_RELU) return __float2half(rf::fmax(0.f, __half2float(v)));          // :46
-        if (act == D_ACT_SINE) return hsin(__hmul(v, a.p));                                   // :103
-        if (act == D_ACT_SNAKE) { const __half s = hsin(__hmul(a.p, v)); return __hadd(v, __hmul(a.q, __hmul(s, s))); }   // :266-269
-        if (act == D_ACT_SNAKEALT) { const __half x0 = hcos(__hmul(a.q, v)); return __hdiv(__hsub(__hadd(v, a.one), x0), a.q); }  // :333-337
+        if (act == D_ACT_SINE) return exact_hsin(__hmul(v, a.p));                                   // :103
+        if (act == D_ACT_SNAKE) { const __half s = exact_hsin(__hmul(a.p, v)); return __hadd(v, __hmul(a.q, __hmul(s, s))); }   // :266-269
+        if (act == D_ACT_SNAKEALT) { const __half x0 = exact_hcos(__hmul(a.q, v)); return __hdiv(__hsub(__hadd(v, a.one), x0), a.q); }  // :333-337
         return v;
     }
     static __device__ __forceinline__ void activate(uint32_t (&r)[2][NT][2], int act, const Act& a) {
@@ -119,7 +126,7 @@ struct SrnExact {
                 c = __hfma(dy, F[i + 4 * NF], c);
                 c = __hfma(dz, F[i + 5 * NF], c);
             }
-            cs[i] = hcos(c); sn[i] = hsin(c);
+            cs[i] = exact_hcos(c); sn[i] = exact_hsin(c);
         }
 #pragma unroll
         for (int i = 0; i < NF; i += 2) {
@@ -136,8 +143,8 @@ struct SrnExact {
                 for (int k = 0; k < 4; ++k) {
                     float ta = pa[k], tb = pb[k];
                     if (P.grid_encoding == 2) {
-                        ta = rf::mul(1.4142135623730951f, erfinvf(rf::mul(rf::add(ta, -0.5f), 2.0f - 1e-4f)));
-                        tb = rf::mul(1.4142135623730951f, erfinvf(rf::mul(rf::add(tb, -0.5f), 2.0f - 1e-4f)));
+                        ta = rf::mul(1.4142135623730951f, exact_erfinv(rf::mul(rf::add(ta, -0.5f), 2.0f - 1e-4f)));
+                        tb = rf::mul(1.4142135623730951f, exact_erfinv(rf::mul(rf::add(tb, -0.5f), 2.0f - 1e-4f)));
                     }
                     pa[k] = rf::fma(ta, P.enc_scale_a[4 * q + k], P.enc_offset_a[4 * q + k]);
                     pb[k] = rf::fma(tb, P.enc_scale_a[4 * q + k], P.enc_offset_a[4 * q + k]);
@@ -256,9 +263,9 @@ struct SrnExact {
     // ACTIVATION::adjoint(x, zAdj) of the half overloads, the __CUDA_ARCH__ < 800 branches (the reference builds for compute_75)
     static __device__ __forceinline__ __half act_adj1(int act, const AdjAct& a, __half x, __half z) {
         if (act == D_ACT_RELU) return __half2float(x) > 0.f ? z : __float2half(0.f);                         // :66-73
-        if (act == D_ACT_SINE) return __hmul(z, __hmul(a.p, hcos(__hmul(x, a.p))));                         // :123-127
-        if (act == D_ACT_SNAKE) return __hmul(z, __hadd(a.one, hsin(__hmul(a.q2, x))));                     // :295-300
-        if (act == D_ACT_SNAKEALT) return __hmul(z, __hadd(hsin(__hmul(a.q2, x)), a.inv_q2));               // :366-371
+        if (act == D_ACT_SINE) return __hmul(z, __hmul(a.p, exact_hcos(__hmul(x, a.p))));                         // :123-127
+        if (act == D_ACT_SNAKE) return __hmul(z, __hadd(a.one, exact_hsin(__hmul(a.q2, x))));                     // :295-300
+        if (act == D_ACT_SNAKEALT) return __hmul(z, __hadd(exact_hsin(__hmul(a.q2, x)), a.inv_q2));               // :366-371
         return z;
     }
     static __device__ __forceinline__ void act_adjoint(uint32_t (&z)[2][NT][2], const uint32_t (&x)[2][NT][2], int act, const AdjAct& a) {
@@ -387,7 +394,10 @@ struct SrnExact {
             __half c = __hmul(vx, F[i]);
             c = __hfma(vy, F[i + NF], c);
             c = __hfma(vz, F[i + 2 * NF], c);
-            const __half adj_c = __hsub(__hmul(row[FOFF + NF + i], hcos(c)), __hmul(row[FOFF + i], hsin(c)));
+            // hsub(hmul(adjSin, hcos(c)), hmul(adjCos, hsin(c))) in the source (:1486-1495); cuda_fp16.hpp's mul.f16 / sub.f16 carry no
+            // rounding modifier, and the reference's compiled kernel fuses the first product into the subtraction (SASS of the reference
+            // PTX: HMUL2 t = adjCos * sin; HFMA2 adjSin * cos - t) - written out here so that it does not depend on this file's inlining
+            const __half adj_c = __hfma(row[FOFF + NF + i], exact_hcos(c), __hneg(__hmul_rn(row[FOFF + i], exact_hsin(c))));
             out.x = rf::add(out.x, __half2float(__hmul(F[i], adj_c)));
             out.y = rf::add(out.y, __half2float(__hmul(F[i + NF], adj_c)));
             out.z = rf::add(out.z, __half2float(__hmul(F[i + 2 * NF], adj_c)));
