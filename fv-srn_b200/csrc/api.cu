@@ -363,7 +363,7 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
             P.time_value = t;
             const DeviceGrid& A = h->d_time[lo]; const DeviceGrid& B = h->d_time[hi];
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
-            const bool exact = (h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT || h->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD) && !A.tex32.empty() && !B.tex32.empty();
+            const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && !A.tex32.empty() && !B.tex32.empty();
             for (int i = 0; i < A.C / 16; ++i, ++g) {
                 P.groups[g] = GridGroup{grid_ptr(A, i), grid_ptr(B, i), frac, A.encoding ? A.C / 16 : A.C * 2 / 16};
                 fill_encoding(P, g, A, B, i);
@@ -376,7 +376,7 @@ NetParams make_net_params(const fvsrn_network* h, float time_abs, int ensemble, 
         if (!h->d_ens.empty()) {
             const DeviceGrid& A = h->d_ens[n.interpolate_ensemble(ensemble)];
             P.gx = A.X; P.gy = A.Y; P.gz = A.Z;
-            const bool exact = (h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT || h->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD) && !A.tex32.empty();
+            const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && !A.tex32.empty();
             for (int i = 0; i < A.C / 16; ++i, ++g) {
                 P.groups[g] = GridGroup{grid_ptr(A, i), grid_ptr(A, i), 0.f, A.encoding ? A.C / 16 : A.C * 2 / 16};
                 fill_encoding(P, g, A, A, i);
@@ -982,19 +982,20 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
     if (h->gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT && is_rgbo) throw std::runtime_error("gradient modes need a density network (the reference's evalNormal asserts it)");
     D.normals = (om >= OUT_DENSITYGRAD || h->gradient_mode != FVSRN_GRADIENT_OFF_OR_DIRECT || D.brdf_flags) ? 1 : 0;
     // the tcgen05 kernels march density / colour networks without normals; everything with normals runs on the mma.sync family
-    // Adjoint normals (GRADIENT_MODE 2): the backward pass through the network exists in the reference-arithmetic kernel family
-    // only (kernels_exact.cuh, SrnExact::adjoint) - frames that ask for it run there whichever kernel mode is selected.
+    // Adjoint normals (GRADIENT_MODE 2): one backward pass through the network per shaded step - in the fast kernel modes on the
+    // mma.sync family (srn_core.cuh Srn::adjoint), in reference-exact mode bit-identical to the reference (kernels_exact.cuh SrnExact::adjoint)
     const bool adjoint = h->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD;
     if (adjoint) {
         const Network& n = h->net;
         if (n.has_direction) throw std::runtime_error("adjoint gradient mode: networks with a direction input are not supported (the reference's adjoint ignores the direction, :1478-1504)");
         if (om == OUT_DENSITYCURV || om == OUT_DENSITYCURV_DIRECT) throw std::runtime_error("adjoint gradient mode: not defined for densitycurvature networks (reference :1262-1264)");
-        if (h->num_hidden > 7) throw std::runtime_error("adjoint gradient mode: at most 7 hidden layers after the first");
+        if (h->num_hidden > 7 && h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT) throw std::runtime_error("adjoint gradient mode, reference-exact kernels: at most 7 hidden layers after the first");
+        if (h->GC16 < 1) throw std::runtime_error("adjoint gradient mode: networks with a latent grid");
         for (const auto& g : h->d_time) if (g.encoding != GRID_FLOAT) throw std::runtime_error("adjoint gradient mode: float latent grids only");
         for (const auto& g : h->d_ens) if (g.encoding != GRID_FLOAT) throw std::runtime_error("adjoint gradient mode: float latent grids only");
     }
     const bool tc = h->kernel_mode == FVSRN_KERNEL_TCGEN05 && !D.normals;
-    const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT || adjoint;
+    const bool exact = h->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT;
     if (exact) {    // the shapes the reference kernels this mode is validated against cover (kernels_exact.cuh)
         const Network& n = h->net;
         if (is_rgbo || h->GC16 < 1 || h->GC16 > 2 || ((n.has_direction || h->GC16 == 2) && h->H16 != 2 && h->H16 != 4))
@@ -1010,7 +1011,7 @@ void do_render(fvsrn_network* h, const fvsrn_dvr_params* p, float* out, cudaStre
         DvrParams d = D; d.b0 = b0; d.nb = nb;      // the launcher lays the tile raster of its kernel over the rectangle
         d.tile_counter = next_tile_counter(h, ls);
         LaunchCfg cfg; cfg.sm_count = h->sm_count;
-        if (adjoint) CUDA_OK(launch_exact_adjoint(h->H16, h->GC16, P, d, &cfg, ls));
+        if (adjoint && exact) CUDA_OK(launch_exact_adjoint(h->H16, h->GC16, P, d, &cfg, ls));
         else if (exact) CUDA_OK(launch_exact(h->H16, h->GC16, h->dir, P, d, &cfg, ls));
         else CUDA_OK(fn(tc ? KIND_DVR_TC : KIND_DVR, h->GC16, h->dir, P, &d, &cfg, ls));
         if (blended) CUDA_OK(cudaEventRecord(blended->ev_read[ls == h->aux_stream ? 1 : 0], ls));
@@ -1403,7 +1404,7 @@ int fvsrn_query(fvsrn_network* net, int kernel, fvsrn_query_info* info) {
     if (!fn) return fail("no kernel for this hidden width");
     DvrParams dq{}; dq.tf_kind = 0; dq.tf_R = 8;   // a typical piecewise TF: the DVR kernels size their shared memory from it
     dq.tw = 1024; dq.th = 1024; dq.nb = 1;
-    if (net->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD && kernel == 0) CUDA_OK(launch_exact_adjoint(net->H16, net->GC16, P, dq, &cfg, nullptr));
+    if (net->gradient_mode == FVSRN_GRADIENT_ADJOINT_METHOD && net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact_adjoint(net->H16, net->GC16, P, dq, &cfg, nullptr));
     else if (net->kernel_mode == FVSRN_KERNEL_REFERENCE_EXACT && kernel == 0) CUDA_OK(launch_exact(net->H16, net->GC16, net->dir, P, dq, &cfg, nullptr));
     else CUDA_OK(fn((kernel == 0 ? KIND_DVR : KIND_EVAL) + (tc ? 2 : 0), net->GC16, net->dir, P, kernel == 0 ? &dq : nullptr, &cfg, nullptr));
     info->device = net->device; info->sm_count = net->sm_count;

@@ -336,6 +336,8 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
     uint4* stage_all = smem + blob16 + kTfSmemFloats / 4;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint4* stage = stage_all + warp * (Net::STAGE_BYTES / 16);
+    // adjoint gradient mode only (the launch adds the bytes): this warp's pre-activation store
+    uint32_t* pre = reinterpret_cast<uint32_t*>(stage_all + kWarpsPerBlock * (Net::STAGE_BYTES / 16)) + warp * Net::pre_words(P.num_hidden);
 
     load_blob(P, sblob);
     const int tf_floats = D.tf_kind == 0 ? D.tf_R * 5 : (D.tf_kind == 1 ? D.tf_R * 4 : 2);
@@ -423,6 +425,16 @@ dvr_kernel(const __grid_constant__ NetParams P, const __grid_constant__ DvrParam
                         }
                         const float inv2h = __fdividef(1.f, 2.f * h);
                         n = make_float3((d[0] - d[1]) * inv2h, (d[2] - d[3]) * inv2h, (d[4] - d[5]) * inv2h);
+                    }
+                } else if (!DIR && GC16 > 0 && P.gradient_mode == 2) {
+                    // GRADIENT_MODE_ADJOINT_METHOD (:1199-1530): on steps that shade something the forward pass is repeated with its
+                    // pre-activations kept, then one backward pass gives d density / d position (unit-box coordinates, as the reference)
+                    if constexpr (!DIR && GC16 > 0) {
+                        if (__any_sync(0xffffffffu, shaded)) {
+                            float q[4];
+                            Net::template forward<true>(P, sblob_addr, stage, ac, px, py, pz, dir.x, dir.y, dir.z, q, pre);
+                            n = Net::adjoint(P, sblob_addr, stage, pre, ac, px, py, pz, q[0]);
+                        }
                     }
                 } else if (P.output_mode >= D_OUT_DENSITY_GRADIENT) n = normal_from_output(P.output_mode, o);
                 if (valid) ++steps;

@@ -236,11 +236,13 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
         }
     }
     const bool normals = kind == KIND_DVR && kp != nullptr && static_cast<const DvrParams*>(kp)->normals != 0;
+    // adjoint gradient mode: the pre-activations of the repeated forward pass, per warp (srn_core.cuh Srn::adjoint)
+    const int smem_adj = (normals && P.gradient_mode == 2) ? kWarpsPerBlock * Net::pre_words(P.num_hidden) * 4 : 0;
     const void* fn = kind == KIND_DVR ? (normals ? (const void*)dvr_kernel<H16, GC16, DIR, true> : (const void*)dvr_kernel<H16, GC16, DIR, false>)
                    : kind == KIND_EVAL ? (const void*)eval_kernel<H16, GC16, DIR>
                    : kind == KIND_DVR_TC ? (tc_dvr_spec ? tc_dvr_spec : tc_dvr[variant]) : tc_eval[variant];
     KernelFacts kf;
-    const cudaError_t e = kernel_facts(fn, threads, smem, is_tc, SrnTc<H16, GC16, DIR, 0>::TMEM_COLS, &kf);
+    const cudaError_t e = kernel_facts(fn, threads, smem + smem_adj, is_tc, SrnTc<H16, GC16, DIR, 0>::TMEM_COLS, &kf);
     if (e != cudaSuccess) return e;
     const int bps = kf.bps;
     DvrParams dvr;
@@ -254,7 +256,7 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     long long grid = (long long)bps * cfg->sm_count;
     if (cfg->max_blocks > 0 && grid > cfg->max_blocks) grid = cfg->max_blocks;
     if (grid < 1) grid = 1;
-    cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem; cfg->regs = kf.regs; cfg->threads = threads;
+    cfg->blocks_per_sm = bps; cfg->grid = int(grid); cfg->smem = smem + smem_adj; cfg->regs = kf.regs; cfg->threads = threads;
     if (cfg->query_only) return cudaSuccess;
     if (is_tc) {
         void* args[2] = {const_cast<NetParams*>(&P), const_cast<void*>(kp)};
@@ -262,7 +264,7 @@ cudaError_t launch_one(int kind, const NetParams& P, const void* kp, LaunchCfg* 
     }
     switch (kind) {
         case KIND_DVR:
-            if (normals) dvr_kernel<H16, GC16, DIR, true><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
+            if (normals) dvr_kernel<H16, GC16, DIR, true><<<int(grid), threads, smem + smem_adj, s>>>(P, *static_cast<const DvrParams*>(kp));
             else dvr_kernel<H16, GC16, DIR, false><<<int(grid), threads, smem, s>>>(P, *static_cast<const DvrParams*>(kp));
             break;
         default: eval_kernel<H16, GC16, DIR><<<int(grid), threads, smem, s>>>(P, *static_cast<const EvalParams*>(kp)); break;

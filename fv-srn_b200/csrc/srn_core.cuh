@@ -103,6 +103,9 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
     uint2 v; asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];\n" : "=r"(v.x), "=r"(v.y) : "r"(addr));
     return v;
 }
+__device__ __forceinline__ unsigned short lds16(uint32_t addr) {
+    unsigned short v; asm volatile("ld.shared.u16 %0, [%1];\n" : "=h"(v) : "r"(addr)); return v;
+}
 __device__ __forceinline__ uint32_t lds32(uint32_t addr) {
     uint32_t v; asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(v) : "r"(addr));
     return v;
@@ -334,12 +337,205 @@ struct Srn {
         }
     }
 
+    // ------------------------------------------------------------------------------------------------------------------
+    // Adjoint pass (the reference's GRADIENT_MODE 2, renderer_volume_tensorcores.cuh:1205-1530) in this family's arithmetic:
+    // d density / d position of the sample owned by each lane from one backward pass - transposed-weight MMAs (fp16
+    // accumulators from zero), activation adjoints in packed fp16, the latent grid differentiated by central differences with
+    // step P.fd_stepsize in normalised grid coordinates (LoadVolumetricFeaturesAdjoint, :609-735), the Fourier adjoint in fp32.
+    // The reference-arithmetic version (bit-identical to the reference kernel) is SrnExact::adjoint in kernels_exact.cuh.
+    static __host__ __device__ constexpr int pre_words(int num_hidden) { return (1 + num_hidden) * ACC * 32; }
+    static __device__ __forceinline__ void keep_frag(uint32_t* pre, int layer, const uint32_t (&f)[2][NT][2], int lane) {
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) pre[(layer * ACC + (mt * NT + nt) * 2 + j) * 32 + lane] = f[mt][nt][j];
+    }
+    static __device__ __forceinline__ void act_adjoint(uint32_t (&z)[2][NT][2], const uint32_t* pre, int layer, int lane, int act, const ActConst& c) {
+        const __half2 zero = __float2half2_rn(0.f), one = __float2half2_rn(1.f);
+        const __half2 two_p = __hadd2(c.p, c.p), inv_q = __float2half2_rn(c.inv_q);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const __half2 x = u2h(pre[(layer * ACC + (mt * NT + nt) * 2 + j) * 32 + lane]);
+                    __half2 v = u2h(z[mt][nt][j]);
+                    if (act == D_ACT_RELU) v = __hmul2(v, __hgt2(x, zero));                                   // x > 0 ? z : 0
+                    else if (act == D_ACT_SINE) v = __hmul2(v, __hmul2(c.p, cos_h2(__hmul2(x, c.p))));         // z p cos(p x)
+                    else if (act == D_ACT_SNAKE) v = __hmul2(v, __hadd2(one, sin_h2(__hmul2(two_p, x))));      // z (1 + sin(2p x))
+                    else if (act == D_ACT_SNAKEALT) v = __hmul2(v, __hadd2(sin_h2(__hmul2(c.q, x)), inv_q));   // z (sin(2p x) + 1/(2p))
+                    z[mt][nt][j] = h2u(v);
+                }
+    }
+    // out(32 x 8*NTL) = X(32 x H) * B, B = transposed weights as fragments (api.cu build_blob, adjoint sections)
+    template <int NTL>
+    static __device__ __forceinline__ void dense_t(uint32_t (&out)[2][NTL][2], uint32_t w_addr, int lane, const uint32_t (&x)[2][NT][2]) {
+#pragma unroll
+        for (int kt = 0; kt < KTH; ++kt) {
+            uint32_t a[2][4];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                a[mt][0] = x[mt][2 * kt][0]; a[mt][1] = x[mt][2 * kt][1];
+                a[mt][2] = x[mt][2 * kt + 1][0]; a[mt][3] = x[mt][2 * kt + 1][1];
+            }
+#pragma unroll
+            for (int ntp = 0; ntp < NTL / 2; ++ntp) {
+                const uint4 b = lds128(w_addr + ((kt * (NTL / 2) + ntp) * 32 + lane) * 16);
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt) {
+                    if (kt == 0) {
+                        mma16816(out[mt][2 * ntp], a[mt], b.x, b.y, 0u, 0u);
+                        mma16816(out[mt][2 * ntp + 1], a[mt], b.z, b.w, 0u, 0u);
+                    } else {
+                        mma16816(out[mt][2 * ntp], a[mt], b.x, b.y, out[mt][2 * ntp][0], out[mt][2 * ntp][1]);
+                        mma16816(out[mt][2 * ntp + 1], a[mt], b.z, b.w, out[mt][2 * ntp + 1][0], out[mt][2 * ntp + 1][1]);
+                    }
+                }
+            }
+        }
+    }
+    template <int NTL>
+    static __device__ __forceinline__ void frag_to_rows(uint4* stage, const uint32_t (&f)[2][NTL][2], int lane) {
+        uint32_t* st32 = reinterpret_cast<uint32_t*>(stage);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < NTL; ++nt)
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
+                    st32[(mt * 16 + (lane >> 2) + 8 * j) * (RS_CHUNKS * 4) + nt * 4 + (lane & 3)] = f[mt][nt][j];
+    }
+    // the 16 latent channels of group g at one position (float grids; fp16 weights and FMAs as in build_row), as floats
+    static __device__ __forceinline__ void latent16(const NetParams& P, int g, float px, float py, float pz, float (&v)[16]) {
+        const float ux = __fmaf_rn(px, float(P.gx), -0.5f), uy = __fmaf_rn(py, float(P.gy), -0.5f), uz = __fmaf_rn(pz, float(P.gz), -0.5f);
+        const float flx = floorf(ux), fly = floorf(uy), flz = floorf(uz);
+        const float fx = ux - flx, fy = uy - fly, fz = uz - flz;
+        const int ix = int(flx), iy = int(fly), iz = int(flz);
+        const int xs[2] = {min(max(ix, 0), P.gx - 1), min(max(ix + 1, 0), P.gx - 1)};
+        const int ys[2] = {min(max(iy, 0), P.gy - 1), min(max(iy + 1, 0), P.gy - 1)};
+        const int zs[2] = {min(max(iz, 0), P.gz - 1), min(max(iz + 1, 0), P.gz - 1)};
+        const float wx[2] = {1.f - fx, fx}, wy[2] = {1.f - fy, fy}, wz[2] = {1.f - fz, fz};
+        const GridGroup G = P.groups[g];
+        __half2 acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = __float2half2_rn(0.f);
+        const int nsrc = (G.frac > 0.f) ? 2 : 1;
+#pragma unroll 1
+        for (int s = 0; s < nsrc; ++s) {
+            const uint4* base = reinterpret_cast<const uint4*>(s == 0 ? G.a : G.b);
+            const float ws = (nsrc == 1) ? 1.f : (s == 0 ? 1.f - G.frac : G.frac);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const uint4* ptr = base + (size_t)((zs[c >> 2] * P.gy + ys[(c >> 1) & 1]) * P.gx + xs[c & 1]) * G.voxel_stride;
+                const uint4 v0 = __ldg(ptr), v1 = __ldg(ptr + 1);
+                const __half2 w2 = __float2half2_rn(__fmul_rn(__fmul_rn(__fmul_rn(wz[c >> 2], wy[(c >> 1) & 1]), wx[c & 1]), ws));
+                const uint32_t u[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] = __hfma2(w2, u2h(u[j]), acc[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float2 f = __half22float2(acc[j]); v[2 * j] = f.x; v[2 * j + 1] = f.y; }
+    }
+    // all 32 lanes call, after forward<true> of the same positions. raw0 = the raw density output of this lane's sample.
+    static __device__ __forceinline__ float3 adjoint(const NetParams& P, uint32_t sblob, uint4* stage, const uint32_t* pre, const ActConst& ac,
+                                                     float px, float py, float pz, float raw0) {
+        const int lane = threadIdx.x & 31;
+        // adjoint of the output parametrisation (:1233-1246): sigmoid'(raw) for the sigmoid modes, else 1
+        float adj_out = 1.f;
+        if (P.output_mode == D_OUT_DENSITY || P.output_mode == D_OUT_DENSITY_GRADIENT) {
+            const float ev = __expf(raw0);
+            adj_out = __fdividef(ev, (ev + 1.f) * (ev + 1.f));
+        }
+        const __half adj_h = __float2half_rn(adj_out);
+        const uint32_t adj_bits = uint32_t(__half_as_ushort(adj_h));
+        // adjoint of the last layer (:1248-1262), built directly as accumulator fragments: sample mt*16 + lane/4 + 8j, channel pair nt*4 + lane%4
+        uint32_t z[2][NT][2];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const __half a = __ushort_as_half((unsigned short)__shfl_sync(0xffffffffu, adj_bits, mt * 16 + (lane >> 2) + 8 * j));
+                const __half2 a2 = __halves2half2(a, a);
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) z[mt][nt][j] = h2u(__hmul2(u2h(P.wlast2[nt * 4 + (lane & 3)]), a2));
+            }
+#pragma unroll 1
+        for (int l = P.num_hidden - 1; l >= 0; --l) {
+            act_adjoint(z, pre, 1 + l, lane, P.activation, ac);
+            uint32_t nxt[2][NT][2];
+            dense_t<NT>(nxt, sblob + P.off_adj_wh + l * wh_bytes(), lane, z);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) { z[mt][nt][0] = nxt[mt][nt][0]; z[mt][nt][1] = nxt[mt][nt][1]; }
+        }
+        act_adjoint(z, pre, 0, lane, P.activation, ac);
+        float3 out = make_float3(0.f, 0.f, 0.f);
+        const float h = P.fd_stepsize;
+        const float s = __fdividef(1.f, 2.f * h);
+#pragma unroll
+        for (int g = 0; g < GC16; ++g) {
+            uint32_t c16[2][2][2];
+            dense_t<2>(c16, sblob + P.off_adj_w0g + g * (H * 16 * 2), lane, z);
+            __syncwarp();
+            frag_to_rows<2>(stage, c16, lane);
+            __syncwarp();
+            const uint4 r0 = stage[lane * RS_CHUNKS], r1 = stage[lane * RS_CHUNKS + 1];
+            const uint32_t u[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+            float adj[16];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) { const float2 f = __half22float2(u2h(u[k])); adj[2 * k] = f.x; adj[2 * k + 1] = f.y; }
+#pragma unroll 1
+            for (int axis = 0; axis < 3; ++axis) {
+                float hi[16], lo[16];
+                latent16(P, g, px + (axis == 0 ? h : 0.f), py + (axis == 1 ? h : 0.f), pz + (axis == 2 ? h : 0.f), hi);
+                latent16(P, g, px - (axis == 0 ? h : 0.f), py - (axis == 1 ? h : 0.f), pz - (axis == 2 ? h : 0.f), lo);
+                float d = 0.f;
+#pragma unroll
+                for (int k = 0; k < 16; ++k) d = fmaf(adj[k], s * (hi[k] - lo[k]), d);
+                if (axis == 0) out.x += d; else if (axis == 1) out.y += d; else out.z += d;
+            }
+        }
+        {
+            uint32_t zf[2][NT][2];
+            dense_t<NT>(zf, sblob + P.off_adj_w0f, lane, z);
+            __syncwarp();
+            frag_to_rows<NT>(stage, zf, lane);
+            __syncwarp();
+        }
+        const __half* row = reinterpret_cast<const __half*>(stage + lane * RS_CHUNKS);
+        out.x += __half2float(row[0]); out.y += __half2float(row[1]); out.z += __half2float(row[2]);
+        const __half hx = __float2half_rn(px), hy = __float2half_rn(py), hz = __float2half_rn(pz);
+        const uint32_t f_addr = sblob + P.off_fourier;
+#pragma unroll 2
+        for (int i = 0; i < NF; ++i) {
+            const __half f0 = __ushort_as_half(lds16(f_addr + (i + 0 * NF) * 2)), f1 = __ushort_as_half(lds16(f_addr + (i + 1 * NF) * 2)),
+                         f2 = __ushort_as_half(lds16(f_addr + (i + 2 * NF) * 2));
+            __half c = __hmul(hx, f0);
+            c = __hfma(hy, f1, c);
+            c = __hfma(hz, f2, c);
+            float sn, cs;
+            __sincosf(__half2float(c), &sn, &cs);
+            const float adj_c = __half2float(row[FOFF + NF + i]) * cs - __half2float(row[FOFF + i]) * sn;
+            out.x = fmaf(__half2float(f0), adj_c, out.x); out.y = fmaf(__half2float(f1), adj_c, out.y); out.z = fmaf(__half2float(f2), adj_c, out.z);
+        }
+        __syncwarp();
+        return out;
+    }
+
     // Evaluate the network for the sample owned by this lane. All 32 lanes must call (warp-synchronous).
     // (px,py,pz) is the position in the unit cube, (dx,dy,dz) the ray direction (DIR only).
     // out[0..3]: raw last-layer outputs (before the output parametrisation).
+    // KEEP: the pre-activation accumulators of every activated layer go to `pre` (fragment order, [(layer * ACC + reg) * 32 + lane])
+    // for the adjoint pass below
+    template <bool KEEP = false>
     static __device__ __forceinline__ void forward(const NetParams& P, uint32_t sblob, uint4* stage, const ActConst& ac,
                                                    float px, float py, float pz, float dx, float dy, float dz,
-                                                   float (&out)[4]) {
+                                                   float (&out)[4], uint32_t* pre = nullptr) {
         const int lane = threadIdx.x & 31;
         __syncwarp();
         uint32_t row[K0 / 2];
@@ -361,6 +557,7 @@ struct Srn {
                     ldmatrix_x4(a[mt], stage_addr + ((mt * 16 + lrow) * RS_CHUNKS + kt * 2 + lcol) * 16);
             });
         }
+        if constexpr (KEEP) keep_frag(pre, 0, acc, lane);
         activate(acc, P.activation, ac);
         // ---------------- hidden layers: accumulator fragments are the next A fragments
 #pragma unroll 1
@@ -374,6 +571,7 @@ struct Srn {
                                a[mt][2] = acc[mt][2 * kt + 1][0]; a[mt][3] = acc[mt][2 * kt + 1][1];
                            }
                        });
+            if constexpr (KEEP) keep_frag(pre, 1 + l, nxt, lane);
             activate(nxt, P.activation, ac);
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)

@@ -52,8 +52,8 @@ enum fvsrn_gradient_mode {
     FVSRN_GRADIENT_FINITE_DIFFERENCES = 1,  /* central differences: 6 more SRN evaluations per shaded step */
     /* the backward pass through the SRN (:1205-1530): d density / d position from one more pass with transposed weights,
      * the latent grid differentiated by central differences of its texture (step 1 / (4 * grid resolution) by default).
-     * Runs in the reference-arithmetic kernel family whichever kernel mode is selected; density / densitygrad* networks
-     * without direction input, float latent grids. */
+     * Fast kernel modes: the mma.sync family's own adjoint pass; FVSRN_KERNEL_REFERENCE_EXACT: bit-identical to the reference
+     * kernel built with GRADIENT_MODE 2. Density / densitygrad* networks without direction input, float latent grids. */
     FVSRN_GRADIENT_ADJOINT_METHOD = 2
 };
 /* BRDFLambert::LightType as the kernel sees it, renderer_brdf_lambert.cuh:6-7 */

@@ -123,14 +123,52 @@ def _adjoint_frames(name, plume_tf, modes, size=SIZE):
 
 @pytest.mark.parametrize("name", list(ADJOINT_CASES))
 def test_adjoint_gradient_mode_is_bit_identical_to_the_reference_kernel(ref, name, plume_tf):
-    """Frames in adjoint gradient mode run in the reference-arithmetic kernel family whichever kernel mode is selected: all 8
-    channels bit-identical to the reference kernel built with GRADIENT_MODE 2."""
-    want, got = _adjoint_frames(name, plume_tf, ["reference_exact", "tcgen05"])
+    """Reference-exact kernel mode: all 8 channels of a frame in adjoint gradient mode bit-identical to the reference kernel built
+    with GRADIENT_MODE 2."""
+    want, got = _adjoint_frames(name, plume_tf, ["reference_exact"])
     assert want[:, 3].max() > 0.1 and np.abs(want[:, 4:7]).max() > 0.02
     for mode, img in got.items():
         for c, label in enumerate(("r", "g", "b", "alpha", "normal x", "normal y", "normal z", "depth")):
             same = (img[:, c] == want[:, c]) | (np.isnan(img[:, c]) & np.isnan(want[:, c]))
             assert same.all(), (name, mode, label, int((~same).sum()), float(np.nanmax(np.abs(img[:, c] - want[:, c]))))
+
+
+@pytest.mark.parametrize("name", list(ADJOINT_CASES))
+def test_fast_modes_with_adjoint_normals(ref, name, plume_tf):
+    """The fast kernel modes run the adjoint pass in their own arithmetic (mma.sync family: SFU sin / cos, exact trilinear weights,
+    fp32 Fourier adjoint). The adjoint is a chain of fp16 products through every layer (ReLU masks flip on the last bit of a
+    pre-activation), so two fp16 implementations differ by the noise of the method itself: on these networks the reference's own
+    adjoint is 1 ... 11 % (rms) away from the fp32 gradient (tests/test_oracle_gradients.py). The gate is therefore the fp32 frame -
+    central differences of the fp32 network, CPU oracle - and the criterion "at least as close to it as the reference kernel is"
+    (factor 1.25 + 1e-4 on the mean normal error, PSNR of the shaded colour within 1 dB; measured: equal to 3 digits on all seven
+    networks), next to bounds on the means against the reference frame."""
+    import oracle
+    import parity
+    import fvsrn_b200  # noqa: F401
+    from fvsrn_b200 import scenes, volnet
+    kw, variant, brdf = ADJOINT_CASES[name]
+    net = scenes.make_network(**kw)
+    cam = scenes.camera_reference_frame(**scenes.DEFAULT_CAMERA)
+    W, step = 96, 1 / 96
+    truth, _, _ = oracle.render_dvr(net, width=W, height=W, camera=cam, fov_y=scenes.DEFAULT_FOV_Y, stepsize=step, tf=plume_tf, fp32=True,
+                                    fd_stepsize=1e-3, brdf=brdf)
+    want, _, _ = parity.render_reference(net, W, W, cam, scenes.DEFAULT_FOV_Y, plume_tf, step, variant=variant, brdf=brdf)
+    data = volnet.dumps(net)
+    assert np.abs(truth[:, 4:7]).max() > 0.02
+    err_ref = float(np.abs(want[:, 4:7] - truth[:, 4:7]).mean())
+    psnr_ref = float(parity.psnr(want[:, :4], truth[:, :4]))
+    for mode in ("tcgen05", "mma_sync"):
+        img = parity.render_ours(data, mode, W, W, cam, plume_tf, step, brdf=brdf, adjoint=True)[0]
+        err = float(np.abs(img[:, 4:7] - truth[:, 4:7]).mean())
+        row = dict(config=name, kernel_mode=mode, size=W, normal_mean_abs_vs_fp32=err, reference_normal_mean_abs_vs_fp32=err_ref,
+                   psnr_db_vs_fp32=float(parity.psnr(img[:, :4], truth[:, :4])), reference_psnr_db_vs_fp32=psnr_ref,
+                   rgba_max_abs_vs_reference=float(np.abs(img[:, :4] - want[:, :4]).max()), normal_max_abs_vs_reference=float(np.abs(img[:, 4:7] - want[:, 4:7]).max()),
+                   psnr_db_vs_reference=float(parity.psnr(img[:, :4], want[:, :4])), normal_mean_abs_vs_reference=float(np.abs(img[:, 4:7] - want[:, 4:7]).mean()))
+        _record(row)
+        assert err <= 1.25 * err_ref + 1e-4 and row["psnr_db_vs_fp32"] >= psnr_ref - 1.0, row
+        # against the reference frame itself: means, not maxima - where the gradient is nearly zero its direction is noise in both
+        # implementations (measured maxima: 0.24 on a normal component, 0.08 on a Phong-shaded colour, in isolated pixels)
+        assert row["psnr_db_vs_reference"] >= 50.0 and row["normal_mean_abs_vs_reference"] <= 5e-3, row
 
 
 def test_adjoint_through_time_interpolated_keyframes(ref, plume_tf):

@@ -29,7 +29,8 @@ import parity  # noqa: E402
 import ref_kernel  # noqa: E402
 brdf = dict(flags=("magnitude", "phong"), light_type=1, light=(0.3, -0.5, -0.8), magnitude_scaling=2.0, ambient=0.3, specular=0.5,
             magnitude_center=1.0, magnitude_radius=0.8, specular_exponent=8)
-for label, grad in (("finite differences, mma_sync kernels", 1), ("finite differences, reference-exact kernels", 1), ("adjoint pass", 2)):
+for label, grad in (("finite differences, mma_sync kernels", 1), ("finite differences, reference-exact kernels", 1), ("adjoint pass, mma_sync kernels", 2),
+                    ("adjoint pass, reference-exact kernels", 2)):
     sn = pr.SceneNetwork.from_bytes(volnet.dumps(net)); sn.kernel_mode = "reference_exact" if "exact" in label else "mma_sync"
     vol = pr.VolumeInterpolationNetwork(); vol.set_network(sn)
     vol.gradient_mode = pr.VolumeInterpolationNetwork.FINITE_DIFFERENCES if grad == 1 else pr.VolumeInterpolationNetwork.ADJOINT_METHOD
