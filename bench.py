@@ -475,7 +475,7 @@ def run_b200(args):
             "ms_per_frame": total_ms / args.steps / (1 if tiles else V),
             "e2e": {"value": useful / e2e_s, "unit": "samples/s", "ms_per_frame": 1e3 * e2e_s / args.steps / (1 if tiles else V),
                     "h2d_bytes_per_step": int(host_cam.numel() * 4 + host_tf.numel() * 4) * (world if world > 1 else 1), "d2h_bytes_per_step": int(d2h_bytes),
-                    "what": "fvsrn_render_dvr_host: camera + TF copied up, the kernel writes the (B,4,H,W) fp32 colour straight into the caller's pinned host buffer" if world == 1 else
+                    "what": "fvsrn_render_dvr_host: camera + TF copied up, (B,4,H,W) fp32 colour rendered in four row bands whose D2H copies stream behind the next band's kernel (by_format: rgba8 is written by the kernel straight into the caller's pinned buffer)" if world == 1 else
                             "per step: H2D camera+TF on every rank, render, " + ("peer-memory writes into rank 0's frame" if peer_mode else "NCCL collection on rank 0") + ", D2H of the assembled frames on rank 0",
                     "by_format": e2e_formats or None},
             # one DVR kernel per launch; with per-view keyframe times one launch per view, each preceded by the small kernel that

@@ -1118,9 +1118,11 @@ int fvsrn_render_dvr_host(fvsrn_network* net, const fvsrn_dvr_params* p, float* 
     // Pinned, device-mapped host memory (cudaHostAlloc / cudaHostRegister; every pinned allocation under unified addressing): the
     // kernel writes its pixels straight into the caller's buffer. The 4 - 32 bytes per pixel trickle over PCIe while the frame is
     // marched (16 MiB in 4.7 ms = 3.5 GB/s on C3) - no staging image, no copy left after the kernel.
-    // A/B on one B200 (C3, fp32 colour; kernel 4.67 ms): staged bands 4.84 ms, direct 4.7x ms (profiles/r02k_e2e_direct.log).
+    // A/B on one B200 (C3, kernel 4.67 ms; profiles/r02k_e2e_direct.log, r02q): the packed formats (4 / 8 bytes per pixel) 4.70 ms direct on
+    // every box; fp32 colour (16 B/pixel in four planes) 4.7x ms direct on one box and 6.0 ms on another (4-byte posted writes are at
+    // the mercy of the host's PCIe / NUMA path), 4.84 ms staged on both - so only the packed formats go direct.
     void* direct = nullptr;
-    if (!has_rect && fmt != FVSRN_OUTPUT_RAW8_F32) {     // (the raw tensor's eight scattered 4-byte planes measured 4.75 - 6.2 ms direct vs 4.91 staged)
+    if (!has_rect && (fmt == FVSRN_OUTPUT_RGBA8 || fmt == FVSRN_OUTPUT_RGBA_F16)) {     // (the raw tensor's eight planes: 4.75 - 6.2 ms direct vs 4.91 staged)
         cudaPointerAttributes at{};
         if (cudaPointerGetAttributes(&at, out_host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer != nullptr) direct = at.devicePointer;
         else (void)cudaGetLastError();      // pageable memory: not an error, the staged path below handles it

@@ -127,7 +127,7 @@ def test_host_entry_point_formats_and_band_streaming(env, scene, fmt, planes, dt
         out = np.zeros(shape, dtype)        # pageable host memory: staged through the device image, copied band by band
         env.lib.check(env.lib.lib().fvsrn_render_dvr_host(net._h, C.byref(p), out.ctypes.data, None))
         assert np.array_equal(np.nan_to_num(out.view(dev.dtype) if fmt == "rgba8" else out), np.nan_to_num(dev)), (fmt, W, H)
-        # pinned (device-mapped) host memory: the fused formats are written by the kernel straight into the caller's buffer
+        # pinned (device-mapped) host memory: the packed formats are written by the kernel straight into the caller's buffer
         tdt = {np.float32: env.torch.float32, np.uint32: env.torch.int32, np.float16: env.torch.float16}[dtype]
         pinned = env.torch.zeros(shape, dtype=tdt).pin_memory()
         env.lib.check(env.lib.lib().fvsrn_render_dvr_host(net._h, C.byref(p), pinned.data_ptr(), None))
