@@ -42,7 +42,13 @@ constexpr int kTcTfBins = 64;              // piecewise TF search accelerator: o
 #define FVSRN_NO_SYNCWARP 0
 #endif
 #ifndef FVSRN_TC_ACC16
-#define FVSRN_TC_ACC16 0   // 1: fp16 accumulators in TMEM (kind::f16 with D = F16; still one 32-bit column each), read back packed (tcgen05.ld .pack::16b): no fp32 -> fp16 packs in the layer epilogues. A/B on one B200 (C3, r02c): 5.42 vs 5.49 ms - within 1.2 %, kept opt-in
+// 1 (default since r02, applied to the ReLU instantiations - SrnTc::ACC16): fp16 accumulators in TMEM (kind::f16 with D = F16; an element still occupies one 32-bit column), read back
+// packed (tcgen05.ld .pack::16b): half the registers per epilogue load and no fp32 -> fp16 packs in the layer epilogues. It is the
+// accumulation precision of the reference's own wmma path (fp16 accumulator fragments, renderer_volume_tensorcores.cuh:856-910).
+// A/B of full builds on one B200 (r02, tools/ab_full.sh): C3 4.659 -> 4.572 ms, C4 257.7 -> 249.0 ms, C5 1.198 -> 1.176 ms per view;
+// C3 frame vs the reference kernel 4.2e-4 -> 5.6e-4 (gate 2e-3); every reference-kernel parity gate of the suite unchanged green.
+// 0: fp32 accumulators (the first form of the kernel).
+#define FVSRN_TC_ACC16 1
 #endif
 constexpr int kTcTfFloats = 2560;          // shared-memory TF: up to 204 piecewise intervals x 12 floats, or 256 x float4 texels
 
@@ -128,6 +134,9 @@ struct SrnTc {
     using Core = Srn<H16, GC16, DIR>;
     using TS = TcSpec<SPEC>;
     static constexpr bool RELU = (VARIANT & 1) != 0, NERF = (VARIANT & 2) != 0, SNAKEALT_PRE = (VARIANT & 4) != 0;
+    // fp16 accumulators in TMEM for the ReLU instantiations (see FVSRN_TC_ACC16): max() works on the packed pair as it comes out of
+    // tcgen05.ld.pack::16b; the SFU activations want fp32 inputs and were 3 % slower with packed accumulators (SnakeAlt 10.6 -> 10.9 ms)
+    static constexpr bool ACC16 = (FVSRN_TC_ACC16 != 0) && RELU;
     static constexpr int H = Core::H, K0 = Core::K0, KT0 = K0 / 16, KTH = H / 16;
     static constexpr int NLAST = 16;                       // last layer padded to N = 16 (M=128 needs N % 16 == 0)
     // TMEM columns (32-bit): ones chunk | slot 0: D, A | slot 1: D, A
@@ -373,7 +382,7 @@ struct SrnTc {
     // slot's completion barrier.
     // The smem descriptor of K step kt differs from step 0 only in the address field of its low word.
     static __device__ __forceinline__ void issue_layer(const Ctx& c, int slot, uint32_t w_addr, int n, int kt_data, bool bias_chunk) {
-        const uint32_t idesc = tc::make_idesc(128, n, FVSRN_TC_ACC16 != 0);
+        const uint32_t idesc = tc::make_idesc(128, n, ACC16);
         const uint32_t kstride = uint32_t(n / 8) * 128u;                    // LBO: distance between the two K chunks of a step
         uint32_t lo = ((w_addr >> 4) & 0x3FFFu) | (((kstride >> 4) & 0x3FFFu) << 16);
         const uint32_t hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, descriptor version 1
@@ -410,7 +419,7 @@ struct SrnTc {
     // epilogue of one slot: accumulator row -> activation -> fp16 A operand of the next layer
     template <int ACT>
     static __device__ __forceinline__ void epilogue_t(const Ctx& c, int slot) {
-#if FVSRN_TC_ACC16
+        if constexpr (ACC16) {
 #pragma unroll
         for (int c0 = 0; c0 < H; c0 += 32) {
             uint32_t v[16];
@@ -421,7 +430,7 @@ struct SrnTc {
                 if (H - c0 >= 32 || j < 8) v[j] = tc::act_h2<ACT>(c.af, v[j]);
             if (H - c0 >= 32) tc::tmem_st16(c.tmem_lane + a_col(slot) + c0 / 2, v, 0); else tc::tmem_st8(c.tmem_lane + a_col(slot) + c0 / 2, v, 0);
         }
-#else
+        } else {
 #pragma unroll
         for (int c0 = 0; c0 < H; c0 += 32) {
             uint32_t v[32];
@@ -433,7 +442,7 @@ struct SrnTc {
                 pk[j] = (H - c0 >= 32 || j < 8) ? tc::act_pack<ACT>(c.af, v[2 * j], v[2 * j + 1]) : 0u;
             if (H - c0 >= 32) tc::tmem_st16(c.tmem_lane + a_col(slot) + c0 / 2, pk, 0); else tc::tmem_st8(c.tmem_lane + a_col(slot) + c0 / 2, pk, 0);
         }
-#endif
+        }
     }
     static __device__ __forceinline__ void epilogue(const Ctx& c, int slot, int act) {
         if constexpr (RELU) epilogue_t<D_ACT_RELU>(c, slot);
@@ -453,24 +462,29 @@ struct SrnTc {
 #pragma unroll
         for (int c0 = 0; c0 < H; c0 += 32) {
             __half2 a0 = __float2half2_rn(0.f), a1 = a0;
-#if FVSRN_TC_ACC16
-            uint32_t v[16];
-            if (H - c0 >= 32) tc::tmem_ld16_pack(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld8_pack(c.tmem_lane + d_col(slot) + c0, v);
-#else
-            uint32_t v[32];
-            if (H - c0 >= 32) tc::tmem_ld32(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld16(c.tmem_lane + d_col(slot) + c0, v);
-#endif
-            tc::wait_ld();
+            if constexpr (ACC16) {
+                uint32_t v[16];
+                if (H - c0 >= 32) tc::tmem_ld16_pack(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld8_pack(c.tmem_lane + d_col(slot) + c0, v);
+                tc::wait_ld();
 #pragma unroll
-            for (int j = 0; j < 16; j += 2) {
-                if (H - c0 >= 32 || j < 8) {
-#if FVSRN_TC_ACC16
-                    const uint32_t p0 = tc::act_h2<ACT>(c.af, v[j]), p1 = tc::act_h2<ACT>(c.af, v[j + 1]);
-#else
-                    const uint32_t p0 = tc::act_pack<ACT>(c.af, v[2 * j], v[2 * j + 1]), p1 = tc::act_pack<ACT>(c.af, v[2 * j + 2], v[2 * j + 3]);
-#endif
-                    a0 = __hfma2(u2h(p0), u2h(P.wlast2[c0 / 2 + j]), a0);
-                    a1 = __hfma2(u2h(p1), u2h(P.wlast2[c0 / 2 + j + 1]), a1);
+                for (int j = 0; j < 16; j += 2) {
+                    if (H - c0 >= 32 || j < 8) {
+                        const uint32_t p0 = tc::act_h2<ACT>(c.af, v[j]), p1 = tc::act_h2<ACT>(c.af, v[j + 1]);
+                        a0 = __hfma2(u2h(p0), u2h(P.wlast2[c0 / 2 + j]), a0);
+                        a1 = __hfma2(u2h(p1), u2h(P.wlast2[c0 / 2 + j + 1]), a1);
+                    }
+                }
+            } else {
+                uint32_t v[32];
+                if (H - c0 >= 32) tc::tmem_ld32(c.tmem_lane + d_col(slot) + c0, v); else tc::tmem_ld16(c.tmem_lane + d_col(slot) + c0, v);
+                tc::wait_ld();
+#pragma unroll
+                for (int j = 0; j < 16; j += 2) {
+                    if (H - c0 >= 32 || j < 8) {
+                        const uint32_t p0 = tc::act_pack<ACT>(c.af, v[2 * j], v[2 * j + 1]), p1 = tc::act_pack<ACT>(c.af, v[2 * j + 2], v[2 * j + 3]);
+                        a0 = __hfma2(u2h(p0), u2h(P.wlast2[c0 / 2 + j]), a0);
+                        a1 = __hfma2(u2h(p1), u2h(P.wlast2[c0 / 2 + j + 1]), a1);
+                    }
                 }
             }
             const float2 f0 = __half22float2(a0), f1 = __half22float2(a1);
@@ -522,21 +536,18 @@ struct SrnTc {
                 uint32_t o[4];
                 tc::tmem_ld4(c.tmem_lane + d_col(slot), o);
                 tc::wait_ld();
-#if FVSRN_TC_ACC16
+                if constexpr (ACC16) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) out[k] = __half2float(__ushort_as_half((unsigned short)(o[k] & 0xffffu)));
-#else
-                out[0] = __uint_as_float(o[0]); out[1] = __uint_as_float(o[1]); out[2] = __uint_as_float(o[2]); out[3] = __uint_as_float(o[3]);
-#endif
+                    for (int k = 0; k < 4; ++k) out[k] = __half2float(__ushort_as_half((unsigned short)(o[k] & 0xffffu)));
+                } else {
+                    out[0] = __uint_as_float(o[0]); out[1] = __uint_as_float(o[1]); out[2] = __uint_as_float(o[2]); out[3] = __uint_as_float(o[3]);
+                }
             } else {
                 uint32_t o;
                 tc::tmem_ld1(c.tmem_lane + d_col(slot), o);
                 tc::wait_ld();
-#if FVSRN_TC_ACC16
-                out[0] = __half2float(__ushort_as_half((unsigned short)(o & 0xffffu))); out[1] = out[2] = out[3] = 0.f;
-#else
-                out[0] = __uint_as_float(o); out[1] = out[2] = out[3] = 0.f;
-#endif
+                if constexpr (ACC16) { out[0] = __half2float(__ushort_as_half((unsigned short)(o & 0xffffu))); out[1] = out[2] = out[3] = 0.f; }
+                else { out[0] = __uint_as_float(o); out[1] = out[2] = out[3] = 0.f; }
             }
         }
         c.phase ^= 1u;

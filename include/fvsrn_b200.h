@@ -145,7 +145,7 @@ typedef struct fvsrn_network_info {
 int  fvsrn_network_get_info(const fvsrn_network* net, fvsrn_network_info* info);
 
 /* Which sm_100a kernel family evaluates the SRN (no reference analogue; the reference picks wmma by NVRTC defines):
- *   FVSRN_KERNEL_TCGEN05  (default) tcgen05.mma with TMEM accumulators (fp32 accumulate), 128 rays per CTA in lock-step
+ *   FVSRN_KERNEL_TCGEN05  (default) tcgen05.mma with TMEM accumulators (fp16 for ReLU networks, fp32 otherwise), 128 rays per CTA in lock-step
  *   FVSRN_KERNEL_MMA_SYNC reference-precision mode: mma.sync m16n8k16 with fp16 accumulation in the reference's
  *                         K order (renderer_volume_tensorcores.cuh:856-910), 32 rays per warp
  *   FVSRN_KERNEL_REFERENCE_EXACT  validation mode (DVR frame only): every fp16 and fp32 operation of the reference's

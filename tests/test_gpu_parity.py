@@ -32,7 +32,7 @@ def env(request):
     _lib.lib()
     pr.DEFAULT_KERNEL_MODE = request.param
     # the tcgen05 kernels fetch the latent grid through the texture units like the reference does (8-bit fractional
-    # filter weights) and accumulate in fp32 (TMEM); the mma.sync kernels blend the 8 corners with exact fp32-computed
+    # filter weights) and accumulate in TMEM (fp32; fp16 in the ReLU instantiations since r02 - the fp32 model stays the comparand); the mma.sync kernels blend the 8 corners with exact fp32-computed
     # weights and accumulate in fp16 like the reference's wmma path. The oracle restates either arithmetic.
     import functools, types
     tex = request.param == "tcgen05"
